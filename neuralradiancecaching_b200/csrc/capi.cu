@@ -1,0 +1,403 @@
+// capi.cu -- extern "C" entry points of include/nrc_b200.h (context, parameter stores, stand-alone operators,
+// scene objects).  The renderer's entry points live in renderer.cu.
+#include <stdarg.h>
+#include <string.h>
+#include <math.h>
+#include "nrc_internal.cuh"
+
+// ---- errors -------------------------------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+
+void nrc_set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* nrc_last_error(void) { return g_err; }
+extern "C" const char* nrc_version(void) { return "nrc_b200 0.1 (sm_100a)"; }
+
+// ---- staging helpers ----------------------------------------------------------------------------------------
+bool nrc_is_device_ptr(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+nrc_status nrc_scratch(nrc_ctx* ctx, int slot, size_t bytes, void** out)
+{
+    if (ctx->scratchBytes[slot] < bytes) {
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->scratch[slot]) NRC_CUDA(cudaFree(ctx->scratch[slot]));
+        ctx->scratch[slot] = nullptr;
+        ctx->scratchBytes[slot] = 0;
+        size_t cap = bytes + bytes / 4 + 256;
+        NRC_CUDA(cudaMalloc(&ctx->scratch[slot], cap));
+        ctx->scratchBytes[slot] = cap;
+    }
+    *out = ctx->scratch[slot];
+    return NRC_OK;
+}
+
+nrc_status nrc_stage_in(nrc_ctx* ctx, int slot, const void* p, size_t bytes, const void** dev)
+{
+    if (bytes == 0 || nrc_is_device_ptr(p)) {
+        *dev = p;
+        return NRC_OK;
+    }
+    void* d;
+    NRC_TRY(nrc_scratch(ctx, slot, bytes, &d));
+    // pageable or pinned host memory: cudaMemcpyAsync is stream-ordered and truly asynchronous for pinned sources
+    NRC_CUDA(cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    *dev = d;
+    return NRC_OK;
+}
+
+nrc_status nrc_stage_out(nrc_ctx* ctx, int slot, void* dst, size_t bytes, void** dev)
+{
+    if (bytes == 0 || nrc_is_device_ptr(dst)) {
+        *dev = dst;
+        return NRC_OK;
+    }
+    return nrc_scratch(ctx, slot, bytes, dev);
+}
+
+nrc_status nrc_stage_out_finish(nrc_ctx* ctx, void* dst, const void* dev, size_t bytes)
+{
+    if (bytes == 0 || dst == dev) return NRC_OK;
+    NRC_CUDA(cudaMemcpyAsync(dst, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NRC_OK;
+}
+
+static nrc_status copy_in(nrc_ctx* ctx, void* devDst, const void* src, size_t bytes)
+{
+    cudaMemcpyKind k = nrc_is_device_ptr(src) ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    NRC_CUDA(cudaMemcpyAsync(devDst, src, bytes, k, ctx->stream));
+    if (k == cudaMemcpyHostToDevice) NRC_CUDA(cudaStreamSynchronize(ctx->stream));   // caller may free src on return
+    return NRC_OK;
+}
+
+static nrc_status copy_out(nrc_ctx* ctx, void* dst, const void* devSrc, size_t bytes)
+{
+    cudaMemcpyKind k = nrc_is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    NRC_CUDA(cudaMemcpyAsync(dst, devSrc, bytes, k, ctx->stream));
+    if (k == cudaMemcpyDeviceToHost) NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NRC_OK;
+}
+
+// ---- context -------------------------------------------------------------------------------------------------
+extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
+{
+    if (!out) return NRC_ERR_INVALID;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        nrc_set_error("no CUDA device: this library has no CPU fallback");
+        return NRC_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= count) {
+        nrc_set_error("device %d out of range (have %d)", device, count);
+        return NRC_ERR_INVALID;
+    }
+    cudaDeviceProp prop;
+    NRC_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        nrc_set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+        return NRC_ERR_NO_DEVICE;
+    }
+    NRC_CUDA(cudaSetDevice(device));
+    nrc_ctx* c = new nrc_ctx();
+    c->device = device;
+    c->smCount = prop.multiProcessorCount;
+    NRC_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    NRC_CUDA(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
+    *out = c;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
+{
+    if (!c) return NRC_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaStreamSynchronize(c->stream2);
+    for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
+    if (c->pinned) cudaFreeHost(c->pinned);
+    cudaEventDestroy(c->evFork);
+    cudaEventDestroy(c->evJoin);
+    cudaStreamDestroy(c->stream);
+    cudaStreamDestroy(c->stream2);
+    delete c;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_sync(nrc_ctx* c)
+{
+    NRC_REQUIRE(c, "null context");
+    NRC_CUDA(cudaStreamSynchronize(c->stream));
+    return NRC_OK;
+}
+
+extern "C" void* nrc_ctx_stream(nrc_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int nrc_ctx_sm_count(nrc_ctx* c) { return c ? c->smCount : 0; }
+extern "C" uint64_t nrc_ctx_launch_count(nrc_ctx* c) { return c ? c->launches : 0; }
+
+extern "C" nrc_status nrc_ctx_set_precision(nrc_ctx* c, nrc_mlp_precision p)
+{
+    NRC_REQUIRE(c, "null context");
+    NRC_REQUIRE(p == NRC_MLP_FP32 || p == NRC_MLP_BF16_TC, "unknown precision");
+    c->precision = p;
+    return NRC_OK;
+}
+
+// ---- MLP parameter store --------------------------------------------------------------------------------------
+extern "C" nrc_status nrc_mlp_create(nrc_ctx* ctx, float lr, float wd, float beta1, uint64_t seed, nrc_mlp** out)
+{
+    NRC_REQUIRE(ctx && out, "null argument");
+    NRC_CUDA(cudaSetDevice(ctx->device));
+    nrc_mlp* m = new nrc_mlp();
+    m->ctx = ctx; m->lr = lr; m->wd = wd; m->beta1 = beta1;
+    const size_t padded = 21504 * sizeof(float);
+    NRC_CUDA(cudaMalloc(&m->params, padded));
+    NRC_CUDA(cudaMalloc(&m->grad, padded));
+    NRC_CUDA(cudaMalloc(&m->momentum, padded));
+    NRC_CUDA(cudaMalloc(&m->paramsT, padded));
+    NRC_CUDA(cudaMemsetAsync(m->params, 0, padded, ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(m->grad, 0, padded, ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(m->momentum, 0, padded, ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(m->paramsT, 0, padded, ctx->stream));
+    if (seed != 0) NRC_TRY(launch_init_normal(ctx, m->params, NRC_MLP_WEIGHT_COUNT, 0.01f, seed));   // NeuralRadianceCache.cpp:640-646
+    m->dirtyT = true;
+    *out = m;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_destroy(nrc_mlp* m)
+{
+    if (!m) return NRC_OK;
+    cudaStreamSynchronize(m->ctx->stream);
+    cudaFree(m->params); cudaFree(m->grad); cudaFree(m->momentum); cudaFree(m->paramsT);
+    if (m->partial) cudaFree(m->partial);
+    if (m->paramsBf16) cudaFree(m->paramsBf16);
+    delete m;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_set_config(nrc_mlp* m, float lr, float wd, float beta1)
+{
+    NRC_REQUIRE(m, "null mlp");
+    m->lr = lr; m->wd = wd; m->beta1 = beta1;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_set_params(nrc_mlp* m, const float* params)
+{
+    NRC_REQUIRE(m && params, "null argument");
+    NRC_TRY(copy_in(m->ctx, m->params, params, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    m->dirtyT = true;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_set_state(nrc_mlp* m, const float* delta, const float* momentum)
+{
+    NRC_REQUIRE(m, "null mlp");
+    if (delta) NRC_TRY(copy_in(m->ctx, m->grad, delta, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    if (momentum) NRC_TRY(copy_in(m->ctx, m->momentum, momentum, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_get_params(nrc_mlp* m, float* params, float* delta, float* momentum)
+{
+    NRC_REQUIRE(m, "null mlp");
+    if (params) NRC_TRY(copy_out(m->ctx, params, m->params, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    if (delta) NRC_TRY(copy_out(m->ctx, delta, m->grad, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    if (momentum) NRC_TRY(copy_out(m->ctx, momentum, m->momentum, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_reset_stats(nrc_mlp* m)
+{
+    NRC_REQUIRE(m, "null mlp");
+    NRC_CUDA(cudaMemsetAsync(m->grad + NRC_MLP_PARAM_COUNT, 0, sizeof(float), m->ctx->stream));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_get_stats(nrc_mlp* m, float* mseLoss)
+{
+    NRC_REQUIRE(m && mseLoss, "null argument");
+    NRC_CUDA(cudaMemcpyAsync(mseLoss, m->grad + NRC_MLP_PARAM_COUNT, sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return NRC_OK;
+}
+
+extern "C" float* nrc_mlp_grad_ptr(nrc_mlp* m) { return m ? m->grad : nullptr; }
+extern "C" size_t nrc_mlp_grad_count(nrc_mlp* m) { return m ? (size_t)NRC_MLP_PARAM_COUNT + 1 : 0; }
+
+// ---- MRHE -----------------------------------------------------------------------------------------------------
+extern "C" nrc_status nrc_mrhe_resolutions(uint32_t minRes, uint32_t maxRes, uint32_t levelCount, nrc_resolution_mode mode, uint32_t out[16])
+{
+    NRC_REQUIRE(out && levelCount >= 2 && levelCount <= 16 && minRes > 0 && maxRes >= minRes, "bad resolution arguments");
+    // src/MRHE.cpp:111-121, float32 arithmetic with the C library's expf/logf/powf like the reference
+    uint32_t tight[16];
+    float b = expf((logf((float)maxRes) - logf((float)minRes)) / (float)(levelCount - 1));
+    for (uint32_t i = 0; i < 16; i++) tight[i] = 0;
+    for (uint32_t i = 0; i < levelCount; i++) tight[i] = (uint32_t)((float)minRes * powf(b, (float)i));
+    if (mode == NRC_RES_INTENDED) {
+        for (int i = 0; i < 16; i++) out[i] = tight[i];
+    } else if (mode == NRC_RES_AS_SHIPPED_STD140) {
+        // the shader's std140 block has resolutions at byte 32, stride 16; the host packs them at byte 28, stride 4
+        // => shader res[i] = host word (32 + 16*i - 28)/4 = 1 + 4*i, and reads past the 92-byte block give 0 here
+        for (int i = 0; i < 16; i++) { int j = 1 + 4 * i; out[i] = (j < 16) ? tight[j] : 0u; }
+    } else {
+        NRC_REQUIRE(false, "unknown resolution mode");
+    }
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_create(nrc_ctx* ctx, float lr, float wd, uint32_t L, uint32_t T, uint32_t F, uint32_t minRes, uint32_t maxRes,
+                                      const uint32_t* resolutions, uint64_t seed, nrc_mrhe** out)
+{
+    NRC_REQUIRE(ctx && out, "null argument");
+    NRC_REQUIRE(L >= 1 && L <= 16, "levelCount must be 1..16");
+    NRC_REQUIRE(F == 2, "featureCount must be 2 (the reference's only configuration)");
+    NRC_REQUIRE(T >= 2 && (((size_t)L * T * F) % 4) == 0, "hashTableSize must make L*T*F a multiple of 4");
+    NRC_CUDA(cudaSetDevice(ctx->device));
+    nrc_mrhe* m = new nrc_mrhe();
+    m->ctx = ctx; m->lr = lr; m->wd = wd; m->L = L; m->T = T; m->F = F; m->minRes = minRes; m->maxRes = maxRes;
+    if (resolutions) {
+        for (int i = 0; i < 16; i++) m->res[i] = resolutions[i];
+    } else {
+        NRC_TRY(nrc_mrhe_resolutions(minRes, maxRes, L < 2 ? 2 : L, NRC_RES_INTENDED, m->res));
+    }
+    m->count = (size_t)L * T * F;
+    NRC_CUDA(cudaMalloc(&m->tables, m->count * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&m->delta, m->count * sizeof(float)));
+    NRC_CUDA(cudaMemsetAsync(m->tables, 0, m->count * sizeof(float), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(m->delta, 0, m->count * sizeof(float), ctx->stream));   // zero deltas
+    if (seed != 0) NRC_TRY(launch_init_normal(ctx, m->tables, m->count, 0.1f, seed));   // MRHE.cpp:132-135
+    *out = m;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_destroy(nrc_mrhe* m)
+{
+    if (!m) return NRC_OK;
+    cudaStreamSynchronize(m->ctx->stream);
+    cudaFree(m->tables); cudaFree(m->delta);
+    delete m;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_set_config(nrc_mrhe* m, float lr, float wd)
+{
+    NRC_REQUIRE(m, "null mrhe");
+    m->lr = lr; m->wd = wd;
+    return NRC_OK;
+}
+
+extern "C" size_t nrc_mrhe_table_bytes(nrc_mrhe* m) { return m ? m->count * sizeof(float) : 0; }
+
+extern "C" nrc_status nrc_mrhe_set_tables(nrc_mrhe* m, const float* tables, const float* delta)
+{
+    NRC_REQUIRE(m, "null mrhe");
+    if (tables) NRC_TRY(copy_in(m->ctx, m->tables, tables, m->count * sizeof(float)));
+    if (delta) NRC_TRY(copy_in(m->ctx, m->delta, delta, m->count * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_get_tables(nrc_mrhe* m, float* tables, float* delta)
+{
+    NRC_REQUIRE(m, "null mrhe");
+    if (tables) NRC_TRY(copy_out(m->ctx, tables, m->tables, m->count * sizeof(float)));
+    if (delta) NRC_TRY(copy_out(m->ctx, delta, m->delta, m->count * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" float* nrc_mrhe_grad_ptr(nrc_mrhe* m) { return m ? m->delta : nullptr; }
+extern "C" size_t nrc_mrhe_grad_extent(nrc_mrhe* m)
+{
+    if (!m) return 0;
+    size_t e = (size_t)2 * m->T;
+    return e < m->count ? e : m->count;
+}
+
+// ---- stand-alone operators ------------------------------------------------------------------------------------
+extern "C" nrc_status nrc_encode(nrc_mrhe* m, const float* pos, size_t n, float* feat, uint32_t* idx)
+{
+    NRC_REQUIRE(m && pos, "null argument");
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = m->ctx;
+    const void* dpos; void* dfeat = nullptr; void* didx = nullptr;
+    NRC_TRY(nrc_stage_in(ctx, 0, pos, n * 3 * sizeof(float), &dpos));
+    if (feat) NRC_TRY(nrc_stage_out(ctx, 3, feat, n * 32 * sizeof(float), &dfeat));
+    if (idx) NRC_TRY(nrc_stage_out(ctx, 4, idx, n * 128 * sizeof(uint32_t), &didx));
+    NRC_TRY(launch_encode_pos(m, (const float*)dpos, n, (float*)dfeat, (uint32_t*)didx));
+    if (feat) NRC_TRY(nrc_stage_out_finish(ctx, feat, dfeat, n * 32 * sizeof(float)));
+    if (idx) NRC_TRY(nrc_stage_out_finish(ctx, idx, didx, n * 128 * sizeof(uint32_t)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_encode_dir(nrc_ctx* ctx, const float* dir, size_t n, float* feat)
+{
+    NRC_REQUIRE(ctx && dir && feat, "null argument");
+    if (n == 0) return NRC_OK;
+    const void* ddir; void* dfeat;
+    NRC_TRY(nrc_stage_in(ctx, 0, dir, n * 3 * sizeof(float), &ddir));
+    NRC_TRY(nrc_stage_out(ctx, 3, feat, n * 32 * sizeof(float), &dfeat));
+    NRC_TRY(launch_encode_dir(ctx, (const float*)ddir, n, (float*)dfeat));
+    NRC_TRY(nrc_stage_out_finish(ctx, feat, dfeat, n * 32 * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_infer(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, size_t n, float* rgb)
+{
+    NRC_REQUIRE(mlp && m && pos && dir && rgb, "null argument");
+    NRC_REQUIRE(mlp->ctx == m->ctx, "mlp and mrhe belong to different contexts");
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = mlp->ctx;
+    const void *dpos, *ddir; void* drgb;
+    NRC_TRY(nrc_stage_in(ctx, 0, pos, n * 3 * sizeof(float), &dpos));
+    NRC_TRY(nrc_stage_in(ctx, 1, dir, n * 3 * sizeof(float), &ddir));
+    NRC_TRY(nrc_stage_out(ctx, 3, rgb, n * 3 * sizeof(float), &drgb));
+    if (ctx->precision == NRC_MLP_BF16_TC)
+        NRC_TRY(launch_infer_tc(mlp, m, (const float*)dpos, (const float*)ddir, nullptr, n, (float*)drgb, ctx->stream));
+    else
+        NRC_TRY(launch_infer_fp32(mlp, m, (const float*)dpos, (const float*)ddir, nullptr, n, (float*)drgb, ctx->stream));
+    NRC_TRY(nrc_stage_out_finish(ctx, rgb, drgb, n * 3 * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_train_accumulate(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n,
+                                           float lossScale, float* pred)
+{
+    NRC_REQUIRE(mlp && m && pos && dir && target, "null argument");
+    NRC_REQUIRE(mlp->ctx == m->ctx, "mlp and mrhe belong to different contexts");
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = mlp->ctx;
+    const void *dpos, *ddir, *dtgt; void* dpred = nullptr;
+    NRC_TRY(nrc_stage_in(ctx, 0, pos, n * 3 * sizeof(float), &dpos));
+    NRC_TRY(nrc_stage_in(ctx, 1, dir, n * 3 * sizeof(float), &ddir));
+    NRC_TRY(nrc_stage_in(ctx, 2, target, n * 3 * sizeof(float), &dtgt));
+    if (pred) NRC_TRY(nrc_stage_out(ctx, 3, pred, n * 3 * sizeof(float), &dpred));
+    NRC_TRY(launch_train_fp32(mlp, m, (const float*)dpos, (const float*)ddir, (const float*)dtgt, n, lossScale, (float*)dpred, ctx->stream));
+    if (pred) NRC_TRY(nrc_stage_out_finish(ctx, pred, dpred, n * 3 * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_optimizer_step(nrc_mlp* mlp, nrc_mrhe* m)
+{
+    NRC_REQUIRE(mlp || m, "nothing to step");
+    if (mlp) NRC_TRY(launch_nrc_step(mlp, mlp->ctx->stream));
+    if (m) NRC_TRY(launch_mrhe_step(m, m->ctx->stream));
+    return NRC_OK;
+}

@@ -1,0 +1,496 @@
+// mlp_fp32.cu -- fused MRHE/OneBlob encode + 64-wide MLP, fp32 on the CUDA cores.
+//
+// This is the 1e-3 parity path of SURVEY.md 8a rows a11 (Forward, nrc-forward.frag:503-534), a12 (Backprop,
+// nrc-train.comp:743-945, 985-1028) and a13 (BackpropMrhe, :947-983).  The reference runs one thread per
+// sample with 7 x 64 private floats and one global float atomic per weight per sample; here a CTA owns a
+// tile of 64 samples and every layer is a 64x64x64 shared-memory GEMM:
+//
+//   C[m][n] = sum_k P[k][m] * Q[k][n]      (both operands "k-major": the reduction index is the slow one)
+//
+//   forward   : act_{l+1}[r][c] = sum_k  Xt[k][r]   * Wt_l[k][c]     (k = input feature)
+//   back-data : err_l[r][c]     = sum_k  Et[k][r]   * W_{l+1}[k][c]  (k = output feature of layer l+1)
+//   back-wgt  : dW_l[o][i]      = sum_r  Es[r][o]   * As_l[r][i]     (k = sample)
+//
+// so activations/errors are kept feature-major (Xt, Et) for the first two and sample-major (As, Es) for the
+// third.  256 threads, 4x4 register tile each, k sequential 0..63 with one fmaf per term: the same summation
+// order as the reference's "sum += in * w" loop.  Weight gradients are reduced in-CTA over the 64 samples,
+// accumulated into a per-CTA partial arena in L2, and summed over CTAs in fixed order by k_reduce_partials:
+// deterministic, and no float atomics on the 20 995 MLP parameters at all.  The hash-table gradient keeps
+// the reference's scatter (one red.global.add.v2.f32 per corner).
+#include "nrc_internal.cuh"
+#include "strict.cuh"
+
+#define TILE 64          // samples per CTA tile
+#define NTHREADS 256
+
+struct MlpDev {
+    const float* params;    // packed arena (W row-major [out][in], biases)
+    const float* paramsT;   // Wt[l][in][out], l = 0..4
+};
+
+// ---- shared device pieces -----------------------------------------------------------------------------
+
+__device__ __forceinline__ void copy16k(float* dst, const float* __restrict__ src)
+{
+    const float4* s = reinterpret_cast<const float4*>(src);
+    float4* d = reinterpret_cast<float4*>(dst);
+#pragma unroll
+    for (int i = 0; i < 4; i++) d[threadIdx.x + i * NTHREADS] = __ldg(s + threadIdx.x + i * NTHREADS);
+}
+
+// acc[i][j] += sum_k P[k*64 + 4*tm + i] * Q[k*64 + 4*tn + j]
+__device__ __forceinline__ void gemm64(const float* __restrict__ P, const float* __restrict__ Q, int tm, int tn, float acc[4][4])
+{
+#pragma unroll 8
+    for (int k = 0; k < 64; k++) {
+        float4 p = *reinterpret_cast<const float4*>(P + k * 64 + 4 * tm);
+        float4 q = *reinterpret_cast<const float4*>(Q + k * 64 + 4 * tn);
+        float pv[4] = {p.x, p.y, p.z, p.w};
+        float qv[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[i][j] = fmaf(pv[i], qv[j], acc[i][j]);
+    }
+}
+
+// Encode TILE queries into Xt (feature-major [64][TILE]) and optionally As (sample-major [TILE][64]).
+// Thread t: sample r = t % 64, quarter h = t / 64 -> MRHE levels 4h..4h+3 and 8 of the 32 OneBlob features.
+// Returns (for h == 0 threads) whether the sample trips the reference's NaN guard on nr0[0..4].
+__device__ __forceinline__ void encode_tile(const float* __restrict__ pos, const float* __restrict__ dir, size_t base, size_t n,
+                                            const MrheDev& m, float* Xt, float* As)
+{
+    int r = threadIdx.x & 63, h = threadIdx.x >> 6;
+    size_t q = base + r;
+    f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
+    if (q < n) {
+        p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
+        d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
+    }
+    f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
+    f3 np = mrhe_norm_pos(p, sky);
+#pragma unroll
+    for (int li = 0; li < 4; li++) {
+        uint32_t level = 4 * h + li;
+        float o0 = 0.0f, o1 = 0.0f;
+        if (level < m.L) {
+            uint32_t idx[8];
+            f3 lerp;
+            mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp);
+            const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
+            float f0[8], f1[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                float2 v = __ldg(tab + idx[c]);
+                f0[c] = v.x;
+                f1[c] = v.y;
+            }
+            o0 = mrhe_blend(f0, lerp);
+            o1 = mrhe_blend(f1, lerp);
+        }
+        Xt[(2 * level) * TILE + r] = o0;
+        Xt[(2 * level + 1) * TILE + r] = o1;
+        if (As) { As[r * 64 + 2 * level] = o0; As[r * 64 + 2 * level + 1] = o1; }
+    }
+    // OneBlob: quarter h owns bins 8*(h&1)..+7 of theta (h < 2) or phi (h >= 2)
+    {
+        float ang;
+        if (h < 2) {
+            ang = NRC_ADD(NRC_DIV(nrc_atan2(d.z, d.x), NRC_PI), 0.5f);
+        } else {
+            float lenxz = NRC_SQRT(NRC_ADD(NRC_MUL(d.x, d.x), NRC_MUL(d.z, d.z)));
+            ang = NRC_ADD(NRC_DIV(nrc_atan2(lenxz, d.y), NRC_PI), 0.5f);
+        }
+        const float sigma = 0.25f;
+        float term1 = NRC_DIV(1.0f, NRC_MUL(sigma, NRC_SQRT(NRC_MUL(2.0f, NRC_PI))));
+        int f0 = 32 + ((h >= 2) ? 16 : 0) + 8 * (h & 1);
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            float fi = (float)(8 * (h & 1) + i);
+            float t2 = NRC_DIV(NRC_SUB(fi, ang), sigma);
+            float v = NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2)));
+            Xt[(f0 + i) * TILE + r] = v;
+            if (As) As[r * 64 + f0 + i] = v;
+        }
+    }
+}
+
+// One hidden layer: Xout = relu(Xin * Wt + b), feature-major in and out; optional sample-major copy.
+__device__ __forceinline__ void hidden_layer(const float* Xin, const float* Wt, const float* __restrict__ bias, float* Xout, float* AsOut)
+{
+    int tm = threadIdx.x & 15, tn = threadIdx.x >> 4;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.0f;
+    gemm64(Xin, Wt, tm, tn, acc);
+    float b[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) b[j] = __ldg(bias + 4 * tn + j);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        float4 col;
+        col.x = fmaxf(acc[0][j] + b[j], 0.0f);
+        col.y = fmaxf(acc[1][j] + b[j], 0.0f);
+        col.z = fmaxf(acc[2][j] + b[j], 0.0f);
+        col.w = fmaxf(acc[3][j] + b[j], 0.0f);
+        *reinterpret_cast<float4*>(Xout + (4 * tn + j) * TILE + 4 * tm) = col;
+        acc[0][j] = col.x; acc[1][j] = col.y; acc[2][j] = col.z; acc[3][j] = col.w;
+    }
+    if (AsOut) {
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            *reinterpret_cast<float4*>(AsOut + (4 * tm + i) * 64 + 4 * tn) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    }
+}
+
+// ---- inference -------------------------------------------------------------------------------------------
+// smem: W (16 KB) + X0, X1 (16 KB each) = 48 KB -> 4 CTAs/SM.
+__global__ void __launch_bounds__(NTHREADS, 4) k_infer_fp32(const float* __restrict__ pos, const float* __restrict__ dir,
+                                                            const uint32_t* __restrict__ countDev, size_t nMax, MlpDev w, MrheDev m,
+                                                            float* __restrict__ rgb)
+{
+    extern __shared__ __align__(16) float smem[];
+    float* W = smem;
+    float* X0 = smem + 4096;
+    float* X1 = smem + 8192;
+    size_t n = nMax;
+    if (countDev) { size_t c = *countDev; n = c < nMax ? c : nMax; }
+    size_t tiles = (n + TILE - 1) / TILE;
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        size_t base = tile * TILE;
+        encode_tile(pos, dir, base, n, m, X0, nullptr);
+        float* xin = X0;
+        float* xout = X1;
+#pragma unroll 1
+        for (int l = 0; l < 5; l++) {
+            copy16k(W, w.paramsT + l * 4096);
+            __syncthreads();
+            hidden_layer(xin, W, w.params + NRC_B_OFF(l), xout, nullptr);
+            __syncthreads();
+            float* t = xin; xin = xout; xout = t;
+        }
+        // output layer 64 -> 3 (+ ReLU twice, nrc-forward.frag:525-531): thread t < 192: row r = t%64, out j = t/64
+        if (threadIdx.x < 192) {
+            int r = threadIdx.x & 63, j = threadIdx.x >> 6;
+            const float* w5 = w.params + NRC_W_OFF(5) + j * 64;
+            float sum = 0.0f;
+#pragma unroll 8
+            for (int k = 0; k < 64; k++) sum = fmaf(xin[k * TILE + r], __ldg(w5 + k), sum);
+            sum = fmaxf(sum + __ldg(w.params + NRC_B_OFF(5) + j), 0.0f);
+            if (base + r < n) rgb[3 * (base + r) + j] = sum;
+        }
+        __syncthreads();
+    }
+}
+
+// ---- training --------------------------------------------------------------------------------------------
+// smem (floats): As[6][64][64] | XE0, XE1 (feature-major) | ES0, ES1 (sample-major) | W | small  = ~178 KB, 1 CTA/SM.
+#define TRAIN_SMEM_FLOATS (6 * 4096 + 2 * 4096 + 2 * 4096 + 4096 + 1024)
+
+__device__ __forceinline__ void zero_acc(float acc[4][4])
+{
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.0f;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) k_train_fp32(const float* __restrict__ pos, const float* __restrict__ dir,
+                                                            const float* __restrict__ target, const uint32_t* __restrict__ countDev,
+                                                            size_t nMax, float scale, MlpDev w, MrheDev m, float* __restrict__ partialAll,
+                                                            float* __restrict__ predOut)
+{
+    extern __shared__ __align__(16) float smem[];
+    float* As = smem;                     // [6][64][64]
+    float* XE0 = smem + 6 * 4096;
+    float* XE1 = XE0 + 4096;
+    float* ES0 = XE1 + 4096;
+    float* ES1 = ES0 + 4096;
+    float* W = ES1 + 4096;
+    float* predS = W + 4096;              // [64][4]
+    float* e6S = predS + 256;             // [64][4]
+    float* lossS = e6S + 256;             // [8]
+    int* dropS = reinterpret_cast<int*>(lossS + 8);   // [64]
+
+    const int tid = threadIdx.x;
+    const int tm = tid & 15, tn = tid >> 4;
+    float* partial = partialAll + (size_t)blockIdx.x * NRC_PARTIAL_STRIDE;
+    for (int i = tid; i < NRC_PARTIAL_STRIDE; i += NTHREADS) partial[i] = 0.0f;
+    __syncthreads();
+
+    size_t n = nMax;
+    if (countDev) { size_t c = *countDev; n = c < nMax ? c : nMax; }
+    size_t tiles = (n + TILE - 1) / TILE;
+    float lossAcc = 0.0f;   // thread 0 only
+
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const size_t base = tile * TILE;
+        // ---- encode (EncodeRay, nrc-train.comp:703-713) ----
+        encode_tile(pos, dir, base, n, m, XE0, As);
+        __syncthreads();
+        // NaN guard on nr0[0..4] (nrc-train.comp:993-999); rows past n are dropped too
+        if (tid < 64) {
+            const float* a0 = As + tid * 64;
+            int bad = (base + tid >= n);
+            for (int i = 0; i < 5; i++) bad |= (a0[i] != a0[i]);
+            dropS[tid] = bad;
+        }
+        __syncthreads();
+        {
+            int r = tid & 63, h = tid >> 6;
+            if (dropS[r]) {
+                for (int f = 16 * h; f < 16 * h + 16; f++) { XE0[f * TILE + r] = 0.0f; As[r * 64 + f] = 0.0f; }
+            }
+        }
+        __syncthreads();
+        // ---- forward (nrc-train.comp:715-741) ----
+        float* xin = XE0;
+        float* xout = XE1;
+#pragma unroll 1
+        for (int l = 0; l < 5; l++) {
+            copy16k(W, w.paramsT + l * 4096);
+            __syncthreads();
+            hidden_layer(xin, W, w.params + NRC_B_OFF(l), xout, As + (l + 1) * 4096);
+            __syncthreads();
+            float* t = xin; xin = xout; xout = t;
+        }
+        // xin == XE1 holds A5 feature-major; XE0 is free.
+        if (tid < 192) {
+            int r = tid & 63, j = tid >> 6;
+            const float* w5 = w.params + NRC_W_OFF(5) + j * 64;
+            float sum = 0.0f;
+#pragma unroll 8
+            for (int k = 0; k < 64; k++) sum = fmaf(xin[k * TILE + r], __ldg(w5 + k), sum);
+            predS[r * 4 + j] = fmaxf(sum + __ldg(w.params + NRC_B_OFF(5) + j), 0.0f);
+        }
+        __syncthreads();
+        // ---- loss and output error (nrc-train.comp:1002-1012) with the layer-5 gate of Backprop5 (:746-749) ----
+        if (tid < 64) {
+            int r = tid;
+            float l = 0.0f;
+            float e[3] = {0.0f, 0.0f, 0.0f};
+            bool live = !dropS[r];
+            if (live) {
+                const float* a5 = As + 5 * 4096 + r * 64;
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                    float tg = fminf(__ldg(target + 3 * (base + r) + j), 1024.0f);
+                    float err = predS[r * 4 + j] - tg;
+                    l += err * err;
+                    e[j] = (a5[j] > 0.0f) ? 2.0f * err : 0.0f;
+                }
+                l = (l / 3.0f) * scale;
+            }
+            e6S[r * 4 + 0] = e[0]; e6S[r * 4 + 1] = e[1]; e6S[r * 4 + 2] = e[2]; e6S[r * 4 + 3] = 0.0f;
+            if (predOut && base + r < n) {
+#pragma unroll
+                for (int j = 0; j < 3; j++) predOut[3 * (base + r) + j] = live ? predS[r * 4 + j] : 0.0f;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+            if ((tid & 31) == 0) lossS[tid >> 5] = l;
+        }
+        __syncthreads();
+        if (tid == 0) lossAcc += lossS[0] + lossS[1];
+        // ---- layer 5: dW5, db5, and E5 = (W5^T e6) gated by A4 (Backprop5 :751-774 + Backprop4 gate :780-783) ----
+        if (tid < 192) {
+            int c = tid & 63, j = tid >> 6;
+            const float* a5 = As + 5 * 4096;
+            float s = 0.0f;
+#pragma unroll 8
+            for (int r = 0; r < 64; r++) s = fmaf(a5[r * 64 + c], e6S[r * 4 + j], s);
+            partial[NRC_W_OFF(5) + j * 64 + c] += -s * scale;
+        } else if (tid < 195) {
+            int j = tid - 192;
+            float s = 0.0f;
+            for (int r = 0; r < 64; r++) s += e6S[r * 4 + j];
+            partial[NRC_B_OFF(5) + j] += -s * scale;
+        }
+        {
+            const float* w5 = w.params + NRC_W_OFF(5);
+            const float* a4 = As + 4 * 4096;
+            float ev[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                int r = 4 * tm + i;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    int c = 4 * tn + j;
+                    float err = 0.0f;
+                    err = fmaf(__ldg(w5 + c), e6S[r * 4 + 0], err);
+                    err = fmaf(__ldg(w5 + 64 + c), e6S[r * 4 + 1], err);
+                    err = fmaf(__ldg(w5 + 128 + c), e6S[r * 4 + 2], err);
+                    ev[i][j] = (a4[r * 64 + c] > 0.0f) ? err : 0.0f;
+                }
+                *reinterpret_cast<float4*>(ES0 + r * 64 + 4 * tn) = make_float4(ev[i][0], ev[i][1], ev[i][2], ev[i][3]);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                *reinterpret_cast<float4*>(XE0 + (4 * tn + j) * TILE + 4 * tm) = make_float4(ev[0][j], ev[1][j], ev[2][j], ev[3][j]);
+        }
+        __syncthreads();
+        // ---- hidden layers 4..0 (Backprop4..Backprop0, nrc-train.comp:777-945) ----
+        float* et = XE0; float* es = ES0;
+        float* etn = XE1; float* esn = ES1;
+#pragma unroll 1
+        for (int l = 4; l >= 0; l--) {
+            copy16k(W, w.params + NRC_W_OFF(l));   // row-major [out][in]: k-major for the back-data GEMM
+            // weight gradient: dW_l[o][i] = -scale * sum_r E[r][o] * A_l[r][i]
+            float acc[4][4];
+            zero_acc(acc);
+            gemm64(es, As + l * 4096, tm, tn, acc);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                float4* dst = reinterpret_cast<float4*>(partial + NRC_W_OFF(l) + (4 * tm + i) * 64 + 4 * tn);
+                float4 v = *dst;
+                v.x += -acc[i][0] * scale; v.y += -acc[i][1] * scale; v.z += -acc[i][2] * scale; v.w += -acc[i][3] * scale;
+                *dst = v;
+            }
+            if (tid < 64) {
+                float s = 0.0f;
+#pragma unroll 8
+                for (int r = 0; r < 64; r++) s += es[r * 64 + tid];
+                partial[NRC_B_OFF(l) + tid] += -s * scale;
+            }
+            __syncthreads();   // W staged
+            // back-data: err[r][c] = sum_o E[r][o] * W_l[o][c]
+            zero_acc(acc);
+            gemm64(et, W, tm, tn, acc);
+            const float* gate = (l > 0) ? (As + (l - 1) * 4096) : nullptr;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                int r = 4 * tm + i;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    int c = 4 * tn + j;
+                    if (gate) acc[i][j] = (gate[r * 64 + c] > 0.0f) ? acc[i][j] : 0.0f;
+                }
+                *reinterpret_cast<float4*>(esn + r * 64 + 4 * tn) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+            }
+            if (gate) {
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    *reinterpret_cast<float4*>(etn + (4 * tn + j) * TILE + 4 * tm) = make_float4(acc[0][j], acc[1][j], acc[2][j], acc[3][j]);
+            }
+            __syncthreads();
+            float* t1 = et; et = etn; etn = t1;
+            float* t2 = es; es = esn; esn = t2;
+        }
+        // ---- hash-table gradient (BackpropMrhe, nrc-train.comp:947-983) ----
+        {
+            int r = tid & 63, h = tid >> 6;
+            size_t q = base + r;
+            if (!dropS[r]) {
+                f3 p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
+                f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
+                f3 np = mrhe_norm_pos(p, sky);
+                float2* dtab = reinterpret_cast<float2*>(m.delta);
+                for (int li = 0; li < 4; li++) {
+                    uint32_t level = 4 * h + li;
+                    if (level >= m.L) break;
+                    uint32_t idx[8];
+                    f3 lf;
+                    mrhe_level_indices(p, np, m.res[level], m.T, idx, lf);
+                    float g = es[r * 64 + 2 * level];   // feature 0's error for both features (A9)
+                    float ng = -g;
+#pragma unroll
+                    for (int c = 0; c < 8; c++) {
+                        float xf = (c & 4) ? lf.x : (1.0f - lf.x);
+                        float yf = (c & 2) ? lf.y : (1.0f - lf.y);
+                        float zf = (c & 1) ? lf.z : (1.0f - lf.z);
+                        float wgt = (xf * yf) * zf;
+                        float dlt = (ng * wgt) * scale;
+                        atomicAdd(dtab + idx[c], make_float2(dlt, dlt));   // no level offset (A10)
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) partial[20995] = lossAcc;
+}
+
+// grad[i] += sum over CTAs (fixed order) of partial[b][i]; i == 20995 is the mseLoss accumulator.
+__global__ void __launch_bounds__(256) k_reduce_partials(const float* __restrict__ partial, int nb, float* __restrict__ grad)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NRC_MLP_PARAM_COUNT + 1) return;
+    float s = 0.0f;
+    for (int b = 0; b < nb; b++) s += partial[(size_t)b * NRC_PARTIAL_STRIDE + i];
+    grad[i] += s;
+}
+
+// Wt[l][in][out] = W[l][out][in] for the five hidden layers.
+__global__ void __launch_bounds__(256) k_transpose_weights(const float* __restrict__ params, float* __restrict__ paramsT)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 5 * 4096) return;
+    int l = i >> 12, rem = i & 4095, k = rem >> 6, c = rem & 63;
+    paramsT[i] = params[l * 4096 + c * 64 + k];
+}
+
+// ---- host launchers -----------------------------------------------------------------------------------------
+
+nrc_status launch_mlp_prepare(nrc_mlp* mlp)
+{
+    if (!mlp->dirtyT) return NRC_OK;
+    k_transpose_weights<<<(5 * 4096 + 255) / 256, 256, 0, mlp->ctx->stream>>>(mlp->params, mlp->paramsT);
+    mlp->ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    mlp->dirtyT = false;
+    return NRC_OK;
+}
+
+nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, float* rgb,
+                             cudaStream_t st)
+{
+    if (n == 0) return NRC_OK;
+    NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
+    NRC_TRY(launch_mlp_prepare(mlp));
+    static bool attr = false;
+    size_t smem = 3 * 4096 * sizeof(float);
+    if (!attr) {
+        NRC_CUDA(cudaFuncSetAttribute(k_infer_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    size_t tiles = (n + TILE - 1) / TILE;
+    size_t cap = (size_t)mlp->ctx->smCount * 4 * 4;   // 4 CTAs/SM resident, a few waves, grid-stride beyond
+    unsigned blocks = (unsigned)(tiles < cap ? tiles : cap);
+    MlpDev w{mlp->params, mlp->paramsT};
+    k_infer_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, countDev, n, w, make_mrhe_dev(m), rgb);
+    mlp->ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    return NRC_OK;
+}
+
+nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
+                             float* pred, cudaStream_t st)
+{
+    if (n == 0) return NRC_OK;
+    NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
+    NRC_TRY(launch_mlp_prepare(mlp));
+    static bool attr = false;
+    size_t smem = TRAIN_SMEM_FLOATS * sizeof(float);
+    if (!attr) {
+        NRC_CUDA(cudaFuncSetAttribute(k_train_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    size_t tiles = (n + TILE - 1) / TILE;
+    int blocks = (int)(tiles < (size_t)mlp->ctx->smCount ? tiles : (size_t)mlp->ctx->smCount);
+    if (blocks > mlp->partialBlocks) {
+        if (mlp->partial) NRC_CUDA(cudaFree(mlp->partial));
+        mlp->partial = nullptr;
+        NRC_CUDA(cudaMalloc(&mlp->partial, (size_t)mlp->ctx->smCount * NRC_PARTIAL_STRIDE * sizeof(float)));
+        mlp->partialBlocks = mlp->ctx->smCount;
+    }
+    MlpDev w{mlp->params, mlp->paramsT};
+    k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), mlp->partial, pred);
+    mlp->ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    k_reduce_partials<<<(NRC_MLP_PARAM_COUNT + 1 + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad);
+    mlp->ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    return NRC_OK;
+}

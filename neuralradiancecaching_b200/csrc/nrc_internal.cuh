@@ -1,0 +1,158 @@
+// nrc_internal.cuh -- shared declarations of the sm_100a NRC library (not part of the C-ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/nrc_b200.h"
+#include "../../include/nrc_math.h"
+
+// ---- error plumbing -------------------------------------------------------------------------------
+void nrc_set_error(const char* fmt, ...);
+
+#define NRC_CUDA(call)                                                                                    \
+    do {                                                                                                  \
+        cudaError_t e__ = (call);                                                                         \
+        if (e__ != cudaSuccess) {                                                                         \
+            nrc_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));         \
+            return (e__ == cudaErrorMemoryAllocation) ? NRC_ERR_OOM : NRC_ERR_CUDA;                        \
+        }                                                                                                 \
+    } while (0)
+
+#define NRC_TRY(call)                           \
+    do {                                        \
+        nrc_status s__ = (call);                \
+        if (s__ != NRC_OK) return s__;          \
+    } while (0)
+
+#define NRC_REQUIRE(cond, msg)                                     \
+    do {                                                           \
+        if (!(cond)) {                                             \
+            nrc_set_error("%s:%d: %s", __FILE__, __LINE__, msg);   \
+            return NRC_ERR_INVALID;                                \
+        }                                                          \
+    } while (0)
+
+// ---- MLP arena layout (same packing as the C-ABI comment) -----------------------------------------
+#define NRC_W_OFF(l) ((l) * 4096)
+#define NRC_B_OFF(l) (20672 + (l) * 64)
+
+// ---- handles ---------------------------------------------------------------------------------------
+struct nrc_ctx {
+    int device = 0;
+    int smCount = 0;
+    cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;       // second stream: render walk overlaps the training chain
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    nrc_mlp_precision precision = NRC_MLP_FP32;
+    uint64_t launches = 0;
+    // pinned staging for [h] pointers
+    void* pinned = nullptr;
+    size_t pinnedBytes = 0;
+    // device scratch for staged inputs/outputs of the stand-alone ops
+    void* scratch[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t scratchBytes[6] = {0, 0, 0, 0, 0, 0};
+};
+
+struct nrc_mlp {
+    nrc_ctx* ctx = nullptr;
+    float lr = 0.001f, wd = 0.0f, beta1 = 0.5f;
+    float* params = nullptr;     // 20995 (+pad)
+    float* grad = nullptr;       // 20995 negative-gradient accumulators + 1 mseLoss  (20996, padded)
+    float* momentum = nullptr;   // 20995
+    float* paramsT = nullptr;    // transposed weight copy Wt[l][in][out] for the forward GEMMs (5*4096 + 64*4)
+    float* partial = nullptr;    // per-block partial gradients of the train kernel [maxBlocks][NRC_PARTIAL_STRIDE]
+    int partialBlocks = 0;
+    uint16_t* paramsBf16 = nullptr;  // bf16 operand images for the tcgen05 path (built on demand)
+    bool dirtyT = true;          // paramsT / paramsBf16 need a rebuild after params changed
+};
+
+#define NRC_PARTIAL_STRIDE 21000   // 20995 grads + loss + pad
+
+struct nrc_mrhe {
+    nrc_ctx* ctx = nullptr;
+    float lr = 0.01f, wd = 0.0f;
+    uint32_t L = 16, T = 16384, F = 2, minRes = 16, maxRes = 512;
+    uint32_t res[16] = {0};
+    float* tables = nullptr;     // [L][T][F]
+    float* delta = nullptr;      // [L][T][F]
+    size_t count = 0;            // L*T*F
+};
+
+struct nrc_volume {
+    nrc_ctx* ctx = nullptr;
+    uint32_t nx = 0, ny = 0, nz = 0;
+    // 2x2x2 corner bricks: cell (i,j,k), i in [-1,nx-1], holds the 8 UNORM8 texels it interpolates,
+    // border texels are 0 (CLAMP_TO_BORDER, opaque black): one 8-byte load per density tap.
+    uint2* bricks = nullptr;     // [(nz+1)][(ny+1)][(nx+1)]
+    nrc_volume_params params;
+};
+
+struct nrc_envmap {
+    nrc_ctx* ctx = nullptr;
+    uint32_t w = 0, h = 0;
+    float4* rgba = nullptr;
+    float* invCdfX = nullptr;
+    float* invCdfY = nullptr;
+    float directStrength = 1.0f, hpmStrength = 8.0f;
+};
+
+// Everything the trace kernels need, passed by value as a __grid_constant__ kernel parameter.
+struct TraceParams {
+    float invProjView[16];
+    float camPos[3];
+    float random[4];
+    uint32_t useNN, showNonNN;
+    float densityFactor, g;
+    int noNnSpp, withNnSpp;
+    float dirDir[3], dirStrength;
+    float ptPos[3], ptStrength, ptColor[3];
+    float envDirect, envHpm;
+    float skySize[3];
+    float exitJump;               // length(2*skySize), find_entry_exit
+    int nx, ny, nz;
+    const uint2* bricks;
+    const float4* env;
+    int envW, envH;
+    uint32_t width, height;       // frame
+    uint32_t trainW, trainH;
+    float widthFactor, heightFactor;
+};
+
+// MRHE view handed to kernels by value.
+struct MrheDev {
+    const float* tables;
+    float* delta;
+    uint32_t L, T;
+    uint32_t res[16];
+    float skySize[3];
+};
+MrheDev make_mrhe_dev(const nrc_mrhe* m);
+
+// ---- helpers implemented in capi.cu ---------------------------------------------------------------
+bool nrc_is_device_ptr(const void* p);
+nrc_status nrc_scratch(nrc_ctx* ctx, int slot, size_t bytes, void** out);
+// returns a device pointer holding the data of `p` (p itself when it already is one)
+nrc_status nrc_stage_in(nrc_ctx* ctx, int slot, const void* p, size_t bytes, const void** dev);
+// returns a device pointer to write results to; nrc_stage_out_finish copies back when dst is host memory
+nrc_status nrc_stage_out(nrc_ctx* ctx, int slot, void* dst, size_t bytes, void** dev);
+nrc_status nrc_stage_out_finish(nrc_ctx* ctx, void* dst, const void* dev, size_t bytes);
+
+// ---- kernels' host launchers (one per .cu) --------------------------------------------------------
+// encode.cu
+nrc_status launch_encode_pos(nrc_mrhe* m, const float* pos, size_t n, float* feat, uint32_t* idx);
+nrc_status launch_encode_dir(nrc_ctx* ctx, const float* dir, size_t n, float* feat);
+// mlp_fp32.cu
+nrc_status launch_mlp_prepare(nrc_mlp* mlp);   // rebuild transposed weights after a parameter change
+nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n,
+                             float* rgb, cudaStream_t st);
+nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n,
+                             float lossScale, float* pred, cudaStream_t st);
+// steps.cu
+nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st);
+nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st);
+nrc_status launch_init_normal(nrc_ctx* ctx, float* dst, size_t n, float scale, uint64_t seed);
+// mlp_tc.cu (tcgen05 path)
+nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n,
+                           float* rgb, cudaStream_t st);

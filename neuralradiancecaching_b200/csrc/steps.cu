@@ -1,0 +1,114 @@
+// steps.cu -- optimiser steps and parameter initialisation.
+//
+// nrc-step.comp:200-406  : g' = (bad(g) ? 1000*sign(g) : g) - wd*w ; m = (1-b1)*g' + b1*m ; w += lr*m ;
+//                          bad(w) -> 0 for weights only (A14) ; delta = 0.      24 B/param, 20 995 params.
+// mrhe-step.comp:27-74   : g' = (bad(g) ? 100*sign(g) : g) - wd*w ; w += lr*g' ; bad(w) -> 0 ; delta = 0.
+//                          16 B/param streamed with 128-bit accesses; HBM-bound at T = 2^22 (2 GiB / step).
+// Both are pure streaming kernels: grid sized in multiples of the SM count, float4 accesses, no reuse.
+#include "nrc_internal.cuh"
+
+__device__ __forceinline__ bool bad_value(float x) { return (x != x) || (fabsf(x) == INFINITY) || (fabsf(x) > 1000.0f); }
+__device__ __forceinline__ float sign_nan0(float x) { return (x > 0.0f) ? 1.0f : ((x < 0.0f) ? -1.0f : 0.0f); }
+
+// Also refreshes the transposed weight image Wt[l][in][out] used by the forward GEMMs and clears mseLoss? No:
+// mseLoss (grad[20995]) is reset by ResetStats, as in the reference (src/main.cpp:215).
+__global__ void __launch_bounds__(256) k_nrc_step(float* __restrict__ params, float* __restrict__ grad, float* __restrict__ momentum,
+                                                  float* __restrict__ paramsT, float lr, float wd, float beta1)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NRC_MLP_PARAM_COUNT) return;
+    float w = params[i];
+    float g = grad[i];
+    if (bad_value(g)) g = __fmul_rn(1000.0f, sign_nan0(g));
+    g = __fadd_rn(g, __fmul_rn(-w, wd));
+    float d = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, beta1), g), __fmul_rn(beta1, momentum[i]));
+    momentum[i] = d;
+    float nw = __fadd_rn(w, __fmul_rn(d, lr));
+    if (i < NRC_MLP_WEIGHT_COUNT && bad_value(nw)) nw = 0.0f;
+    params[i] = nw;
+    grad[i] = 0.0f;
+    if (i < 5 * 4096) {
+        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+        paramsT[l * 4096 + k * 64 + o] = nw;
+    }
+}
+
+__device__ __forceinline__ float mrhe_update(float w, float g, float lr, float wd)
+{
+    if (bad_value(g)) g = __fmul_rn(100.0f, sign_nan0(g));
+    g = __fadd_rn(g, __fmul_rn(-w, wd));
+    float nw = __fadd_rn(w, __fmul_rn(g, lr));
+    return bad_value(nw) ? 0.0f : nw;
+}
+
+__global__ void __launch_bounds__(256) k_mrhe_step(float4* __restrict__ tables, float4* __restrict__ delta, size_t n4, float lr, float wd)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 w = tables[i];
+        float4 g = delta[i];
+        w.x = mrhe_update(w.x, g.x, lr, wd);
+        w.y = mrhe_update(w.y, g.y, lr, wd);
+        w.z = mrhe_update(w.z, g.z, lr, wd);
+        w.w = mrhe_update(w.w, g.w, lr, wd);
+        tables[i] = w;
+        delta[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
+// Counter-based N(0,1)*scale: splitmix64 per element + Box-Muller.  (The reference seeds from
+// std::random_device, src/NeuralRadianceCache.cpp:629 / src/MRHE.cpp:127: not reproducible; parity runs set
+// parameters explicitly.)
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
+__global__ void __launch_bounds__(256) k_init_normal(float* __restrict__ dst, size_t n, float scale, uint64_t seed)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint64_t h = splitmix64(seed * 0xD1342543DE82EF95ull + i);
+        float u1 = ((float)((h >> 40) + 1)) * (1.0f / 16777217.0f);
+        float u2 = ((float)((h >> 8) & 0xffffffu)) * (1.0f / 16777216.0f);
+        float r = sqrtf(-2.0f * logf(u1));
+        dst[i] = r * cosf(6.283185307179586f * u2) * scale;
+    }
+}
+
+nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st)
+{
+    k_nrc_step<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->paramsT, mlp->lr, mlp->wd,
+                                                                 mlp->beta1);
+    mlp->ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    return NRC_OK;
+}
+
+nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
+{
+    size_t n4 = m->count / 4;   // L*T*F is a multiple of 4 for every supported shape (F == 2, T even)
+    size_t want = (n4 + 255) / 256;
+    size_t cap = (size_t)m->ctx->smCount * 8;
+    unsigned blocks = (unsigned)(want < cap ? want : cap);
+    if (blocks == 0) return NRC_OK;
+    k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables), reinterpret_cast<float4*>(m->delta), n4, m->lr, m->wd);
+    m->ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    return NRC_OK;
+}
+
+nrc_status launch_init_normal(nrc_ctx* ctx, float* dst, size_t n, float scale, uint64_t seed)
+{
+    if (n == 0) return NRC_OK;
+    size_t want = (n + 255) / 256;
+    size_t cap = (size_t)ctx->smCount * 8;
+    unsigned blocks = (unsigned)(want < cap ? want : cap);
+    k_init_normal<<<blocks, 256, 0, ctx->stream>>>(dst, n, scale, seed);
+    ctx->launches++;
+    NRC_CUDA(cudaGetLastError());
+    return NRC_OK;
+}
