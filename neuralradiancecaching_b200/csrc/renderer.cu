@@ -1,0 +1,422 @@
+// renderer.cu -- nrc_renderer: the frame graph that replaces NrcHpmRenderer's recorded command buffer
+// (src/NrcHpmRenderer.cpp:571-730): train -> nrc-step -> mrhe-step -> render.
+//
+//   stream  : train walk -> light -> combine -> fused encode+MLP fwd/bwd -> [host all-reduce] -> steps
+//   stream2 : render walk -> light -> combine (compacts the NRC queries)           (independent of the weights)
+//   join    : batched inference over the compacted queries -> composite
+#include <math.h>
+#include <string.h>
+#include "trace.cuh"
+
+struct nrc_renderer {
+    nrc_ctx* ctx = nullptr;
+    nrc_volume* vol = nullptr;
+    nrc_envmap* env = nullptr;
+    nrc_mlp* mlp = nullptr;
+    nrc_mrhe* mrhe = nullptr;
+    uint32_t width = 0, height = 0, trainW = 0, trainH = 0;
+    uint32_t y0 = 0, y1 = 0, i0 = 0, i1 = 0;   // this rank's partition
+    nrc_camera cam;
+    nrc_dir_light dirLight;
+    nrc_point_light ptLight;
+    // frame
+    float4* frame = nullptr;
+    uint32_t* frame8 = nullptr;
+    float4* background = nullptr;
+    uint32_t* counters = nullptr;     // [h*w][4]
+    float* queryProbe = nullptr;      // [h*w][8]
+    // render paths / pool / queries
+    uint32_t sppAlloc = 0;
+    RenderPaths rp;
+    VertexPool rpool;
+    QueryList ql;
+    // train
+    TrainPaths tp;
+    VertexPool tpool;
+    uint32_t* trainCounters = nullptr;
+    uint32_t trainAlloc = 0;
+    // device scalars: [0] render vertex count, [1] render overflow, [2] train vertex count, [3] train overflow, [4] query count
+    uint32_t* scalars = nullptr;
+    unsigned long long* taps = nullptr;   // [0] render taps, [1] train taps
+    uint32_t* hostScalars = nullptr;      // pinned mirror
+    unsigned long long* hostTaps = nullptr;
+    bool framePending = false;            // evFork marks the end of the previous frame's composite
+};
+
+#define FREE(p) do { if (p) { cudaFree(p); (p) = nullptr; } } while (0)
+
+static void free_pool(VertexPool& p) { FREE(p.a); FREE(p.b); FREE(p.c); FREE(p.rnd); FREE(p.out); p.cap = 0; }
+
+static nrc_status alloc_pool(VertexPool& p, uint32_t cap, bool withRnd, uint32_t* count, uint32_t* overflow)
+{
+    free_pool(p);
+    NRC_CUDA(cudaMalloc(&p.a, (size_t)cap * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&p.b, (size_t)cap * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&p.c, (size_t)cap * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&p.out, (size_t)cap * sizeof(float4)));
+    if (withRnd) NRC_CUDA(cudaMalloc(&p.rnd, (size_t)cap * 4 * sizeof(float4)));
+    p.cap = cap; p.count = count; p.overflow = overflow;
+    return NRC_OK;
+}
+
+static void free_frame(nrc_renderer* r)
+{
+    FREE(r->frame); FREE(r->frame8); FREE(r->background); FREE(r->counters); FREE(r->queryProbe);
+    FREE(r->rp.head); FREE(r->rp.qposPhase); FREE(r->rp.qdirValid); FREE(r->rp.result); FREE(r->rp.qweight); FREE(r->rp.qslot);
+    FREE(r->ql.pos); FREE(r->ql.dir); FREE(r->ql.rgb);
+    free_pool(r->rpool);
+    r->sppAlloc = 0;
+}
+
+// (Re)allocate everything whose size depends on the frame size and spp.
+static nrc_status alloc_frame(nrc_renderer* r, uint32_t spp, uint32_t poolCap)
+{
+    free_frame(r);
+    size_t px = (size_t)r->width * r->height;
+    size_t paths = px * spp;
+    NRC_CUDA(cudaMalloc(&r->frame, px * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&r->frame8, px * sizeof(uint32_t)));
+    NRC_CUDA(cudaMalloc(&r->background, px * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&r->counters, px * 4 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMalloc(&r->queryProbe, px * 8 * sizeof(float)));
+    NRC_CUDA(cudaMemsetAsync(r->frame, 0, px * sizeof(float4), r->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->frame8, 0, px * sizeof(uint32_t), r->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->counters, 0, px * 4 * sizeof(uint32_t), r->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->queryProbe, 0, px * 8 * sizeof(float), r->ctx->stream));
+    NRC_CUDA(cudaMalloc(&r->rp.head, paths * sizeof(int)));
+    NRC_CUDA(cudaMalloc(&r->rp.qposPhase, paths * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&r->rp.qdirValid, paths * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&r->rp.result, paths * sizeof(float4)));
+    NRC_CUDA(cudaMalloc(&r->rp.qweight, paths * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&r->rp.qslot, paths * sizeof(int)));
+    NRC_CUDA(cudaMalloc(&r->ql.pos, paths * 3 * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&r->ql.dir, paths * 3 * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&r->ql.rgb, paths * 3 * sizeof(float)));
+    r->ql.cap = (uint32_t)paths;
+    r->ql.count = r->scalars + 4;
+    NRC_TRY(alloc_pool(r->rpool, poolCap, true, r->scalars + 0, r->scalars + 1));
+    r->sppAlloc = spp;
+    return NRC_OK;
+}
+
+static void free_train(nrc_renderer* r)
+{
+    FREE(r->tp.head); FREE(r->tp.pos); FREE(r->tp.dir); FREE(r->tp.target); FREE(r->trainCounters);
+    free_pool(r->tpool);
+    r->trainAlloc = 0;
+}
+
+static nrc_status alloc_train(nrc_renderer* r)
+{
+    free_train(r);
+    uint32_t n = r->trainW * r->trainH;
+    NRC_CUDA(cudaMalloc(&r->tp.head, (size_t)n * 8 * sizeof(int)));
+    NRC_CUDA(cudaMalloc(&r->tp.pos, (size_t)n * 3 * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&r->tp.dir, (size_t)n * 3 * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&r->tp.target, (size_t)n * 3 * sizeof(float)));
+    NRC_CUDA(cudaMalloc(&r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMemsetAsync(r->tp.pos, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->tp.dir, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->trainCounters, 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
+    // worst case: 8 paths x 64 lit vertices per training sample -- this pool cannot overflow
+    size_t cap = (size_t)n * 8 * 64;
+    NRC_REQUIRE(cap < ((size_t)1 << 31), "train grid too large for the vertex pool");
+    NRC_TRY(alloc_pool(r->tpool, (uint32_t)cap, false, r->scalars + 2, r->scalars + 3));
+    r->trainAlloc = n;
+    return NRC_OK;
+}
+
+// ---- create / destroy / setters ------------------------------------------------------------------------------------------
+extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t height, uint32_t trainWidth, uint32_t trainHeight,
+                                          nrc_volume* vol, nrc_envmap* env, nrc_mlp* mlp, nrc_mrhe* mrhe, nrc_renderer** out)
+{
+    NRC_REQUIRE(ctx && vol && env && mlp && mrhe && out, "null argument");
+    NRC_REQUIRE(width > 0 && height > 0 && trainWidth > 0 && trainHeight > 0, "empty frame or train grid");
+    NRC_REQUIRE((size_t)width * height < ((size_t)1 << 28), "frame too large");
+    NRC_CUDA(cudaSetDevice(ctx->device));
+    nrc_renderer* r = new nrc_renderer();
+    r->ctx = ctx; r->vol = vol; r->env = env; r->mlp = mlp; r->mrhe = mrhe;
+    r->width = width; r->height = height; r->trainW = trainWidth; r->trainH = trainHeight;
+    r->y0 = 0; r->y1 = height; r->i0 = 0; r->i1 = trainWidth * trainHeight;
+    memset(&r->cam, 0, sizeof(r->cam));
+    memset(&r->dirLight, 0, sizeof(r->dirLight));
+    memset(&r->ptLight, 0, sizeof(r->ptLight));
+    memset(&r->rp, 0, sizeof(r->rp)); memset(&r->rpool, 0, sizeof(r->rpool)); memset(&r->ql, 0, sizeof(r->ql));
+    memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
+    NRC_CUDA(cudaMalloc(&r->scalars, 8 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMalloc(&r->taps, 2 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 8 * sizeof(uint32_t), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    NRC_CUDA(cudaMallocHost(&r->hostScalars, 8 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMallocHost(&r->hostTaps, 2 * sizeof(unsigned long long)));
+    memset(r->hostScalars, 0, 8 * sizeof(uint32_t));
+    memset(r->hostTaps, 0, 2 * sizeof(unsigned long long));
+    NRC_TRY(alloc_frame(r, 1, (uint32_t)((size_t)width * height * 4)));
+    NRC_TRY(alloc_train(r));
+    *out = r;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
+{
+    if (!r) return NRC_OK;
+    cudaStreamSynchronize(r->ctx->stream);
+    cudaStreamSynchronize(r->ctx->stream2);
+    free_frame(r);
+    free_train(r);
+    FREE(r->scalars); FREE(r->taps);
+    if (r->hostScalars) cudaFreeHost(r->hostScalars);
+    if (r->hostTaps) cudaFreeHost(r->hostTaps);
+    delete r;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_renderer_set_camera(nrc_renderer* r, const nrc_camera* cam)
+{
+    NRC_REQUIRE(r && cam, "null argument");
+    r->cam = *cam;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_renderer_set_dir_light(nrc_renderer* r, const nrc_dir_light* l)
+{
+    NRC_REQUIRE(r && l, "null argument");
+    r->dirLight = *l;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_renderer_set_point_light(nrc_renderer* r, const nrc_point_light* l)
+{
+    NRC_REQUIRE(r && l, "null argument");
+    r->ptLight = *l;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_renderer_set_partition(nrc_renderer* r, uint32_t y0, uint32_t y1, uint32_t i0, uint32_t i1)
+{
+    NRC_REQUIRE(r, "null renderer");
+    NRC_REQUIRE(y0 <= y1 && y1 <= r->height, "row partition out of range");
+    NRC_REQUIRE(i0 <= i1 && i1 <= r->trainW * r->trainH, "train partition out of range");
+    r->y0 = y0; r->y1 = y1; r->i0 = i0; r->i1 = i1;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t height)
+{
+    NRC_REQUIRE(r && width > 0 && height > 0, "bad size");
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
+    r->width = width; r->height = height;
+    r->y0 = 0; r->y1 = height;
+    return alloc_frame(r, r->sppAlloc ? r->sppAlloc : 1, (uint32_t)((size_t)width * height * 4));
+}
+
+static TraceParams make_params(const nrc_renderer* r)
+{
+    TraceParams P;
+    memset(&P, 0, sizeof(P));
+    memcpy(P.invProjView, r->cam.invProjView, sizeof(P.invProjView));
+    memcpy(P.camPos, r->cam.pos, sizeof(P.camPos));
+    const nrc_volume_params& v = r->vol->params;
+    memcpy(P.random, v.random, sizeof(P.random));
+    P.useNN = v.useNN; P.showNonNN = v.showNonNN; P.densityFactor = v.densityFactor; P.g = v.g;
+    P.noNnSpp = v.noNnSpp; P.withNnSpp = v.withNnSpp;
+    memcpy(P.dirDir, r->dirLight.dir, sizeof(P.dirDir));
+    P.dirStrength = r->dirLight.strength;
+    memcpy(P.ptPos, r->ptLight.pos, sizeof(P.ptPos));
+    P.ptStrength = r->ptLight.strength;
+    memcpy(P.ptColor, r->ptLight.color, sizeof(P.ptColor));
+    P.envDirect = r->env->directStrength; P.envHpm = r->env->hpmStrength;
+    P.skySize[0] = 62.5f; P.skySize[1] = 42.5f; P.skySize[2] = 76.5f;   // vec3(125,85,153)/2 (nrc-train.comp:212)
+    // length(2*skySize) with the oracle's evaluation order: sqrt((x*x + y*y) + z*z), IEEE float on the host
+    {
+        volatile float x = 2.0f * P.skySize[0], y = 2.0f * P.skySize[1], z = 2.0f * P.skySize[2];
+        volatile float xx = x * x, yy = y * y, zz = z * z;
+        volatile float s = xx + yy;
+        volatile float t = s + zz;
+        P.exitJump = sqrtf(t);
+    }
+    P.nx = (int)r->vol->nx; P.ny = (int)r->vol->ny; P.nz = (int)r->vol->nz;
+    P.bricks = r->vol->bricks;
+    P.env = r->env->rgba; P.envW = (int)r->env->w; P.envH = (int)r->env->h;
+    P.width = r->width; P.height = r->height; P.trainW = r->trainW; P.trainH = r->trainH;
+    P.widthFactor = 1.0f / (float)r->trainW;     // NrcHpmRenderer.cpp:409-411
+    P.heightFactor = 1.0f / (float)r->trainH;
+    return P;
+}
+
+// ---- the frame ---------------------------------------------------------------------------------------------------------------
+static nrc_status infer_queries(nrc_renderer* r, cudaStream_t st)
+{
+    if (r->ctx->precision == NRC_MLP_BF16_TC)
+        return launch_infer_tc(r->mlp, r->mrhe, r->ql.pos, r->ql.dir, r->ql.count, r->ql.cap, r->ql.rgb, st);
+    return launch_infer_fp32(r->mlp, r->mrhe, r->ql.pos, r->ql.dir, r->ql.count, r->ql.cap, r->ql.rgb, st);
+}
+
+// nrc-train.comp over this rank's invocations: trace the records, then Backprop() them (gradients accumulate
+// into the MLP / MRHE delta arenas; the optimiser step is separate).
+extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
+{
+    NRC_REQUIRE(r, "null renderer");
+    nrc_ctx* ctx = r->ctx;
+    cudaStream_t st = ctx->stream;
+    uint32_t n = r->i1 - r->i0;
+    if (n == 0) return NRC_OK;
+    TraceParams P = make_params(r);
+    NRC_CUDA(cudaMemsetAsync(r->scalars + 2, 0, 2 * sizeof(uint32_t), st));
+    NRC_CUDA(cudaMemsetAsync(r->taps + 1, 0, sizeof(unsigned long long), st));
+    NRC_TRY(launch_train_walk(ctx, st, P, r->i0, r->i1, r->tpool, r->tp, r->trainCounters));
+    NRC_TRY(launch_light(ctx, st, P, r->tpool, false, r->taps + 1));
+    NRC_TRY(launch_train_combine(ctx, st, n, r->tpool, r->tp));
+    float lossScale = P.widthFactor * P.heightFactor;   // ONE_OVER_PIXEL_COUNT (nrc-train.comp:210)
+    NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
+    return NRC_OK;
+}
+
+// nrc-forward.{vert,frag} over this rank's rows.  The trace part runs on stream2 and may overlap whatever is
+// still queued on the main stream (training, steps); inference waits for both.
+extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
+{
+    NRC_REQUIRE(r, "null renderer");
+    nrc_ctx* ctx = r->ctx;
+    if (r->y1 == r->y0) return NRC_OK;
+    const nrc_volume_params& v = r->vol->params;
+    const bool useNN = (v.useNN == 1u);
+    uint32_t spp = (uint32_t)(useNN ? v.withNnSpp : v.noNnSpp);
+    size_t px = (size_t)r->width * r->height;
+    size_t wantCap = px * spp * (useNN ? 4 : 32);
+    if (wantCap > 0x7fffffffu) wantCap = 0x7fffffffu;
+    if (spp != r->sppAlloc || r->rpool.cap < wantCap) {
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
+        NRC_TRY(alloc_frame(r, spp, (uint32_t)wantCap));
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    TraceParams P = make_params(r);
+    for (int attempt = 0; attempt < 2; attempt++) {
+        cudaStream_t s2 = ctx->stream2;
+        // the previous frame's composite (main stream) still reads the buffers this walk overwrites
+        if (r->framePending) NRC_CUDA(cudaStreamWaitEvent(s2, ctx->evFork, 0));
+        // order stream2 after the allocations/memsets above, not after the training work
+        NRC_CUDA(cudaMemsetAsync(r->scalars + 0, 0, 2 * sizeof(uint32_t), s2));
+        NRC_CUDA(cudaMemsetAsync(r->scalars + 4, 0, sizeof(uint32_t), s2));
+        NRC_CUDA(cudaMemsetAsync(r->taps + 0, 0, sizeof(unsigned long long), s2));
+        NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, r->y1, spp, r->rpool, r->rp, r->background, r->counters));
+        NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, r->taps + 0));
+        NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, r->y1, spp, r->rpool, r->rp, r->ql));
+        NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s2));
+        NRC_CUDA(cudaEventRecord(ctx->evJoin, s2));
+        NRC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->evJoin, 0));
+        if (useNN && v.showNonNN == 0u) NRC_TRY(infer_queries(r, ctx->stream));
+        NRC_TRY(launch_composite(ctx, ctx->stream, P, r->y0, r->y1, spp, r->rp, r->ql, r->background, r->frame, r->frame8, r->queryProbe));
+        NRC_CUDA(cudaEventRecord(ctx->evFork, ctx->stream));
+        r->framePending = true;
+        // Overflow of the vertex pool is checked lazily: only a pool smaller than the worst case can overflow,
+        // and then the frame is redone once with the worst-case pool.
+        if ((size_t)r->rpool.cap >= px * spp * 32) break;
+        NRC_CUDA(cudaEventSynchronize(ctx->evJoin));
+        if (r->hostScalars[1] == 0) break;
+        NRC_REQUIRE(attempt == 0, "vertex pool overflow after growing it");
+        size_t cap = px * spp * 32;
+        if (cap > 0x7fffffffu) cap = 0x7fffffffu;
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+        NRC_TRY(alloc_frame(r, spp, (uint32_t)cap));
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return NRC_OK;
+}
+
+// Render(): train -> nrc-step -> mrhe-step -> render, like the recorded command buffer.
+extern "C" nrc_status nrc_render(nrc_renderer* r)
+{
+    NRC_REQUIRE(r, "null renderer");
+    NRC_TRY(nrc_frame_train(r));
+    NRC_TRY(nrc_optimizer_step(r->mlp, r->mrhe));
+    NRC_TRY(nrc_frame_render(r));
+    return NRC_OK;
+}
+
+// ---- read-back ---------------------------------------------------------------------------------------------------------------
+extern "C" size_t nrc_frame_bytes(nrc_renderer* r, nrc_frame_format fmt)
+{
+    if (!r) return 0;
+    size_t px = (size_t)r->width * r->height;
+    return fmt == NRC_FRAME_RGBA32F ? px * 16 : px * 4;
+}
+
+extern "C" void* nrc_frame_ptr(nrc_renderer* r, nrc_frame_format fmt)
+{
+    if (!r) return nullptr;
+    return fmt == NRC_FRAME_RGBA32F ? (void*)r->frame : (void*)r->frame8;
+}
+
+static nrc_status read_back(nrc_ctx* ctx, void* dst, const void* src, size_t bytes)
+{
+    cudaMemcpyKind k = nrc_is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    NRC_CUDA(cudaMemcpyAsync(dst, src, bytes, k, ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_read_frame(nrc_renderer* r, void* dst, nrc_frame_format fmt)
+{
+    NRC_REQUIRE(r && dst, "null argument");
+    NRC_REQUIRE(fmt == NRC_FRAME_RGBA32F || fmt == NRC_FRAME_BGRA8, "unknown frame format");
+    return read_back(r->ctx, dst, nrc_frame_ptr(r, fmt), nrc_frame_bytes(r, fmt));
+}
+
+extern "C" nrc_status nrc_read_render_probes(nrc_renderer* r, uint32_t* counters, float* query)
+{
+    NRC_REQUIRE(r, "null renderer");
+    size_t px = (size_t)r->width * r->height;
+    if (counters) NRC_TRY(read_back(r->ctx, counters, r->counters, px * 4 * sizeof(uint32_t)));
+    if (query) NRC_TRY(read_back(r->ctx, query, r->queryProbe, px * 8 * sizeof(float)));
+    return NRC_OK;
+}
+
+__global__ void k_pack_records(const float* __restrict__ pos, const float* __restrict__ dir, const float* __restrict__ target, uint32_t n,
+                               float* __restrict__ rec)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int k = 0; k < 3; k++) {
+        rec[9 * (size_t)i + k] = pos[3 * (size_t)i + k];
+        rec[9 * (size_t)i + 3 + k] = dir[3 * (size_t)i + k];
+        rec[9 * (size_t)i + 6 + k] = target[3 * (size_t)i + k];
+    }
+}
+
+// records / trainCounters hold trainW*trainH rows; this rank's rows are [i0, i1), the rest are left untouched.
+extern "C" nrc_status nrc_read_train_probes(nrc_renderer* r, float* records, uint32_t* trainCounters)
+{
+    NRC_REQUIRE(r, "null renderer");
+    uint32_t n = r->i1 - r->i0;
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = r->ctx;
+    if (records) {
+        void* tmp;
+        NRC_TRY(nrc_scratch(ctx, 5, (size_t)n * 9 * sizeof(float), &tmp));
+        k_pack_records<<<(n + 255) / 256, 256, 0, ctx->stream>>>(r->tp.pos, r->tp.dir, r->tp.target, n, (float*)tmp);
+        ctx->launches++;
+        NRC_CUDA(cudaGetLastError());
+        NRC_TRY(read_back(ctx, records + (size_t)r->i0 * 9, tmp, (size_t)n * 9 * sizeof(float)));
+    }
+    if (trainCounters) NRC_TRY(read_back(ctx, trainCounters + (size_t)r->i0 * 4, r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, uint64_t* trainSamples, uint64_t* densityTaps)
+{
+    NRC_REQUIRE(r, "null renderer");
+    nrc_ctx* ctx = r->ctx;
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
+    NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (inferQueries) *inferQueries = r->hostScalars[4];
+    if (trainSamples) *trainSamples = r->i1 - r->i0;
+    // + one tap per walk step is not counted here: densityTaps are the light kernels' taps (the bulk)
+    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[0] + (uint64_t)r->hostTaps[1];
+    return NRC_OK;
+}

@@ -3,7 +3,7 @@
 // walk kernels use strict.cuh (bit-exact control flow against the oracle); light/combine kernels use fast
 // math: their results are radiance values only.
 #include "trace.cuh"
-#include "strict.cuh"
+#include "walk.cuh"
 
 // ---- small device helpers ---------------------------------------------------------------------------------------
 
@@ -69,22 +69,40 @@ __device__ __forceinline__ f3 env_lookup(const TraceParams& P, f3 d, float stren
                (w00 * t00.z + w10 * t10.z + w01 * t01.z + w11 * t11.z) * strength);
 }
 
-// One walk step shared by all walks: exit along dir, next point (nrc-forward.frag:813-818).
-__device__ __forceinline__ f3 walk_advance(const Box& box, f3 cur, f3 dir, Rng& rng, unsigned& sdf)
+__device__ __forceinline__ WalkParams make_walk(const TraceParams& P)
 {
-    f3 en, ex;
-    find_entry_exit(box, cur, dir, en, ex, sdf);
-    float maxDistance = NRC_MUL(s_length(s_sub(ex, cur)), 0.1f);
-    float nextDistance = NRC_MUL(rng_next(rng), maxDistance);
-    return s_madd(cur, dir, nextDistance);
+    WalkParams w;
+#pragma unroll
+    for (int i = 0; i < 16; i++) w.invProjView[i] = P.invProjView[i];
+    w.camPos[0] = P.camPos[0]; w.camPos[1] = P.camPos[1]; w.camPos[2] = P.camPos[2];
+    w.randomX = P.random[0]; w.randomY = P.random[1];
+    w.g = P.g; w.useNN = P.useNN; w.showNonNN = P.showNonNN;
+    w.width = P.width; w.height = P.height; w.trainW = P.trainW;
+    w.widthFactor = P.widthFactor; w.heightFactor = P.heightFactor;
+    return w;
 }
 
-__device__ __forceinline__ void store_vertex(const VertexPool& pool, uint32_t slot, f3 pos, float density, f3 dir, f3 last)
-{
-    pool.a[slot] = make_float4(pos.x, pos.y, pos.z, density);
-    pool.b[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(-1));
-    pool.c[slot] = make_float4(last.x, last.y, last.z, 0.0f);
-}
+// Appends lit vertices to the pool and chains them per path.
+struct PoolEmitter {
+    VertexPool pool;
+    int head, prev;
+    __device__ __forceinline__ void begin() { head = -1; prev = -1; }
+    __device__ __forceinline__ bool vertex(f3 pos, float density, f3 dir, f3 last, const float* r)
+    {
+        uint32_t slot = alloc_slot(pool.count);
+        if (slot >= pool.cap) { *pool.overflow = 1u; return false; }
+        pool.a[slot] = make_float4(pos.x, pos.y, pos.z, density);
+        pool.b[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(-1));
+        pool.c[slot] = make_float4(last.x, last.y, last.z, 0.0f);
+        if (r) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) pool.rnd[(size_t)slot * 4 + k] = make_float4(r[4 * k], r[4 * k + 1], r[4 * k + 2], r[4 * k + 3]);
+        }
+        if (prev >= 0) pool.b[prev].w = __int_as_float((int)slot); else head = (int)slot;
+        prev = (int)slot;
+        return true;
+    }
+};
 
 // ---- render walk (nrc-forward.vert:28-40, nrc-forward.frag:757-870 minus lighting and Forward()) ------------------
 __global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t y1, uint32_t spp,
@@ -98,76 +116,36 @@ __global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ Tra
     size_t pix = (size_t)py * P.width + px;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
-
-    float u = NRC_DIV(NRC_ADD((float)px, 0.5f), (float)P.width);
-    float v = NRC_DIV(NRC_ADD((float)py, 0.5f), (float)P.height);
-    float sx = NRC_SUB(NRC_MUL(u, 2.0f), 1.0f);
-    float sy = NRC_MUL(NRC_SUB(NRC_MUL(v, 2.0f), 1.0f), -1.0f);   // y flipped at the vertices (A18)
-    f3 ro = mk3(P.camPos[0], P.camPos[1], P.camPos[2]);
-    f3 rd = s_normalize(s_sub(unproject(P.invProjView, sx, sy), ro));
+    const WalkParams W = make_walk(P);
+    f3 ro, rd;
     Rng rng;
-    rng.pre = NRC_MUL(P.random[0], u);
-    rng.prePre = NRC_MUL(P.random[1], v);
-    rng.draws = 0;
-    unsigned sdf = 0, lit = 0, steps = 0, emitted = 0;
-
+    render_ray(W, px, py, ro, rd, rng);
+    WalkCounters wc = {0u, 0u, 0u, 0u};
     f3 entry, exitp;
-    find_entry_exit(box, ro, rd, entry, exitp, sdf);
+    find_entry_exit(box, ro, rd, entry, exitp, wc.sdf);
     f3 envc = env_lookup(P, rd, P.envDirect);
     bool miss = sky_sdf(box, entry) > NRC_MAX_RAY_DISTANCE;
     background[pix] = make_float4(envc.x, envc.y, envc.z, miss ? 1.0f : 0.0f);
-    const bool useNN = (P.useNN == 1u);
-
+    PoolEmitter em;
+    em.pool = pool;
     for (uint32_t s = 0; s < spp; s++) {
         size_t path = pix * spp + s;
-        int head = -1;
-        int prevSlot = -1;
+        em.begin();
         float4 qp = make_float4(0.0f, 0.0f, 0.0f, 0.0f), qd = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         if (!miss) {
-            f3 cur = entry, last = entry, dir = rd, lastDir = mk3(0.0f, 0.0f, 0.0f);
-            float termProb = 1.0f;
-            for (int i = 0; i < 32; i++) {
-                steps++;
-                float density = grid_density(grid, cur);
-                if (density > 0.0f) {
-                    if (useNN) {
-                        if (rng_next(rng) > termProb) {
-                            if (P.showNonNN == 0u) {
-                                float ph = hg_phase(P.g, -dot3(dir, lastDir));   // A19: lastDir = 0 before the first scatter
-                                qp = make_float4(cur.x, cur.y, cur.z, ph);
-                                qd = make_float4(dir.x, dir.y, dir.z, 1.0f);
-                                emitted++;
-                            }
-                            break;
-                        }
-                        termProb = NRC_MUL(termProb, 0.5f);
-                    }
-                    uint32_t slot = alloc_slot(pool.count);
-                    if (slot >= pool.cap) { *pool.overflow = 1u; break; }
-                    store_vertex(pool, slot, cur, density, dir, last);
-                    float r[16];
-#pragma unroll
-                    for (int k = 0; k < 16; k++) r[k] = rng_next(rng);   // the 8 NewRayDir calls of SampleHdrEnvMap (fwd.frag:717-725)
-#pragma unroll
-                    for (int k = 0; k < 4; k++) pool.rnd[(size_t)slot * 4 + k] = make_float4(r[4 * k], r[4 * k + 1], r[4 * k + 2], r[4 * k + 3]);
-                    if (prevSlot >= 0) pool.b[prevSlot].w = __int_as_float((int)slot); else head = (int)slot;
-                    prevSlot = (int)slot;
-                    lit++;
-                    last = cur;
-                    lastDir = dir;
-                    dir = new_ray_dir(dir, P.g, rng);
-                }
-                cur = walk_advance(box, cur, dir, rng, sdf);
+            WalkQuery q;
+            render_walk_path(W, box, grid, entry, rd, rng, em, wc, q);
+            if (q.valid) {
+                float ph = hg_phase(P.g, -dot3(q.dir, q.lastDir));   // dirPhase (fwd.frag:785)
+                qp = make_float4(q.pos.x, q.pos.y, q.pos.z, ph);
+                qd = make_float4(q.dir.x, q.dir.y, q.dir.z, 1.0f);
             }
         }
-        paths.head[path] = head;
+        paths.head[path] = em.head;
         paths.qposPhase[path] = qp;
         paths.qdirValid[path] = qd;
     }
-    if (counters) {
-        uint4 c = make_uint4(rng.draws, lit, steps, emitted);
-        reinterpret_cast<uint4*>(counters)[pix] = c;
-    }
+    if (counters) reinterpret_cast<uint4*>(counters)[pix] = make_uint4(rng.draws, wc.lit, wc.steps, wc.emitted);
 }
 
 // ---- train walk (nrc-train.comp:1122-1259 minus lighting and Backprop) ------------------------------------------------
@@ -176,74 +154,360 @@ __global__ void __launch_bounds__(64) k_train_walk(const __grid_constant__ Trace
 {
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= i1 - i0) return;
-    uint32_t inv = i0 + local;
-    uint32_t x = inv % P.trainW, y = inv / P.trainW;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
-
-    float u = NRC_MUL((float)x, P.widthFactor);     // uv at the corner, no y flip (A18)
-    float v = NRC_MUL((float)y, P.heightFactor);
-    float sx = NRC_SUB(NRC_MUL(u, 2.0f), 1.0f);
-    float sy = NRC_SUB(NRC_MUL(v, 2.0f), 1.0f);
-    f3 ro = mk3(P.camPos[0], P.camPos[1], P.camPos[2]);
-    f3 rd = s_normalize(s_sub(unproject(P.invProjView, sx, sy), ro));
+    const WalkParams W = make_walk(P);
     Rng rng;
-    rng.pre = NRC_MUL(P.random[0], u);
-    rng.prePre = NRC_MUL(P.random[1], v);
-    rng.draws = 0;
-    unsigned sdf = 0, lit = 0, steps = 0;
-
-    f3 entry, exitp;
-    find_entry_exit(box, ro, rd, entry, exitp, sdf);
-    if (sky_sdf(box, entry) > NRC_MAX_RAY_DISTANCE) {
-        rd = s_neg(s_normalize(ro));
-        find_entry_exit(box, ro, rd, entry, exitp, sdf);   // TracePathAndLearn recomputes it with the new direction
-    }
-    // TracePathAndLearn (:1173-1215): pick the training vertex
-    f3 cur = entry, dir = rd;
-    {
-        float termProb = 1.0f;
-        bool didScatter = false;
-        for (int i = 0; i < 64; i++) {
-            if (rng_next(rng) > termProb) break;
-            termProb = NRC_MUL(termProb, 0.5f);
-            steps++;
-            if (grid_density(grid, cur) > 0.0f) {
-                didScatter = true;
-                dir = new_ray_dir(dir, P.g, rng);
-            }
-            cur = walk_advance(box, cur, dir, rng, sdf);
-        }
-        if (!didScatter) {
-            cur = entry;
-            dir = s_neg(s_normalize(cur));
-        }
-    }
+    WalkCounters wc = {0u, 0u, 0u, 0u};
+    f3 cur, dir;
+    train_pick_vertex(W, box, grid, i0 + local, rng, wc, cur, dir);
     paths.pos[3 * (size_t)local] = cur.x; paths.pos[3 * (size_t)local + 1] = cur.y; paths.pos[3 * (size_t)local + 2] = cur.z;
     paths.dir[3 * (size_t)local] = dir.x; paths.dir[3 * (size_t)local + 1] = dir.y; paths.dir[3 * (size_t)local + 2] = dir.z;
-    // 8 x TracePath (:1122-1171), RNG chained from one to the next
-    const f3 startP = cur, startD = dir;
-    for (int p = 0; p < 8; p++) {
-        f3 en, ex;
-        find_entry_exit(box, startP, startD, en, ex, sdf);
-        f3 c = en, last = en, d = startD;
-        int head = -1, prevSlot = -1;
-        for (int i = 0; i < 64; i++) {
-            steps++;
-            float density = grid_density(grid, c);
-            if (density > 0.0f) {
-                uint32_t slot = alloc_slot(pool.count);
-                if (slot >= pool.cap) { *pool.overflow = 1u; break; }
-                store_vertex(pool, slot, c, density, d, last);
-                if (prevSlot >= 0) pool.b[prevSlot].w = __int_as_float((int)slot); else head = (int)slot;
-                prevSlot = (int)slot;
-                lit++;
-                last = c;
-                d = new_ray_dir(d, P.g, rng);
-            }
-            c = walk_advance(box, c, d, rng, sdf);
-        }
-        paths.head[(size_t)local * 8 + p] = head;
+    PoolEmitter em;
+    em.pool = pool;
+    for (int p = 0; p < 8; p++) {   // 8 x TracePath (:1217-1222), RNG chained from one to the next
+        em.begin();
+        train_walk_path(W, box, grid, cur, dir, rng, em, wc);
+        paths.head[(size_t)local * 8 + p] = em.head;
     }
-    if (counters) reinterpret_cast<uint4*>(counters)[local] = make_uint4(rng.draws, lit, steps, 0u);
+    if (counters) reinterpret_cast<uint4*>(counters)[local] = make_uint4(rng.draws, wc.lit, wc.steps, 0u);
+}
+
+// ---- light kernel: every density tap of the frame happens here -----------------------------------------------------
+// Fast tap: u = p * (n/skySize) + (0.5*n - 0.5) folded into one FMA per axis, one 8-byte brick load, PRMT-style
+// byte->float conversion, 7 lerps.  Values only (never steers control flow).
+struct TapCtx {
+    float sx, sy, sz, ox, oy, oz;   // scale/offset per axis
+    float nx, ny, nz;
+    int strideY, strideZ;
+    const uint2* bricks;
+};
+
+__device__ __forceinline__ TapCtx make_tap(const TraceParams& P)
+{
+    TapCtx t;
+    t.sx = (float)P.nx / P.skySize[0]; t.sy = (float)P.ny / P.skySize[1]; t.sz = (float)P.nz / P.skySize[2];
+    t.ox = 0.5f * (float)P.nx - 0.5f; t.oy = 0.5f * (float)P.ny - 0.5f; t.oz = 0.5f * (float)P.nz - 0.5f;
+    t.nx = (float)P.nx; t.ny = (float)P.ny; t.nz = (float)P.nz;
+    t.strideY = P.nx + 1; t.strideZ = (P.nx + 1) * (P.ny + 1);
+    t.bricks = P.bricks;
+    return t;
+}
+
+__device__ __forceinline__ float byte_to_float(uint32_t w, int sel)
+{
+    // place byte `sel` of w into the low mantissa bits of 2^23, subtract 2^23
+    uint32_t v = __byte_perm(w, 0x4B000000u, 0x7650 + sel);
+    return __uint_as_float(v) - 8388608.0f;
+}
+
+// texel sum (0..255 scale) at world position p
+__device__ __forceinline__ float tap_raw(const TapCtx& t, float px, float py, float pz)
+{
+    float u = fmaf(px, t.sx, t.ox), v = fmaf(py, t.sy, t.oy), s = fmaf(pz, t.sz, t.oz);
+    bool in = (u >= -1.0f) & (u < t.nx) & (v >= -1.0f) & (v < t.ny) & (s >= -1.0f) & (s < t.nz);
+    if (!in) return 0.0f;
+    float fu = floorf(u), fv = floorf(v), fs = floorf(s);
+    float a = u - fu, b = v - fv, c = s - fs;
+    int cell = ((int)fs + 1) * t.strideZ + ((int)fv + 1) * t.strideY + ((int)fu + 1);
+    uint2 q = __ldg(t.bricks + cell);
+    float t000 = byte_to_float(q.x, 0), t100 = byte_to_float(q.x, 1), t010 = byte_to_float(q.x, 2), t110 = byte_to_float(q.x, 3);
+    float t001 = byte_to_float(q.y, 0), t101 = byte_to_float(q.y, 1), t011 = byte_to_float(q.y, 2), t111 = byte_to_float(q.y, 3);
+    float x00 = fmaf(a, t100 - t000, t000), x10 = fmaf(a, t110 - t010, t010);
+    float x01 = fmaf(a, t101 - t001, t001), x11 = fmaf(a, t111 - t011, t011);
+    float y0 = fmaf(b, x10 - x00, x00), y1 = fmaf(b, x11 - x01, x01);
+    return fmaf(c, y1 - y0, y0);
+}
+
+// GetTransmittance(start, end, count) (nrc-forward.frag:641-662): prod exp(-d_i*step) = exp(-step * sum d_i)
+template <int COUNT>
+__device__ __forceinline__ float transmittance(const TapCtx& t, float kDensity, f3 a, f3 b, unsigned& taps)
+{
+    float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
+    float stepSize = sqrtf(dx * dx + dy * dy + dz * dz) / (float)COUNT;
+    if (stepSize == 0.0f) return 1.0f;
+    float sum = 0.0f;
+#pragma unroll 4
+    for (int i = 0; i < COUNT; i++) {
+        float f = (float)i * (1.0f / (float)COUNT);
+        sum += tap_raw(t, fmaf(f, dx, a.x), fmaf(f, dy, a.y), fmaf(f, dz, a.z));
+    }
+    taps += COUNT;
+    return __expf(-(sum * kDensity) * stepSize);
+}
+
+template <bool RENDER>
+__global__ void __launch_bounds__(128) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
+{
+    const uint32_t count = min(*pool.count, pool.cap);
+    const Box box = make_box(P);
+    const TapCtx tc = make_tap(P);
+    const float kDensity = P.densityFactor * (1.0f / 255.0f);
+    unsigned taps = 0;
+    for (uint32_t vtx = blockIdx.x * blockDim.x + threadIdx.x; vtx < count; vtx += gridDim.x * blockDim.x) {
+        float4 A = pool.a[vtx], B = pool.b[vtx], C = pool.c[vtx];
+        f3 pos = mk3(A.x, A.y, A.z), dir = mk3(B.x, B.y, B.z), last = mk3(C.x, C.y, C.z);
+        f3 light = mk3(0.0f, 0.0f, 0.0f);
+        unsigned sdf = 0;
+        if (P.dirStrength != 0.0f) {   // TraceDirLight (fwd.frag:664-675), colour ignored (A21)
+            f3 L = mk3(P.dirDir[0], P.dirDir[1], P.dirDir[2]);
+            f3 en, ex;
+            find_entry_exit(box, pos, s_neg(s_normalize(L)), en, ex, sdf);
+            float T = transmittance<32>(tc, kDensity, pos, ex, taps);
+            float l = T * P.dirStrength * hg_phase(P.g, -dot3(L, dir));
+            light.x += l; light.y += l; light.z += l;
+        }
+        if (P.ptStrength != 0.0f) {    // TracePointLight (fwd.frag:677-688)
+            f3 lp = mk3(P.ptPos[0], P.ptPos[1], P.ptPos[2]);
+            float T = transmittance<32>(tc, kDensity, lp, pos, taps);
+            f3 tl = mk3(lp.x - pos.x, lp.y - pos.y, lp.z - pos.z);
+            float inv = rsqrtf(dot3(tl, tl));
+            float ph = hg_phase(P.g, -dot3(tl, dir) * inv);
+            float l = P.ptStrength * T * ph;
+            light.x += P.ptColor[0] * l; light.y += P.ptColor[1] * l; light.z += P.ptColor[2] * l;
+        }
+        if (RENDER) {                  // SampleHdrEnvMap(pos, dir, 8) (fwd.frag:710-749), first loop only
+            f3 acc = mk3(0.0f, 0.0f, 0.0f);
+#pragma unroll 1
+            for (int k = 0; k < 4; k++) {
+                float4 r = pool.rnd[(size_t)vtx * 4 + k];
+#pragma unroll 1
+                for (int h = 0; h < 2; h++) {
+                    f3 rdir = new_ray_dir_given(dir, P.g, h ? r.z : r.x, h ? r.w : r.y);
+                    f3 en, ex;
+                    find_entry_exit(box, pos, rdir, en, ex, sdf);
+                    float T = transmittance<16>(tc, kDensity, pos, ex, taps);
+                    f3 c = env_lookup(P, rdir, P.envHpm);
+                    acc.x += c.x * T; acc.y += c.y * T; acc.z += c.z * T;
+                }
+            }
+            light.x += acc.x * 0.125f; light.y += acc.y * 0.125f; light.z += acc.z * 0.125f;
+        }
+        float tr = transmittance<32>(tc, kDensity, pos, last, taps);
+        pool.out[vtx] = make_float4(light.x, light.y, light.z, tr);
+    }
+    if (tapCounter) {
+        unsigned long long t = taps;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(tapCounter, t);
+    }
+}
+
+// ---- combine kernels: fold vertices in path order -------------------------------------------------------------------
+__device__ __forceinline__ void fold_path(const VertexPool& pool, int head, f3& L, float& T)
+{
+    L = mk3(0.0f, 0.0f, 0.0f);
+    T = 1.0f;
+    int v = head;
+    while (v >= 0) {
+        float4 o = pool.out[v];
+        float dens = pool.a[v].w;
+        L.x += T * (dens * o.x); L.y += T * (dens * o.y); L.z += T * (dens * o.z);   // scatteredLight += T * (density * light)
+        T *= o.w;                                                                    // transmittance *= t_r
+        v = __float_as_int(pool.b[v].w);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_render_combine(uint32_t width, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
+                                                        RenderPaths paths, QueryList q)
+{
+    uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (local >= (y1 - y0) * width * spp) return;
+    size_t path = (size_t)y0 * width * spp + local;
+    f3 L; float T;
+    fold_path(pool, paths.head[path], L, T);
+    paths.result[path] = make_float4(L.x, L.y, L.z, T);
+    float4 qd = paths.qdirValid[path];
+    int slot = -1;
+    float w = 0.0f;
+    if (qd.w != 0.0f) {
+        float4 qp = paths.qposPhase[path];
+        w = T * qp.w;
+        uint32_t s = alloc_slot(q.count);
+        if (s < q.cap) {
+            slot = (int)s;
+            q.pos[3 * s] = qp.x; q.pos[3 * s + 1] = qp.y; q.pos[3 * s + 2] = qp.z;
+            q.dir[3 * s] = qd.x; q.dir[3 * s + 1] = qd.y; q.dir[3 * s + 2] = qd.z;
+        }
+    }
+    paths.qweight[path] = w;
+    paths.qslot[path] = slot;
+}
+
+__global__ void __launch_bounds__(128) k_train_combine(uint32_t nLocal, VertexPool pool, TrainPaths paths)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nLocal) return;
+    f3 sum = mk3(0.0f, 0.0f, 0.0f);
+    for (int p = 0; p < 8; p++) {
+        f3 L; float T;
+        fold_path(pool, paths.head[(size_t)i * 8 + p], L, T);
+        sum.x += L.x; sum.y += L.y; sum.z += L.z;
+    }
+    paths.target[3 * (size_t)i] = sum.x / 8.0f;
+    paths.target[3 * (size_t)i + 1] = sum.y / 8.0f;
+    paths.target[3 * (size_t)i + 2] = sum.z / 8.0f;
+}
+
+// fwd.frag:824-870: average the spp paths, add the NRC radiance, env-map colour for misses and T == 1 (A20).
+__global__ void __launch_bounds__(128) k_composite(uint32_t width, uint32_t y0, uint32_t y1, uint32_t spp, RenderPaths paths, QueryList q,
+                                                   const float4* __restrict__ background, float4* __restrict__ frame,
+                                                   uint32_t* __restrict__ frame8, float* __restrict__ queryProbe)
+{
+    uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    if (local >= (y1 - y0) * width) return;
+    size_t pix = (size_t)y0 * width + local;
+    float4 bg = background[pix];
+    float4 outc;
+    if (bg.w != 0.0f) {
+        outc = make_float4(bg.x, bg.y, bg.z, 1.0f);
+    } else {
+        float4 avg = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (uint32_t s = 0; s < spp; s++) {
+            size_t path = pix * spp + s;
+            float4 r = paths.result[path];
+            int slot = paths.qslot[path];
+            if (slot >= 0) {
+                float w = paths.qweight[path];
+                r.x += w * q.rgb[3 * slot]; r.y += w * q.rgb[3 * slot + 1]; r.z += w * q.rgb[3 * slot + 2];
+            }
+            avg.x += r.x; avg.y += r.y; avg.z += r.z; avg.w += r.w;
+        }
+        float inv = (float)spp;
+        avg.x /= inv; avg.y /= inv; avg.z /= inv; avg.w /= inv;
+        outc = (avg.w == 1.0f) ? make_float4(bg.x, bg.y, bg.z, 1.0f) : avg;
+    }
+    frame[pix] = outc;
+    if (frame8) {   // B8G8R8A8_UNORM store: clamp to [0,1], round to nearest
+        uint32_t r = (uint32_t)__float2int_rn(__saturatef(outc.x) * 255.0f), g = (uint32_t)__float2int_rn(__saturatef(outc.y) * 255.0f);
+        uint32_t b = (uint32_t)__float2int_rn(__saturatef(outc.z) * 255.0f), a = (uint32_t)__float2int_rn(__saturatef(outc.w) * 255.0f);
+        frame8[pix] = b | (g << 8) | (r << 16) | (a << 24);
+    }
+    if (queryProbe) {   // last spp path's query, like the oracle's lastQuery
+        size_t path = pix * spp + (spp - 1);
+        float4 qp = paths.qposPhase[path], qd = paths.qdirValid[path];
+        float* o = queryProbe + 8 * pix;
+        o[0] = qp.x; o[1] = qp.y; o[2] = qp.z; o[3] = qd.x; o[4] = qd.y; o[5] = qd.z;
+        o[6] = paths.qweight[path]; o[7] = qd.w;
+    }
+}
+
+// ---- volume: UNORM8 quantisation + 2x2x2 corner bricks (src/Texture3D.cpp:25-40) -----------------------------------
+__device__ __forceinline__ uint32_t quant_texel(const float* __restrict__ d, int i, int j, int k, int nx, int ny, int nz)
+{
+    if (i < 0 || j < 0 || k < 0 || i >= nx || j >= ny || k >= nz) return 0u;   // CLAMP_TO_BORDER, opaque black
+    float v = __fmul_rn(d[((size_t)i * ny + j) * nz + k], 255.0f);             // file order x*ny*nz + y*nz + z
+    return (uint32_t)((int)v) & 0xffu;                                          // static_cast<uint8_t>(value * 255.0f)
+}
+
+__global__ void __launch_bounds__(256) k_build_bricks(const float* __restrict__ d, int nx, int ny, int nz, uint2* __restrict__ bricks)
+{
+    size_t cells = (size_t)(nx + 1) * (ny + 1) * (nz + 1);
+    size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cells) return;
+    int ci = (int)(c % (nx + 1)), cj = (int)((c / (nx + 1)) % (ny + 1)), ck = (int)(c / ((size_t)(nx + 1) * (ny + 1)));
+    int i0 = ci - 1, j0 = cj - 1, k0 = ck - 1;
+    uint32_t lo = 0, hi = 0;
+    for (int t = 0; t < 4; t++) {
+        lo |= quant_texel(d, i0 + (t & 1), j0 + (t >> 1), k0, nx, ny, nz) << (8 * t);
+        hi |= quant_texel(d, i0 + (t & 1), j0 + (t >> 1), k0 + 1, nx, ny, nz) << (8 * t);
+    }
+    bricks[c] = make_uint2(lo, hi);
+}
+
+__global__ void __launch_bounds__(256) k_volume_sample(Grid g, const float* __restrict__ pos, size_t n, float* __restrict__ out)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = grid_density(g, mk3(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]));
+}
+
+// ---- launchers -----------------------------------------------------------------------------------------------------------
+#define LAUNCH_CHECK(ctx)            \
+    do {                             \
+        (ctx)->launches++;           \
+        NRC_CUDA(cudaGetLastError()); \
+    } while (0)
+
+nrc_status launch_build_bricks(nrc_volume* vol, const float* densityDev)
+{
+    size_t cells = (size_t)(vol->nx + 1) * (vol->ny + 1) * (vol->nz + 1);
+    k_build_bricks<<<(unsigned)((cells + 255) / 256), 256, 0, vol->ctx->stream>>>(densityDev, (int)vol->nx, (int)vol->ny, (int)vol->nz, vol->bricks);
+    LAUNCH_CHECK(vol->ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, float* out)
+{
+    if (n == 0) return NRC_OK;
+    Grid g;
+    g.nx = (int)vol->nx; g.ny = (int)vol->ny; g.nz = (int)vol->nz;
+    g.bricks = vol->bricks;
+    g.skySize = mk3(62.5f, 42.5f, 76.5f);
+    g.densityFactor = vol->params.densityFactor;
+    k_volume_sample<<<(unsigned)((n + 255) / 256), 256, 0, vol->ctx->stream>>>(g, pos, n, out);
+    LAUNCH_CHECK(vol->ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
+                              RenderPaths paths, float4* background, uint32_t* counters)
+{
+    uint32_t n = (y1 - y0) * P.width;
+    if (n == 0) return NRC_OK;
+    k_render_walk<<<(n + 127) / 128, 128, 0, st>>>(P, y0, y1, spp, pool, paths, background, counters);
+    LAUNCH_CHECK(ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t i0, uint32_t i1, VertexPool pool, TrainPaths paths,
+                             uint32_t* counters)
+{
+    uint32_t n = i1 - i0;
+    if (n == 0) return NRC_OK;
+    k_train_walk<<<(n + 63) / 64, 64, 0, st>>>(P, i0, i1, pool, paths, counters);
+    LAUNCH_CHECK(ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, VertexPool pool, bool render, unsigned long long* tapCounter)
+{
+    // the vertex count lives on the device: a grid-stride launch sized for the machine, not for the count
+    unsigned want = (pool.cap + 127) / 128;
+    unsigned cap = (unsigned)ctx->smCount * 16;
+    unsigned blocks = want < cap ? want : cap;
+    if (blocks == 0) return NRC_OK;
+    if (render) k_light<true><<<blocks, 128, 0, st>>>(P, pool, tapCounter);
+    else k_light<false><<<blocks, 128, 0, st>>>(P, pool, tapCounter);
+    LAUNCH_CHECK(ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
+                                 RenderPaths paths, QueryList q)
+{
+    uint32_t n = (y1 - y0) * P.width * spp;
+    if (n == 0) return NRC_OK;
+    k_render_combine<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, y1, spp, pool, paths, q);
+    LAUNCH_CHECK(ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, VertexPool pool, TrainPaths paths)
+{
+    if (nLocal == 0) return NRC_OK;
+    k_train_combine<<<(nLocal + 127) / 128, 128, 0, st>>>(nLocal, pool, paths);
+    LAUNCH_CHECK(ctx);
+    return NRC_OK;
+}
+
+nrc_status launch_composite(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, RenderPaths paths,
+                            QueryList q, const float4* background, float4* frame, uint32_t* frame8, float* queryProbe)
+{
+    uint32_t n = (y1 - y0) * P.width;
+    if (n == 0) return NRC_OK;
+    k_composite<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, y1, spp, paths, q, background, frame, frame8, queryProbe);
+    LAUNCH_CHECK(ctx);
+    return NRC_OK;
 }

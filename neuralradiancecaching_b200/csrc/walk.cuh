@@ -1,0 +1,155 @@
+// walk.cuh -- the serial random walks of the tracer as host/device templates.
+//
+// The kernels in trace.cu instantiate these with an emitter that appends vertices to the device pool;
+// tests/host_emul instantiates the very same code on the CPU build machine (no GPU there) with a recording
+// emitter and compares every draw count, vertex and query with the oracle.  It is a debugging harness for the
+// device code, not a product path: nothing in the library calls the host instantiation.
+//
+// Reference: nrc-forward.vert:28-40, nrc-forward.frag:757-870 (render); nrc-train.comp:1122-1259 (train).
+#pragma once
+#include "strict.cuh"
+
+struct WalkParams {
+    float invProjView[16];
+    float camPos[3];
+    float randomX, randomY;     // volumeData.random.xy
+    float g;
+    unsigned useNN, showNonNN;
+    unsigned width, height;     // frame
+    unsigned trainW;
+    float widthFactor, heightFactor;
+};
+
+struct WalkCounters { unsigned lit, steps, sdf, emitted; };
+
+struct WalkQuery { f3 pos, dir, lastDir; bool valid; };
+
+// One walk step shared by all walks: exit along dir, next point (nrc-forward.frag:813-818).
+NRC_HD f3 walk_advance(const Box& box, f3 cur, f3 dir, Rng& rng, unsigned& sdf)
+{
+    f3 en, ex;
+    find_entry_exit(box, cur, dir, en, ex, sdf);
+    float maxDistance = NRC_MUL(s_length(s_sub(ex, cur)), 0.1f);
+    float nextDistance = NRC_MUL(rng_next(rng), maxDistance);
+    return s_madd(cur, dir, nextDistance);
+}
+
+// Camera ray + RNG seed of render pixel (px, py): fragUV at the pixel centre, y flipped at the vertices (A18).
+NRC_HD void render_ray(const WalkParams& P, unsigned px, unsigned py, f3& ro, f3& rd, Rng& rng)
+{
+    float u = NRC_DIV(NRC_ADD((float)px, 0.5f), (float)P.width);
+    float v = NRC_DIV(NRC_ADD((float)py, 0.5f), (float)P.height);
+    float sx = NRC_SUB(NRC_MUL(u, 2.0f), 1.0f);
+    float sy = NRC_MUL(NRC_SUB(NRC_MUL(v, 2.0f), 1.0f), -1.0f);
+    ro = mk3(P.camPos[0], P.camPos[1], P.camPos[2]);
+    rd = s_normalize(s_sub(unproject(P.invProjView, sx, sy), ro));
+    rng.pre = NRC_MUL(P.randomX, u);
+    rng.prePre = NRC_MUL(P.randomY, v);
+    rng.draws = 0;
+}
+
+#if defined(__CUDACC__)
+#pragma nv_exec_check_disable
+#endif
+// TracePath(ro, rd, useNN) of the render shader without lighting and Forward(): walks from `entry`, calls
+// em.vertex(pos, density, dir, last, rands16) for every lit vertex (false = pool full, stop) and fills `q` when the
+// path terminates into the cache.
+template <class Emitter>
+NRC_HD void render_walk_path(const WalkParams& P, const Box& box, const Grid& grid, f3 entry, f3 rd, Rng& rng, Emitter& em,
+                             WalkCounters& wc, WalkQuery& q)
+{
+    const bool useNN = (P.useNN == 1u);
+    f3 cur = entry, last = entry, dir = rd, lastDir = mk3(0.0f, 0.0f, 0.0f);
+    float termProb = 1.0f;
+    q.valid = false;
+    for (int i = 0; i < 32; i++) {
+        wc.steps++;
+        float density = grid_density(grid, cur);
+        if (density > 0.0f) {
+            if (useNN) {
+                if (rng_next(rng) > termProb) {
+                    if (P.showNonNN == 0u) {
+                        q.pos = cur; q.dir = dir; q.lastDir = lastDir; q.valid = true;   // A19: lastDir = 0 before the first scatter
+                        wc.emitted++;
+                    }
+                    return;
+                }
+                termProb = NRC_MUL(termProb, 0.5f);
+            }
+            float r[16];
+            for (int k = 0; k < 16; k++) r[k] = rng_next(rng);   // the 8 NewRayDir calls of SampleHdrEnvMap (fwd.frag:717-725)
+            if (!em.vertex(cur, density, dir, last, r)) return;
+            wc.lit++;
+            last = cur;
+            lastDir = dir;
+            dir = new_ray_dir(dir, P.g, rng);
+        }
+        cur = walk_advance(box, cur, dir, rng, wc.sdf);
+    }
+}
+
+// main() of nrc-train.comp (:1228-1259) + the vertex-picking walk of TracePathAndLearn (:1173-1215): returns the
+// training record's position and direction.
+NRC_HD void train_pick_vertex(const WalkParams& P, const Box& box, const Grid& grid, unsigned inv, Rng& rng, WalkCounters& wc,
+                              f3& outPos, f3& outDir)
+{
+    unsigned x = inv % P.trainW, y = inv / P.trainW;
+    float u = NRC_MUL((float)x, P.widthFactor);     // uv at the corner, no y flip (A18)
+    float v = NRC_MUL((float)y, P.heightFactor);
+    float sx = NRC_SUB(NRC_MUL(u, 2.0f), 1.0f);
+    float sy = NRC_SUB(NRC_MUL(v, 2.0f), 1.0f);
+    f3 ro = mk3(P.camPos[0], P.camPos[1], P.camPos[2]);
+    f3 rd = s_normalize(s_sub(unproject(P.invProjView, sx, sy), ro));
+    rng.pre = NRC_MUL(P.randomX, u);
+    rng.prePre = NRC_MUL(P.randomY, v);
+    rng.draws = 0;
+    f3 entry, exitp;
+    find_entry_exit(box, ro, rd, entry, exitp, wc.sdf);
+    if (sky_sdf(box, entry) > NRC_MAX_RAY_DISTANCE) {
+        rd = s_neg(s_normalize(ro));
+        find_entry_exit(box, ro, rd, entry, exitp, wc.sdf);   // TracePathAndLearn recomputes it with the new direction
+    }
+    f3 cur = entry, dir = rd;
+    float termProb = 1.0f;
+    bool didScatter = false;
+    for (int i = 0; i < 64; i++) {
+        if (rng_next(rng) > termProb) break;
+        termProb = NRC_MUL(termProb, 0.5f);
+        wc.steps++;
+        if (grid_density(grid, cur) > 0.0f) {
+            didScatter = true;
+            dir = new_ray_dir(dir, P.g, rng);
+        }
+        cur = walk_advance(box, cur, dir, rng, wc.sdf);
+    }
+    if (!didScatter) {
+        cur = entry;
+        dir = s_neg(s_normalize(cur));
+    }
+    outPos = cur;
+    outDir = dir;
+}
+
+#if defined(__CUDACC__)
+#pragma nv_exec_check_disable
+#endif
+// TracePath(rayOrigin, rayDir) of the train shader (:1122-1171) without lighting.
+template <class Emitter>
+NRC_HD void train_walk_path(const WalkParams& P, const Box& box, const Grid& grid, f3 startP, f3 startD, Rng& rng, Emitter& em,
+                            WalkCounters& wc)
+{
+    f3 en, ex;
+    find_entry_exit(box, startP, startD, en, ex, wc.sdf);
+    f3 c = en, last = en, d = startD;
+    for (int i = 0; i < 64; i++) {
+        wc.steps++;
+        float density = grid_density(grid, c);
+        if (density > 0.0f) {
+            if (!em.vertex(c, density, d, last, nullptr)) return;
+            wc.lit++;
+            last = c;
+            d = new_ray_dir(d, P.g, rng);
+        }
+        c = walk_advance(box, c, d, rng, wc.sdf);
+    }
+}
