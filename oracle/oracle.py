@@ -20,7 +20,8 @@ BIAS_OFFSET = (20672, 20736, 20800, 20864, 20928, 20992)
 
 def build(force=False):
     """Compile the oracle with its Makefile (g++ only; seconds)."""
-    if force or not os.path.exists(_SO):
+    src_there = os.path.exists(os.path.join(_HERE, "Makefile"))
+    if force or not os.path.exists(_SO) or src_there:   # make is a no-op when the library is up to date
         subprocess.check_call(["make", "-C", _HERE] + (["-B"] if force else []),
                               stdout=subprocess.DEVNULL)
     return _SO
@@ -160,6 +161,12 @@ class OracleScene:
         feat = np.empty((n, 32), np.float32)
         self.l.orc_encode_dir(self.h, _p(d), C.c_long(n), _p(feat))
         return feat
+
+    def density(self, pos):
+        pos = _f(pos).reshape(-1, 3)
+        out = np.empty(pos.shape[0], np.float32)
+        self.l.orc_density(self.h, _p(pos), C.c_long(pos.shape[0]), _p(out))
+        return out
 
     def infer(self, pos, d):
         pos, d = _f(pos).reshape(-1, 3), _f(d).reshape(-1, 3)

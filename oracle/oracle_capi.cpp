@@ -389,6 +389,16 @@ void orc_hdr4f_to_cdf(const float* hdr4f, long width, long height, float* invCdf
     for (long y = 0; y < height; y++) invCdfYOut[y] = invY[y];
 }
 
+// getDensity (fwd.frag:579-582) at N world positions
+void orc_density(void* sp, const float* pos, long N, float* out)
+{
+    const Scene& S = *(Scene*)sp;
+    for (long n = 0; n < N; n++) {
+        Invocation inv(S);
+        out[n] = inv.getDensity(vec3(pos[3 * n], pos[3 * n + 1], pos[3 * n + 2]));
+    }
+}
+
 // ---- nrc_math.h probes (tests/test_nrc_math.py) ----
 void orc_math_eval(int fn, const float* x, const float* y, long N, float* out)
 {

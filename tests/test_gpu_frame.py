@@ -1,0 +1,147 @@
+"""-m gpu: the tracer and the whole frame (train -> steps -> render) against the oracle.
+Control flow (RNG draw counts, lit vertices, walk steps, emitted queries, query/record positions and directions) is
+compared BIT FOR BIT; radiance values within fp32 tolerance; frames by PSNR (stated: >= 60 dB on the float frame)."""
+import numpy as np
+import pytest
+
+import common as Cm
+
+pytestmark = pytest.mark.gpu
+
+PSNR_MIN = 60.0
+
+
+@pytest.fixture(scope="module")
+def N():
+    import neuralradiancecaching_b200 as N
+    return N
+
+
+@pytest.fixture(scope="module")
+def ctx(N):
+    c = N.Context(0)
+    yield c
+    c.destroy()
+
+
+def build(N, ctx, cfg, W, H, tw, th, params=None, tables=None):
+    vol = N.VolumeData(ctx, Cm.density())
+    vol.useNN, vol.showNonNN, vol.densityFactor, vol.g = cfg["use_nn"], cfg["show_non_nn"], cfg["density_factor"], cfg["g"]
+    vol.random = cfg["random4"]
+    env_rgba = Cm.envmap()
+    env = N.HdrEnvMap(ctx, env_rgba.shape[1], env_rgba.shape[0], env_rgba)
+    env.set_strengths(cfg["env_direct"], cfg["env_hpm"])
+    dl = N.DirLight(Cm.DIR_ZENITH, Cm.DIR_AZIMUTH, (1, 1, 1), cfg["dir_strength"])
+    pl = N.PointLight(cfg["pt_pos"], cfg["pt_color"], cfg["pt_strength"])
+    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
+    nrc.set_params(Cm.S.mlp_init(1) if params is None else params)
+    m = N.MRHE(ctx, 0.01, 0.0, seed=0)
+    m.set_tables(Cm.S.table_init() if tables is None else tables)
+    r = N.NrcHpmRenderer(W, H, tw, th, cfg["cam"], vol, dl, pl, env, nrc, m)
+    return r, nrc, m, vol
+
+
+def _relmax(a, b):
+    return float(np.max(np.abs(a.astype(np.float64) - b.astype(np.float64))) / max(float(np.max(np.abs(b))), 1e-30))
+
+
+@pytest.mark.parametrize("use_nn", [1, 0])
+def test_render_pass_parity(N, ctx, use_nn):
+    W, H = 96, 64
+    cfg = Cm.scene_cfg(use_nn=use_nn, aspect=W / H)
+    sc = Cm.oracle_scene(cfg)
+    orgba, ocnt, oqry = sc.render(W, H)
+    r, nrc, m, vol = build(N, ctx, cfg, W, H, 8, 8)
+    r.FrameRender()
+    ctx.sync()
+    cnt, qry = r.read_render_probes()
+    np.testing.assert_array_equal(cnt[..., 0], ocnt[..., 0])              # RNG draws
+    np.testing.assert_array_equal(cnt[..., 1], ocnt[..., 1])              # lit vertices
+    np.testing.assert_array_equal(cnt[..., 2], ocnt[..., 3])              # walk steps
+    np.testing.assert_array_equal(cnt[..., 3], oqry[..., 7].astype(np.uint32))   # query emitted
+    np.testing.assert_array_equal(qry[..., :6].view(np.uint32), oqry[..., :6].view(np.uint32))
+    np.testing.assert_allclose(qry[..., 6], oqry[..., 6], rtol=2e-4, atol=1e-7)   # T * dirPhase
+    frame = r.read_frame()
+    assert Cm.psnr(frame, orgba) >= PSNR_MIN
+    assert _relmax(frame, orgba) < 1e-3
+    st = r.stats()
+    assert st["infer_queries"] == int(oqry[..., 7].sum())
+    # density taps of the light kernel == the oracle's taps minus one per walk step
+    assert st["density_taps"] == int(ocnt[..., 2].sum()) - int(ocnt[..., 3].sum())
+    # BGRA8 frame = clamp + round of the float frame, B,G,R,A byte order (VK_FORMAT_B8G8R8A8_UNORM)
+    f8 = r.read_frame(N._lib.FRAME_BGRA8)
+    want8 = np.rint(np.clip(frame[..., [2, 1, 0, 3]], 0, 1) * 255).astype(np.uint8)
+    assert np.abs(f8.astype(int) - want8.astype(int)).max() <= 1
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+
+
+def test_train_pass_parity(N, ctx):
+    tw, th = 20, 12
+    cfg = Cm.scene_cfg()
+    sc = Cm.oracle_scene(cfg)
+    sc.set_train_size(tw, th)
+    orec, ocnt = sc.train_trace(tw, th)
+    r, nrc, m, vol = build(N, ctx, cfg, 32, 32, tw, th)
+    r.FrameTrain()
+    ctx.sync()
+    rec, cnt = r.read_train_probes()
+    np.testing.assert_array_equal(cnt[:, 0], ocnt[:, 0])
+    np.testing.assert_array_equal(cnt[:, 1], ocnt[:, 1])
+    np.testing.assert_array_equal(cnt[:, 2], ocnt[:, 3])
+    np.testing.assert_array_equal(rec[:, :6].view(np.uint32), orec[:, :6].view(np.uint32))
+    assert _relmax(rec[:, 6:], orec[:, 6:]) < 1e-4
+    # gradients accumulated by the same call == oracle Backprop over the oracle's records
+    sc.train_accumulate(orec[:, 0:3], orec[:, 3:6], orec[:, 6:9])
+    _, od, _ = sc.get_mlp()
+    _, gd, _ = nrc.get_params()
+    assert _relmax(gd, od) < 1e-3
+    assert abs(nrc.GetStats().mseLoss - sc.mse_loss()) <= 1e-3 * abs(sc.mse_loss()) + 1e-12
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+
+
+def test_whole_frames_parity_and_partition(N, ctx):
+    """Three Render() frames (train -> nrc-step -> mrhe-step -> render, new `random` each frame) against orc_frame; then the
+    same frame rendered as two row bands + two train shards must be bit-identical to the single-partition frame."""
+    W, H, tw, th = 64, 48, 16, 16
+    cfg = Cm.scene_cfg(aspect=W / H)
+    sc = Cm.oracle_scene(cfg)
+    r, nrc, m, vol = build(N, ctx, cfg, W, H, tw, th)
+    rnd = [(0.37, 0.61, 0.13, 0.89), (0.11, 0.93, 0.5, 0.2), (0.71, 0.29, 0.4, 0.6)]
+    for f in range(3):
+        sc.set_volume_params(rnd[f], 1, 0, 0.4, 0.7, 1, 1)
+        sc.reset_stats()
+        oframe = sc.frame(W, H, tw, th)
+        vol.random = np.asarray(rnd[f], np.float32)
+        nrc.ResetStats()
+        r.Render()
+        ctx.sync()
+        frame = r.read_frame()
+        assert Cm.psnr(frame, oframe) >= PSNR_MIN, f
+        assert abs(nrc.GetStats().mseLoss - sc.mse_loss()) <= 2e-3 * abs(sc.mse_loss()) + 1e-12
+    assert _relmax(nrc.get_params()[0], sc.get_mlp()[0]) < 1e-4
+    assert _relmax(m.get_tables()[0], sc.get_mrhe()[0]) < 1e-4
+    # partition invariance of the render pass (weights fixed now)
+    r.FrameRender(); ctx.sync()
+    full = r.read_frame().copy()
+    r.SetPartition(0, H // 2, 0, tw * th // 2); r.FrameRender(); ctx.sync()
+    top = r.read_frame()[:H // 2].copy()
+    r.SetPartition(H // 2, H, tw * th // 2, tw * th); r.FrameRender(); ctx.sync()
+    bottom = r.read_frame()[H // 2:].copy()
+    np.testing.assert_array_equal(np.concatenate([top, bottom]).view(np.uint32), full.view(np.uint32))
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+
+
+def test_resize_and_spp(N, ctx):
+    cfg = Cm.scene_cfg(use_nn=0)
+    r, nrc, m, vol = build(N, ctx, cfg, 32, 24, 4, 4)
+    r.ResizeFrame(48, 40)
+    cfg2 = Cm.scene_cfg(use_nn=0, aspect=48 / 40)
+    r.camera = cfg2["cam"]
+    vol.noNnSpp = 2
+    sc = Cm.oracle_scene(cfg2)
+    sc.set_volume_params(cfg2["random4"], 0, 0, 0.4, 0.7, 2, 1)
+    orgba, _, _ = sc.render(48, 40)
+    r.FrameRender(); ctx.sync()
+    assert r.GetImageDataSize() == 48 * 40 * 4
+    assert Cm.psnr(r.read_frame(), orgba) >= PSNR_MIN
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()

@@ -1,0 +1,194 @@
+"""-m gpu: the stand-alone operators of the C-ABI against the CPU oracle on the same seeded inputs.
+Integer/index work is compared bit for bit; fp32 results within the stated tolerances."""
+import numpy as np
+import pytest
+
+import common as Cm
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-3   # north_star: MLP / encoding outputs within 1e-3 relative in fp32
+
+
+@pytest.fixture(scope="module")
+def N():
+    import neuralradiancecaching_b200 as N
+    return N
+
+
+@pytest.fixture(scope="module")
+def ctx(N):
+    c = N.Context(0)
+    yield c
+    c.destroy()
+
+
+def _rel(a, b):
+    """max |a-b| relative to the largest magnitude of the reference array"""
+    return float(np.max(np.abs(a.astype(np.float64) - b.astype(np.float64))) / max(float(np.max(np.abs(b))), 1e-30))
+
+
+@pytest.mark.parametrize("res", [Cm.RES_INTENDED, Cm.RES_SHIPPED], ids=["intended", "as_shipped_std140"])
+@pytest.mark.parametrize("T", [16384, 1 << 18])
+def test_encode_bit_exact(N, ctx, res, T):
+    pos, _ = Cm.rand_queries(1 << 14, seed=11)
+    pos[:6] = [[0, 0, 0], [31.25, 21.25, 38.25], [-31.25, -21.25, -38.25], [-31.4, 0, 0], [0, -21.4, 38.3], [40, 40, 40]]
+    tables = Cm.S.table_init(2, 16, T, 2)
+    sc = Cm.oracle_scene(Cm.scene_cfg(), tables=tables, res=res, T=T)
+    f, i, _ = sc.encode_pos(pos)
+    m = N.MRHE(ctx, 0.01, 0.0, 16, T, 2, 16, 512, res, seed=0)
+    m.set_tables(tables)
+    gf, gi = N.encode(m, pos)
+    np.testing.assert_array_equal(gi, i)                                   # hash indices: bit-exact
+    np.testing.assert_array_equal(gf.view(np.uint32), f.view(np.uint32))   # same op order -> bit-exact features
+    m.Destroy()
+
+
+def test_encode_empty_and_ragged(N, ctx):
+    m = N.MRHE(ctx, 0.01, 0.0)
+    f, i = N.encode(m, np.zeros((0, 3), np.float32))
+    assert f.shape == (0, 32) and i.shape == (0, 128)
+    tables = Cm.S.table_init()
+    m.set_tables(tables)
+    sc = Cm.oracle_scene(Cm.scene_cfg(), tables=tables)
+    for n in (1, 15, 17, 257):
+        pos, _ = Cm.rand_queries(n, seed=n)
+        gf, gi = N.encode(m, pos)
+        of, oi, _ = sc.encode_pos(pos)
+        np.testing.assert_array_equal(gi, oi)
+        np.testing.assert_array_equal(gf.view(np.uint32), of.view(np.uint32))
+    m.Destroy()
+
+
+def test_encode_dir_bit_exact(N, ctx):
+    _, d = Cm.rand_queries(1 << 14, seed=5)
+    d[:4] = [[0, 1, 0], [0, -1, 0], [1, 0, 0], [0, 0, -1]]
+    sc = Cm.oracle_scene(Cm.scene_cfg())
+    np.testing.assert_array_equal(N.encode_dir(ctx, d).view(np.uint32), sc.encode_dir(d).view(np.uint32))
+
+
+def test_volume_sample_matches_oracle_texture(N, ctx):
+    """getDensity: brick layout + fp32 trilinear vs the oracle's Vulkan-style sampler; zero/non-zero must agree exactly
+    (it steers the walk), values to 1e-5."""
+    from host_emul import emul
+    vol = N.VolumeData(ctx, Cm.density())
+    vol.push()
+    pos, _ = Cm.rand_queries(1 << 14, seed=9)
+    pos *= 1.05   # some just outside the box
+    got = vol.sample(pos)
+    shape = emul.set_volume(Cm.density())
+    want_dev = np.array([emul.density_at(p, 0.4, shape) for p in pos[:2048]], np.float32)
+    np.testing.assert_array_equal(got[:2048].view(np.uint32), want_dev.view(np.uint32))
+    # against the oracle's own Vulkan-style sampler (weighted-sum blend): values to 1e-5, zero-ness exactly
+    want = Cm.oracle_scene(Cm.scene_cfg()).density(pos)
+    np.testing.assert_array_equal(got > 0, want > 0)
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-7)
+    vol.Destroy()
+
+
+def _mlp_pair(N, ctx, T=16384, res=Cm.RES_INTENDED, scale_feat=True):
+    params = Cm.S.mlp_init(1)
+    params[20672:] = Cm.S.init_params(7, 323, 0.01)   # non-zero biases exercise the bias path
+    tables = Cm.S.table_init(2, 16, T, 2)
+    sc = Cm.oracle_scene(Cm.scene_cfg(), params=params, tables=tables, res=res, T=T)
+    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
+    nrc.set_params(params)
+    m = N.MRHE(ctx, 0.01, 0.0, 16, T, 2, 16, 512, res, seed=0)
+    m.set_tables(tables)
+    return sc, nrc, m, params, tables
+
+
+def test_infer_fp32_parity(N, ctx):
+    sc, nrc, m, _, _ = _mlp_pair(N, ctx)
+    for n in (1, 63, 64, 65, 4096 + 17):
+        pos, d = Cm.rand_queries(n, seed=100 + n)
+        got = N.infer(nrc, m, pos, d)
+        want = sc.infer(pos, d)
+        assert _rel(got, want) < REL, n
+    nrc.Destroy(); m.Destroy()
+
+
+def test_train_accumulate_and_steps_parity(N, ctx):
+    sc, nrc, m, params, tables = _mlp_pair(N, ctx)
+    n = 3000   # ragged: 46 full tiles + a tail
+    pos, d = Cm.rand_queries(n, seed=21)
+    g = np.random.Generator(np.random.PCG64(4))
+    target = (g.random((n, 3)) * 3.0).astype(np.float32)
+    target[5] = [2000.0, 0.5, 0.1]      # exercises the 1024 clamp
+    pos[7] = [np.nan, 0.0, 0.0]         # exercises the NaN guard
+    scale = 1.0 / n
+    sc.set_loss_scale(scale, 1.0)
+    opred, dropped = sc.train_accumulate(pos, d, target)
+    assert dropped[7] == 1 and dropped.sum() == 1
+    gpred = N.train_accumulate(nrc, m, pos, d, target, scale, want_pred=True)
+    assert _rel(gpred, opred) < REL
+    _, od, _ = sc.get_mlp()
+    _, gd, _ = nrc.get_params()
+    for l in range(6):
+        a, b = (l * 4096, l * 4096 + (4096 if l < 5 else 192))
+        assert _rel(gd[a:b], od[a:b]) < REL, "dW%d" % l
+        a, b = (20672 + 64 * l, 20672 + 64 * l + (64 if l < 5 else 3))
+        assert _rel(gd[a:b], od[a:b]) < REL, "db%d" % l
+    _, otd = sc.get_mrhe()
+    _, gtd = m.get_tables()
+    assert np.count_nonzero(gtd[2 * 16384:]) == 0          # only level 0's slice is ever touched
+    assert _rel(gtd[:2 * 16384], otd[:2 * 16384]) < REL
+    assert abs(nrc.GetStats().mseLoss - sc.mse_loss()) <= REL * abs(sc.mse_loss())
+    # optimiser steps from IDENTICAL gradients are bit-exact (strict arithmetic on both sides)
+    nrc.set_state(delta=od)
+    m.set_tables(delta=otd)
+    N.optimizer_step(nrc, m)
+    sc.nrc_step(); sc.mrhe_step()
+    op, od2, om = sc.get_mlp()
+    gp, gd2, gm = nrc.get_params()
+    np.testing.assert_array_equal(gp.view(np.uint32), op.view(np.uint32))
+    np.testing.assert_array_equal(gm.view(np.uint32), om.view(np.uint32))
+    assert not gd2.any() and not od2.any()
+    ot, otd2 = sc.get_mrhe()
+    gt, gtd2 = m.get_tables()
+    np.testing.assert_array_equal(gt.view(np.uint32), ot.view(np.uint32))
+    assert not gtd2.any()
+    # forward after the step uses the refreshed transposed weights
+    got = N.infer(nrc, m, pos[:512], d[:512])
+    assert _rel(got[8:], sc.infer(pos[:512], d[:512])[8:]) < REL
+    nrc.Destroy(); m.Destroy()
+
+
+def test_step_scrubbing_rules(N, ctx):
+    """NaN/Inf/|x|>1000 handling of nrc-step.comp:200-236 and mrhe-step.comp:27-56."""
+    sc, nrc, m, params, tables = _mlp_pair(N, ctx)
+    delta = np.zeros(20995, np.float32)
+    delta[[0, 1, 2, 3, 20672, 20673]] = [np.nan, np.inf, -np.inf, 5000.0, np.nan, -1e9]
+    p2 = params.copy(); p2[10] = 999.9999; delta[10] = 1e3
+    mom = Cm.S.init_params(5, 20995, 0.01)
+    for o in (sc,):
+        o.set_mlp(p2, 0.5, 0.01, 0.5); o.set_mlp_state(delta, mom)
+    nrc.set_config(0.5, 0.01, 0.5); nrc.set_params(p2); nrc.set_state(delta, mom)
+    td = np.zeros_like(tables); td[[0, 1, 2, 3]] = [np.nan, np.inf, -1e6, 99.0]
+    sc.set_mrhe(tables, Cm.RES_INTENDED, 0.5, 0.01); sc.set_mrhe_delta(td)
+    m.set_config(0.5, 0.01); m.set_tables(tables, td)
+    N.optimizer_step(nrc, m); sc.nrc_step(); sc.mrhe_step()
+    np.testing.assert_array_equal(nrc.get_params()[0].view(np.uint32), sc.get_mlp()[0].view(np.uint32))
+    np.testing.assert_array_equal(nrc.get_params()[2].view(np.uint32), sc.get_mlp()[2].view(np.uint32))
+    np.testing.assert_array_equal(m.get_tables()[0].view(np.uint32), sc.get_mrhe()[0].view(np.uint32))
+    nrc.Destroy(); m.Destroy()
+
+
+def test_hdr4f_to_cdf_bit_exact(N, ctx):
+    from oracle import oracle as O
+    env = Cm.envmap()
+    ox, oy = O.hdr4f_to_cdf(env)
+    gx, gy = N.hdr4f_to_cdf(ctx, env, env.shape[1], env.shape[0])
+    np.testing.assert_array_equal(gx.view(np.uint32), ox.view(np.uint32))
+    np.testing.assert_array_equal(gy.view(np.uint32), oy.view(np.uint32))
+
+
+def test_device_pointers_accepted(N, ctx):
+    import torch
+    sc, nrc, m, _, _ = _mlp_pair(N, ctx)
+    pos, d = Cm.rand_queries(1000, seed=1)
+    tp, td = torch.from_numpy(pos).cuda(), torch.from_numpy(d).cuda()
+    out = N.infer(nrc, m, tp, td)
+    ctx.sync()
+    assert out.is_cuda and _rel(out.cpu().numpy(), sc.infer(pos, d)) < REL
+    nrc.Destroy(); m.Destroy()
