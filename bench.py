@@ -1,0 +1,433 @@
+"""bench.py -- headline benchmark of the NRC hot path (BASELINE.json: NRC queries/s and ms/frame, cloud 1080p).
+
+A step = one frame of NrcHpmRenderer::Render (train trace -> encode+MLP fwd/bwd -> nrc-step -> mrhe-step -> render
+trace -> batched NRC inference -> composite) on the synthetic cloud_sixteenth stand-in (the real blob is missing from
+the reference, .MISSING_LARGE_BLOBS).  At N GPUs the frame holds N x 1080p pixels (16:9 kept, both sides scaled by
+sqrt(N)), split into interleaved row sets, and the train grid holds N x 10 000 samples, sharded; gradients are
+all-reduced over NCCL (weak scaling).  value = (inference queries + training samples) of all ranks / max-over-ranks
+device time.  `e2e` is the same through the host-facing call sequence with the frame read back to pinned host memory
+every step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload frame|fit]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "nrc_queries_per_s"
+UNIT = "queries/s"
+BASE_W, BASE_H, BASE_TW, BASE_TH = 1920, 1080, 100, 100
+
+
+def frame_shape(n_gpus):
+    s = float(n_gpus) ** 0.5
+    w = int(round(BASE_W * s / 8.0)) * 8
+    h = int(round(BASE_H * s / 8.0)) * 8
+    return w, h, BASE_TW, BASE_TH * n_gpus
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+        except Exception:
+            pass
+    return 6650.0, 1590.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                sm.append(float(s[0]))
+                mx = max(mx, float(s[1]))
+                for n, v in zip(names, s[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---- scene shared by both arms -------------------------------------------------------------------------------------
+def scene_inputs(width, height):
+    from neuralradiancecaching_b200 import scene as S
+    from neuralradiancecaching_b200.objects import Camera, vec_from_angles
+    dens = S.cloud_density()                      # 125 x 85 x 153, deterministic (SHA-256 in BASELINE.md)
+    env = S.sky_envmap(1024, 512)                 # the shape of data/image/photostudio.hdr
+    cam = Camera((0.0, 0.0, -64.0), (0.0, 0.0, 1.0), (0.0, 1.0, 0.0), width / float(height), np.radians(60.0), 0.1, 100.0)
+    return dict(density=dens, env=env, cam=cam, dir_dir=vec_from_angles(-1.57, 0.0), params=S.mlp_init(1), tables=S.table_init(2))
+
+
+def lcg_randoms(n, seed=0x2545F491):
+    """the per-frame `random` vec4 (VolumeData::Update, src/VolumeData.cpp:105-109) from a seeded LCG"""
+    out, s = [], seed
+    for _ in range(n):
+        r = []
+        for _ in range(4):
+            s = (s * 1664525 + 1013904223) & 0xFFFFFFFF
+            r.append((s >> 8) / float(1 << 24))
+        out.append(np.asarray(r, np.float32))
+    return out
+
+
+class DevArray:
+    """__cuda_array_interface__ view of a raw device pointer (for torch.as_tensor: zero-copy)."""
+
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+# ---- the B200 arm ------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import neuralradiancecaching_b200 as N
+    from neuralradiancecaching_b200 import _lib as L
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_gpus = world
+    W, H, TW, TH = frame_shape(n_gpus)
+    if args.width:
+        W, H = args.width, args.height
+    inp = scene_inputs(W, H)
+
+    ctx = N.Context(local)
+    vol = N.VolumeData(ctx, inp["density"])
+    vol.useNN = 1
+    env = N.HdrEnvMap(ctx, 1024, 512, inp["env"])
+    dl = N.DirLight(-1.57, 0.0, (1, 1, 1), 1.0)      # strengths 1.0: the reference default 0 makes the target == 0 (SURVEY finding 9)
+    pl = N.PointLight((0, 0, 0), (1, 1, 1), 1.0)
+    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
+    nrc.set_params(inp["params"])
+    mrhe = N.MRHE(ctx, 0.01, 0.0, seed=0)
+    mrhe.set_tables(inp["tables"])
+    if args.precision == "bf16":
+        ctx.set_precision(L.MLP_BF16_TC)
+    r = N.NrcHpmRenderer(W, H, TW, TH, inp["cam"], vol, dl, pl, env, nrc, mrhe)
+    if world > 1:
+        r.SetPartitionStrided(rank, world, rank, world)
+
+    ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
+    gm_ptr, gm_n = nrc.grad_ptr()
+    gt_ptr, gt_n = mrhe.grad_ptr()
+    g_mlp = torch.as_tensor(DevArray(gm_ptr, gm_n), device=torch.device("cuda", local))
+    g_tab = torch.as_tensor(DevArray(gt_ptr, gt_n), device=torch.device("cuda", local))
+
+    def frame(random4):
+        vol.Update(random4=random4)
+        nrc.ResetStats()
+        if world == 1:
+            r.Render()
+        else:
+            r.FrameTrain()
+            with torch.cuda.stream(ext):
+                dist.all_reduce(g_mlp)
+                dist.all_reduce(g_tab)
+            N.optimizer_step(nrc, mrhe)
+            r.FrameRender()
+
+    def barrier():
+        ctx.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    K, Wm = args.steps, args.warmup
+    rnd = lcg_randoms(2 * (K + Wm) + 16)
+    ri = iter(rnd)
+    # ---- device-resident timing (value) ----
+    for _ in range(Wm):
+        frame(next(ri))
+    barrier()
+    r.totals(reset=True)
+    launches0 = ctx.launch_count()
+    ctx.profile(True)
+    ctx.profile_read(reset=True)
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(ext):
+        ev0.record()
+    for _ in range(K):
+        frame(next(ri))
+    with torch.cuda.stream(ext):
+        ev1.record()
+    barrier()
+    sampler.stop_flag = True
+    ms_total = ev0.elapsed_time(ev1)
+    prof = ctx.profile_read(reset=True)
+    ctx.profile(False)
+    launches = ctx.launch_count() - launches0
+    tot = r.totals(reset=True)
+    mse = nrc.GetStats().mseLoss
+
+    # ---- end to end: the host-facing call sequence; per step the scene/camera/RNG structs go host->device (kernel
+    # parameters) and this rank's rows of the BGRA8 frame plus the loss come back to pinned host memory ----
+    d2h_bytes = r.partition_bytes(L.FRAME_BGRA8)
+    host_frame = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
+    hf = host_frame.numpy()
+    for _ in range(3):
+        frame(next(ri))
+        r.read_frame_partition(hf, L.FRAME_BGRA8)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    with torch.cuda.stream(ext):
+        e0.record()
+    for _ in range(K):
+        frame(next(ri))
+        r.read_frame_partition(hf, L.FRAME_BGRA8)    # synchronous D2H of this rank's rows
+        _ = nrc.GetStats().mseLoss                    # D2H of the loss (src/main.cpp:220-224)
+    with torch.cuda.stream(ext):
+        e1.record()
+    barrier()
+    e2e_wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max(e0.elapsed_time(e1), 0.0)
+    tot_e2e = r.totals(reset=True)
+    return finish_b200(args, locals())
+
+
+# algorithmic work per unit (DESIGN.md "Kernels")
+TAP_BYTES = 8.0              # one density tap = one 2x2x2 UNORM8 brick
+FLOP_INFER = 41344.0         # 2 * 20 672 MAC per query
+FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
+
+
+def kernel_work(name, tot, pixels, table_floats):
+    """(bound, algorithmic units per timed region, unit) of one kernel, from the run's exact counters"""
+    if name == "k_light<render>":
+        return "hbm", tot["render_taps"] * TAP_BYTES + tot["render_vertices"] * 128.0, "GB/s"
+    if name == "k_light<train>":
+        return "hbm", tot["train_taps"] * TAP_BYTES + tot["train_vertices"] * 64.0, "GB/s"
+    if name in ("k_infer_fp32", "k_infer_tc"):
+        return "tensor", tot["infer_queries"] * FLOP_INFER, "TFLOP/s"
+    if name in ("k_train_fp32", "k_train_tc"):
+        return "tensor", tot["train_samples"] * FLOP_TRAIN, "TFLOP/s"
+    if name == "k_render_walk":
+        return "hbm", pixels * 68.0 + tot["render_vertices"] * 112.0, "GB/s"
+    if name == "k_train_walk":
+        return "hbm", tot["train_samples"] * 72.0 + tot["train_vertices"] * 48.0, "GB/s"
+    if name == "k_mrhe_step":
+        return "hbm", None, "GB/s"      # filled by the caller: 16 B/param/launch
+    return "hbm", None, "GB/s"
+
+
+def finish_b200(args, v):
+    import torch
+    import torch.distributed as dist
+    world, rank, K = v["world"], v["rank"], v["K"]
+    tot, tot_e2e, prof = v["tot"], v["tot_e2e"], v["prof"]
+    W, H = v["W"], v["H"]
+    dev = torch.device("cuda", v["local"])
+    # max over ranks of the device time; sums over ranks of the units processed
+    t = torch.tensor([v["ms_total"], v["e2e_ms"]], dtype=torch.float64, device=dev)
+    c = torch.tensor([tot["infer_queries"] + tot["train_samples"], tot_e2e["infer_queries"] + tot_e2e["train_samples"],
+                      v["launches"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    units, units_e2e, launches = float(c[0]), float(c[1]), int(c[2])
+    hbm, tflops, which = peaks()
+    # dominant kernel of this rank's timed region
+    top = max(prof.items(), key=lambda kv: kv[1][0])
+    name, (kms, kcount) = top
+    my_rows = len(range(rank, H, world)) if world > 1 else H
+    bound, work, unit = kernel_work(name, tot, my_rows * W, v["mrhe"].count)
+    if name == "k_mrhe_step":
+        work = 16.0 * v["mrhe"].count * kcount
+    roof = {"kernel": name, "bound": bound, "achieved": None, "peak": hbm if bound == "hbm" else tflops, "unit": unit, "frac": None,
+            "traffic": None, "peak_source": which, "launches": kcount, "avg_launch_ms": kms / max(kcount, 1),
+            "share_of_step": kms / max(v["ms_total"], 1e-9)}
+    if work is not None and kms > 0:
+        ach = work / (kms * 1e-3) / (1e9 if bound == "hbm" else 1e12)
+        roof["achieved"] = ach
+        roof["frac"] = ach / roof["peak"]
+        roof["algorithmic_per_launch"] = work / max(kcount, 1)
+    kernels = {}
+    for kn, (ms, cnt) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
+        b, wk, un = kernel_work(kn, tot, my_rows * W, v["mrhe"].count)
+        if kn == "k_mrhe_step":
+            wk = 16.0 * v["mrhe"].count * cnt
+        e = {"ms_per_step": ms / K, "launches_per_step": cnt / K}
+        if wk is not None and ms > 0:
+            e[un] = wk / (ms * 1e-3) / (1e9 if b == "hbm" else 1e12)
+        kernels[kn] = e
+    clocks = v["sampler"].summary()
+    line = {
+        "metric": METRIC, "value": units / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": v["Wm"],
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if args.precision == "fp32" else "bf16(mlp)+f32", "data": "synthetic",
+        "config": {"workload": "cloud_sixteenth (synthetic 125x85x153 stand-in) %dx%d 1 spp, online NRC training %dx%d samples/frame, "
+                               "dir+point+env lights, useNN=1" % (W, H, v["TW"], v["TH"]),
+                   "frame": [W, H], "train_grid": [v["TW"], v["TH"]], "hash_table": [16, 16384, 2], "mlp": "64x5->3 relu",
+                   "parallelism": "rows interleaved over %d GPU(s), train samples sharded, NCCL all-reduce of gradients" % world,
+                   "l2": "fresh per-frame RNG seed: every frame traces new paths; per-frame buffers (%.0f MB) exceed nothing but are rewritten, "
+                         "the density grid (3.4 MB) is L2-resident by design" % (W * H * 120 / 1e6)},
+        "e2e": {"value": units_e2e / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / K,
+                "h2d_bytes_per_step": 40 + 140 + 36 + 28 + 8, "d2h_bytes_per_step": v["d2h_bytes"] + 4},
+        "gpu_launches": launches, "roofline": roof, "kernels": kernels, "clocks": clocks,
+        "queries_per_step": {"infer": tot["infer_queries"] / K, "train": tot["train_samples"] / K,
+                             "density_taps": (tot["render_taps"] + tot["train_taps"]) / K},
+        "mse_loss_last": v["mse"],
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            line["cpu_baseline"] = cpu_reference_sample(W, H, v["TW"], v["TH"], budget_s=args.cpu_budget)
+        except Exception as e:   # the checker failing must not hide the GPU number
+            line["cpu_baseline"] = {"error": repr(e)}
+    if rank == 0:
+        print(json.dumps(line))
+    v["r"].Destroy()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+# ---- the CPU arm: the oracle (a C++ restatement of the reference's shaders; the reference has no CPU code for this path) ------
+def cpu_reference_sample(W, H, TW, TH, budget_s=20.0, steps=1, rows_per_step=None):
+    """Times the oracle on a bounded, evenly spread sample of the same frame: every (H/rows)-th frame row through the
+    render pass and evenly spread chunks of the train grid through trace + Backprop, then both optimiser steps.
+    value = (inference queries + training samples processed) / wall time, on all host threads."""
+    from oracle import oracle as O
+    inp = scene_inputs(W, H)
+    sc = O.OracleScene()
+    cam = inp["cam"]
+    sc.set_camera(cam.projView, cam.invProjView, cam.m_Pos)
+    sc.set_volume(inp["density"])
+    sc.set_dir_light((1, 1, 1), -1.57, inp["dir_dir"], 0.0, 1.0)
+    sc.set_point_light((0, 0, 0), 1.0, (1, 1, 1))
+    sc.set_envmap(inp["env"], None, None, 1.0, 8.0)
+    sc.set_mlp(inp["params"], 0.001, 0.0, 0.5)
+    sc.set_mrhe(inp["tables"], O.mrhe_resolutions(), 0.01, 0.0, 16, 16384, 2)
+    sc.set_train_size(TW, TH)
+    rnd = lcg_randoms(steps + 1)
+    threads = O.num_threads()
+    import ctypes as C
+    rgba = np.zeros((H, W, 4), np.float32)
+    qry = np.zeros((H, W, 8), np.float32)
+
+    def one(rows, chunks, chunk, random4):
+        sc.set_volume_params(random4, 1, 0, 0.4, 0.7, 1, 1)
+        q = 0
+        t0 = time.perf_counter()
+        n_train = TW * TH
+        for k in range(chunks):                       # train: trace + Backprop over evenly spread chunks
+            i0 = (k * n_train) // chunks
+            rec, _ = sc.train_trace(TW, TH, i0, min(i0 + chunk, n_train))
+            sc.train_accumulate(rec[:, 0:3], rec[:, 3:6], rec[:, 6:9])
+            q += rec.shape[0]
+        sc.nrc_step()
+        sc.mrhe_step()
+        for k in range(rows):                         # render: evenly spread rows
+            y = (k * H) // rows + (H // rows) // 2
+            sc.l.orc_render(sc.h, C.c_uint(W), C.c_uint(H), C.c_uint(y), C.c_uint(y + 1), O._p(rgba), None, O._p(qry))
+            q += int(qry[y, :, 7].sum())
+        return q, time.perf_counter() - t0
+
+    # calibrate on a tiny sample, then size the sample for the budget; rows and train samples keep the frame's proportions
+    n_train = TW * TH
+    chunks = 25
+    q0, t0 = one(4, 4, max(1, -(-n_train * 4 // H) // 4), rnd[0])
+    per_row = max(t0 / 4.0, 1e-4)
+    rows = rows_per_step or int(max(4, min(H, budget_s / per_row / max(steps, 1))))
+    chunk = int(max(1, min(n_train // chunks, -(-n_train * rows // H) // chunks)))
+    total_q, total_t = 0, 0.0
+    for s in range(steps):
+        q, t = one(rows, chunks, chunk, rnd[s + 1])
+        total_q += q
+        total_t += t
+    return {"value": total_q / total_t, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d of %d frame rows (evenly spread) + %d of %d train samples (%d chunks) per step, %d step(s), %.1f s; "
+                      "oracle = C++ restatement of the reference's GLSL (no CPU implementation exists in the reference; "
+                      "lavapipe unavailable on this box)" % (rows, H, chunks * chunk, TW * TH, chunks, steps, total_t),
+            "seconds": total_t, "queries": total_q}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    W, H, TW, TH = frame_shape(world)
+    K, Wm = args.steps, args.warmup
+    # each "step" is a bounded sample of one frame; the whole run stays within a few minutes
+    per_step_budget = max(2.0, min(20.0, 120.0 / max(K + Wm, 1)))
+    cpu_reference_sample(W, H, TW, TH, budget_s=2.0, steps=max(min(Wm, 1), 0) or 1)      # warm caches, page in
+    t0 = time.perf_counter()
+    cb = cpu_reference_sample(W, H, TW, TH, budget_s=per_step_budget * K, steps=K)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": cb["seconds"] / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "cloud_sixteenth (synthetic 125x85x153 stand-in) %dx%d 1 spp, online NRC training %dx%d samples/frame, "
+                                   "dir+point+env lights, useNN=1; CPU, bounded sample of each frame" % (W, H, TW, TH)},
+            "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

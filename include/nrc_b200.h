@@ -116,6 +116,15 @@ NRC_API nrc_status nrc_ctx_set_precision(nrc_ctx* ctx, nrc_mlp_precision p);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 NRC_API uint64_t nrc_ctx_launch_count(nrc_ctx* ctx);
 
+/* Per-kernel timing with CUDA events recorded on the launching stream (replaces nothing in the reference, which has
+ * only a wall-clock FPS counter, src/Time.cpp:8-25).  While enabled every kernel launch of this context is
+ * bracketed by two events; nrc_ctx_profile_read waits for them and returns accumulated milliseconds and launch
+ * counts per kernel id (arrays of nrc_kernel_count() entries). */
+NRC_API int nrc_kernel_count(void);
+NRC_API const char* nrc_kernel_name(int kernelId);
+NRC_API nrc_status nrc_ctx_profile_enable(nrc_ctx* ctx, int on);
+NRC_API nrc_status nrc_ctx_profile_read(nrc_ctx* ctx, double* ms, uint64_t* counts, int reset);
+
 /* ---- NeuralRadianceCache: MLP parameter store (src/NeuralRadianceCache.cpp:370-512, 596-700) ---- */
 /* seed != 0: W ~ N(0,1)*0.01 from a counter-based generator, biases/deltas/momenta zero. */
 NRC_API nrc_status nrc_mlp_create(nrc_ctx* ctx, float learningRate, float weightDecay, float beta1, uint64_t seed, nrc_mlp** out);
@@ -190,6 +199,9 @@ NRC_API nrc_status nrc_renderer_set_point_light(nrc_renderer* r, const nrc_point
 /* Multi-GPU partition: this rank renders frame rows [y0,y1) and traces train invocations [i0,i1)
  * (i = y*trainWidth + x).  Seeds use GLOBAL coordinates, so the union over ranks equals one GPU. */
 NRC_API nrc_status nrc_renderer_set_partition(nrc_renderer* r, uint32_t y0, uint32_t y1, uint32_t i0, uint32_t i1);
+/* Interleaved partition for load balance (cloud pixels cluster mid-frame): this rank renders rows yFirst, yFirst+yStride, ...
+ * and traces train invocations iFirst, iFirst+iStride, ...  (rank, worldSize, rank, worldSize) for data-parallel hosts. */
+NRC_API nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32_t yFirst, uint32_t yStride, uint32_t iFirst, uint32_t iStride);
 /* ResizeFrame, NrcHpmRenderer.cpp:103-126 */
 NRC_API nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t height);
 
@@ -206,6 +218,10 @@ NRC_API size_t nrc_frame_bytes(nrc_renderer* r, nrc_frame_format fmt);   /* GetI
 NRC_API void* nrc_frame_ptr(nrc_renderer* r, nrc_frame_format fmt);      /* device address of the full frame */
 NRC_API nrc_status nrc_read_frame(nrc_renderer* r, void* dst /*[h|d]*/, nrc_frame_format fmt);
 
+/* this rank's rows only, compacted (row k of dst = frame row y0 + k*stride); nrc_frame_partition_bytes is its size */
+NRC_API nrc_status nrc_read_frame_partition(nrc_renderer* r, void* dst /*[h|d]*/, nrc_frame_format fmt);
+NRC_API size_t nrc_frame_partition_bytes(nrc_renderer* r, nrc_frame_format fmt);
+
 /* Parity probes of the last frame (rows/invocations of this rank's partition only are meaningful):
  *   counters[h*w][4] = {randDraws, litVertices, walkSteps, queryEmitted}
  *   query[h*w][8]    = {pos.xyz, dir.xyz, weight, valid}
@@ -214,6 +230,10 @@ NRC_API nrc_status nrc_read_render_probes(nrc_renderer* r, uint32_t* counters, f
 NRC_API nrc_status nrc_read_train_probes(nrc_renderer* r, float* records, uint32_t* trainCounters);
 /* queries inferred + samples trained by the last frame on this rank, and density taps taken */
 NRC_API nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, uint64_t* trainSamples, uint64_t* densityTaps);
+/* running totals over all frames since creation (or the last reset) on this rank:
+ * totals[0] inference queries, [1] training samples, [2] render-side density taps, [3] train-side density taps,
+ * [4] render vertices lit, [5] train vertices lit.  Synchronises the context. */
+NRC_API nrc_status nrc_frame_totals(nrc_renderer* r, uint64_t totals[6], int reset);
 
 #ifdef __cplusplus
 }

@@ -47,7 +47,9 @@ nrc_optimizer_step nrc_volume_create nrc_volume_destroy nrc_volume_set_params nr
 nrc_envmap_destroy nrc_envmap_set_strengths nrc_hdr4f_to_cdf nrc_renderer_create nrc_renderer_destroy
 nrc_renderer_set_camera nrc_renderer_set_dir_light nrc_renderer_set_point_light nrc_renderer_set_partition nrc_resize
 nrc_render nrc_frame_train nrc_frame_render nrc_frame_bytes nrc_frame_ptr nrc_read_frame nrc_read_render_probes
-nrc_read_train_probes nrc_frame_stats""".split()
+nrc_read_train_probes nrc_frame_stats nrc_frame_totals nrc_renderer_set_partition_strided nrc_read_frame_partition
+nrc_frame_partition_bytes nrc_kernel_count nrc_kernel_name
+nrc_ctx_profile_enable nrc_ctx_profile_read""".split()
 
 _lib = None
 
@@ -61,11 +63,12 @@ def lib():
         L = C.CDLL(SO_PATH)
         L.nrc_last_error.restype = C.c_char_p
         L.nrc_version.restype = C.c_char_p
+        L.nrc_kernel_name.restype = C.c_char_p
         L.nrc_ctx_stream.restype = C.c_void_p
         L.nrc_ctx_launch_count.restype = C.c_uint64
         for n in ("nrc_mlp_grad_ptr", "nrc_mrhe_grad_ptr", "nrc_frame_ptr"):
             getattr(L, n).restype = C.c_void_p
-        for n in ("nrc_mlp_grad_count", "nrc_mrhe_table_bytes", "nrc_mrhe_grad_extent", "nrc_frame_bytes"):
+        for n in ("nrc_mlp_grad_count", "nrc_mrhe_table_bytes", "nrc_mrhe_grad_extent", "nrc_frame_bytes", "nrc_frame_partition_bytes"):
             getattr(L, n).restype = C.c_size_t
         _lib = L
     return _lib

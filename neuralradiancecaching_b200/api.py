@@ -58,6 +58,18 @@ class Context:
     def launch_count(self):
         return int(L.lib().nrc_ctx_launch_count(self.h))
 
+    def profile(self, on):
+        """Bracket every kernel launch with CUDA events on its stream (per-kernel device time)."""
+        L.check(L.lib().nrc_ctx_profile_enable(self.h, C.c_int(1 if on else 0)))
+
+    def profile_read(self, reset=True):
+        """{kernel name: (total ms, launches)} accumulated since the last reset."""
+        k = int(L.lib().nrc_kernel_count())
+        ms = (C.c_double * k)()
+        cnt = (C.c_uint64 * k)()
+        L.check(L.lib().nrc_ctx_profile_read(self.h, ms, cnt, C.c_int(1 if reset else 0)))
+        return {L.lib().nrc_kernel_name(i).decode(): (ms[i], int(cnt[i])) for i in range(k) if cnt[i]}
+
     def set_precision(self, p):
         L.check(L.lib().nrc_ctx_set_precision(self.h, C.c_int(p)))
 

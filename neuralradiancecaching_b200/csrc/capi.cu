@@ -92,6 +92,72 @@ static nrc_status copy_out(nrc_ctx* ctx, void* dst, const void* devSrc, size_t b
     return NRC_OK;
 }
 
+// ---- per-kernel event timing ------------------------------------------------------------------------------
+static const char* const g_kernelNames[K_COUNT] = {
+    "k_encode_pos", "k_encode_dir", "k_infer_fp32", "k_train_fp32", "k_reduce_partials", "k_transpose_weights", "k_nrc_step",
+    "k_mrhe_step", "k_init_normal", "k_render_walk", "k_train_walk", "k_light<render>", "k_light<train>", "k_render_combine",
+    "k_train_combine", "k_composite", "k_build_bricks", "k_volume_sample", "k_pack_records", "k_cdf_rows", "k_cdf_y",
+    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc"};
+
+void nrc_prof_begin(nrc_ctx* ctx, cudaStream_t st, int kid)
+{
+    if (!ctx->profiling) return;
+    NrcProfRec r;
+    if (!ctx->profFree.empty()) {
+        r = ctx->profFree.back();
+        ctx->profFree.pop_back();
+    } else {
+        if (cudaEventCreate(&r.a) != cudaSuccess || cudaEventCreate(&r.b) != cudaSuccess) { cudaGetLastError(); return; }
+    }
+    r.kid = kid;
+    cudaEventRecord(r.a, st);
+    ctx->profOpen.push_back(r);
+}
+
+void nrc_prof_end(nrc_ctx* ctx, cudaStream_t st)
+{
+    if (!ctx->profiling || ctx->profOpen.empty()) return;
+    cudaEventRecord(ctx->profOpen.back().b, st);
+}
+
+static void prof_drain(nrc_ctx* c)
+{
+    for (NrcProfRec& r : c->profOpen) {
+        float ms = 0.0f;
+        if (cudaEventSynchronize(r.b) == cudaSuccess && cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+            c->profMs[r.kid] += ms;
+            c->profCount[r.kid]++;
+        } else {
+            cudaGetLastError();
+        }
+        c->profFree.push_back(r);
+    }
+    c->profOpen.clear();
+}
+
+extern "C" int nrc_kernel_count(void) { return K_COUNT; }
+extern "C" const char* nrc_kernel_name(int kid) { return (kid >= 0 && kid < K_COUNT) ? g_kernelNames[kid] : ""; }
+
+extern "C" nrc_status nrc_ctx_profile_enable(nrc_ctx* c, int on)
+{
+    NRC_REQUIRE(c, "null context");
+    prof_drain(c);
+    c->profiling = (on != 0);
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_ctx_profile_read(nrc_ctx* c, double* ms, uint64_t* counts, int reset)
+{
+    NRC_REQUIRE(c, "null context");
+    prof_drain(c);
+    for (int k = 0; k < K_COUNT; k++) {
+        if (ms) ms[k] = c->profMs[k];
+        if (counts) counts[k] = c->profCount[k];
+        if (reset) { c->profMs[k] = 0.0; c->profCount[k] = 0; }
+    }
+    return NRC_OK;
+}
+
 // ---- context -------------------------------------------------------------------------------------------------
 extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
 {
@@ -133,6 +199,8 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamSynchronize(c->stream2);
     for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
     if (c->pinned) cudaFreeHost(c->pinned);
+    prof_drain(c);
+    for (NrcProfRec& r : c->profFree) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
     cudaEventDestroy(c->evFork);
     cudaEventDestroy(c->evJoin);
     cudaStreamDestroy(c->stream);

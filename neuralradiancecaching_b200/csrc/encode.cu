@@ -73,9 +73,7 @@ nrc_status launch_encode_pos(nrc_mrhe* m, const float* pos, size_t n, float* fea
     NRC_REQUIRE(m->F == 2, "the encoder kernels are written for featureCount == 2 (the reference's only value)");
     size_t threads = n * 16;
     unsigned blocks = (unsigned)((threads + 255) / 256);
-    k_encode_pos<<<blocks, 256, 0, m->ctx->stream>>>(pos, n, make_mrhe_dev(m), feat, idx);
-    m->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(m->ctx, m->ctx->stream, K_ENCODE_POS, k_encode_pos<<<blocks, 256, 0, m->ctx->stream>>>(pos, n, make_mrhe_dev(m), feat, idx));
     return NRC_OK;
 }
 
@@ -83,8 +81,6 @@ nrc_status launch_encode_dir(nrc_ctx* ctx, const float* dir, size_t n, float* fe
 {
     if (n == 0) return NRC_OK;
     unsigned blocks = (unsigned)((n + 255) / 256);
-    k_encode_dir<<<blocks, 256, 0, ctx->stream>>>(dir, n, feat);
-    ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(ctx, ctx->stream, K_ENCODE_DIR, k_encode_dir<<<blocks, 256, 0, ctx->stream>>>(dir, n, feat));
     return NRC_OK;
 }

@@ -436,9 +436,8 @@ __global__ void __launch_bounds__(256) k_transpose_weights(const float* __restri
 nrc_status launch_mlp_prepare(nrc_mlp* mlp)
 {
     if (!mlp->dirtyT) return NRC_OK;
-    k_transpose_weights<<<(5 * 4096 + 255) / 256, 256, 0, mlp->ctx->stream>>>(mlp->params, mlp->paramsT);
-    mlp->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(mlp->ctx, mlp->ctx->stream, K_TRANSPOSE_WEIGHTS,
+               k_transpose_weights<<<(5 * 4096 + 255) / 256, 256, 0, mlp->ctx->stream>>>(mlp->params, mlp->paramsT));
     mlp->dirtyT = false;
     return NRC_OK;
 }
@@ -459,9 +458,7 @@ nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
     size_t cap = (size_t)mlp->ctx->smCount * 4 * 4;   // 4 CTAs/SM resident, a few waves, grid-stride beyond
     unsigned blocks = (unsigned)(tiles < cap ? tiles : cap);
     MlpDev w{mlp->params, mlp->paramsT};
-    k_infer_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, countDev, n, w, make_mrhe_dev(m), rgb);
-    mlp->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(mlp->ctx, st, K_INFER_FP32, k_infer_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, countDev, n, w, make_mrhe_dev(m), rgb));
     return NRC_OK;
 }
 
@@ -486,11 +483,9 @@ nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
         mlp->partialBlocks = mlp->ctx->smCount;
     }
     MlpDev w{mlp->params, mlp->paramsT};
-    k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), mlp->partial, pred);
-    mlp->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
-    k_reduce_partials<<<(NRC_MLP_PARAM_COUNT + 1 + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad);
-    mlp->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(mlp->ctx, st, K_TRAIN_FP32,
+               k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), mlp->partial, pred));
+    NRC_LAUNCH(mlp->ctx, st, K_REDUCE_PARTIALS,
+               k_reduce_partials<<<(NRC_MLP_PARAM_COUNT + 1 + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad));
     return NRC_OK;
 }

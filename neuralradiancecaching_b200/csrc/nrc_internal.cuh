@@ -38,6 +38,16 @@ void nrc_set_error(const char* fmt, ...);
 #define NRC_W_OFF(l) ((l) * 4096)
 #define NRC_B_OFF(l) (20672 + (l) * 64)
 
+// ---- kernel ids: launch counting and per-kernel CUDA-event timing (nrc_ctx_profile_*) ---------------
+enum NrcKernelId {
+    K_ENCODE_POS = 0, K_ENCODE_DIR, K_INFER_FP32, K_TRAIN_FP32, K_REDUCE_PARTIALS, K_TRANSPOSE_WEIGHTS, K_NRC_STEP, K_MRHE_STEP,
+    K_INIT_NORMAL, K_RENDER_WALK, K_TRAIN_WALK, K_LIGHT_RENDER, K_LIGHT_TRAIN, K_RENDER_COMBINE, K_TRAIN_COMBINE, K_COMPOSITE,
+    K_BUILD_BRICKS, K_VOLUME_SAMPLE, K_PACK_RECORDS, K_CDF_ROWS, K_CDF_Y, K_INFER_TC, K_TRAIN_TC, K_PACK_BF16, K_MISC,
+    K_COUNT
+};
+
+struct NrcProfRec { int kid; cudaEvent_t a, b; };
+
 // ---- handles ---------------------------------------------------------------------------------------
 struct nrc_ctx {
     int device = 0;
@@ -47,6 +57,12 @@ struct nrc_ctx {
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
     nrc_mlp_precision precision = NRC_MLP_FP32;
     uint64_t launches = 0;
+    // per-kernel event timing (off by default; bench.py turns it on over its timed region)
+    bool profiling = false;
+    std::vector<NrcProfRec> profOpen;       // recorded, not yet read
+    std::vector<NrcProfRec> profFree;       // event pairs for reuse
+    double profMs[K_COUNT] = {0};
+    uint64_t profCount[K_COUNT] = {0};
     // pinned staging for [h] pointers
     void* pinned = nullptr;
     size_t pinnedBytes = 0;
@@ -131,6 +147,18 @@ struct MrheDev {
 MrheDev make_mrhe_dev(const nrc_mrhe* m);
 
 // ---- helpers implemented in capi.cu ---------------------------------------------------------------
+void nrc_prof_begin(nrc_ctx* ctx, cudaStream_t st, int kid);
+void nrc_prof_end(nrc_ctx* ctx, cudaStream_t st);
+// Every kernel launch of the library goes through this: counts it, brackets it with CUDA events on the launching
+// stream when profiling is on, and checks the launch.
+#define NRC_LAUNCH(ctx, st, kid, ...)            \
+    do {                                         \
+        nrc_prof_begin((ctx), (st), (kid));      \
+        __VA_ARGS__;                             \
+        nrc_prof_end((ctx), (st));               \
+        (ctx)->launches++;                       \
+        NRC_CUDA(cudaGetLastError());            \
+    } while (0)
 bool nrc_is_device_ptr(const void* p);
 nrc_status nrc_scratch(nrc_ctx* ctx, int slot, size_t bytes, void** out);
 // returns a device pointer holding the data of `p` (p itself when it already is one)

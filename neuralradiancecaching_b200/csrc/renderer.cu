@@ -15,7 +15,8 @@ struct nrc_renderer {
     nrc_mlp* mlp = nullptr;
     nrc_mrhe* mrhe = nullptr;
     uint32_t width = 0, height = 0, trainW = 0, trainH = 0;
-    uint32_t y0 = 0, y1 = 0, i0 = 0, i1 = 0;   // this rank's partition
+    uint32_t y0 = 0, y1 = 0, i0 = 0, i1 = 0;   // this rank's partition: rows y0, y0+ystride, ... < y1; invocations i0, i0+istride, ... < i1
+    uint32_t ystride = 1, istride = 1;
     nrc_camera cam;
     nrc_dir_light dirLight;
     nrc_point_light ptLight;
@@ -38,6 +39,7 @@ struct nrc_renderer {
     // device scalars: [0] render vertex count, [1] render overflow, [2] train vertex count, [3] train overflow, [4] query count
     uint32_t* scalars = nullptr;
     unsigned long long* taps = nullptr;   // [0] render taps, [1] train taps
+    unsigned long long* totals = nullptr; // [6] running totals (nrc_frame_totals)
     uint32_t* hostScalars = nullptr;      // pinned mirror
     unsigned long long* hostTaps = nullptr;
     bool framePending = false;            // evFork marks the end of the previous frame's composite
@@ -146,6 +148,8 @@ extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t
     memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
     NRC_CUDA(cudaMalloc(&r->scalars, 8 * sizeof(uint32_t)));
     NRC_CUDA(cudaMalloc(&r->taps, 2 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMalloc(&r->totals, 6 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMemsetAsync(r->totals, 0, 6 * sizeof(unsigned long long), ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 8 * sizeof(uint32_t), ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->taps, 0, 2 * sizeof(unsigned long long), ctx->stream));
     NRC_CUDA(cudaMallocHost(&r->hostScalars, 8 * sizeof(uint32_t)));
@@ -165,7 +169,7 @@ extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
     cudaStreamSynchronize(r->ctx->stream2);
     free_frame(r);
     free_train(r);
-    FREE(r->scalars); FREE(r->taps);
+    FREE(r->scalars); FREE(r->taps); FREE(r->totals);
     if (r->hostScalars) cudaFreeHost(r->hostScalars);
     if (r->hostTaps) cudaFreeHost(r->hostTaps);
     delete r;
@@ -199,8 +203,20 @@ extern "C" nrc_status nrc_renderer_set_partition(nrc_renderer* r, uint32_t y0, u
     NRC_REQUIRE(y0 <= y1 && y1 <= r->height, "row partition out of range");
     NRC_REQUIRE(i0 <= i1 && i1 <= r->trainW * r->trainH, "train partition out of range");
     r->y0 = y0; r->y1 = y1; r->i0 = i0; r->i1 = i1;
+    r->ystride = 1; r->istride = 1;
     return NRC_OK;
 }
+
+extern "C" nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32_t yFirst, uint32_t yStride, uint32_t iFirst, uint32_t iStride)
+{
+    NRC_REQUIRE(r, "null renderer");
+    NRC_REQUIRE(yStride >= 1 && iStride >= 1 && yFirst < yStride && iFirst < iStride, "bad strided partition");
+    r->y0 = yFirst; r->y1 = r->height; r->ystride = yStride;
+    r->i0 = iFirst; r->i1 = r->trainW * r->trainH; r->istride = iStride;
+    return NRC_OK;
+}
+
+static inline uint32_t part_count(uint32_t first, uint32_t end, uint32_t stride) { return first >= end ? 0u : (end - first + stride - 1) / stride; }
 
 extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t height)
 {
@@ -208,7 +224,7 @@ extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t heigh
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     r->width = width; r->height = height;
-    r->y0 = 0; r->y1 = height;
+    r->y0 = r->ystride > 1 ? r->y0 : 0; r->y1 = height;
     return alloc_frame(r, r->sppAlloc ? r->sppAlloc : 1, (uint32_t)((size_t)width * height * 4));
 }
 
@@ -261,14 +277,14 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     NRC_REQUIRE(r, "null renderer");
     nrc_ctx* ctx = r->ctx;
     cudaStream_t st = ctx->stream;
-    uint32_t n = r->i1 - r->i0;
+    uint32_t n = part_count(r->i0, r->i1, r->istride);
     if (n == 0) return NRC_OK;
     TraceParams P = make_params(r);
     NRC_CUDA(cudaMemsetAsync(r->scalars + 2, 0, 2 * sizeof(uint32_t), st));
     NRC_CUDA(cudaMemsetAsync(r->taps + 1, 0, sizeof(unsigned long long), st));
-    NRC_TRY(launch_train_walk(ctx, st, P, r->i0, r->i1, r->tpool, r->tp, r->trainCounters));
+    NRC_TRY(launch_train_walk(ctx, st, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
     NRC_TRY(launch_light(ctx, st, P, r->tpool, false, r->taps + 1));
-    NRC_TRY(launch_train_combine(ctx, st, n, r->tpool, r->tp));
+    NRC_TRY(launch_train_combine(ctx, st, n, r->tpool, r->tp, r->taps, r->totals));
     float lossScale = P.widthFactor * P.heightFactor;   // ONE_OVER_PIXEL_COUNT (nrc-train.comp:210)
     NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
     return NRC_OK;
@@ -280,7 +296,8 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
 {
     NRC_REQUIRE(r, "null renderer");
     nrc_ctx* ctx = r->ctx;
-    if (r->y1 == r->y0) return NRC_OK;
+    const uint32_t rows = part_count(r->y0, r->y1, r->ystride);
+    if (rows == 0) return NRC_OK;
     const nrc_volume_params& v = r->vol->params;
     const bool useNN = (v.useNN == 1u);
     uint32_t spp = (uint32_t)(useNN ? v.withNnSpp : v.noNnSpp);
@@ -302,14 +319,15 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
         NRC_CUDA(cudaMemsetAsync(r->scalars + 0, 0, 2 * sizeof(uint32_t), s2));
         NRC_CUDA(cudaMemsetAsync(r->scalars + 4, 0, sizeof(uint32_t), s2));
         NRC_CUDA(cudaMemsetAsync(r->taps + 0, 0, sizeof(unsigned long long), s2));
-        NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, r->y1, spp, r->rpool, r->rp, r->background, r->counters));
+        NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
         NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, r->taps + 0));
-        NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, r->y1, spp, r->rpool, r->rp, r->ql));
+        NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
         NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s2));
         NRC_CUDA(cudaEventRecord(ctx->evJoin, s2));
         NRC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->evJoin, 0));
         if (useNN && v.showNonNN == 0u) NRC_TRY(infer_queries(r, ctx->stream));
-        NRC_TRY(launch_composite(ctx, ctx->stream, P, r->y0, r->y1, spp, r->rp, r->ql, r->background, r->frame, r->frame8, r->queryProbe));
+        NRC_TRY(launch_composite(ctx, ctx->stream, P, r->y0, rows, r->ystride, spp, r->rp, r->ql, r->background, r->frame, r->frame8, r->queryProbe,
+                                 r->scalars, r->taps, r->totals));
         NRC_CUDA(cudaEventRecord(ctx->evFork, ctx->stream));
         r->framePending = true;
         // Overflow of the vertex pool is checked lazily: only a pool smaller than the worst case can overflow,
@@ -366,6 +384,27 @@ extern "C" nrc_status nrc_read_frame(nrc_renderer* r, void* dst, nrc_frame_forma
     return read_back(r->ctx, dst, nrc_frame_ptr(r, fmt), nrc_frame_bytes(r, fmt));
 }
 
+// This rank's rows only, compacted: dst[k][width] = frame row y0 + k*ystride.
+extern "C" nrc_status nrc_read_frame_partition(nrc_renderer* r, void* dst, nrc_frame_format fmt)
+{
+    NRC_REQUIRE(r && dst, "null argument");
+    NRC_REQUIRE(fmt == NRC_FRAME_RGBA32F || fmt == NRC_FRAME_BGRA8, "unknown frame format");
+    uint32_t rows = part_count(r->y0, r->y1, r->ystride);
+    if (rows == 0) return NRC_OK;
+    size_t rowBytes = (size_t)r->width * (fmt == NRC_FRAME_RGBA32F ? 16 : 4);
+    const char* src = (const char*)nrc_frame_ptr(r, fmt) + (size_t)r->y0 * rowBytes;
+    cudaMemcpyKind k = nrc_is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+    NRC_CUDA(cudaMemcpy2DAsync(dst, rowBytes, src, rowBytes * r->ystride, rowBytes, rows, k, r->ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
+    return NRC_OK;
+}
+
+extern "C" size_t nrc_frame_partition_bytes(nrc_renderer* r, nrc_frame_format fmt)
+{
+    if (!r) return 0;
+    return (size_t)part_count(r->y0, r->y1, r->ystride) * r->width * (fmt == NRC_FRAME_RGBA32F ? 16 : 4);
+}
+
 extern "C" nrc_status nrc_read_render_probes(nrc_renderer* r, uint32_t* counters, float* query)
 {
     NRC_REQUIRE(r, "null renderer");
@@ -391,18 +430,44 @@ __global__ void k_pack_records(const float* __restrict__ pos, const float* __res
 extern "C" nrc_status nrc_read_train_probes(nrc_renderer* r, float* records, uint32_t* trainCounters)
 {
     NRC_REQUIRE(r, "null renderer");
-    uint32_t n = r->i1 - r->i0;
+    uint32_t n = part_count(r->i0, r->i1, r->istride);
     if (n == 0) return NRC_OK;
     nrc_ctx* ctx = r->ctx;
+    if (r->istride > 1) {   // strided shard: scatter rows i0 + k*istride
+        cudaMemcpyKind k = nrc_is_device_ptr(records ? (void*)records : (void*)trainCounters) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+        if (records) {
+            void* tmp;
+            NRC_TRY(nrc_scratch(ctx, 5, (size_t)n * 9 * sizeof(float), &tmp));
+            NRC_LAUNCH(ctx, ctx->stream, K_PACK_RECORDS,
+                       k_pack_records<<<(n + 255) / 256, 256, 0, ctx->stream>>>(r->tp.pos, r->tp.dir, r->tp.target, n, (float*)tmp));
+            NRC_CUDA(cudaMemcpy2DAsync(records + (size_t)r->i0 * 9, 36 * (size_t)r->istride, tmp, 36, 36, n, k, ctx->stream));
+        }
+        if (trainCounters)
+            NRC_CUDA(cudaMemcpy2DAsync(trainCounters + (size_t)r->i0 * 4, 16 * (size_t)r->istride, r->trainCounters, 16, 16, n, k, ctx->stream));
+        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+        return NRC_OK;
+    }
     if (records) {
         void* tmp;
         NRC_TRY(nrc_scratch(ctx, 5, (size_t)n * 9 * sizeof(float), &tmp));
-        k_pack_records<<<(n + 255) / 256, 256, 0, ctx->stream>>>(r->tp.pos, r->tp.dir, r->tp.target, n, (float*)tmp);
-        ctx->launches++;
-        NRC_CUDA(cudaGetLastError());
+        NRC_LAUNCH(ctx, ctx->stream, K_PACK_RECORDS,
+                   k_pack_records<<<(n + 255) / 256, 256, 0, ctx->stream>>>(r->tp.pos, r->tp.dir, r->tp.target, n, (float*)tmp));
         NRC_TRY(read_back(ctx, records + (size_t)r->i0 * 9, tmp, (size_t)n * 9 * sizeof(float)));
     }
     if (trainCounters) NRC_TRY(read_back(ctx, trainCounters + (size_t)r->i0 * 4, r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_frame_totals(nrc_renderer* r, uint64_t totals[6], int reset)
+{
+    NRC_REQUIRE(r && totals, "null argument");
+    nrc_ctx* ctx = r->ctx;
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    unsigned long long t[6];
+    NRC_CUDA(cudaMemcpy(t, r->totals, sizeof(t), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 6; i++) totals[i] = t[i];
+    if (reset) NRC_CUDA(cudaMemset(r->totals, 0, sizeof(t)));
     return NRC_OK;
 }
 
@@ -415,7 +480,7 @@ extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, u
     NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     if (inferQueries) *inferQueries = r->hostScalars[4];
-    if (trainSamples) *trainSamples = r->i1 - r->i0;
+    if (trainSamples) *trainSamples = part_count(r->i0, r->i1, r->istride);
     // + one tap per walk step is not counted here: densityTaps are the light kernels' taps (the bulk)
     if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[0] + (uint64_t)r->hostTaps[1];
     return NRC_OK;

@@ -150,12 +150,9 @@ extern "C" nrc_status nrc_hdr4f_to_cdf(nrc_ctx* ctx, const float* rgba, uint32_t
     float* cdfX = (float*)tmp;
     float* pdfY = cdfX + px;
     float* cdfY = pdfY + height;
-    k_cdf_rows<<<(height + 63) / 64, 64, 0, ctx->stream>>>((const float4*)drgba, (int)width, (int)height, cdfX, (float*)dX, pdfY);
-    ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
-    k_cdf_y<<<1, 32, 0, ctx->stream>>>(pdfY, (int)height, cdfY, (float*)dY);
-    ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(ctx, ctx->stream, K_CDF_ROWS,
+               k_cdf_rows<<<(height + 63) / 64, 64, 0, ctx->stream>>>((const float4*)drgba, (int)width, (int)height, cdfX, (float*)dX, pdfY));
+    NRC_LAUNCH(ctx, ctx->stream, K_CDF_Y, k_cdf_y<<<1, 32, 0, ctx->stream>>>(pdfY, (int)height, cdfY, (float*)dY));
     NRC_TRY(nrc_stage_out_finish(ctx, invCdfX, dX, px * sizeof(float)));
     NRC_TRY(nrc_stage_out_finish(ctx, invCdfY, dY, height * sizeof(float)));
     return NRC_OK;

@@ -81,10 +81,9 @@ __global__ void __launch_bounds__(256) k_init_normal(float* __restrict__ dst, si
 
 nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st)
 {
-    k_nrc_step<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->paramsT, mlp->lr, mlp->wd,
-                                                                 mlp->beta1);
-    mlp->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(mlp->ctx, st, K_NRC_STEP,
+               k_nrc_step<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->paramsT, mlp->lr,
+                                                                            mlp->wd, mlp->beta1));
     return NRC_OK;
 }
 
@@ -95,9 +94,8 @@ nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
     size_t cap = (size_t)m->ctx->smCount * 8;
     unsigned blocks = (unsigned)(want < cap ? want : cap);
     if (blocks == 0) return NRC_OK;
-    k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables), reinterpret_cast<float4*>(m->delta), n4, m->lr, m->wd);
-    m->ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
+               k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables), reinterpret_cast<float4*>(m->delta), n4, m->lr, m->wd));
     return NRC_OK;
 }
 
@@ -107,8 +105,6 @@ nrc_status launch_init_normal(nrc_ctx* ctx, float* dst, size_t n, float scale, u
     size_t want = (n + 255) / 256;
     size_t cap = (size_t)ctx->smCount * 8;
     unsigned blocks = (unsigned)(want < cap ? want : cap);
-    k_init_normal<<<blocks, 256, 0, ctx->stream>>>(dst, n, scale, seed);
-    ctx->launches++;
-    NRC_CUDA(cudaGetLastError());
+    NRC_LAUNCH(ctx, ctx->stream, K_INIT_NORMAL, k_init_normal<<<blocks, 256, 0, ctx->stream>>>(dst, n, scale, seed));
     return NRC_OK;
 }

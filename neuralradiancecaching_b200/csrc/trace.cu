@@ -105,14 +105,13 @@ struct PoolEmitter {
 };
 
 // ---- render walk (nrc-forward.vert:28-40, nrc-forward.frag:757-870 minus lighting and Forward()) ------------------
-__global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t y1, uint32_t spp,
-                                                     VertexPool pool, RenderPaths paths, float4* __restrict__ background,
+__global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
+                                                     uint32_t spp, VertexPool pool, RenderPaths paths, float4* __restrict__ background,
                                                      uint32_t* __restrict__ counters)
 {
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t rows = y1 - y0;
     if (local >= rows * P.width) return;
-    uint32_t px = local % P.width, py = y0 + local / P.width;
+    uint32_t px = local % P.width, py = y0 + (local / P.width) * ystride;
     size_t pix = (size_t)py * P.width + px;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
@@ -149,18 +148,18 @@ __global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ Tra
 }
 
 // ---- train walk (nrc-train.comp:1122-1259 minus lighting and Backprop) ------------------------------------------------
-__global__ void __launch_bounds__(64) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t i1, VertexPool pool,
-                                                   TrainPaths paths, uint32_t* __restrict__ counters)
+__global__ void __launch_bounds__(64) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
+                                                   VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
 {
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-    if (local >= i1 - i0) return;
+    if (local >= n) return;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
     const WalkParams W = make_walk(P);
     Rng rng;
     WalkCounters wc = {0u, 0u, 0u, 0u};
     f3 cur, dir;
-    train_pick_vertex(W, box, grid, i0 + local, rng, wc, cur, dir);
+    train_pick_vertex(W, box, grid, i0 + local * istride, rng, wc, cur, dir);
     paths.pos[3 * (size_t)local] = cur.x; paths.pos[3 * (size_t)local + 1] = cur.y; paths.pos[3 * (size_t)local + 2] = cur.z;
     paths.dir[3 * (size_t)local] = dir.x; paths.dir[3 * (size_t)local + 1] = dir.y; paths.dir[3 * (size_t)local + 2] = dir.z;
     PoolEmitter em;
@@ -319,12 +318,13 @@ __device__ __forceinline__ void fold_path(const VertexPool& pool, int head, f3& 
     }
 }
 
-__global__ void __launch_bounds__(128) k_render_combine(uint32_t width, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
-                                                        RenderPaths paths, QueryList q)
+__global__ void __launch_bounds__(128) k_render_combine(uint32_t width, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                                                        VertexPool pool, RenderPaths paths, QueryList q)
 {
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-    if (local >= (y1 - y0) * width * spp) return;
-    size_t path = (size_t)y0 * width * spp + local;
+    if (local >= rows * width * spp) return;
+    uint32_t rowLen = width * spp;
+    size_t path = (size_t)(y0 + (local / rowLen) * ystride) * rowLen + (local % rowLen);
     f3 L; float T;
     fold_path(pool, paths.head[path], L, T);
     paths.result[path] = make_float4(L.x, L.y, L.z, T);
@@ -345,10 +345,16 @@ __global__ void __launch_bounds__(128) k_render_combine(uint32_t width, uint32_t
     paths.qslot[path] = slot;
 }
 
-__global__ void __launch_bounds__(128) k_train_combine(uint32_t nLocal, VertexPool pool, TrainPaths paths)
+__global__ void __launch_bounds__(128) k_train_combine(uint32_t nLocal, VertexPool pool, TrainPaths paths,
+                                                       const unsigned long long* __restrict__ taps, unsigned long long* __restrict__ totals)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nLocal) return;
+    if (i == 0 && totals) {   // running totals of this rank (nrc_frame_totals)
+        totals[1] += nLocal;
+        totals[3] += taps[1];
+        totals[5] += min(*pool.count, pool.cap);
+    }
     f3 sum = mk3(0.0f, 0.0f, 0.0f);
     for (int p = 0; p < 8; p++) {
         f3 L; float T;
@@ -361,13 +367,21 @@ __global__ void __launch_bounds__(128) k_train_combine(uint32_t nLocal, VertexPo
 }
 
 // fwd.frag:824-870: average the spp paths, add the NRC radiance, env-map colour for misses and T == 1 (A20).
-__global__ void __launch_bounds__(128) k_composite(uint32_t width, uint32_t y0, uint32_t y1, uint32_t spp, RenderPaths paths, QueryList q,
+__global__ void __launch_bounds__(128) k_composite(uint32_t width, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                                                   RenderPaths paths, QueryList q,
                                                    const float4* __restrict__ background, float4* __restrict__ frame,
-                                                   uint32_t* __restrict__ frame8, float* __restrict__ queryProbe)
+                                                   uint32_t* __restrict__ frame8, float* __restrict__ queryProbe,
+                                                   const uint32_t* __restrict__ scalars, const unsigned long long* __restrict__ taps,
+                                                   unsigned long long* __restrict__ totals)
 {
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-    if (local >= (y1 - y0) * width) return;
-    size_t pix = (size_t)y0 * width + local;
+    if (local >= rows * width) return;
+    if (local == 0 && totals) {   // running totals of this rank (nrc_frame_totals)
+        totals[0] += min(*q.count, q.cap);
+        totals[2] += taps[0];
+        totals[4] += scalars[0];
+    }
+    size_t pix = (size_t)(y0 + (local / width) * ystride) * width + (local % width);
     float4 bg = background[pix];
     float4 outc;
     if (bg.w != 0.0f) {
@@ -434,17 +448,12 @@ __global__ void __launch_bounds__(256) k_volume_sample(Grid g, const float* __re
 }
 
 // ---- launchers -----------------------------------------------------------------------------------------------------------
-#define LAUNCH_CHECK(ctx)            \
-    do {                             \
-        (ctx)->launches++;           \
-        NRC_CUDA(cudaGetLastError()); \
-    } while (0)
-
 nrc_status launch_build_bricks(nrc_volume* vol, const float* densityDev)
 {
     size_t cells = (size_t)(vol->nx + 1) * (vol->ny + 1) * (vol->nz + 1);
-    k_build_bricks<<<(unsigned)((cells + 255) / 256), 256, 0, vol->ctx->stream>>>(densityDev, (int)vol->nx, (int)vol->ny, (int)vol->nz, vol->bricks);
-    LAUNCH_CHECK(vol->ctx);
+    cudaStream_t st = vol->ctx->stream;
+    NRC_LAUNCH(vol->ctx, st, K_BUILD_BRICKS,
+               k_build_bricks<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(densityDev, (int)vol->nx, (int)vol->ny, (int)vol->nz, vol->bricks));
     return NRC_OK;
 }
 
@@ -456,28 +465,26 @@ nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, flo
     g.bricks = vol->bricks;
     g.skySize = mk3(62.5f, 42.5f, 76.5f);
     g.densityFactor = vol->params.densityFactor;
-    k_volume_sample<<<(unsigned)((n + 255) / 256), 256, 0, vol->ctx->stream>>>(g, pos, n, out);
-    LAUNCH_CHECK(vol->ctx);
+    cudaStream_t st = vol->ctx->stream;
+    NRC_LAUNCH(vol->ctx, st, K_VOLUME_SAMPLE, k_volume_sample<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g, pos, n, out));
     return NRC_OK;
 }
 
-nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
-                              RenderPaths paths, float4* background, uint32_t* counters)
+nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                              VertexPool pool, RenderPaths paths, float4* background, uint32_t* counters)
 {
-    uint32_t n = (y1 - y0) * P.width;
+    uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
-    k_render_walk<<<(n + 127) / 128, 128, 0, st>>>(P, y0, y1, spp, pool, paths, background, counters);
-    LAUNCH_CHECK(ctx);
+    NRC_LAUNCH(ctx, st, K_RENDER_WALK,
+               k_render_walk<<<(n + 127) / 128, 128, 0, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters));
     return NRC_OK;
 }
 
-nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t i0, uint32_t i1, VertexPool pool, TrainPaths paths,
-                             uint32_t* counters)
+nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t i0, uint32_t n, uint32_t istride, VertexPool pool,
+                             TrainPaths paths, uint32_t* counters)
 {
-    uint32_t n = i1 - i0;
     if (n == 0) return NRC_OK;
-    k_train_walk<<<(n + 63) / 64, 64, 0, st>>>(P, i0, i1, pool, paths, counters);
-    LAUNCH_CHECK(ctx);
+    NRC_LAUNCH(ctx, st, K_TRAIN_WALK, k_train_walk<<<(n + 63) / 64, 64, 0, st>>>(P, i0, n, istride, pool, paths, counters));
     return NRC_OK;
 }
 
@@ -488,36 +495,38 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
     unsigned cap = (unsigned)ctx->smCount * 16;
     unsigned blocks = want < cap ? want : cap;
     if (blocks == 0) return NRC_OK;
-    if (render) k_light<true><<<blocks, 128, 0, st>>>(P, pool, tapCounter);
-    else k_light<false><<<blocks, 128, 0, st>>>(P, pool, tapCounter);
-    LAUNCH_CHECK(ctx);
+    if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, k_light<true><<<blocks, 128, 0, st>>>(P, pool, tapCounter));
+    else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, k_light<false><<<blocks, 128, 0, st>>>(P, pool, tapCounter));
     return NRC_OK;
 }
 
-nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
-                                 RenderPaths paths, QueryList q)
+nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                                 VertexPool pool, RenderPaths paths, QueryList q)
 {
-    uint32_t n = (y1 - y0) * P.width * spp;
+    uint32_t n = rows * P.width * spp;
     if (n == 0) return NRC_OK;
-    k_render_combine<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, y1, spp, pool, paths, q);
-    LAUNCH_CHECK(ctx);
+    NRC_LAUNCH(ctx, st, K_RENDER_COMBINE,
+               k_render_combine<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, rows, ystride, spp, pool, paths, q));
     return NRC_OK;
 }
 
-nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, VertexPool pool, TrainPaths paths)
+nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, VertexPool pool, TrainPaths paths,
+                                const unsigned long long* taps, unsigned long long* totals)
 {
     if (nLocal == 0) return NRC_OK;
-    k_train_combine<<<(nLocal + 127) / 128, 128, 0, st>>>(nLocal, pool, paths);
-    LAUNCH_CHECK(ctx);
+    NRC_LAUNCH(ctx, st, K_TRAIN_COMBINE, k_train_combine<<<(nLocal + 127) / 128, 128, 0, st>>>(nLocal, pool, paths, taps, totals));
     return NRC_OK;
 }
 
-nrc_status launch_composite(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, RenderPaths paths,
-                            QueryList q, const float4* background, float4* frame, uint32_t* frame8, float* queryProbe)
+nrc_status launch_composite(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                            RenderPaths paths,
+                            QueryList q, const float4* background, float4* frame, uint32_t* frame8, float* queryProbe,
+                            const uint32_t* scalars, const unsigned long long* taps, unsigned long long* totals)
 {
-    uint32_t n = (y1 - y0) * P.width;
+    uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
-    k_composite<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, y1, spp, paths, q, background, frame, frame8, queryProbe);
-    LAUNCH_CHECK(ctx);
+    NRC_LAUNCH(ctx, st, K_COMPOSITE,
+               k_composite<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, rows, ystride, spp, paths, q, background, frame, frame8, queryProbe, scalars,
+                                                            taps, totals));
     return NRC_OK;
 }

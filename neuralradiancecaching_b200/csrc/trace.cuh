@@ -53,15 +53,18 @@ struct TrainPaths {
 };
 
 // counters[.][4] = randDraws, litVertices, walkSteps, queryEmitted
-nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
-                              RenderPaths paths, float4* background, uint32_t* counters);
-nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t i0, uint32_t i1, VertexPool pool, TrainPaths paths,
-                             uint32_t* counters);
+// rows y0 + k*ystride (k < rows) of the frame; train invocations i0 + k*istride (k < n)
+nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                              VertexPool pool, RenderPaths paths, float4* background, uint32_t* counters);
+nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t i0, uint32_t n, uint32_t istride, VertexPool pool,
+                             TrainPaths paths, uint32_t* counters);
 nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, VertexPool pool, bool render, unsigned long long* tapCounter);
-nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, VertexPool pool,
-                                 RenderPaths paths, QueryList q);
-nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, VertexPool pool, TrainPaths paths);
-nrc_status launch_composite(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t y1, uint32_t spp, RenderPaths paths,
-                            QueryList q, const float4* background, float4* frame, uint32_t* frame8, float* queryProbe);
+nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                                 VertexPool pool, RenderPaths paths, QueryList q);
+nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, VertexPool pool, TrainPaths paths,
+                                const unsigned long long* taps, unsigned long long* totals);
+nrc_status launch_composite(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
+                            RenderPaths paths, QueryList q, const float4* background, float4* frame, uint32_t* frame8, float* queryProbe,
+                            const uint32_t* scalars, const unsigned long long* taps, unsigned long long* totals);
 nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, float* out);
 nrc_status launch_build_bricks(nrc_volume* vol, const float* densityDev);

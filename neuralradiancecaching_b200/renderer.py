@@ -47,6 +47,18 @@ class NrcHpmRenderer:
     def SetPartition(self, y0, y1, i0, i1):
         L.check(L.lib().nrc_renderer_set_partition(self.h, C.c_uint32(y0), C.c_uint32(y1), C.c_uint32(i0), C.c_uint32(i1)))
 
+    def SetPartitionStrided(self, y_first, y_stride, i_first, i_stride):
+        L.check(L.lib().nrc_renderer_set_partition_strided(self.h, C.c_uint32(y_first), C.c_uint32(y_stride), C.c_uint32(i_first),
+                                                           C.c_uint32(i_stride)))
+
+    def partition_bytes(self, fmt=L.FRAME_BGRA8):
+        return int(L.lib().nrc_frame_partition_bytes(self.h, C.c_int(fmt)))
+
+    def read_frame_partition(self, out, fmt=L.FRAME_BGRA8):
+        """This rank's rows only, compacted into `out` (partition_bytes() bytes)."""
+        L.check(L.lib().nrc_read_frame_partition(self.h, _ptr(out), C.c_int(fmt)))
+        return out
+
     def ResizeFrame(self, width, height):
         L.check(L.lib().nrc_resize(self.h, C.c_uint32(width), C.c_uint32(height)))
         self.width, self.height = width, height
@@ -82,6 +94,12 @@ class NrcHpmRenderer:
         a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
         L.check(L.lib().nrc_frame_stats(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return {"infer_queries": a.value, "train_samples": b.value, "density_taps": c.value}
+
+    def totals(self, reset=False):
+        t = (C.c_uint64 * 6)()
+        L.check(L.lib().nrc_frame_totals(self.h, t, C.c_int(1 if reset else 0)))
+        keys = ("infer_queries", "train_samples", "render_taps", "train_taps", "render_vertices", "train_vertices")
+        return dict(zip(keys, (int(x) for x in t)))
 
     def Destroy(self):
         if self.h:

@@ -128,6 +128,16 @@ def test_whole_frames_parity_and_partition(N, ctx):
     r.SetPartition(H // 2, H, tw * th // 2, tw * th); r.FrameRender(); ctx.sync()
     bottom = r.read_frame()[H // 2:].copy()
     np.testing.assert_array_equal(np.concatenate([top, bottom]).view(np.uint32), full.view(np.uint32))
+    # interleaved (strided) partition: rank k of 3 renders rows k, k+3, ...; compacted read-back, union == full frame
+    union = np.zeros_like(full)
+    for k in range(3):
+        r.SetPartitionStrided(k, 3, k, 3); r.FrameRender(); ctx.sync()
+        nrows = len(range(k, H, 3))
+        assert r.partition_bytes(N._lib.FRAME_RGBA32F) == nrows * W * 16
+        part = np.zeros((nrows, W, 4), np.float32)
+        r.read_frame_partition(part, N._lib.FRAME_RGBA32F)
+        union[k::3] = part
+    np.testing.assert_array_equal(union.view(np.uint32), full.view(np.uint32))
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
 
 
@@ -144,4 +154,31 @@ def test_resize_and_spp(N, ctx):
     r.FrameRender(); ctx.sync()
     assert r.GetImageDataSize() == 48 * 40 * 4
     assert Cm.psnr(r.read_frame(), orgba) >= PSNR_MIN
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+
+
+def test_train_shards_sum_to_whole(N, ctx):
+    """Data-parallel training: the gradients of 2 strided shards add up to the single-GPU gradients (fp32 reassociation
+    tolerance), and the shards' records interleave to the whole record list bit for bit."""
+    tw, th = 16, 10
+    cfg = Cm.scene_cfg()
+    r, nrc, m, vol = build(N, ctx, cfg, 32, 32, tw, th)
+    r.FrameTrain(); ctx.sync()
+    rec_full, cnt_full = r.read_train_probes()
+    g_full = nrc.get_params()[1].copy()
+    t_full = m.get_tables()[1][:2 * 16384].copy()
+    loss_full = nrc.GetStats().mseLoss
+    g_sum, t_sum, loss_sum = np.zeros_like(g_full), np.zeros_like(t_full), 0.0
+    rec = np.zeros_like(rec_full); cnt = np.zeros_like(cnt_full)
+    for k in range(2):
+        nrc.set_state(delta=np.zeros(20995, np.float32)); m.set_tables(delta=np.zeros(m.count, np.float32)); nrc.ResetStats()
+        r.SetPartitionStrided(0, 1, k, 2); r.FrameTrain(); ctx.sync()
+        rk, ck = r.read_train_probes()
+        rec[k::2], cnt[k::2] = rk[k::2], ck[k::2]
+        g_sum += nrc.get_params()[1]; t_sum += m.get_tables()[1][:2 * 16384]; loss_sum += nrc.GetStats().mseLoss
+    np.testing.assert_array_equal(rec.view(np.uint32), rec_full.view(np.uint32))
+    np.testing.assert_array_equal(cnt, cnt_full)
+    assert _relmax(g_sum, g_full) < 1e-5
+    assert _relmax(t_sum, t_full) < 1e-5
+    assert abs(loss_sum - loss_full) <= 1e-5 * abs(loss_full) + 1e-12
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
