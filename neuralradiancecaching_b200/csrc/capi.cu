@@ -273,6 +273,7 @@ extern "C" nrc_status nrc_mlp_set_params(nrc_mlp* m, const float* params)
     NRC_REQUIRE(m && params, "null argument");
     NRC_TRY(copy_in(m->ctx, m->params, params, NRC_MLP_PARAM_COUNT * sizeof(float)));
     m->dirtyT = true;
+    m->dirtyBf16 = true;
     return NRC_OK;
 }
 

@@ -81,7 +81,8 @@ struct nrc_mlp {
     float* partial = nullptr;    // per-block partial gradients of the train kernel [maxBlocks][NRC_PARTIAL_STRIDE]
     int partialBlocks = 0;
     uint16_t* paramsBf16 = nullptr;  // bf16 operand images for the tcgen05 path (built on demand)
-    bool dirtyT = true;          // paramsT / paramsBf16 need a rebuild after params changed
+    bool dirtyT = true;          // paramsT needs a rebuild after params changed
+    bool dirtyBf16 = true;       // paramsBf16 needs a rebuild
 };
 
 #define NRC_PARTIAL_STRIDE 21000   // 20995 grads + loss + pad

@@ -6,6 +6,7 @@
 //   join    : batched inference over the compacted queries -> composite
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include "trace.cuh"
 
 struct nrc_renderer {
@@ -312,7 +313,9 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
     }
     TraceParams P = make_params(r);
     for (int attempt = 0; attempt < 2; attempt++) {
-        cudaStream_t s2 = ctx->stream2;
+        static int noOverlap = -1;
+        if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
+        cudaStream_t s2 = noOverlap ? ctx->stream : ctx->stream2;
         // the previous frame's composite (main stream) still reads the buffers this walk overwrites
         if (r->framePending) NRC_CUDA(cudaStreamWaitEvent(s2, ctx->evFork, 0));
         // order stream2 after the allocations/memsets above, not after the training work

@@ -5,6 +5,7 @@
 // mrhe-step.comp:27-74   : g' = (bad(g) ? 100*sign(g) : g) - wd*w ; w += lr*g' ; bad(w) -> 0 ; delta = 0.
 //                          16 B/param streamed with 128-bit accesses; HBM-bound at T = 2^22 (2 GiB / step).
 // Both are pure streaming kernels: grid sized in multiples of the SM count, float4 accesses, no reuse.
+#include <cuda_bf16.h>
 #include "nrc_internal.cuh"
 
 __device__ __forceinline__ bool bad_value(float x) { return (x != x) || (fabsf(x) == INFINITY) || (fabsf(x) > 1000.0f); }
@@ -13,7 +14,8 @@ __device__ __forceinline__ float sign_nan0(float x) { return (x > 0.0f) ? 1.0f :
 // Also refreshes the transposed weight image Wt[l][in][out] used by the forward GEMMs and clears mseLoss? No:
 // mseLoss (grad[20995]) is reset by ResetStats, as in the reference (src/main.cpp:215).
 __global__ void __launch_bounds__(256) k_nrc_step(float* __restrict__ params, float* __restrict__ grad, float* __restrict__ momentum,
-                                                  float* __restrict__ paramsT, float lr, float wd, float beta1)
+                                                  float* __restrict__ paramsT, unsigned short* __restrict__ imgBf16, float lr, float wd,
+                                                  float beta1)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= NRC_MLP_PARAM_COUNT) return;
@@ -30,6 +32,11 @@ __global__ void __launch_bounds__(256) k_nrc_step(float* __restrict__ params, fl
     if (i < 5 * 4096) {
         int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
         paramsT[l * 4096 + k * 64 + o] = nw;
+    }
+    if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {   // operand image of the tcgen05 path (layout: mlp_tc.cu)
+        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+        int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
+        imgBf16[dst] = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
     }
 }
 
@@ -82,8 +89,8 @@ __global__ void __launch_bounds__(256) k_init_normal(float* __restrict__ dst, si
 nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st)
 {
     NRC_LAUNCH(mlp->ctx, st, K_NRC_STEP,
-               k_nrc_step<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->paramsT, mlp->lr,
-                                                                            mlp->wd, mlp->beta1));
+               k_nrc_step<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->paramsT,
+                                                                            mlp->paramsBf16, mlp->lr, mlp->wd, mlp->beta1));
     return NRC_OK;
 }
 

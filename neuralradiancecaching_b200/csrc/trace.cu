@@ -4,6 +4,7 @@
 // math: their results are radiance values only.
 #include "trace.cuh"
 #include "walk.cuh"
+#include <stdlib.h>
 
 // ---- small device helpers ---------------------------------------------------------------------------------------
 
@@ -148,10 +149,17 @@ __global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ Tra
 }
 
 // ---- train walk (nrc-train.comp:1122-1259 minus lighting and Backprop) ------------------------------------------------
-__global__ void __launch_bounds__(64) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
-                                                   VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
+#define TRAIN_WARPS 4u   // warps per block
+__global__ void __launch_bounds__(32 * TRAIN_WARPS) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
+                                                   uint32_t lanes, VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
 {
-    uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    // Thin warps: a training sample is one long serial chain (1 + 8 walks of 64 steps, RNG chained through all of
+    // them) and a frame has only ~10^4 of them, so the kernel is latency-bound with most schedulers idle.  Only
+    // TRAIN_LANES lanes of each warp carry a sample: a warp waits for the slowest of 4 sphere traces instead of 32,
+    // and the 8x more warps interleave on the otherwise idle schedulers.
+    const uint32_t lane = threadIdx.x & 31u;
+    if (lane >= lanes) return;
+    uint32_t local = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * lanes + lane;
     if (local >= n) return;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
@@ -345,25 +353,35 @@ __global__ void __launch_bounds__(128) k_render_combine(uint32_t width, uint32_t
     paths.qslot[path] = slot;
 }
 
+// One thread per (sample, path): the 8 folds of a sample run in 8 adjacent lanes (each is a pointer chase through the
+// vertex chain, latency-bound), then lane 0 of the group adds them up in path order like the reference's loop
+// (nrc-train.comp:1217-1223).
 __global__ void __launch_bounds__(128) k_train_combine(uint32_t nLocal, VertexPool pool, TrainPaths paths,
                                                        const unsigned long long* __restrict__ taps, unsigned long long* __restrict__ totals)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nLocal) return;
-    if (i == 0 && totals) {   // running totals of this rank (nrc_frame_totals)
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i = t >> 3, p = t & 7u;
+    if (t == 0 && totals) {   // running totals of this rank (nrc_frame_totals)
         totals[1] += nLocal;
         totals[3] += taps[1];
         totals[5] += min(*pool.count, pool.cap);
     }
+    f3 L = mk3(0.0f, 0.0f, 0.0f);
+    float T = 1.0f;
+    if (i < nLocal) fold_path(pool, paths.head[(size_t)i * 8 + p], L, T);
     f3 sum = mk3(0.0f, 0.0f, 0.0f);
-    for (int p = 0; p < 8; p++) {
-        f3 L; float T;
-        fold_path(pool, paths.head[(size_t)i * 8 + p], L, T);
-        sum.x += L.x; sum.y += L.y; sum.z += L.z;
+    const unsigned base = (threadIdx.x & 31u) & ~7u;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        sum.x += __shfl_sync(0xffffffffu, L.x, base + k);
+        sum.y += __shfl_sync(0xffffffffu, L.y, base + k);
+        sum.z += __shfl_sync(0xffffffffu, L.z, base + k);
     }
-    paths.target[3 * (size_t)i] = sum.x / 8.0f;
-    paths.target[3 * (size_t)i + 1] = sum.y / 8.0f;
-    paths.target[3 * (size_t)i + 2] = sum.z / 8.0f;
+    if (i < nLocal && p == 0) {
+        paths.target[3 * (size_t)i] = sum.x / 8.0f;
+        paths.target[3 * (size_t)i + 1] = sum.y / 8.0f;
+        paths.target[3 * (size_t)i + 2] = sum.z / 8.0f;
+    }
 }
 
 // fwd.frag:824-870: average the spp paths, add the NRC radiance, env-map colour for misses and T == 1 (A20).
@@ -484,7 +502,15 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
                              TrainPaths paths, uint32_t* counters)
 {
     if (n == 0) return NRC_OK;
-    NRC_LAUNCH(ctx, st, K_TRAIN_WALK, k_train_walk<<<(n + 63) / 64, 64, 0, st>>>(P, i0, n, istride, pool, paths, counters));
+    static int lanesEnv = -1;
+    if (lanesEnv < 0) {
+        const char* e = getenv("NRC_TRAIN_LANES");
+        lanesEnv = e ? atoi(e) : 4;
+        if (lanesEnv < 1 || lanesEnv > 32) lanesEnv = 4;
+    }
+    const uint32_t lanes = (uint32_t)lanesEnv, perBlock = lanes * TRAIN_WARPS;
+    NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
+               k_train_walk<<<(n + perBlock - 1) / perBlock, 32 * TRAIN_WARPS, 0, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
     return NRC_OK;
 }
 
@@ -514,7 +540,7 @@ nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, 
                                 const unsigned long long* taps, unsigned long long* totals)
 {
     if (nLocal == 0) return NRC_OK;
-    NRC_LAUNCH(ctx, st, K_TRAIN_COMBINE, k_train_combine<<<(nLocal + 127) / 128, 128, 0, st>>>(nLocal, pool, paths, taps, totals));
+    NRC_LAUNCH(ctx, st, K_TRAIN_COMBINE, k_train_combine<<<(nLocal * 8 + 127) / 128, 128, 0, st>>>(nLocal, pool, paths, taps, totals));
     return NRC_OK;
 }
 
