@@ -181,14 +181,20 @@ __global__ void __launch_bounds__(32 * TRAIN_WARPS) k_train_walk(const __grid_co
 }
 
 // ---- light kernel: every density tap of the frame happens here -----------------------------------------------------
-// Fast tap: u = p * (n/skySize) + (0.5*n - 0.5) folded into one FMA per axis, one 8-byte brick load, PRMT-style
-// byte->float conversion, 7 lerps.  Values only (never steers control flow).
+// A tap is ~45 instructions: the segment is stepped in TEXEL space (u_i = u0 + i*du: one FFMA per axis), floor by
+// FRND, the integer cell index read off the mantissa of (floor + 1.5*2^23) so that no F2I/I2F is needed, one 8-byte
+// brick load, byte -> float by PRMT into the mantissa of 2^23 (the x-lerp differences are taken on the biased values,
+// which is exact), 7 lerps.  The in-volume test is done once per SEGMENT: the region where the filter footprint
+// exists (u in (-1, n) per axis) is convex, so a segment whose end points are inside never leaves it.  Values only
+// (never steers control flow).
 struct TapCtx {
-    float sx, sy, sz, ox, oy, oz;   // scale/offset per axis
+    float sx, sy, sz, ox, oy, oz;   // texel coordinate = world * s + o  (= uvw * n - 0.5)
     float nx, ny, nz;
-    int strideY, strideZ;
+    int strideY, strideZ, bias;     // cell = iz*strideZ + iy*strideY + ix + bias on the magic-biased integers
     const uint2* bricks;
 };
+
+#define TAP_MAGIC 12582912.0f   // 1.5 * 2^23: float bits of (k + TAP_MAGIC) = 0x4B400000 + k for integer |k| < 2^22
 
 __device__ __forceinline__ TapCtx make_tap(const TraceParams& P)
 {
@@ -197,31 +203,27 @@ __device__ __forceinline__ TapCtx make_tap(const TraceParams& P)
     t.ox = 0.5f * (float)P.nx - 0.5f; t.oy = 0.5f * (float)P.ny - 0.5f; t.oz = 0.5f * (float)P.nz - 0.5f;
     t.nx = (float)P.nx; t.ny = (float)P.ny; t.nz = (float)P.nz;
     t.strideY = P.nx + 1; t.strideZ = (P.nx + 1) * (P.ny + 1);
+    // brick cell of texel-floor (i,j,k) is (i+1, j+1, k+1); the three indices arrive biased by 0x4B400000 each
+    t.bias = (int)((1u + (unsigned)t.strideY + (unsigned)t.strideZ) * (1u - 0x4B400000u));
     t.bricks = P.bricks;
     return t;
 }
 
-__device__ __forceinline__ float byte_to_float(uint32_t w, int sel)
+// texel sum (0..255 scale) at texel-space position (u, v, s); the caller guarantees -1 < u < nx etc.
+__device__ __forceinline__ float tap_texel(const TapCtx& t, float u, float v, float s)
 {
-    // place byte `sel` of w into the low mantissa bits of 2^23, subtract 2^23
-    uint32_t v = __byte_perm(w, 0x4B000000u, 0x7650 + sel);
-    return __uint_as_float(v) - 8388608.0f;
-}
-
-// texel sum (0..255 scale) at world position p
-__device__ __forceinline__ float tap_raw(const TapCtx& t, float px, float py, float pz)
-{
-    float u = fmaf(px, t.sx, t.ox), v = fmaf(py, t.sy, t.oy), s = fmaf(pz, t.sz, t.oz);
-    bool in = (u >= -1.0f) & (u < t.nx) & (v >= -1.0f) & (v < t.ny) & (s >= -1.0f) & (s < t.nz);
-    if (!in) return 0.0f;
     float fu = floorf(u), fv = floorf(v), fs = floorf(s);
     float a = u - fu, b = v - fv, c = s - fs;
-    int cell = ((int)fs + 1) * t.strideZ + ((int)fv + 1) * t.strideY + ((int)fu + 1);
+    int ix = __float_as_int(fu + TAP_MAGIC), iy = __float_as_int(fv + TAP_MAGIC), iz = __float_as_int(fs + TAP_MAGIC);
+    int cell = iz * t.strideZ + iy * t.strideY + ix + t.bias;
     uint2 q = __ldg(t.bricks + cell);
-    float t000 = byte_to_float(q.x, 0), t100 = byte_to_float(q.x, 1), t010 = byte_to_float(q.x, 2), t110 = byte_to_float(q.x, 3);
-    float t001 = byte_to_float(q.y, 0), t101 = byte_to_float(q.y, 1), t011 = byte_to_float(q.y, 2), t111 = byte_to_float(q.y, 3);
-    float x00 = fmaf(a, t100 - t000, t000), x10 = fmaf(a, t110 - t010, t010);
-    float x01 = fmaf(a, t101 - t001, t001), x11 = fmaf(a, t111 - t011, t011);
+    // byte k of the word -> float bits 0x4B0000kk = 2^23 + k
+    float b000 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7650)), b100 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7651));
+    float b010 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7652)), b110 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7653));
+    float b001 = __uint_as_float(__byte_perm(q.y, 0x4B000000u, 0x7650)), b101 = __uint_as_float(__byte_perm(q.y, 0x4B000000u, 0x7651));
+    float b011 = __uint_as_float(__byte_perm(q.y, 0x4B000000u, 0x7652)), b111 = __uint_as_float(__byte_perm(q.y, 0x4B000000u, 0x7653));
+    float x00 = fmaf(a, b100 - b000, b000 - 8388608.0f), x10 = fmaf(a, b110 - b010, b010 - 8388608.0f);
+    float x01 = fmaf(a, b101 - b001, b001 - 8388608.0f), x11 = fmaf(a, b111 - b011, b011 - 8388608.0f);
     float y0 = fmaf(b, x10 - x00, x00), y1 = fmaf(b, x11 - x01, x01);
     return fmaf(c, y1 - y0, y0);
 }
@@ -238,13 +240,32 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
     float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
     float stepSize = sqrtf(dx * dx + dy * dy + dz * dz) / (float)COUNT;
     if (stepSize == 0.0f) return 1.0f;
+    const float u0 = fmaf(a.x, t.sx, t.ox), v0 = fmaf(a.y, t.sy, t.oy), s0 = fmaf(a.z, t.sz, t.oz);
+    const float u1 = fmaf(b.x, t.sx, t.ox), v1 = fmaf(b.y, t.sy, t.oy), s1 = fmaf(b.z, t.sz, t.oz);
+    const float du = (u1 - u0) * (1.0f / (float)COUNT), dv = (v1 - v0) * (1.0f / (float)COUNT), ds = (s1 - s0) * (1.0f / (float)COUNT);
+    const bool inside = (fminf(u0, u1) > -1.0f) & (fmaxf(u0, u1) < t.nx) & (fminf(v0, v1) > -1.0f) & (fmaxf(v0, v1) < t.ny) &
+                        (fminf(s0, s1) > -1.0f) & (fmaxf(s0, s1) < t.nz);
     float sum = 0.0f, dmax = 0.0f;
-#pragma unroll 4
-    for (int i = 0; i < COUNT; i++) {
-        float f = (float)i * (1.0f / (float)COUNT);
-        float d = tap_raw(t, fmaf(f, dx, a.x), fmaf(f, dy, a.y), fmaf(f, dz, a.z));
-        sum += d;
-        dmax = fmaxf(dmax, d);
+    if (inside) {
+        float fi = 0.0f;
+#pragma unroll 8
+        for (int i = 0; i < COUNT; i++) {
+            float d = tap_texel(t, fmaf(fi, du, u0), fmaf(fi, dv, v0), fmaf(fi, ds, s0));
+            fi += 1.0f;
+            sum += d;
+            dmax = fmaxf(dmax, d);
+        }
+    } else {   // segment leaves the sampled region (or is not finite): test every tap
+        float fi = 0.0f;
+#pragma unroll 1
+        for (int i = 0; i < COUNT; i++) {
+            float u = fmaf(fi, du, u0), v = fmaf(fi, dv, v0), s = fmaf(fi, ds, s0);
+            fi += 1.0f;
+            bool in = (u > -1.0f) & (u < t.nx) & (v > -1.0f) & (v < t.ny) & (s > -1.0f) & (s < t.nz);
+            float d = in ? tap_texel(t, u, v, s) : 0.0f;
+            sum += d;
+            dmax = fmaxf(dmax, d);
+        }
     }
     taps += COUNT;
     const float k = densityFactor * (1.0f / 255.0f);

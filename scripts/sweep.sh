@@ -10,6 +10,5 @@ run NRC_TRAIN_LANES=32 NRC_NO_OVERLAP=0
 run NRC_TRAIN_LANES=32 NRC_NO_OVERLAP=1
 run NRC_TRAIN_LANES=8 NRC_NO_OVERLAP=0
 run NRC_TRAIN_LANES=8 NRC_NO_OVERLAP=1
+run NRC_TRAIN_LANES=4 NRC_NO_OVERLAP=0
 run NRC_TRAIN_LANES=4 NRC_NO_OVERLAP=1
-run NRC_TRAIN_LANES=2 NRC_NO_OVERLAP=1
-run NRC_TRAIN_LANES=16 NRC_NO_OVERLAP=1
