@@ -124,6 +124,8 @@ NRC_API int nrc_kernel_count(void);
 NRC_API const char* nrc_kernel_name(int kernelId);
 NRC_API nrc_status nrc_ctx_profile_enable(nrc_ctx* ctx, int on);
 NRC_API nrc_status nrc_ctx_profile_read(nrc_ctx* ctx, double* ms, uint64_t* counts, int reset);
+/* the launches since the last read as (kernel id, start, end) in ms relative to the first launch: the timeline over both streams */
+NRC_API nrc_status nrc_ctx_profile_timeline(nrc_ctx* ctx, int maxRecords, int* kernelId, float* startMs, float* endMs, int* count);
 
 /* ---- NeuralRadianceCache: MLP parameter store (src/NeuralRadianceCache.cpp:370-512, 596-700) ---- */
 /* seed != 0: W ~ N(0,1)*0.01 from a counter-based generator, biases/deltas/momenta zero. */

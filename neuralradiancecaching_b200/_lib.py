@@ -49,7 +49,7 @@ nrc_renderer_set_camera nrc_renderer_set_dir_light nrc_renderer_set_point_light 
 nrc_render nrc_frame_train nrc_frame_render nrc_frame_bytes nrc_frame_ptr nrc_read_frame nrc_read_render_probes
 nrc_read_train_probes nrc_frame_stats nrc_frame_totals nrc_renderer_set_partition_strided nrc_read_frame_partition
 nrc_frame_partition_bytes nrc_kernel_count nrc_kernel_name
-nrc_ctx_profile_enable nrc_ctx_profile_read""".split()
+nrc_ctx_profile_enable nrc_ctx_profile_read nrc_ctx_profile_timeline""".split()
 
 _lib = None
 

@@ -70,6 +70,15 @@ class Context:
         L.check(L.lib().nrc_ctx_profile_read(self.h, ms, cnt, C.c_int(1 if reset else 0)))
         return {L.lib().nrc_kernel_name(i).decode(): (ms[i], int(cnt[i])) for i in range(k) if cnt[i]}
 
+    def profile_timeline(self, max_records=4096):
+        """[(kernel name, start ms, end ms)] of the launches since the last read, relative to the first."""
+        kid = (C.c_int * max_records)()
+        s = (C.c_float * max_records)()
+        e = (C.c_float * max_records)()
+        n = C.c_int()
+        L.check(L.lib().nrc_ctx_profile_timeline(self.h, C.c_int(max_records), kid, s, e, C.byref(n)))
+        return [(L.lib().nrc_kernel_name(kid[i]).decode(), s[i], e[i]) for i in range(n.value)]
+
     def set_precision(self, p):
         L.check(L.lib().nrc_ctx_set_precision(self.h, C.c_int(p)))
 

@@ -135,6 +135,28 @@ static void prof_drain(nrc_ctx* c)
     c->profOpen.clear();
 }
 
+// The launches recorded since the last read, in launch order, as (kernel id, start ms, end ms) relative to the first
+// one's start: the frame's timeline across both streams.  Consumes the records (they are also accumulated).
+extern "C" nrc_status nrc_ctx_profile_timeline(nrc_ctx* c, int maxRecords, int* kid, float* startMs, float* endMs, int* count)
+{
+    NRC_REQUIRE(c && kid && startMs && endMs && count, "null argument");
+    int n = 0;
+    if (!c->profOpen.empty()) {
+        cudaEvent_t ref = c->profOpen.front().a;
+        for (NrcProfRec& r : c->profOpen) {
+            if (n >= maxRecords) break;
+            float s = 0.0f, e = 0.0f;
+            if (cudaEventSynchronize(r.b) != cudaSuccess || cudaEventElapsedTime(&s, ref, r.a) != cudaSuccess ||
+                cudaEventElapsedTime(&e, ref, r.b) != cudaSuccess) { cudaGetLastError(); continue; }
+            kid[n] = r.kid; startMs[n] = s; endMs[n] = e;
+            n++;
+        }
+    }
+    *count = n;
+    prof_drain(c);
+    return NRC_OK;
+}
+
 extern "C" int nrc_kernel_count(void) { return K_COUNT; }
 extern "C" const char* nrc_kernel_name(int kid) { return (kid >= 0 && kid < K_COUNT) ? g_kernelNames[kid] : ""; }
 
@@ -183,8 +205,12 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     nrc_ctx* c = new nrc_ctx();
     c->device = device;
     c->smCount = prop.multiProcessorCount;
-    NRC_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    NRC_CUDA(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+    // the main stream carries the frame's critical path (the latency-bound train chain): highest priority, so its blocks
+    // are placed before pending blocks of the render walk running beside it on stream2
+    int prLow = 0, prHigh = 0;
+    NRC_CUDA(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
+    NRC_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prHigh));
+    NRC_CUDA(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prLow));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
     *out = c;

@@ -123,7 +123,7 @@ static nrc_status alloc_train(nrc_renderer* r)
     NRC_CUDA(cudaMemsetAsync(r->tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->trainCounters, 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
     // worst case: 8 paths x 64 lit vertices per training sample -- this pool cannot overflow
-    size_t cap = (size_t)n * 8 * 64;
+    size_t cap = (size_t)n * (8 * 64 + 2 * 16);   // + the two partly used chunks a thread can end with (TRAIN_CHUNK)
     NRC_REQUIRE(cap < ((size_t)1 << 31), "train grid too large for the vertex pool");
     NRC_TRY(alloc_pool(r->tpool, (uint32_t)cap, false, r->scalars + 2, r->scalars + 3));
     r->trainAlloc = n;

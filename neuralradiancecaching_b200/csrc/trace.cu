@@ -6,6 +6,10 @@
 #include "walk.cuh"
 #include <stdlib.h>
 
+// dynamic shared memory requested (and not used) by the kernels that may run beside the train walk, so that an SM whose
+// shared memory the train walk has reserved (NRC_TRAIN_SMS) cannot take their blocks
+#define NRC_PAD_SMEM 2048
+
 // ---- small device helpers ---------------------------------------------------------------------------------------
 
 __device__ __forceinline__ Box make_box(const TraceParams& P)
@@ -105,6 +109,40 @@ struct PoolEmitter {
     }
 };
 
+// Emitter of the train walk.  There the walk is a latency-bound serial chain, and a slot allocation per vertex (an L2
+// atomic whose result the next instructions need) would sit on it.  Each thread instead owns a chunk of TRAIN_CHUNK
+// slots and fetches the next chunk one chunk ahead, so no atomic result is ever waited for.  Slots left unused at the
+// end are marked dead (density < 0): the light kernel skips them and no path links to them.
+#define TRAIN_CHUNK 16u
+struct ChunkEmitter {
+    VertexPool pool;
+    int head, prev;
+    uint32_t cur, end, next;
+    __device__ __forceinline__ void init() { cur = 0u; end = 0u; next = atomicAdd(pool.count, TRAIN_CHUNK); }
+    __device__ __forceinline__ void begin() { head = -1; prev = -1; }
+    __device__ __forceinline__ bool vertex(f3 pos, float density, f3 dir, f3 last, const float*)
+    {
+        if (cur == end) {
+            cur = next;
+            end = cur + TRAIN_CHUNK;
+            next = atomicAdd(pool.count, TRAIN_CHUNK);
+        }
+        uint32_t slot = cur++;
+        if (slot >= pool.cap) { *pool.overflow = 1u; return false; }
+        pool.a[slot] = make_float4(pos.x, pos.y, pos.z, density);
+        pool.b[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(-1));
+        pool.c[slot] = make_float4(last.x, last.y, last.z, 0.0f);
+        if (prev >= 0) pool.b[prev].w = __int_as_float((int)slot); else head = (int)slot;
+        prev = (int)slot;
+        return true;
+    }
+    __device__ __forceinline__ void finish()
+    {
+        for (uint32_t s = cur; s < end; s++) if (s < pool.cap) pool.a[s].w = -1.0f;
+        for (uint32_t s = next; s < next + TRAIN_CHUNK; s++) if (s < pool.cap) pool.a[s].w = -1.0f;
+    }
+};
+
 // ---- render walk (nrc-forward.vert:28-40, nrc-forward.frag:757-870 minus lighting and Forward()) ------------------
 __global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
                                                      uint32_t spp, VertexPool pool, RenderPaths paths, float4* __restrict__ background,
@@ -149,35 +187,41 @@ __global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ Tra
 }
 
 // ---- train walk (nrc-train.comp:1122-1259 minus lighting and Backprop) ------------------------------------------------
-#define TRAIN_WARPS 4u   // warps per block
-__global__ void __launch_bounds__(32 * TRAIN_WARPS) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
-                                                   uint32_t lanes, VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
+// A training sample is ONE long serial chain (1 + 8 walks of 64 steps, the RNG chained through all of them) and a frame
+// has only ~10^4 of them: ~300 warps, latency-bound, a few per cent of the machine -- but the frame's critical path.
+// Sharing schedulers with the render walk (which saturates issue slots) nearly doubles its latency, so the kernel is
+// given SMs of its own: `gridDim.x` blocks that each reserve the whole shared memory of an SM (dynamic smem, unused),
+// which keeps every other block off that SM; the render chain runs on the rest of the machine meanwhile.
+__global__ void __launch_bounds__(1024, 1) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
+                                                        uint32_t lanes, VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
 {
-    // Thin warps: a training sample is one long serial chain (1 + 8 walks of 64 steps, RNG chained through all of
-    // them) and a frame has only ~10^4 of them, so the kernel is latency-bound with most schedulers idle.  Only
-    // TRAIN_LANES lanes of each warp carry a sample: a warp waits for the slowest of 4 sphere traces instead of 32,
-    // and the 8x more warps interleave on the otherwise idle schedulers.
     const uint32_t lane = threadIdx.x & 31u;
     if (lane >= lanes) return;
-    uint32_t local = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * lanes + lane;
-    if (local >= n) return;
+    const uint32_t warpsPerBlock = blockDim.x >> 5;
+    const uint32_t totalWarps = (n + lanes - 1) / lanes;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
     const WalkParams W = make_walk(P);
+    for (uint32_t w = blockIdx.x * warpsPerBlock + (threadIdx.x >> 5); w < totalWarps; w += gridDim.x * warpsPerBlock) {
+    const uint32_t local = w * lanes + lane;
+    if (local >= n) continue;
+    ChunkEmitter em;
+    em.pool = pool;
+    em.init();                      // the first chunk arrives while the vertex-picking walk runs
     Rng rng;
     WalkCounters wc = {0u, 0u, 0u, 0u};
     f3 cur, dir;
     train_pick_vertex(W, box, grid, i0 + local * istride, rng, wc, cur, dir);
     paths.pos[3 * (size_t)local] = cur.x; paths.pos[3 * (size_t)local + 1] = cur.y; paths.pos[3 * (size_t)local + 2] = cur.z;
     paths.dir[3 * (size_t)local] = dir.x; paths.dir[3 * (size_t)local + 1] = dir.y; paths.dir[3 * (size_t)local + 2] = dir.z;
-    PoolEmitter em;
-    em.pool = pool;
     for (int p = 0; p < 8; p++) {   // 8 x TracePath (:1217-1222), RNG chained from one to the next
         em.begin();
         train_walk_path(W, box, grid, cur, dir, rng, em, wc);
         paths.head[(size_t)local * 8 + p] = em.head;
     }
+    em.finish();
     if (counters) reinterpret_cast<uint4*>(counters)[local] = make_uint4(rng.draws, wc.lit, wc.steps, 0u);
+    }
 }
 
 // ---- light kernel: every density tap of the frame happens here -----------------------------------------------------
@@ -283,7 +327,9 @@ __global__ void __launch_bounds__(128) k_light(const __grid_constant__ TracePara
     const float kDensity = P.densityFactor;
     unsigned taps = 0;
     for (uint32_t vtx = blockIdx.x * blockDim.x + threadIdx.x; vtx < count; vtx += gridDim.x * blockDim.x) {
-        float4 A = pool.a[vtx], B = pool.b[vtx], C = pool.c[vtx];
+        float4 A = pool.a[vtx];
+        if (A.w < 0.0f) continue;   // unused slot of a train-walk chunk
+        float4 B = pool.b[vtx], C = pool.c[vtx];
         f3 pos = mk3(A.x, A.y, A.z), dir = mk3(B.x, B.y, B.z), last = mk3(C.x, C.y, C.z);
         f3 light = mk3(0.0f, 0.0f, 0.0f);
         unsigned sdf = 0;
@@ -515,7 +561,7 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
     uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
     NRC_LAUNCH(ctx, st, K_RENDER_WALK,
-               k_render_walk<<<(n + 127) / 128, 128, 0, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters));
+               k_render_walk<<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters));
     return NRC_OK;
 }
 
@@ -523,15 +569,31 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
                              TrainPaths paths, uint32_t* counters)
 {
     if (n == 0) return NRC_OK;
-    static int lanesEnv = -1;
+    static int lanesEnv = -1, smsEnv = -1;
     if (lanesEnv < 0) {
         const char* e = getenv("NRC_TRAIN_LANES");
-        lanesEnv = e ? atoi(e) : 4;
-        if (lanesEnv < 1 || lanesEnv > 32) lanesEnv = 4;
+        lanesEnv = e ? atoi(e) : 32;
+        if (lanesEnv < 1 || lanesEnv > 32) lanesEnv = 32;
+        e = getenv("NRC_TRAIN_SMS");           // SMs reserved for the train walk; 0 = share the machine
+        smsEnv = e ? atoi(e) : 0;
+        if (smsEnv < 0 || smsEnv > ctx->smCount) smsEnv = 0;
+        NRC_CUDA(cudaFuncSetAttribute(k_train_walk, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
-    const uint32_t lanes = (uint32_t)lanesEnv, perBlock = lanes * TRAIN_WARPS;
+    const uint32_t lanes = (uint32_t)lanesEnv;
+    const uint32_t totalWarps = (n + lanes - 1) / lanes;
+    uint32_t blocks, warpsPerBlock;
+    size_t smem = 0;
+    if (smsEnv > 0) {
+        blocks = (uint32_t)smsEnv < totalWarps ? (uint32_t)smsEnv : totalWarps;
+        warpsPerBlock = (totalWarps + blocks - 1) / blocks;
+        if (warpsPerBlock > 32) warpsPerBlock = 32;
+        smem = 227 * 1024;                     // the whole SM: no other block can be co-resident
+    } else {
+        warpsPerBlock = 4;
+        blocks = (totalWarps + warpsPerBlock - 1) / warpsPerBlock;
+    }
     NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
-               k_train_walk<<<(n + perBlock - 1) / perBlock, 32 * TRAIN_WARPS, 0, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
+               k_train_walk<<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
     return NRC_OK;
 }
 
@@ -542,8 +604,8 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
     unsigned cap = (unsigned)ctx->smCount * 16;
     unsigned blocks = want < cap ? want : cap;
     if (blocks == 0) return NRC_OK;
-    if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, k_light<true><<<blocks, 128, 0, st>>>(P, pool, tapCounter));
-    else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, k_light<false><<<blocks, 128, 0, st>>>(P, pool, tapCounter));
+    if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, k_light<true><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter));
+    else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, k_light<false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter));
     return NRC_OK;
 }
 
@@ -553,7 +615,7 @@ nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParam
     uint32_t n = rows * P.width * spp;
     if (n == 0) return NRC_OK;
     NRC_LAUNCH(ctx, st, K_RENDER_COMBINE,
-               k_render_combine<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, rows, ystride, spp, pool, paths, q));
+               k_render_combine<<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P.width, y0, rows, ystride, spp, pool, paths, q));
     return NRC_OK;
 }
 

@@ -134,6 +134,10 @@ NRC_HD void train_pick_vertex(const WalkParams& P, const Box& box, const Grid& g
 #pragma nv_exec_check_disable
 #endif
 // TracePath(rayOrigin, rayDir) of the train shader (:1122-1171) without lighting.
+// Written for latency, not instruction count (the train walk is a serial chain on a handful of warps): the scatter
+// direction is computed from the next two draws BEFORE the density tap has returned, so the tap's memory latency, the
+// RNG chain and the rotation arithmetic overlap; which of the two continuations is taken is a select.  Same draws,
+// same operations, same results as the straightforward order.
 template <class Emitter>
 NRC_HD void train_walk_path(const WalkParams& P, const Box& box, const Grid& grid, f3 startP, f3 startD, Rng& rng, Emitter& em,
                             WalkCounters& wc)
@@ -144,11 +148,14 @@ NRC_HD void train_walk_path(const WalkParams& P, const Box& box, const Grid& gri
     for (int i = 0; i < 64; i++) {
         wc.steps++;
         float density = grid_density(grid, c);
+        Rng spec = rng;                                  // speculative: the two draws of NewRayDir
+        f3 nd = new_ray_dir(d, P.g, spec);
         if (density > 0.0f) {
             if (!em.vertex(c, density, d, last, nullptr)) return;
             wc.lit++;
             last = c;
-            d = new_ray_dir(d, P.g, rng);
+            d = nd;
+            rng = spec;
         }
         c = walk_advance(box, c, d, rng, wc.sdf);
     }

@@ -1,14 +1,12 @@
 #!/bin/bash
-# usage: scripts/sweep.sh  -- bench under several env settings, prints ms/frame + top kernels
 run() {
   echo "== $*"
   env "$@" timeout 200 python bench.py --steps 20 --warmup 3 --no-cpu-baseline --precision bf16 2>&1 | tail -1 | python -c "
 import json,sys
 d=json.loads(sys.stdin.read()); print('ms/frame %.3f  e2e %.3f' % (d['ms_per_step'], d['e2e']['ms_per_step'])); print({k:round(v['ms_per_step'],3) for k,v in list(d['kernels'].items())[:8]})"
 }
-run NRC_TRAIN_LANES=32 NRC_NO_OVERLAP=0
-run NRC_TRAIN_LANES=32 NRC_NO_OVERLAP=1
-run NRC_TRAIN_LANES=8 NRC_NO_OVERLAP=0
-run NRC_TRAIN_LANES=8 NRC_NO_OVERLAP=1
-run NRC_TRAIN_LANES=4 NRC_NO_OVERLAP=0
-run NRC_TRAIN_LANES=4 NRC_NO_OVERLAP=1
+run NRC_TRAIN_SMS=0
+run NRC_TRAIN_SMS=16
+run NRC_TRAIN_SMS=24
+run NRC_TRAIN_SMS=32
+run NRC_TRAIN_SMS=48
