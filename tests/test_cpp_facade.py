@@ -1,0 +1,39 @@
+"""The header-only C++ facade (include/nrc_b200.hpp) and examples/headless_main.cpp compile against the C-ABI library;
+without a GPU the program fails loudly (no CPU fallback), with one it renders frames."""
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIBDIR = os.path.join(ROOT, "neuralradiancecaching_b200")
+EXE = os.path.join(ROOT, "examples", "_build", "headless_main")
+
+
+def _build():
+    os.makedirs(os.path.dirname(EXE), exist_ok=True)
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "headless_main.cpp"), "-o", EXE, "-L" + LIBDIR, "-lnrc_b200",
+                           "-Wl,-rpath," + LIBDIR])
+    return EXE
+
+
+def test_facade_compiles_and_fails_loudly_without_gpu():
+    import torch
+    exe = _build()
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    p = subprocess.run([exe, "1", "32", "32", "/tmp/nrc_x.ppm"], capture_output=True, text=True)
+    assert p.returncode == 1 and "no CPU fallback" in p.stderr
+
+
+@pytest.mark.gpu
+def test_headless_main_renders(tmp_path):
+    exe = _build()
+    out = str(tmp_path / "f.ppm")
+    p = subprocess.run([exe, "30", "160", "96", out], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    assert "NRC MSE Loss" in p.stdout
+    data = open(out, "rb").read()
+    assert data.startswith(b"P6\n160 96\n255\n") and len(data) == len(b"P6\n160 96\n255\n") + 160 * 96 * 3
+    assert len(set(data[15:])) > 8   # not a constant image
