@@ -30,10 +30,8 @@ BASE_W, BASE_H, BASE_TW, BASE_TH = 1920, 1080, 100, 100
 
 
 def frame_shape(n_gpus):
-    s = float(n_gpus) ** 0.5
-    w = int(round(BASE_W * s / 8.0)) * 8
-    h = int(round(BASE_H * s / 8.0)) * 8
-    return w, h, BASE_TW, BASE_TH * n_gpus
+    from neuralradiancecaching_b200.dist import frame_shape as fs
+    return fs(n_gpus, (BASE_W, BASE_H, BASE_TW, BASE_TH))
 
 
 def peaks():
@@ -106,13 +104,6 @@ def lcg_randoms(n, seed=0x2545F491):
     return out
 
 
-class DevArray:
-    """__cuda_array_interface__ view of a raw device pointer (for torch.as_tensor: zero-copy)."""
-
-    def __init__(self, ptr, count):
-        self.__cuda_array_interface__ = {"shape": (count,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
-
-
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
 def run_b200(args):
     import torch
@@ -150,11 +141,9 @@ def run_b200(args):
     if world > 1:
         r.SetPartitionStrided(rank, world, rank, world)
 
-    ext = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
-    gm_ptr, gm_n = nrc.grad_ptr()
-    gt_ptr, gt_n = mrhe.grad_ptr()
-    g_mlp = torch.as_tensor(DevArray(gm_ptr, gm_n), device=torch.device("cuda", local))
-    g_tab = torch.as_tensor(DevArray(gt_ptr, gt_n), device=torch.device("cuda", local))
+    from neuralradiancecaching_b200.dist import GradientExchange
+    exchange = GradientExchange(ctx, nrc, mrhe, torch.device("cuda", local))
+    ext = exchange.stream
 
     def frame(random4):
         vol.Update(random4=random4)
@@ -163,9 +152,7 @@ def run_b200(args):
             r.Render()
         else:
             r.FrameTrain()
-            with torch.cuda.stream(ext):
-                dist.all_reduce(g_mlp)
-                dist.all_reduce(g_tab)
+            exchange()                       # NCCL all-reduce of the MLP gradient arena (+loss) and the delta-table head
             N.optimizer_step(nrc, mrhe)
             r.FrameRender()
 

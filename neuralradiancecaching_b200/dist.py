@@ -1,0 +1,59 @@
+"""Data-parallel plumbing: one process per GPU, torch.distributed for the rendezvous and the collective.
+
+The reference has no multi-GPU path; the protocol is ours:
+  rows / train invocations are interleaved over ranks (rank, rank+world, ...) with GLOBAL coordinates in the RNG seeds,
+  gradients (packed MLP arena incl. the loss accumulator + the touched head of the delta hash table) are summed over
+  ranks between nrc-train and the optimiser steps, every rank then applies identical steps."""
+import numpy as np
+
+
+class DevArray:
+    """__cuda_array_interface__ view of a raw device pointer (torch.as_tensor makes a zero-copy tensor of it)."""
+
+    def __init__(self, ptr, count):
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def strided_count(first, end, stride):
+    """number of indices first, first+stride, ... < end"""
+    return 0 if first >= end else (end - first + stride - 1) // stride
+
+
+def shard_rows(rank, world, height):
+    return np.arange(rank, height, world)
+
+
+def frame_shape(n_gpus, base=(1920, 1080, 100, 100)):
+    """Weak scaling: n x the pixels of the base frame (aspect kept, both sides a multiple of 8) and n x the samples."""
+    w, h, tw, th = base
+    s = float(n_gpus) ** 0.5
+    return int(round(w * s / 8.0)) * 8, int(round(h * s / 8.0)) * 8, tw, th * n_gpus
+
+
+class GradientExchange:
+    """All-reduce of the two gradient arenas, in place, ordered on the library's stream."""
+
+    def __init__(self, ctx, nrc, mrhe, device):
+        import torch
+        gm_ptr, gm_n = nrc.grad_ptr()
+        gt_ptr, gt_n = mrhe.grad_ptr()
+        self.g_mlp = torch.as_tensor(DevArray(gm_ptr, gm_n), device=device)
+        self.g_tab = torch.as_tensor(DevArray(gt_ptr, gt_n), device=device)
+        self.stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+
+    def __call__(self):
+        import torch
+        import torch.distributed as dist
+        with torch.cuda.stream(self.stream):
+            dist.all_reduce(self.g_mlp)
+            dist.all_reduce(self.g_tab)
+
+
+def allreduce_host(arrays):
+    """gloo/CPU variant used by the world_size-2 tests: numpy arrays summed over ranks in place."""
+    import torch
+    import torch.distributed as dist
+    for a in arrays:
+        t = torch.from_numpy(a)
+        dist.all_reduce(t)
+    return arrays
