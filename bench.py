@@ -164,7 +164,7 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     K, Wm = args.steps, args.warmup
-    rnd = lcg_randoms(2 * (K + Wm) + 16)
+    rnd = lcg_randoms(2 * (K + Wm) + 40)
     ri = iter(rnd)
     # ---- device-resident timing (value) ----
     for _ in range(Wm):
@@ -215,6 +215,24 @@ def run_b200(args):
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = max(e0.elapsed_time(e1), 0.0)
     tot_e2e = r.totals(reset=True)
+    # ---- the same frames with the fp32 CUDA-core MLP (the 1e-3 parity path), reported beside the headline ----
+    fp32_ms = None
+    if args.precision == "bf16" and not args.no_fp32_line:
+        ctx.set_precision(L.MLP_FP32)
+        for _ in range(3):
+            frame(next(ri))
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(ext):
+            f0.record()
+        kf = min(K, 10)
+        for _ in range(kf):
+            frame(next(ri))
+        with torch.cuda.stream(ext):
+            f1.record()
+        barrier()
+        fp32_ms = f0.elapsed_time(f1) / kf
+        r.totals(reset=True)
     return finish_b200(args, locals())
 
 
@@ -288,7 +306,7 @@ def finish_b200(args, v):
     line = {
         "metric": METRIC, "value": units / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": v["Wm"],
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32" if args.precision == "fp32" else "bf16(mlp)+f32", "data": "synthetic",
+        "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
         "config": {"workload": "cloud_sixteenth (synthetic 125x85x153 stand-in) %dx%d 1 spp, online NRC training %dx%d samples/frame, "
                                "dir+point+env lights, useNN=1" % (W, H, v["TW"], v["TH"]),
                    "frame": [W, H], "train_grid": [v["TW"], v["TH"]], "hash_table": [16, 16384, 2], "mlp": "64x5->3 relu",
@@ -302,6 +320,8 @@ def finish_b200(args, v):
                              "density_taps": (tot["render_taps"] + tot["train_taps"]) / K},
         "mse_loss_last": v["mse"],
     }
+    if v.get("fp32_ms") is not None:
+        line["fp32_mlp_path"] = {"ms_per_step": v["fp32_ms"], "note": "same frames with the fp32 CUDA-core MLP kernels (1e-3 parity path), this rank"}
     if world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_reference_sample(W, H, v["TW"], v["TH"], budget_s=args.cpu_budget)
@@ -404,7 +424,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"],
+                    help="MLP arithmetic: bf16 = tcgen05 tensor cores (bf16 operands, fp32 accumulate; north_star's tensor-core path), "
+                         "fp32 = CUDA-core 1e-3 parity path.  Tracing is fp32 either way.")
+    ap.add_argument("--no-fp32-line", action="store_true", help="skip the extra fp32-path measurement")
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -484,7 +484,10 @@ extern "C" nrc_status nrc_train_accumulate(nrc_mlp* mlp, nrc_mrhe* m, const floa
     NRC_TRY(nrc_stage_in(ctx, 1, dir, n * 3 * sizeof(float), &ddir));
     NRC_TRY(nrc_stage_in(ctx, 2, target, n * 3 * sizeof(float), &dtgt));
     if (pred) NRC_TRY(nrc_stage_out(ctx, 3, pred, n * 3 * sizeof(float), &dpred));
-    NRC_TRY(launch_train_fp32(mlp, m, (const float*)dpos, (const float*)ddir, (const float*)dtgt, n, lossScale, (float*)dpred, ctx->stream));
+    if (ctx->precision == NRC_MLP_BF16_TC)
+        NRC_TRY(launch_train_tc(mlp, m, (const float*)dpos, (const float*)ddir, (const float*)dtgt, n, lossScale, (float*)dpred, ctx->stream));
+    else
+        NRC_TRY(launch_train_fp32(mlp, m, (const float*)dpos, (const float*)ddir, (const float*)dtgt, n, lossScale, (float*)dpred, ctx->stream));
     if (pred) NRC_TRY(nrc_stage_out_finish(ctx, pred, dpred, n * 3 * sizeof(float)));
     return NRC_OK;
 }

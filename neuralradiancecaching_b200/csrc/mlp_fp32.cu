@@ -462,6 +462,13 @@ nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
     return NRC_OK;
 }
 
+nrc_status launch_reduce_partials(nrc_mlp* mlp, int blocks, cudaStream_t st)
+{
+    NRC_LAUNCH(mlp->ctx, st, K_REDUCE_PARTIALS,
+               k_reduce_partials<<<(NRC_MLP_PARAM_COUNT + 1 + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad));
+    return NRC_OK;
+}
+
 nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
                              float* pred, cudaStream_t st)
 {

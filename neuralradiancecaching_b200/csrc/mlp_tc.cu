@@ -28,21 +28,35 @@
 #define TC_THREADS 256
 #define TC_TMEM_COLS 64
 
-// ---- bf16 weight image -----------------------------------------------------------------------------------------------
-// elements: layer l < 5 at l*4096: (k/8)*512 + n*8 + k%8 ; layer 5 (3 rows padded to 16) at 20480: (k/8)*128 + n*8 + k%8
+// ---- bf16 weight images ----------------------------------------------------------------------------------------------
+// forward image (B operand of x*W^T: rows n = out, K = in), elements:
+//   layer l < 5 at l*4096: (k/8)*512 + n*8 + k%8 ; layer 5 (3 rows padded to 16) at 20480: (k/8)*128 + n*8 + k%8
+// transposed image at TC_W_ELEMS (B operand of the back-data GEMM e*W: rows n = in, K = out):
+//   layer l < 5 at l*4096: (k/8)*512 + n*8 + k%8 with k = out ; layer 5 at 20480: K = 16 (3 real outputs), same formula
 #define TC_W_ELEMS (5 * 4096 + 1024)
 
 __global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ params, __nv_bfloat16* __restrict__ img)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= TC_W_ELEMS) return;
+    if (i >= 2 * TC_W_ELEMS) return;
     float v = 0.0f;
-    if (i < 5 * 4096) {
-        int l = i >> 12, rem = i & 4095, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7;
-        v = params[l * 4096 + n * 64 + kc * 8 + kk];
+    if (i < TC_W_ELEMS) {
+        if (i < 5 * 4096) {
+            int l = i >> 12, rem = i & 4095, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7;
+            v = params[l * 4096 + n * 64 + kc * 8 + kk];
+        } else {
+            int rem = i - 5 * 4096, kc = rem >> 7, n = (rem >> 3) & 15, kk = rem & 7;
+            if (n < 3) v = params[NRC_W_OFF(5) + n * 64 + kc * 8 + kk];
+        }
     } else {
-        int rem = i - 5 * 4096, kc = rem >> 7, n = (rem >> 3) & 15, kk = rem & 7;
-        if (n < 3) v = params[NRC_W_OFF(5) + n * 64 + kc * 8 + kk];
+        int j = i - TC_W_ELEMS;
+        if (j < 5 * 4096) {
+            int l = j >> 12, rem = j & 4095, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7;
+            v = params[l * 4096 + (kc * 8 + kk) * 64 + n];
+        } else {
+            int rem = j - 5 * 4096, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7, o = kc * 8 + kk;
+            if (o < 3) v = params[NRC_W_OFF(5) + o * 64 + n];
+        }
     }
     img[i] = __float2bfloat16_rn(v);
 }
@@ -161,8 +175,9 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
 // Encode half of row `r`'s network inputs into the A tile.  half 0: MRHE levels 0-7 + OneBlob theta; half 1: levels
 // 8-15 + OneBlob phi.  Index arithmetic and blends are the strict ones (bit-identical hash indices); only the final
 // rounding to bf16 differs from the fp32 path.
-__device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int half, bool live, f3 p, f3 d, const MrheDev& m)
+__device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int half, bool live, f3 p, f3 d, const MrheDev& m, bool& nanIn04)
 {
+    nanIn04 = false;
     uint4* chunk = reinterpret_cast<uint4*>(aTile);   // chunk(kc, row) = chunk[kc * 128 + row]
     f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
     f3 np = mrhe_norm_pos(p, sky);
@@ -191,6 +206,7 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int 
             o[2 * li] = o0;
             o[2 * li + 1] = o1;
         }
+        if (half == 0 && g == 0) nanIn04 = (o[0] != o[0]) | (o[1] != o[1]) | (o[2] != o[2]) | (o[3] != o[3]) | (o[4] != o[4]);   // train.comp:993-999
         chunk[(2 * half + g) * TC_ROWS + r] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
     }
     float ang;
@@ -261,7 +277,8 @@ __global__ void __launch_bounds__(TC_THREADS, 3) k_infer_tc(const float* __restr
             p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
             d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
         }
-        tc_encode_half(aTile, row, half, live, p, d, m);
+        bool nanFlag;
+        tc_encode_half(aTile, row, half, live, p, d, m, nanFlag);
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
@@ -319,10 +336,10 @@ __global__ void __launch_bounds__(TC_THREADS, 3) k_infer_tc(const float* __restr
 // ---- host launchers -----------------------------------------------------------------------------------------------------------
 static nrc_status tc_prepare(nrc_mlp* mlp, cudaStream_t st)
 {
-    if (!mlp->paramsBf16) NRC_CUDA(cudaMalloc(&mlp->paramsBf16, TC_W_ELEMS * sizeof(uint16_t)));
+    if (!mlp->paramsBf16) NRC_CUDA(cudaMalloc(&mlp->paramsBf16, 2 * TC_W_ELEMS * sizeof(uint16_t)));
     if (mlp->dirtyBf16) {
         NRC_LAUNCH(mlp->ctx, st, K_PACK_BF16,
-                   k_pack_bf16<<<(TC_W_ELEMS + 255) / 256, 256, 0, st>>>(mlp->params, reinterpret_cast<__nv_bfloat16*>(mlp->paramsBf16)));
+                   k_pack_bf16<<<(2 * TC_W_ELEMS + 255) / 256, 256, 0, st>>>(mlp->params, reinterpret_cast<__nv_bfloat16*>(mlp->paramsBf16)));
         mlp->dirtyBf16 = false;
     }
     return NRC_OK;
@@ -346,4 +363,350 @@ nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
                k_infer_tc<<<blocks, TC_THREADS, TC_SMEM_BYTES, st>>>(pos, dir, countDev, n, reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16),
                                                                      mlp->params, make_mrhe_dev(m), rgb));
     return NRC_OK;
+}
+
+// ==================================================================================================================
+// Training on the tensor cores: EncodeRay + Forward + Backprop (train.comp:703-741, 743-1028) for a tile of 128 samples.
+//
+//   forward   A_{l+1} = relu(A_l W_l^T + b_l)                  tcgen05.mma M=128 (samples) N=64 K=64, as in k_infer_tc;
+//                                                              every A_l stays in shared memory (bf16) for the backward
+//   back-data E_l     = gate(E_{l+1} W_l)                      M=128 N=64 K=64, B = the TRANSPOSED weight image
+//   dW_l, db_l        = E_{l+1}^T [A_l | 1]                    M=128 (64 out rows + 64 zero rows) N=80 K=128 (the samples):
+//                                                              both operands are written transposed (K = sample) by the
+//                                                              epilogues; the accumulators of all five hidden layers live in
+//                                                              TMEM (5 x 80 columns) across ALL tiles of the CTA and are read
+//                                                              once at the end -> per-CTA partials, summed in fixed order by
+//                                                              k_reduce_partials.  No atomics on the MLP parameters.
+//   layer 5 (64 -> 3): forward and back-data on the tensor cores (N = 16 / K = 16 padded), dW5/db5 on CUDA cores.
+//   gates, loss, clamp, NaN guard, the feature-0-for-both / no-level-offset hash scatter: the reference's.
+// TMEM: columns 0-63 forward/back-data accumulator, 64 + 80*l .. dW_l | db_l (464 of 512 columns).
+// ==================================================================================================================
+#define TT_WF 0                                    // forward weight stage (8 KB); reused for the hash-gradient staging
+#define TT_WB 8192                                 // transposed weight stage (8 KB)
+#define TT_ACT 16384                               // A_0..A_5, 16 KB each, K-major (K = feature)
+#define TT_E (TT_ACT + 6 * 16384)                  // E tile, K-major (K = feature): A operand of the back-data GEMM
+#define TT_ET_LBO (128 * 16 + 16)                  // padded so that the transposing 2-byte stores spread over the banks
+#define TT_ET (TT_E + 16384)                       // E^T, K = sample: 16 chunks x (128 rows x 16 B + pad)
+#define TT_AT_LBO (80 * 16 + 16)
+#define TT_AT (TT_ET + 16 * TT_ET_LBO)             // [A_l | 1]^T, K = sample: 16 chunks x (80 rows x 16 B + pad)
+#define TT_BIAS (TT_AT + 16 * TT_AT_LBO)           // 336 floats
+#define TT_E6 (TT_BIAS + 336 * 4)                  // [128][4] fp32 output errors
+#define TT_PRED (TT_E6 + 2048)                     // [128][4] fp32 predictions
+#define TT_DROP (TT_PRED + 2048)                   // [128] int
+#define TT_LOSS (TT_DROP + 512)                    // [8] float
+#define TT_BAR (TT_LOSS + 64)
+#define TT_SMEM_BYTES (TT_BAR + 16)
+#define TT_DW_COL(l) (64u + 80u * (uint32_t)(l))
+
+__device__ __forceinline__ void tt_stage8k(unsigned char* dst, const __nv_bfloat16* __restrict__ src, int bytes)
+{
+    const uint4* s = reinterpret_cast<const uint4*>(src);
+    uint4* d = reinterpret_cast<uint4*>(dst);
+    for (int i = threadIdx.x; i < bytes / 16; i += TC_THREADS) d[i] = __ldg(s + i);
+}
+
+// element (feature m, sample k) of a K=sample operand
+__device__ __forceinline__ void tt_store_t(unsigned char* base, uint32_t lbo, int m, int k, unsigned short v)
+{
+    *reinterpret_cast<unsigned short*>(base + (k >> 3) * lbo + m * 16 + (k & 7) * 2) = v;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restrict__ pos, const float* __restrict__ dir,
+                                                            const float* __restrict__ target, size_t n, float scale,
+                                                            const __nv_bfloat16* __restrict__ wimg, const float* __restrict__ params, MrheDev m,
+                                                            float* __restrict__ partialAll, float* __restrict__ predOut)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    float* biasS = reinterpret_cast<float*>(smem + TT_BIAS);
+    float* e6S = reinterpret_cast<float*>(smem + TT_E6);
+    float* predS = reinterpret_cast<float*>(smem + TT_PRED);
+    int* dropS = reinterpret_cast<int*>(smem + TT_DROP);
+    float* lossS = reinterpret_cast<float*>(smem + TT_LOSS);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + TT_BAR);
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(smem + TT_BAR + 8);
+    float* gS = reinterpret_cast<float*>(smem + TT_WF);   // [128][16] hash-gradient staging (the forward stage is idle then)
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int quad = warp & 3, half = warp >> 2;
+    const int row = quad * 32 + lane;
+    float* partial = partialAll + (size_t)blockIdx.x * NRC_PARTIAL_STRIDE;
+
+    // ---- one-time setup ----
+    for (int i = tid; i < NRC_PARTIAL_STRIDE; i += TC_THREADS) partial[i] = 0.0f;
+    for (int i = tid; i < (TT_BIAS - TT_ET) / 16; i += TC_THREADS) reinterpret_cast<uint4*>(smem + TT_ET)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 336; i += TC_THREADS) biasS[i] = (i < 323) ? __ldg(params + NRC_B_OFF(0) + i) : 0.0f;
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(tmemSlot, 512);
+    __syncthreads();
+    if (tid < 128) tt_store_t(smem + TT_AT, TT_AT_LBO, 64, tid, 0x3F80u);   // the ones row of [A | 1]^T (bf16 1.0)
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmemBase = *tmemSlot;
+    const uint32_t sBase = smem_u32(smem);
+    uint32_t phase = 0;
+    float lossAcc = 0.0f;        // thread 0
+    float dw5Acc = 0.0f;         // threads < 192: dW5[j][c]; threads 192..194: db5[j]
+
+    const size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
+    bool firstTile = true;
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, firstTile = false) {
+        const size_t q = tile * TC_ROWS + row;
+        const bool inRange = q < n;
+        f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
+        if (inRange) {
+            p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
+            d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
+        }
+        // ---- encode into A_0 (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
+        bool nanFlag;
+        tc_encode_half(smem + TT_ACT, row, half, inRange, p, d, m, nanFlag);
+        if (half == 0) dropS[row] = (!inRange || nanFlag) ? 1 : 0;
+        tt_stage8k(smem + TT_WF, wimg, 8192);
+        __syncthreads();
+        const bool dropped = dropS[row] != 0;
+        if (dropped) {   // a dropped sample contributes nothing: zero its inputs (its error rows are zeroed below)
+            uint4* chunk = reinterpret_cast<uint4*>(smem + TT_ACT);
+            for (int c = 4 * half; c < 4 * half + 4; c++) chunk[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        fence_async_smem();
+        tc_fence_before();
+        __syncthreads();
+        // ---- forward (train.comp:715-741) ----
+#pragma unroll 1
+        for (int l = 0; l < 6; l++) {
+            const uint32_t actIn = sBase + TT_ACT + (uint32_t)l * 16384u;
+            if (tid == 0) {
+                tc_fence_after();
+                const uint32_t nOut = (l < 5) ? 64u : 16u;
+                const uint32_t idesc = umma_idesc(TC_ROWS, nOut);
+                const uint32_t wLbo = nOut * 16u;
+#pragma unroll
+                for (int ks = 0; ks < 4; ks++)
+                    umma_bf16(tmemBase, umma_desc(actIn + ks * 4096, 2048, 128), umma_desc(sBase + TT_WF + ks * 2 * wLbo, wLbo, 128), idesc,
+                              ks > 0 ? 1u : 0u);
+                umma_commit(bar);
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            tc_fence_after();
+            // the forward stage is free again: fetch the next layer's weights (or the first backward stage) behind the epilogue
+            if (l < 4) tt_stage8k(smem + TT_WF, wimg + (l + 1) * 4096, 8192);
+            else if (l == 4) tt_stage8k(smem + TT_WF, wimg + 5 * 4096, 2048);
+            else tt_stage8k(smem + TT_WB, wimg + TC_W_ELEMS + 5 * 4096, 2048);     // W5^T: 64 rows x K 16
+            if (l < 5) {
+                uint32_t v[32];
+                tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
+                tmem_ld_wait();
+                const float* b = biasS + l * 64 + half * 32;
+                uint4* chunk = reinterpret_cast<uint4*>(smem + TT_ACT + (l + 1) * 16384);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    float x[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) x[j] = fmaxf(__uint_as_float(v[8 * c + j]) + b[8 * c + j], 0.0f);
+                    chunk[(4 * half + c) * TC_ROWS + row] =
+                        make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]), pack_bf16(x[6], x[7]));
+                }
+            } else if (half == 0) {
+                // ---- output, loss, output error with the layer-5 gate (train.comp:1002-1012, 746-749) ----
+                uint32_t v[4];
+                tmem_ld4(tmemBase + ((uint32_t)(quad * 32) << 16), v);
+                tmem_ld_wait();
+                const unsigned short* a5 = reinterpret_cast<const unsigned short*>(smem + TT_ACT + 5 * 16384 + row * 16);   // features 0..7 of this row
+                float lsum = 0.0f, e[3];
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                    float y = fmaxf(__uint_as_float(v[j]) + biasS[320 + j], 0.0f);
+                    float err = 0.0f;
+                    e[j] = 0.0f;
+                    if (!dropped) {
+                        float tg = fminf(__ldg(target + 3 * q + j), 1024.0f);
+                        err = y - tg;
+                        lsum += err * err;
+                        bool gate = (a5[j] & 0x7fffu) != 0u && (a5[j] & 0x8000u) == 0u;     // bf16 value > 0
+                        e[j] = gate ? 2.0f * err : 0.0f;
+                    }
+                    predS[row * 4 + j] = dropped ? 0.0f : y;
+                    e6S[row * 4 + j] = e[j];
+                }
+                e6S[row * 4 + 3] = 0.0f;
+                if (predOut && inRange) {
+#pragma unroll
+                    for (int j = 0; j < 3; j++) predOut[3 * q + j] = predS[row * 4 + j];
+                }
+                // E_6 as the A operand of the layer-5 back-data GEMM (K = 16: two chunks)
+                uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
+                echunk[row] = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], 0.0f), 0u, 0u);
+                echunk[TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+                lsum = (lsum / 3.0f) * scale;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) lsum += __shfl_xor_sync(0xffffffffu, lsum, o);
+                if (lane == 0) lossS[quad] = lsum;
+            }
+            fence_async_smem();
+            tc_fence_before();
+            __syncthreads();
+        }
+        if (tid == 0) lossAcc += (lossS[0] + lossS[1]) + (lossS[2] + lossS[3]);
+        // ---- dW5, db5 on the CUDA cores (Backprop5, train.comp:751-774): 192 + 3 threads, accumulated over the CTA's tiles ----
+        if (tid < 192) {
+            int c = tid & 63, j = tid >> 6;
+            const unsigned char* a5 = smem + TT_ACT + 5 * 16384 + (c >> 3) * 2048 + (c & 7) * 2;
+            float s = 0.0f;
+#pragma unroll 8
+            for (int r = 0; r < TC_ROWS; r++)
+                s = fmaf(__bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(a5 + r * 16)), e6S[r * 4 + j], s);
+            dw5Acc += s;
+        } else if (tid < 195) {
+            int j = tid - 192;
+            float s = 0.0f;
+            for (int r = 0; r < TC_ROWS; r++) s += e6S[r * 4 + j];
+            dw5Acc += s;
+        }
+        // ---- backward (Backprop5..Backprop0, train.comp:743-945).  Step L computes dX_L = E_{L+1} W_L into the main
+        // accumulator (and, for L <= 4, dW_L | db_L += E_{L+1}^T [A_L | 1] into its own TMEM columns); its epilogue gates dX_L
+        // with A_{L-1} into E_L -- K-major for the next back-data GEMM and transposed for the next dW GEMM --
+        // and stages what step L-1 needs: W_{L-1}^T and [A_{L-1} | 1]^T. ----
+#pragma unroll 1
+        for (int L = 5; L >= 0; L--) {
+            if (tid == 0) {
+                tc_fence_after();
+                if (L <= 4) {
+                    const uint32_t idw = umma_idesc(128, 80);
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++)
+                        umma_bf16(tmemBase + TT_DW_COL(L), umma_desc(sBase + TT_ET + ks * 2 * TT_ET_LBO, TT_ET_LBO, 128),
+                                  umma_desc(sBase + TT_AT + ks * 2 * TT_AT_LBO, TT_AT_LBO, 128), idw, (firstTile && ks == 0) ? 0u : 1u);
+                }
+                const uint32_t idx = umma_idesc(TC_ROWS, 64);
+                const int ksteps = (L == 5) ? 1 : 4;
+                for (int ks = 0; ks < ksteps; ks++)
+                    umma_bf16(tmemBase, umma_desc(sBase + TT_E + ks * 4096, 2048, 128), umma_desc(sBase + TT_WB + ks * 2048, 1024, 128), idx,
+                              ks > 0 ? 1u : 0u);
+                umma_commit(bar);
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1u;
+            tc_fence_after();
+            uint32_t v[32];
+            tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
+            tmem_ld_wait();
+            if (L >= 1) {
+                tt_stage8k(smem + TT_WB, wimg + TC_W_ELEMS + (L - 1) * 4096, 8192);
+                const uint4* aprev = reinterpret_cast<const uint4*>(smem + TT_ACT + (L - 1) * 16384);
+                uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    uint4 a = aprev[(4 * half + c) * TC_ROWS + row];       // A_{L-1}[row][32h + 8c .. +7]
+                    uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+                    uint32_t ew[4];
+#pragma unroll
+                    for (int j2 = 0; j2 < 4; j2++) {
+                        unsigned short alo = (unsigned short)(aw[j2] & 0xffffu), ahi = (unsigned short)(aw[j2] >> 16);
+                        float elo = __uint_as_float(v[8 * c + 2 * j2]), ehi = __uint_as_float(v[8 * c + 2 * j2 + 1]);
+                        if (!((alo & 0x7fffu) != 0u && (alo & 0x8000u) == 0u)) elo = 0.0f;    // gate: A_{L-1} > 0
+                        if (!((ahi & 0x7fffu) != 0u && (ahi & 0x8000u) == 0u)) ehi = 0.0f;
+                        ew[j2] = pack_bf16(elo, ehi);
+                        const int f = 32 * half + 8 * c + 2 * j2;
+                        tt_store_t(smem + TT_ET, TT_ET_LBO, f, row, (unsigned short)(ew[j2] & 0xffffu));
+                        tt_store_t(smem + TT_ET, TT_ET_LBO, f + 1, row, (unsigned short)(ew[j2] >> 16));
+                        tt_store_t(smem + TT_AT, TT_AT_LBO, f, row, alo);
+                        tt_store_t(smem + TT_AT, TT_AT_LBO, f + 1, row, ahi);
+                    }
+                    echunk[(4 * half + c) * TC_ROWS + row] = make_uint4(ew[0], ew[1], ew[2], ew[3]);
+                }
+            } else if (half == 0) {
+                // dX_0: the hash encoding's gradient lives in features 0..31 (feature 2*level is used for both features, A9)
+#pragma unroll
+                for (int lv = 0; lv < 16; lv++) gS[row * 16 + lv] = __uint_as_float(v[2 * lv]);
+            }
+            fence_async_smem();
+            tc_fence_before();
+            __syncthreads();
+        }
+        // ---- hash-table gradient (BackpropMrhe, train.comp:947-983): thread (row, half) -> 8 levels ----
+        if (!dropped) {
+            f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
+            f3 np = mrhe_norm_pos(p, sky);
+            float2* dtab = reinterpret_cast<float2*>(m.delta);
+            for (int li = 0; li < 8; li++) {
+                uint32_t level = 8 * half + li;
+                if (level >= m.L) break;
+                uint32_t idx[8];
+                f3 lf;
+                mrhe_level_indices(p, np, m.res[level], m.T, idx, lf);
+                float ng = -gS[row * 16 + level];
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    float xf = (c & 4) ? lf.x : (1.0f - lf.x);
+                    float yf = (c & 2) ? lf.y : (1.0f - lf.y);
+                    float zf = (c & 1) ? lf.z : (1.0f - lf.z);
+                    float dlt = (ng * ((xf * yf) * zf)) * scale;
+                    atomicAdd(dtab + idx[c], make_float2(dlt, dlt));   // no level offset (A10)
+                }
+            }
+        }
+        __syncthreads();   // gS (the forward weight stage) is rewritten by the next tile
+    }
+    // ---- gradients out: TMEM -> this CTA's partial arena (negative gradient times ONE_OVER_PIXEL_COUNT, A8) ----
+    tc_fence_after();
+    if (quad < 2) {
+        const int o = quad * 32 + lane;   // output feature = TMEM lane
+#pragma unroll 1
+        for (int l = 0; l < 5; l++) {
+            uint32_t v[32];
+            tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + TT_DW_COL(l) + (uint32_t)(half * 32), v);
+            tmem_ld_wait();
+            float4* dst = reinterpret_cast<float4*>(partial + NRC_W_OFF(l) + o * 64 + half * 32);
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                dst[j] = make_float4(-__uint_as_float(v[4 * j]) * scale, -__uint_as_float(v[4 * j + 1]) * scale,
+                                     -__uint_as_float(v[4 * j + 2]) * scale, -__uint_as_float(v[4 * j + 3]) * scale);
+            if (half == 1) {
+                uint32_t b[4];
+                tmem_ld4(tmemBase + ((uint32_t)(quad * 32) << 16) + TT_DW_COL(l) + 64u, b);
+                tmem_ld_wait();
+                partial[NRC_B_OFF(l) + o] = -__uint_as_float(b[0]) * scale;
+            }
+        }
+    }
+    if (tid < 192) partial[NRC_W_OFF(5) + (tid >> 6) * 64 + (tid & 63)] = -dw5Acc * scale;
+    else if (tid < 195) partial[NRC_B_OFF(5) + (tid - 192)] = -dw5Acc * scale;
+    if (tid == 0) partial[20995] = lossAcc;
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmemBase, 512);
+}
+
+nrc_status launch_reduce_partials(nrc_mlp* mlp, int blocks, cudaStream_t st);   // mlp_fp32.cu
+
+nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
+                           float* pred, cudaStream_t st)
+{
+    if (n == 0) return NRC_OK;
+    NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
+    NRC_TRY(tc_prepare(mlp, st));
+    static bool attr = false;
+    if (!attr) {
+        NRC_CUDA(cudaFuncSetAttribute(k_train_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
+        attr = true;
+    }
+    size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
+    int blocks = (int)(tiles < (size_t)mlp->ctx->smCount ? tiles : (size_t)mlp->ctx->smCount);
+    if (blocks > mlp->partialBlocks) {
+        if (mlp->partial) NRC_CUDA(cudaFree(mlp->partial));
+        mlp->partial = nullptr;
+        NRC_CUDA(cudaMalloc(&mlp->partial, (size_t)mlp->ctx->smCount * NRC_PARTIAL_STRIDE * sizeof(float)));
+        mlp->partialBlocks = mlp->ctx->smCount;
+    }
+    NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
+               k_train_tc<<<blocks, TC_THREADS, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale,
+                                                                     reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16), mlp->params,
+                                                                     make_mrhe_dev(m), mlp->partial, pred));
+    return launch_reduce_partials(mlp, blocks, st);
 }

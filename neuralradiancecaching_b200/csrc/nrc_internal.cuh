@@ -183,5 +183,7 @@ nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st);
 nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st);
 nrc_status launch_init_normal(nrc_ctx* ctx, float* dst, size_t n, float scale, uint64_t seed);
 // mlp_tc.cu (tcgen05 path)
+nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
+                           float* pred, cudaStream_t st);
 nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n,
                            float* rgb, cudaStream_t st);

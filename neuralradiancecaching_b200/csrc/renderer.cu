@@ -287,7 +287,10 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     NRC_TRY(launch_light(ctx, st, P, r->tpool, false, r->taps + 1));
     NRC_TRY(launch_train_combine(ctx, st, n, r->tpool, r->tp, r->taps, r->totals));
     float lossScale = P.widthFactor * P.heightFactor;   // ONE_OVER_PIXEL_COUNT (nrc-train.comp:210)
-    NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
+    if (ctx->precision == NRC_MLP_BF16_TC)
+        NRC_TRY(launch_train_tc(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
+    else
+        NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
     return NRC_OK;
 }
 

@@ -36,7 +36,11 @@ __global__ void __launch_bounds__(256) k_nrc_step(float* __restrict__ params, fl
     if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {   // operand image of the tcgen05 path (layout: mlp_tc.cu)
         int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
         int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
-        imgBf16[dst] = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
+        unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
+        imgBf16[dst] = h;
+        // transposed image (rows = in, K = out); layer 5 has K = 16
+        int dstT = (5 * 4096 + 1024) + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7);
+        imgBf16[dstT] = h;
     }
 }
 
