@@ -4,6 +4,7 @@ csrc/      CUDA kernels + the C-ABI (include/nrc_b200.h)  -> libnrc_b200.so
 api.py     NeuralRadianceCache, MRHE and the stand-alone operators
 objects.py Camera, DirLight, PointLight, VolumeData, HdrEnvMap
 renderer.py NrcHpmRenderer
+loaders.py ReadFileDensity3D, ReadFileHdr4f (src/read_file.cpp); dist.py data-parallel plumbing
 """
 from . import _lib
 from ._lib import NrcError, PARAM_COUNT
@@ -11,3 +12,4 @@ from .api import (Context, NeuralRadianceCache, MRHE, mrhe_resolutions, encode, 
                   optimizer_step)
 from .objects import Camera, DirLight, PointLight, VolumeData, HdrEnvMap, hdr4f_to_cdf, vec_from_angles
 from .renderer import NrcHpmRenderer
+from .loaders import ReadFileDensity3D, ReadFileHdr4f

@@ -8,7 +8,9 @@
 
 // dynamic shared memory requested (and not used) by the kernels that may run beside the train walk, so that an SM whose
 // shared memory the train walk has reserved (NRC_TRAIN_SMS) cannot take their blocks
-#define NRC_PAD_SMEM 2048
+// (only when SMs are reserved: the padding costs the render walk ~10 % through the L1 carve-out)
+static size_t g_padSmem = 0;
+#define NRC_PAD_SMEM g_padSmem
 
 // ---- small device helpers ---------------------------------------------------------------------------------------
 
@@ -577,6 +579,7 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
         e = getenv("NRC_TRAIN_SMS");           // SMs reserved for the train walk; 0 = share the machine
         smsEnv = e ? atoi(e) : 0;
         if (smsEnv < 0 || smsEnv > ctx->smCount) smsEnv = 0;
+        g_padSmem = smsEnv > 0 ? 2048 : 0;
         NRC_CUDA(cudaFuncSetAttribute(k_train_walk, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
     const uint32_t lanes = (uint32_t)lanesEnv;
