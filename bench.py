@@ -215,6 +215,30 @@ def run_b200(args):
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = max(e0.elapsed_time(e1), 0.0)
     tot_e2e = r.totals(reset=True)
+    if os.environ.get("NRC_BENCH_TIMELINE") and rank == 0:      # kernel timeline of two more frames (both streams), to stderr
+        ctx.profile(True)
+    if os.environ.get("NRC_BENCH_TIMELINE"):
+        for _ in range(2):
+            frame(next(ri))
+        barrier()
+        if rank == 0:
+            for name, s0, s1 in ctx.profile_timeline():
+                sys.stderr.write("TIMELINE %-18s %8.3f -> %8.3f  (%.3f ms)\n" % (name, s0, s1, s1 - s0))
+            ctx.profile(False)
+        r.totals(reset=True)
+        if world > 1:      # the exchange alone, ranks aligned: pure collective cost
+            barrier()
+            x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(ext):
+                x0.record()
+            for _ in range(50):
+                exchange()
+            with torch.cuda.stream(ext):
+                x1.record()
+            barrier()
+            if rank == 0:
+                sys.stderr.write("TIMELINE exchange alone: %.1f us per frame (2 all-reduces)\n" % (x0.elapsed_time(x1) / 50 * 1e3))
+            nrc.set_state(delta=np.zeros(20995, np.float32)); mrhe.set_tables(delta=np.zeros(mrhe.count, np.float32))
     # ---- the same frames with the fp32 CUDA-core MLP (the 1e-3 parity path), reported beside the headline ----
     fp32_ms = None
     if args.precision == "bf16" and not args.no_fp32_line:
