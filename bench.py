@@ -141,9 +141,10 @@ def run_b200(args):
     if world > 1:
         r.SetPartitionStrided(rank, world, rank, world)
 
-    from neuralradiancecaching_b200.dist import GradientExchange
+    from neuralradiancecaching_b200.dist import GradientExchange, FusedExchange
     exchange = GradientExchange(ctx, nrc, mrhe, torch.device("cuda", local))
     ext = exchange.stream
+    fused = FusedExchange(nrc, mrhe, rank, world, torch.device("cuda", local)) if (world > 1 and args.exchange == "fused") else None
 
     def frame(random4):
         vol.Update(random4=random4)
@@ -152,8 +153,11 @@ def run_b200(args):
             r.Render()
         else:
             r.FrameTrain()
-            exchange()                       # NCCL all-reduce of the MLP gradient arena (+loss) and the delta-table head
-            N.optimizer_step(nrc, mrhe)
+            if fused is not None:
+                fused()                      # one kernel: peer-memory sum over NVLink + nrc-step + mrhe-step (csrc/dp.cu)
+            else:
+                exchange()                   # NCCL all-reduce of the MLP gradient arena (+loss) and the delta-table head
+                N.optimizer_step(nrc, mrhe)
             r.FrameRender()
 
     def barrier():
@@ -174,8 +178,9 @@ def run_b200(args):
     launches0 = ctx.launch_count()
     ctx.profile(True)
     ctx.profile_read(reset=True)
-    sampler = ClockSampler(local)
-    sampler.start()
+    sampler = ClockSampler(local)      # rank 0 only: N concurrent nvidia-smi pollers perturb the ranks they poll
+    if rank == 0:
+        sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(ext):
         ev0.record()
@@ -424,7 +429,9 @@ def finish_b200(args, v):
         "config": {"workload": "cloud_sixteenth (synthetic 125x85x153 stand-in) %dx%d 1 spp, online NRC training %dx%d samples/frame, "
                                "dir+point+env lights, useNN=1" % (W, H, v["TW"], v["TH"]),
                    "frame": [W, H], "train_grid": [v["TW"], v["TH"]], "hash_table": [16, 16384, 2], "mlp": "64x5->3 relu",
-                   "parallelism": "rows interleaved over %d GPU(s), train samples sharded, NCCL all-reduce of gradients" % world,
+                   "parallelism": "rows interleaved over %d GPU(s), train samples sharded, %s" % (
+                       world, "gradients summed over NVLink peer memory inside the fused step kernel" if (world > 1 and args.exchange == "fused")
+                       else "NCCL all-reduce of gradients"),
                    "l2": "fresh per-frame RNG seed: every frame traces new paths; per-frame buffers (%.0f MB) exceed nothing but are rewritten, "
                          "the density grid (3.4 MB) is L2-resident by design" % (W * H * 120 / 1e6)},
         "e2e": {"value": units_e2e / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / K,
@@ -549,6 +556,8 @@ def main():
                     help="MLP arithmetic: bf16 = tcgen05 tensor cores (bf16 operands, fp32 accumulate; north_star's tensor-core path), "
                          "fp32 = CUDA-core 1e-3 parity path.  Tracing is fp32 either way.")
     ap.add_argument("--no-fp32-line", action="store_true", help="skip the extra fp32-path measurement")
+    ap.add_argument("--exchange", default=os.environ.get("NRC_EXCHANGE", "nccl"), choices=["nccl", "fused"],
+                    help="multi-GPU gradient exchange: two NCCL all-reduces + step kernels, or the fused peer-memory kernel (csrc/dp.cu)")
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

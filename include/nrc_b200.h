@@ -224,6 +224,24 @@ NRC_API nrc_status nrc_read_frame(nrc_renderer* r, void* dst /*[h|d]*/, nrc_fram
 NRC_API nrc_status nrc_read_frame_partition(nrc_renderer* r, void* dst /*[h|d]*/, nrc_frame_format fmt);
 NRC_API size_t nrc_frame_partition_bytes(nrc_renderer* r, nrc_frame_format fmt);
 
+/* ---- data-parallel exchange fused with the optimiser steps (the reference is single-GPU) ----
+ * One process per GPU.  Every rank creates an nrc_dp for its replica, publishes nrc_dp_handle_bytes() opaque bytes
+ * (nrc_dp_export; CUDA-IPC handles of its gradient arenas and flag block), gathers the handles of all ranks in rank
+ * order by whatever transport the host has (torch.distributed, MPI, a file) and calls nrc_dp_connect.  After that
+ * nrc_dp_reduce_step replaces {all-reduce(MLP gradients), all-reduce(delta-table head), nrc-step, mrhe-step} of
+ * one frame by one kernel per rank that reads the peers' gradients over NVLink, sums them in rank order and
+ * applies both steps (src/NeuralRadianceCache.cpp:512-539 and src/MRHE.cpp:189-225 are the single-GPU steps it
+ * subsumes).  Every rank must call it once per frame; the kernels wait for each other on the device. */
+typedef struct nrc_dp nrc_dp;
+NRC_API size_t nrc_dp_handle_bytes(void);
+NRC_API nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int world, nrc_dp** out);
+NRC_API nrc_status nrc_dp_export(nrc_dp* dp, void* handle /*host, nrc_dp_handle_bytes()*/);
+NRC_API nrc_status nrc_dp_connect(nrc_dp* dp, const void* allHandles /*host, world handles in rank order*/, int sameProcess);
+NRC_API nrc_status nrc_dp_reduce_step(nrc_dp* dp);
+/* replicas inside one process (single-GPU parity test): phase 0 on every replica, then phase 1 on every replica */
+NRC_API nrc_status nrc_dp_reduce_step_phase(nrc_dp* dp, int phase);
+NRC_API nrc_status nrc_dp_destroy(nrc_dp* dp);
+
 /* Parity probes of the last frame (rows/invocations of this rank's partition only are meaningful):
  *   counters[h*w][4] = {randDraws, litVertices, walkSteps, queryEmitted}
  *   query[h*w][8]    = {pos.xyz, dir.xyz, weight, valid}

@@ -49,7 +49,8 @@ nrc_renderer_set_camera nrc_renderer_set_dir_light nrc_renderer_set_point_light 
 nrc_render nrc_frame_train nrc_frame_render nrc_frame_bytes nrc_frame_ptr nrc_read_frame nrc_read_render_probes
 nrc_read_train_probes nrc_frame_stats nrc_frame_totals nrc_renderer_set_partition_strided nrc_read_frame_partition
 nrc_frame_partition_bytes nrc_kernel_count nrc_kernel_name
-nrc_ctx_profile_enable nrc_ctx_profile_read nrc_ctx_profile_timeline""".split()
+nrc_ctx_profile_enable nrc_ctx_profile_read nrc_ctx_profile_timeline nrc_dp_handle_bytes nrc_dp_create nrc_dp_export
+nrc_dp_connect nrc_dp_reduce_step nrc_dp_reduce_step_phase nrc_dp_destroy""".split()
 
 _lib = None
 
@@ -68,7 +69,8 @@ def lib():
         L.nrc_ctx_launch_count.restype = C.c_uint64
         for n in ("nrc_mlp_grad_ptr", "nrc_mrhe_grad_ptr", "nrc_frame_ptr"):
             getattr(L, n).restype = C.c_void_p
-        for n in ("nrc_mlp_grad_count", "nrc_mrhe_table_bytes", "nrc_mrhe_grad_extent", "nrc_frame_bytes", "nrc_frame_partition_bytes"):
+        for n in ("nrc_mlp_grad_count", "nrc_mrhe_table_bytes", "nrc_mrhe_grad_extent", "nrc_frame_bytes", "nrc_frame_partition_bytes",
+                  "nrc_dp_handle_bytes"):
             getattr(L, n).restype = C.c_size_t
         _lib = L
     return _lib

@@ -97,7 +97,7 @@ static const char* const g_kernelNames[K_COUNT] = {
     "k_encode_pos", "k_encode_dir", "k_infer_fp32", "k_train_fp32", "k_reduce_partials", "k_transpose_weights", "k_nrc_step",
     "k_mrhe_step", "k_init_normal", "k_render_walk", "k_train_walk", "k_light<render>", "k_light<train>", "k_render_combine",
     "k_train_combine", "k_composite", "k_build_bricks", "k_volume_sample", "k_pack_records", "k_cdf_rows", "k_cdf_y",
-    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc"};
+    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc", "k_dp_reduce_step"};
 
 void nrc_prof_begin(nrc_ctx* ctx, cudaStream_t st, int kid)
 {
@@ -211,6 +211,10 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prHigh));
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prLow));
+    // the train trace is the long pole of the frame: just below the main stream (whose kernels are short), above the render trace
+    NRC_CUDA(cudaStreamCreateWithPriority(&c->stream3, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainTrace, cudaEventDisableTiming));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
     *out = c;
@@ -223,6 +227,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->stream2);
+    cudaStreamSynchronize(c->stream3);
     for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
     if (c->pinned) cudaFreeHost(c->pinned);
     prof_drain(c);
@@ -231,6 +236,9 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaEventDestroy(c->evJoin);
     cudaStreamDestroy(c->stream);
     cudaStreamDestroy(c->stream2);
+    cudaStreamDestroy(c->stream3);
+    cudaEventDestroy(c->evTrainTrace);
+    cudaEventDestroy(c->evTrainFree);
     delete c;
     return NRC_OK;
 }

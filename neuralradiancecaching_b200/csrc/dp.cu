@@ -1,0 +1,304 @@
+// dp.cu -- data-parallel gradient exchange fused with the optimiser steps, over NVLink peer memory.
+//
+// What the NCCL path does with four launches per frame (all-reduce of the MLP gradient arena, all-reduce of the touched
+// head of the delta hash table, nrc-step, mrhe-step) this does with ONE kernel per rank: every rank maps its peers'
+// gradient arenas (CUDA IPC), and the kernel
+//   1. tells every peer "my gradients are complete" and waits for the same from all of them (flags in peer memory,
+//      release/acquire at system scope),
+//   2. for each parameter reads the W gradients straight from the W GPUs (ld.relaxed.sys over NVLink), adds them in RANK
+//      ORDER -- so every replica computes bit-identical sums, which a ring all-reduce does not promise -- and applies
+//      nrc-step.comp / mrhe-step.comp to its own replica in the same thread,
+//   3. tells every peer "I have read your gradients", waits for all, and clears its own arenas.
+// The exchange is 84 KB + 2*T*4 B: latency-bound (the two NCCL all-reduces alone measure 60 us at 4 GPUs), so the kernel is
+// 16 small blocks that each own a fixed slice of both arenas and handshake with the same block of the peers -- small
+// blocks get an SM slot at once while the render chain fills the GPU, and nothing needs a grid-wide barrier.  For hash tables whose touched head is larger than NRC_DP_MAX_HEAD floats the
+// host falls back to the NCCL path (bandwidth-bound regime).
+// The reference has no multi-GPU path at all; the step arithmetic is the one of steps.cu (nrc-step.comp:200-406,
+// mrhe-step.comp:27-74).
+#include <cuda_bf16.h>
+#include <string.h>
+#include "nrc_internal.cuh"
+
+#define NRC_DP_MAX_WORLD 16
+#define NRC_DP_MAX_HEAD (1u << 20)
+#define NRC_DP_FLAG_COUNT (16 * NRC_DP_MAX_WORLD * 2)
+
+struct nrc_dp {
+    nrc_mlp* mlp = nullptr;
+    nrc_mrhe* mrhe = nullptr;
+    int rank = 0, world = 1;
+    unsigned* flags = nullptr;                 // [DP_BLOCKS][NRC_DP_MAX_WORLD][2], written by the peers
+    unsigned epoch = 0;
+    bool connected = false, sameProcess = false;
+    const float* peerGrad[NRC_DP_MAX_WORLD] = {nullptr};
+    const float* peerDelta[NRC_DP_MAX_WORLD] = {nullptr};
+    unsigned* peerFlags[NRC_DP_MAX_WORLD] = {nullptr};
+    void* opened[NRC_DP_MAX_WORLD][3] = {{nullptr}};
+};
+
+struct DpHandle {   // what one rank publishes to the others
+    cudaIpcMemHandle_t grad, delta, flags;
+    unsigned long long rawGrad, rawDelta, rawFlags;   // same-process emulation
+    unsigned long long extent;
+    int rank, pad;
+};
+
+struct DpArgs {
+    const float* peerGrad[NRC_DP_MAX_WORLD];
+    const float* peerDelta[NRC_DP_MAX_WORLD];
+    unsigned* peerFlags[NRC_DP_MAX_WORLD];
+    unsigned* myFlags;
+    int rank, world;
+    unsigned epoch;
+    int barriers, clear, doStep;   // clear: 1 = clear arenas + publish the global loss, 2 = clear arenas only
+    float* params; float* grad; float* momentum; float* paramsT; unsigned short* imgBf16;
+    float lr, wd, beta1;
+    float* tables; float* delta; unsigned extent;
+    float mlr, mwd;
+};
+
+__device__ __forceinline__ float4 ld_sys4(const float* p)
+{
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ bool dp_bad(float x) { return (x != x) || (fabsf(x) == INFINITY) || (fabsf(x) > 1000.0f); }
+__device__ __forceinline__ float dp_sign(float x) { return (x > 0.0f) ? 1.0f : ((x < 0.0f) ? -1.0f : 0.0f); }
+
+// Block b of every rank owns the same slice of both arenas, so the handshakes are per block: block b signals slot
+// (b, rank, which) of every peer and waits until block b of every peer has signalled its own.  No grid-wide barrier.
+__device__ __forceinline__ void dp_barrier(const DpArgs& a, int which)
+{
+    __syncthreads();
+    if ((int)threadIdx.x < a.world) {
+        __threadfence_system();
+        unsigned slot = (blockIdx.x * NRC_DP_MAX_WORLD) * 2;
+        st_release_sys(a.peerFlags[threadIdx.x] + slot + a.rank * 2 + which, a.epoch);
+        while ((int)(ld_acquire_sys(a.myFlags + slot + threadIdx.x * 2 + which) - a.epoch) < 0) __nanosleep(32);
+    }
+    __syncthreads();
+}
+
+// sum of one float4 over the ranks, in rank order; all W loads are in flight before the first add
+__device__ __forceinline__ float4 dp_sum4(const float* const* peers, int world, size_t i4)
+{
+    float4 v[NRC_DP_MAX_WORLD];
+#pragma unroll
+    for (int r = 0; r < NRC_DP_MAX_WORLD; r++)
+        if (r < world) v[r] = ld_sys4(peers[r] + i4 * 4);
+    float4 g = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+    for (int r = 0; r < NRC_DP_MAX_WORLD; r++)
+        if (r < world) { g.x = __fadd_rn(g.x, v[r].x); g.y = __fadd_rn(g.y, v[r].y); g.z = __fadd_rn(g.z, v[r].z); g.w = __fadd_rn(g.w, v[r].w); }
+    return g;
+}
+
+__device__ __forceinline__ void dp_nrc_update(const DpArgs& a, int i, float g)
+{
+    float w = a.params[i];
+    if (dp_bad(g)) g = __fmul_rn(1000.0f, dp_sign(g));
+    g = __fadd_rn(g, __fmul_rn(-w, a.wd));
+    float d = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, a.beta1), g), __fmul_rn(a.beta1, a.momentum[i]));
+    a.momentum[i] = d;
+    float nw = __fadd_rn(w, __fmul_rn(d, a.lr));
+    if (i < NRC_MLP_WEIGHT_COUNT && dp_bad(nw)) nw = 0.0f;
+    a.params[i] = nw;
+    if (i < 5 * 4096) {
+        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+        a.paramsT[l * 4096 + k * 64 + o] = nw;
+    }
+    if (a.imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {   // both operand images of the tcgen05 path, as k_nrc_step
+        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+        int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
+        unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
+        a.imgBf16[dst] = h;
+        a.imgBf16[(5 * 4096 + 1024) + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7)] = h;
+    }
+}
+
+__device__ __forceinline__ float dp_mrhe_update(float w, float g, float lr, float wd)
+{
+    if (dp_bad(g)) g = __fmul_rn(100.0f, dp_sign(g));
+    g = __fadd_rn(g, __fmul_rn(-w, wd));
+    float nw = __fadd_rn(w, __fmul_rn(g, lr));
+    return dp_bad(nw) ? 0.0f : nw;
+}
+
+#define DP_BLOCKS 16
+#define DP_THREADS 256
+#define DP_MLP_VEC ((NRC_MLP_PARAM_COUNT + 1 + 3) / 4)   // 5249 float4: 20995 gradients + the loss accumulator
+
+__global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_constant__ DpArgs a)
+{
+    const int t = blockIdx.x * DP_THREADS + threadIdx.x;
+    const int stride = DP_BLOCKS * DP_THREADS;
+    if (a.barriers) dp_barrier(a, 0);
+    float lossSum = 0.0f;
+    if (a.doStep) {
+        // ---- MLP arena: sum over ranks in rank order, then nrc-step.comp for this replica ----
+        for (int i4 = t; i4 < DP_MLP_VEC; i4 += stride) {
+            float4 g = dp_sum4(a.peerGrad, a.world, i4);
+            float gs[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                int i = i4 * 4 + c;
+                if (i < NRC_MLP_PARAM_COUNT) dp_nrc_update(a, i, gs[c]);
+                else if (i == NRC_MLP_PARAM_COUNT) lossSum = gs[c];
+            }
+        }
+        // ---- head of the delta hash table (all Backprop can touch): sum + mrhe-step.comp ----
+        for (unsigned i4 = t; i4 < a.extent / 4; i4 += stride) {
+            float4 g = dp_sum4(a.peerDelta, a.world, i4);
+            float4 w = reinterpret_cast<const float4*>(a.tables)[i4];
+            w.x = dp_mrhe_update(w.x, g.x, a.mlr, a.mwd);
+            w.y = dp_mrhe_update(w.y, g.y, a.mlr, a.mwd);
+            w.z = dp_mrhe_update(w.z, g.z, a.mlr, a.mwd);
+            w.w = dp_mrhe_update(w.w, g.w, a.mlr, a.mwd);
+            reinterpret_cast<float4*>(a.tables)[i4] = w;
+        }
+    }
+    if (a.barriers) dp_barrier(a, 1);     // block b of every peer has read my slice b
+    if (a.clear) {
+        for (int i4 = t; i4 < DP_MLP_VEC; i4 += stride) {
+            float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (i4 == DP_MLP_VEC - 1) {   // {b5[0..2] gradients, loss}: every rank reports the global loss
+                float own = a.grad[NRC_MLP_PARAM_COUNT];
+                z.w = (a.clear == 1) ? lossSum : own;
+            }
+            reinterpret_cast<float4*>(a.grad)[i4] = z;
+        }
+        for (unsigned i4 = t; i4 < a.extent / 4; i4 += stride) reinterpret_cast<float4*>(a.delta)[i4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------------------------------------------
+nrc_status launch_mrhe_step_range(nrc_mrhe* m, size_t firstFloat, cudaStream_t st);   // steps.cu
+
+extern "C" size_t nrc_dp_handle_bytes(void) { return sizeof(DpHandle); }
+
+extern "C" nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int world, nrc_dp** out)
+{
+    NRC_REQUIRE(mlp && mrhe && out, "null argument");
+    NRC_REQUIRE(world >= 1 && world <= NRC_DP_MAX_WORLD && rank >= 0 && rank < world, "rank/world out of range");
+    NRC_REQUIRE(nrc_mrhe_grad_extent(mrhe) <= NRC_DP_MAX_HEAD, "delta-table head too large for the fused exchange; use the NCCL path");
+    nrc_dp* d = new nrc_dp();
+    d->mlp = mlp; d->mrhe = mrhe; d->rank = rank; d->world = world;
+    cudaError_t e = cudaMalloc(&d->flags, sizeof(unsigned) * NRC_DP_FLAG_COUNT);
+    if (e == cudaSuccess) e = cudaMemset(d->flags, 0, sizeof(unsigned) * NRC_DP_FLAG_COUNT);
+    if (e != cudaSuccess) {
+        nrc_set_error("nrc_dp_create: %s", cudaGetErrorString(e));
+        delete d;
+        return NRC_ERR_CUDA;
+    }
+    *out = d;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_dp_export(nrc_dp* d, void* handle)
+{
+    NRC_REQUIRE(d && handle, "null argument");
+    DpHandle h;
+    memset(&h, 0, sizeof(h));
+    NRC_CUDA(cudaIpcGetMemHandle(&h.grad, d->mlp->grad));
+    NRC_CUDA(cudaIpcGetMemHandle(&h.delta, d->mrhe->delta));
+    NRC_CUDA(cudaIpcGetMemHandle(&h.flags, d->flags));
+    h.rawGrad = (unsigned long long)(uintptr_t)d->mlp->grad;
+    h.rawDelta = (unsigned long long)(uintptr_t)d->mrhe->delta;
+    h.rawFlags = (unsigned long long)(uintptr_t)d->flags;
+    h.extent = nrc_mrhe_grad_extent(d->mrhe);
+    h.rank = d->rank;
+    memcpy(handle, &h, sizeof(h));
+    return NRC_OK;
+}
+
+// allHandles: world handles in rank order.  sameProcess != 0: the "ranks" are replicas inside this process (raw device
+// pointers are used; the single-GPU parity test runs the exchange that way).
+extern "C" nrc_status nrc_dp_connect(nrc_dp* d, const void* allHandles, int sameProcess)
+{
+    NRC_REQUIRE(d && allHandles, "null argument");
+    NRC_REQUIRE(!d->connected, "already connected");
+    const DpHandle* hs = static_cast<const DpHandle*>(allHandles);
+    size_t extent = nrc_mrhe_grad_extent(d->mrhe);
+    for (int r = 0; r < d->world; r++) {
+        NRC_REQUIRE(hs[r].rank == r, "handles are not in rank order");
+        NRC_REQUIRE(hs[r].extent == extent, "ranks disagree on the hash-table shape");
+        if (r == d->rank) {
+            d->peerGrad[r] = d->mlp->grad; d->peerDelta[r] = d->mrhe->delta; d->peerFlags[r] = d->flags;
+        } else if (sameProcess) {
+            d->peerGrad[r] = (const float*)(uintptr_t)hs[r].rawGrad;
+            d->peerDelta[r] = (const float*)(uintptr_t)hs[r].rawDelta;
+            d->peerFlags[r] = (unsigned*)(uintptr_t)hs[r].rawFlags;
+        } else {
+            NRC_CUDA(cudaIpcOpenMemHandle(&d->opened[r][0], hs[r].grad, cudaIpcMemLazyEnablePeerAccess));
+            NRC_CUDA(cudaIpcOpenMemHandle(&d->opened[r][1], hs[r].delta, cudaIpcMemLazyEnablePeerAccess));
+            NRC_CUDA(cudaIpcOpenMemHandle(&d->opened[r][2], hs[r].flags, cudaIpcMemLazyEnablePeerAccess));
+            d->peerGrad[r] = (const float*)d->opened[r][0];
+            d->peerDelta[r] = (const float*)d->opened[r][1];
+            d->peerFlags[r] = (unsigned*)d->opened[r][2];
+        }
+    }
+    d->connected = true;
+    d->sameProcess = sameProcess != 0;
+    return NRC_OK;
+}
+
+static nrc_status dp_launch(nrc_dp* d, int barriers, int clear, bool reduce)
+{
+    NRC_REQUIRE(d && d->connected, "nrc_dp_connect first");
+    nrc_ctx* ctx = d->mlp->ctx;
+    DpArgs a;
+    memset(&a, 0, sizeof(a));
+    for (int r = 0; r < d->world; r++) { a.peerGrad[r] = d->peerGrad[r]; a.peerDelta[r] = d->peerDelta[r]; a.peerFlags[r] = d->peerFlags[r]; }
+    a.myFlags = d->flags; a.rank = d->rank; a.world = d->world; a.doStep = reduce ? 1 : 0;
+    if (barriers) d->epoch++;
+    a.epoch = d->epoch; a.barriers = barriers; a.clear = clear;
+    a.params = d->mlp->params; a.grad = d->mlp->grad; a.momentum = d->mlp->momentum; a.paramsT = d->mlp->paramsT;
+    a.imgBf16 = d->mlp->paramsBf16;   // kept in step with params whenever it exists, like launch_nrc_step
+    a.lr = d->mlp->lr; a.wd = d->mlp->wd; a.beta1 = d->mlp->beta1;
+    a.tables = d->mrhe->tables; a.delta = d->mrhe->delta; a.extent = (unsigned)nrc_mrhe_grad_extent(d->mrhe);
+    a.mlr = d->mrhe->lr; a.mwd = d->mrhe->wd;
+    NRC_LAUNCH(ctx, ctx->stream, K_DP_REDUCE_STEP, k_dp_reduce_step<<<DP_BLOCKS, DP_THREADS, 0, ctx->stream>>>(a));
+    return NRC_OK;
+}
+
+// One frame's exchange + both optimiser steps.  Multi-process: every rank calls this once per frame, on its own GPU; the
+// kernel waits (on the device) for the peers' kernels of the same frame.
+extern "C" nrc_status nrc_dp_reduce_step(nrc_dp* d)
+{
+    NRC_REQUIRE(d && d->connected, "nrc_dp_connect first");
+    NRC_REQUIRE(!d->sameProcess || d->world == 1, "same-process replicas: use nrc_dp_reduce_step_phase");
+    NRC_TRY(dp_launch(d, d->world > 1, 1, true));
+    return launch_mrhe_step_range(d->mrhe, nrc_mrhe_grad_extent(d->mrhe), d->mrhe->ctx->stream);
+}
+
+// Same-process replicas (tests): phase 0 = reduce + step without barriers or clearing, for every replica; then phase 1 =
+// clear + tail step, for every replica.  The loss accumulator is left per replica in this mode.
+extern "C" nrc_status nrc_dp_reduce_step_phase(nrc_dp* d, int phase)
+{
+    NRC_REQUIRE(d && d->connected, "nrc_dp_connect first");
+    NRC_REQUIRE(phase == 0 || phase == 1, "phase must be 0 or 1");
+    if (phase == 0) return dp_launch(d, 0, 0, true);
+    NRC_TRY(dp_launch(d, 0, 2, false));
+    return launch_mrhe_step_range(d->mrhe, nrc_mrhe_grad_extent(d->mrhe), d->mrhe->ctx->stream);
+}
+
+extern "C" nrc_status nrc_dp_destroy(nrc_dp* d)
+{
+    if (!d) return NRC_OK;
+    cudaStreamSynchronize(d->mlp->ctx->stream);
+    for (int r = 0; r < NRC_DP_MAX_WORLD; r++)
+        for (int k = 0; k < 3; k++)
+            if (d->opened[r][k]) cudaIpcCloseMemHandle(d->opened[r][k]);
+    cudaFree(d->flags);
+    delete d;
+    return NRC_OK;
+}

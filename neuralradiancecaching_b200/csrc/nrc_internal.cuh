@@ -42,7 +42,7 @@ void nrc_set_error(const char* fmt, ...);
 enum NrcKernelId {
     K_ENCODE_POS = 0, K_ENCODE_DIR, K_INFER_FP32, K_TRAIN_FP32, K_REDUCE_PARTIALS, K_TRANSPOSE_WEIGHTS, K_NRC_STEP, K_MRHE_STEP,
     K_INIT_NORMAL, K_RENDER_WALK, K_TRAIN_WALK, K_LIGHT_RENDER, K_LIGHT_TRAIN, K_RENDER_COMBINE, K_TRAIN_COMBINE, K_COMPOSITE,
-    K_BUILD_BRICKS, K_VOLUME_SAMPLE, K_PACK_RECORDS, K_CDF_ROWS, K_CDF_Y, K_INFER_TC, K_TRAIN_TC, K_PACK_BF16, K_MISC,
+    K_BUILD_BRICKS, K_VOLUME_SAMPLE, K_PACK_RECORDS, K_CDF_ROWS, K_CDF_Y, K_INFER_TC, K_TRAIN_TC, K_PACK_BF16, K_MISC, K_DP_REDUCE_STEP,
     K_COUNT
 };
 
@@ -54,7 +54,9 @@ struct nrc_ctx {
     int smCount = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t stream2 = nullptr;       // second stream: render walk overlaps the training chain
+    cudaStream_t stream3 = nullptr;       // third stream: the train TRACE of frame k+1 (needs no weights) runs ahead of frame k's MLP tail
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    cudaEvent_t evTrainTrace = nullptr, evTrainFree = nullptr;
     nrc_mlp_precision precision = NRC_MLP_FP32;
     uint64_t launches = 0;
     // per-kernel event timing (off by default; bench.py turns it on over its timed region)

@@ -1,9 +1,10 @@
 // renderer.cu -- nrc_renderer: the frame graph that replaces NrcHpmRenderer's recorded command buffer
 // (src/NrcHpmRenderer.cpp:571-730): train -> nrc-step -> mrhe-step -> render.
 //
-//   stream  : train walk -> light -> combine -> fused encode+MLP fwd/bwd -> [host all-reduce] -> steps
+//   stream3 : train walk -> light -> combine                                       (independent of the weights: runs AHEAD,
+//             frame k+1's trace overlaps frame k's steps / exchange wait / inference / composite)
+//   stream  : fused encode+MLP fwd/bwd -> [gradient exchange] -> steps -> batched inference -> composite
 //   stream2 : render walk -> light -> combine (compacts the NRC queries)           (independent of the weights)
-//   join    : batched inference over the compacted queries -> composite
 #include <math.h>
 #include <string.h>
 #include <stdlib.h>
@@ -44,6 +45,7 @@ struct nrc_renderer {
     uint32_t* hostScalars = nullptr;      // pinned mirror
     unsigned long long* hostTaps = nullptr;
     bool framePending = false;            // evFork marks the end of the previous frame's composite
+    bool trainPending = false;            // evTrainFree marks the end of the previous frame's train kernel (records consumed)
 };
 
 #define FREE(p) do { if (p) { cudaFree(p); (p) = nullptr; } } while (0)
@@ -168,6 +170,7 @@ extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
     if (!r) return NRC_OK;
     cudaStreamSynchronize(r->ctx->stream);
     cudaStreamSynchronize(r->ctx->stream2);
+    cudaStreamSynchronize(r->ctx->stream3);
     free_frame(r);
     free_train(r);
     FREE(r->scalars); FREE(r->taps); FREE(r->totals);
@@ -224,6 +227,7 @@ extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t heigh
     NRC_REQUIRE(r && width > 0 && height > 0, "bad size");
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
     r->width = width; r->height = height;
     r->y0 = r->ystride > 1 ? r->y0 : 0; r->y1 = height;
     return alloc_frame(r, r->sppAlloc ? r->sppAlloc : 1, (uint32_t)((size_t)width * height * 4));
@@ -281,16 +285,31 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     uint32_t n = part_count(r->i0, r->i1, r->istride);
     if (n == 0) return NRC_OK;
     TraceParams P = make_params(r);
-    NRC_CUDA(cudaMemsetAsync(r->scalars + 2, 0, 2 * sizeof(uint32_t), st));
-    NRC_CUDA(cudaMemsetAsync(r->taps + 1, 0, sizeof(unsigned long long), st));
-    NRC_TRY(launch_train_walk(ctx, st, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
-    NRC_TRY(launch_light(ctx, st, P, r->tpool, false, r->taps + 1));
-    NRC_TRY(launch_train_combine(ctx, st, n, r->tpool, r->tp, r->taps, r->totals));
+    // The trace half (walk, lights, combine) reads no weights: it runs on stream3 and may start while the previous frame's
+    // steps, inference and composite are still on the main stream -- and, on several GPUs, while that frame's exchange
+    // waits for the slowest rank.  It only needs the previous train kernel to have consumed the records.
+    static int noOverlap = -1;
+    if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
+    cudaStream_t tt = (noOverlap || getenv("NRC_NO_TRAIN_AHEAD")) ? st : ctx->stream3;
+    if (tt != st && r->trainPending) NRC_CUDA(cudaStreamWaitEvent(tt, ctx->evTrainFree, 0));
+    NRC_CUDA(cudaMemsetAsync(r->scalars + 2, 0, 2 * sizeof(uint32_t), tt));
+    NRC_CUDA(cudaMemsetAsync(r->taps + 1, 0, sizeof(unsigned long long), tt));
+    NRC_TRY(launch_train_walk(ctx, tt, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
+    NRC_TRY(launch_light(ctx, tt, P, r->tpool, false, r->taps + 1));
+    NRC_TRY(launch_train_combine(ctx, tt, n, r->tpool, r->tp, r->taps, r->totals));
+    if (tt != st) {
+        NRC_CUDA(cudaEventRecord(ctx->evTrainTrace, tt));
+        NRC_CUDA(cudaStreamWaitEvent(st, ctx->evTrainTrace, 0));
+    }
     float lossScale = P.widthFactor * P.heightFactor;   // ONE_OVER_PIXEL_COUNT (nrc-train.comp:210)
     if (ctx->precision == NRC_MLP_BF16_TC)
         NRC_TRY(launch_train_tc(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
     else
         NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
+    if (tt != st) {
+        NRC_CUDA(cudaEventRecord(ctx->evTrainFree, st));
+        r->trainPending = true;
+    }
     return NRC_OK;
 }
 
@@ -468,6 +487,7 @@ extern "C" nrc_status nrc_frame_totals(nrc_renderer* r, uint64_t totals[6], int 
 {
     NRC_REQUIRE(r && totals, "null argument");
     nrc_ctx* ctx = r->ctx;
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     unsigned long long t[6];
@@ -481,6 +501,7 @@ extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, u
 {
     NRC_REQUIRE(r, "null renderer");
     nrc_ctx* ctx = r->ctx;
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));

@@ -110,6 +110,21 @@ nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
     return NRC_OK;
 }
 
+// tail [firstFloat, count) of the tables: the part of mrhe-step the fused data-parallel kernel (dp.cu) leaves to this one
+nrc_status launch_mrhe_step_range(nrc_mrhe* m, size_t firstFloat, cudaStream_t st)
+{
+    if (firstFloat >= m->count) return NRC_OK;
+    size_t n4 = (m->count - firstFloat) / 4;
+    size_t want = (n4 + 255) / 256;
+    size_t cap = (size_t)m->ctx->smCount * 8;
+    unsigned blocks = (unsigned)(want < cap ? want : cap);
+    if (blocks == 0) return NRC_OK;
+    NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
+               k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables + firstFloat),
+                                                   reinterpret_cast<float4*>(m->delta + firstFloat), n4, m->lr, m->wd));
+    return NRC_OK;
+}
+
 nrc_status launch_init_normal(nrc_ctx* ctx, float* dst, size_t n, float scale, uint64_t seed)
 {
     if (n == 0) return NRC_OK;

@@ -49,6 +49,57 @@ class GradientExchange:
             dist.all_reduce(self.g_tab)
 
 
+class FusedExchange:
+    """Peer-memory exchange fused with both optimiser steps (csrc/dp.cu): one kernel per rank and frame instead of two
+    NCCL all-reduces + two step kernels.  __call__ replaces `exchange(); nrc.Step(); mrhe.Step()`.
+
+    handles=None: multi-process; the IPC handles are gathered with torch.distributed (any backend).
+    handles=[...] : replicas inside this process (tests), see connect_local()."""
+
+    def __init__(self, nrc, mrhe, rank, world, device=None, connect=True):
+        import ctypes as C
+        from . import _lib as L
+        self._L, self._C = L, C
+        self.rank, self.world = rank, world
+        self.h = C.c_void_p()
+        L.check(L.lib().nrc_dp_create(nrc.h, mrhe.h, C.c_int(rank), C.c_int(world), C.byref(self.h)))
+        n = int(L.lib().nrc_dp_handle_bytes())
+        buf = (C.c_ubyte * n)()
+        L.check(L.lib().nrc_dp_export(self.h, buf))
+        self.handle = bytes(buf)
+        if connect:
+            self._connect_distributed(device)
+
+    def _connect_distributed(self, device):
+        import torch
+        import torch.distributed as dist
+        if self.world == 1:
+            return self.connect([self.handle], same_process=True)
+        on_gpu = dist.get_backend() == "nccl"
+        mine = torch.tensor(list(self.handle), dtype=torch.uint8, device=device if on_gpu else "cpu")
+        parts = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(parts, mine)
+        self.connect([bytes(p.cpu().numpy().tobytes()) for p in parts], same_process=False)
+        dist.barrier()   # nobody launches before every rank has mapped its peers
+
+    def connect(self, handles, same_process):
+        C, L = self._C, self._L
+        blob = b"".join(handles)
+        arr = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        L.check(L.lib().nrc_dp_connect(self.h, arr, C.c_int(1 if same_process else 0)))
+
+    def __call__(self):
+        self._L.check(self._L.lib().nrc_dp_reduce_step(self.h))
+
+    def phase(self, k):
+        self._L.check(self._L.lib().nrc_dp_reduce_step_phase(self.h, self._C.c_int(k)))
+
+    def close(self):
+        if self.h:
+            self._L.check(self._L.lib().nrc_dp_destroy(self.h))
+            self.h = None
+
+
 def allreduce_host(arrays):
     """gloo/CPU variant used by the world_size-2 tests: numpy arrays summed over ranks in place."""
     import torch
