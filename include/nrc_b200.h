@@ -204,6 +204,10 @@ NRC_API nrc_status nrc_renderer_set_partition(nrc_renderer* r, uint32_t y0, uint
 /* Interleaved partition for load balance (cloud pixels cluster mid-frame): this rank renders rows yFirst, yFirst+yStride, ...
  * and traces train invocations iFirst, iFirst+iStride, ...  (rank, worldSize, rank, worldSize) for data-parallel hosts. */
 NRC_API nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32_t yFirst, uint32_t yStride, uint32_t iFirst, uint32_t iStride);
+/* Initial capacity of the render vertex pool while the cache is on (0 = default: 4 vertices per path; the reference's
+ * bound is 32 lit vertices per path, nrc-forward.frag:772-806, and a pool of that size cannot overflow).  A frame that
+ * overflows a smaller pool is traced again with the worst-case pool before any read-back or nrc_sync returns. */
+NRC_API nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t vertices);
 /* ResizeFrame, NrcHpmRenderer.cpp:103-126 */
 NRC_API nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t height);
 

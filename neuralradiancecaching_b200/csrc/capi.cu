@@ -214,7 +214,10 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     // the train trace is the long pole of the frame: just below the main stream (whose kernels are short), above the render trace
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream3, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainTrace, cudaEventDisableTiming));
-    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree, cudaEventDisableTiming));
+    NRC_CUDA(cudaStreamCreateWithPriority(&c->stream4, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainWalk, cudaEventDisableTiming));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[0], cudaEventDisableTiming));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[1], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
     *out = c;
@@ -228,6 +231,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->stream2);
     cudaStreamSynchronize(c->stream3);
+    cudaStreamSynchronize(c->stream4);
     for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
     if (c->pinned) cudaFreeHost(c->pinned);
     prof_drain(c);
@@ -238,7 +242,10 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamDestroy(c->stream2);
     cudaStreamDestroy(c->stream3);
     cudaEventDestroy(c->evTrainTrace);
-    cudaEventDestroy(c->evTrainFree);
+    cudaEventDestroy(c->evTrainWalk);
+    cudaEventDestroy(c->evTrainFree[0]);
+    cudaEventDestroy(c->evTrainFree[1]);
+    cudaStreamDestroy(c->stream4);
     delete c;
     return NRC_OK;
 }
@@ -246,6 +253,9 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
 extern "C" nrc_status nrc_sync(nrc_ctx* c)
 {
     NRC_REQUIRE(c, "null context");
+    NRC_CUDA(cudaStreamSynchronize(c->stream));
+    // a frame traced with a vertex pool below the worst case is checked now (and redone if it overflowed)
+    for (size_t i = 0; i < c->renderers.size(); i++) NRC_TRY(nrc_renderer_resolve_pending(c->renderers[i]));
     NRC_CUDA(cudaStreamSynchronize(c->stream));
     return NRC_OK;
 }

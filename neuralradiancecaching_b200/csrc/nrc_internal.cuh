@@ -47,6 +47,7 @@ enum NrcKernelId {
 };
 
 struct NrcProfRec { int kid; cudaEvent_t a, b; };
+nrc_status nrc_renderer_resolve_pending(nrc_renderer* r);   // renderer.cu
 
 // ---- handles ---------------------------------------------------------------------------------------
 struct nrc_ctx {
@@ -56,9 +57,11 @@ struct nrc_ctx {
     cudaStream_t stream2 = nullptr;       // second stream: render walk overlaps the training chain
     cudaStream_t stream3 = nullptr;       // third stream: the train TRACE of frame k+1 (needs no weights) runs ahead of frame k's MLP tail
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
-    cudaEvent_t evTrainTrace = nullptr, evTrainFree = nullptr;
+    cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
+    cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[2] = {nullptr, nullptr};
     nrc_mlp_precision precision = NRC_MLP_FP32;
     uint64_t launches = 0;
+    std::vector<nrc_renderer*> renderers;   // nrc_sync settles their deferred vertex-pool checks (renderer.cu)
     // per-kernel event timing (off by default; bench.py turns it on over its timed region)
     bool profiling = false;
     std::vector<NrcProfRec> profOpen;       // recorded, not yet read

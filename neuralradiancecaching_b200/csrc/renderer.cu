@@ -1,8 +1,8 @@
 // renderer.cu -- nrc_renderer: the frame graph that replaces NrcHpmRenderer's recorded command buffer
 // (src/NrcHpmRenderer.cpp:571-730): train -> nrc-step -> mrhe-step -> render.
 //
-//   stream3 : train walk -> light -> combine                                       (independent of the weights: runs AHEAD,
-//             frame k+1's trace overlaps frame k's steps / exchange wait / inference / composite)
+//   stream3 : train walk                 } independent of the weights: run AHEAD on double-buffered pools -- walk(k+1) overlaps
+//   stream4 : train light -> combine     } light(k), and both overlap frame k's steps / exchange wait / inference / composite
 //   stream  : fused encode+MLP fwd/bwd -> [gradient exchange] -> steps -> batched inference -> composite
 //   stream2 : render walk -> light -> combine (compacts the NRC queries)           (independent of the weights)
 #include <math.h>
@@ -28,24 +28,37 @@ struct nrc_renderer {
     float4* background = nullptr;
     uint32_t* counters = nullptr;     // [h*w][4]
     float* queryProbe = nullptr;      // [h*w][8]
-    // render paths / pool / queries
+    // render paths / pool / queries: two sets, so that the trace of frame k+1 never waits for frame k's inference + composite.
+    // rp / rpool / ql / background alias the set of the last nrc_frame_render (what the probes read).
     uint32_t sppAlloc = 0;
     RenderPaths rp;
     VertexPool rpool;
     QueryList ql;
+    struct RenderSet { RenderPaths rp; VertexPool rpool; QueryList ql; float4* background; } rs[2];
+    int renderBuf = 1;
+    bool setPending[2] = {false, false};  // evSetFree[b]: the composite that last read set b has finished
+    cudaEvent_t evSetFree[2] = {nullptr, nullptr};
+    cudaEvent_t evScalars = nullptr;      // the last frame's device scalars have reached hostScalars
+    bool overflowPending = false;         // the last frame used a pool below the worst case and its overflow flag is unread
+    TraceParams lastP;                    // what the last frame was traced with (a redo after an overflow repeats it)
+    uint32_t lastSpp = 0;
+    size_t poolCapHint = 0;               // initial vertex-pool capacity with the cache on (0: 4 vertices per path; worst case: 32)
+    bool lastInfer = false;
     // train
-    TrainPaths tp;
+    TrainPaths tp;                    // = tpb[trainBuf]: the buffers of the last nrc_frame_train (what the probes read)
     VertexPool tpool;
+    TrainPaths tpb[2];                // double-buffered: the walk of frame k+1 fills one set while lights/combine/MLP of frame k read the other
+    VertexPool tpoolb[2];
+    int trainBuf = 1;
     uint32_t* trainCounters = nullptr;
     uint32_t trainAlloc = 0;
-    // device scalars: [0] render vertex count, [1] render overflow, [2] train vertex count, [3] train overflow, [4] query count
+    // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count; train sets: {2,3} and {6,7}
     uint32_t* scalars = nullptr;
-    unsigned long long* taps = nullptr;   // [0] render taps, [1] train taps
+    unsigned long long* taps = nullptr;   // [0], [3] render taps of the two sets; [1], [2] train taps of the two sets
     unsigned long long* totals = nullptr; // [6] running totals (nrc_frame_totals)
     uint32_t* hostScalars = nullptr;      // pinned mirror
     unsigned long long* hostTaps = nullptr;
-    bool framePending = false;            // evFork marks the end of the previous frame's composite
-    bool trainPending = false;            // evTrainFree marks the end of the previous frame's train kernel (records consumed)
+    bool trainPending[2] = {false, false};  // evTrainFree[b] marks the end of the train kernel that last consumed buffer set b
 };
 
 #define FREE(p) do { if (p) { cudaFree(p); (p) = nullptr; } } while (0)
@@ -66,14 +79,28 @@ static nrc_status alloc_pool(VertexPool& p, uint32_t cap, bool withRnd, uint32_t
 
 static void free_frame(nrc_renderer* r)
 {
-    FREE(r->frame); FREE(r->frame8); FREE(r->background); FREE(r->counters); FREE(r->queryProbe);
-    FREE(r->rp.head); FREE(r->rp.qposPhase); FREE(r->rp.qdirValid); FREE(r->rp.result); FREE(r->rp.qweight); FREE(r->rp.qslot);
-    FREE(r->ql.pos); FREE(r->ql.dir); FREE(r->ql.rgb);
-    free_pool(r->rpool);
+    FREE(r->frame); FREE(r->frame8); FREE(r->counters); FREE(r->queryProbe);
+    for (int b = 0; b < 2; b++) {
+        nrc_renderer::RenderSet& S = r->rs[b];
+        FREE(S.background);
+        FREE(S.rp.head); FREE(S.rp.qposPhase); FREE(S.rp.qdirValid); FREE(S.rp.result); FREE(S.rp.qweight); FREE(S.rp.qslot);
+        FREE(S.ql.pos); FREE(S.ql.dir); FREE(S.ql.rgb);
+        free_pool(S.rpool);
+        r->setPending[b] = false;
+    }
+    memset(&r->rp, 0, sizeof(r->rp)); memset(&r->rpool, 0, sizeof(r->rpool)); memset(&r->ql, 0, sizeof(r->ql));
+    r->background = nullptr;
+    r->overflowPending = false;
     r->sppAlloc = 0;
 }
 
-// (Re)allocate everything whose size depends on the frame size and spp.
+static void use_render_set(nrc_renderer* r, int b)
+{
+    r->renderBuf = b;
+    r->rp = r->rs[b].rp; r->rpool = r->rs[b].rpool; r->ql = r->rs[b].ql; r->background = r->rs[b].background;
+}
+
+// (Re)allocate everything whose size depends on the frame size and spp.  The caller has drained every stream.
 static nrc_status alloc_frame(nrc_renderer* r, uint32_t spp, uint32_t poolCap)
 {
     free_frame(r);
@@ -81,33 +108,42 @@ static nrc_status alloc_frame(nrc_renderer* r, uint32_t spp, uint32_t poolCap)
     size_t paths = px * spp;
     NRC_CUDA(cudaMalloc(&r->frame, px * sizeof(float4)));
     NRC_CUDA(cudaMalloc(&r->frame8, px * sizeof(uint32_t)));
-    NRC_CUDA(cudaMalloc(&r->background, px * sizeof(float4)));
     NRC_CUDA(cudaMalloc(&r->counters, px * 4 * sizeof(uint32_t)));
     NRC_CUDA(cudaMalloc(&r->queryProbe, px * 8 * sizeof(float)));
     NRC_CUDA(cudaMemsetAsync(r->frame, 0, px * sizeof(float4), r->ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->frame8, 0, px * sizeof(uint32_t), r->ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->counters, 0, px * 4 * sizeof(uint32_t), r->ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->queryProbe, 0, px * 8 * sizeof(float), r->ctx->stream));
-    NRC_CUDA(cudaMalloc(&r->rp.head, paths * sizeof(int)));
-    NRC_CUDA(cudaMalloc(&r->rp.qposPhase, paths * sizeof(float4)));
-    NRC_CUDA(cudaMalloc(&r->rp.qdirValid, paths * sizeof(float4)));
-    NRC_CUDA(cudaMalloc(&r->rp.result, paths * sizeof(float4)));
-    NRC_CUDA(cudaMalloc(&r->rp.qweight, paths * sizeof(float)));
-    NRC_CUDA(cudaMalloc(&r->rp.qslot, paths * sizeof(int)));
-    NRC_CUDA(cudaMalloc(&r->ql.pos, paths * 3 * sizeof(float)));
-    NRC_CUDA(cudaMalloc(&r->ql.dir, paths * 3 * sizeof(float)));
-    NRC_CUDA(cudaMalloc(&r->ql.rgb, paths * 3 * sizeof(float)));
-    r->ql.cap = (uint32_t)paths;
-    r->ql.count = r->scalars + 4;
-    NRC_TRY(alloc_pool(r->rpool, poolCap, true, r->scalars + 0, r->scalars + 1));
+    for (int b = 0; b < 2; b++) {
+        nrc_renderer::RenderSet& S = r->rs[b];
+        NRC_CUDA(cudaMalloc(&S.background, px * sizeof(float4)));
+        NRC_CUDA(cudaMalloc(&S.rp.head, paths * sizeof(int)));
+        NRC_CUDA(cudaMalloc(&S.rp.qposPhase, paths * sizeof(float4)));
+        NRC_CUDA(cudaMalloc(&S.rp.qdirValid, paths * sizeof(float4)));
+        NRC_CUDA(cudaMalloc(&S.rp.result, paths * sizeof(float4)));
+        NRC_CUDA(cudaMalloc(&S.rp.qweight, paths * sizeof(float)));
+        NRC_CUDA(cudaMalloc(&S.rp.qslot, paths * sizeof(int)));
+        NRC_CUDA(cudaMalloc(&S.ql.pos, paths * 3 * sizeof(float)));
+        NRC_CUDA(cudaMalloc(&S.ql.dir, paths * 3 * sizeof(float)));
+        NRC_CUDA(cudaMalloc(&S.ql.rgb, paths * 3 * sizeof(float)));
+        S.ql.cap = (uint32_t)paths;
+        S.ql.count = r->scalars + 8 * b + 4;
+        NRC_TRY(alloc_pool(S.rpool, poolCap, true, r->scalars + 8 * b + 0, r->scalars + 8 * b + 1));
+    }
+    use_render_set(r, 1);
     r->sppAlloc = spp;
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     return NRC_OK;
 }
 
 static void free_train(nrc_renderer* r)
 {
-    FREE(r->tp.head); FREE(r->tp.pos); FREE(r->tp.dir); FREE(r->tp.target); FREE(r->trainCounters);
-    free_pool(r->tpool);
+    for (int b = 0; b < 2; b++) {
+        FREE(r->tpb[b].head); FREE(r->tpb[b].pos); FREE(r->tpb[b].dir); FREE(r->tpb[b].target);
+        free_pool(r->tpoolb[b]);
+    }
+    FREE(r->trainCounters);
+    memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
     r->trainAlloc = 0;
 }
 
@@ -115,19 +151,25 @@ static nrc_status alloc_train(nrc_renderer* r)
 {
     free_train(r);
     uint32_t n = r->trainW * r->trainH;
-    NRC_CUDA(cudaMalloc(&r->tp.head, (size_t)n * 8 * sizeof(int)));
-    NRC_CUDA(cudaMalloc(&r->tp.pos, (size_t)n * 3 * sizeof(float)));
-    NRC_CUDA(cudaMalloc(&r->tp.dir, (size_t)n * 3 * sizeof(float)));
-    NRC_CUDA(cudaMalloc(&r->tp.target, (size_t)n * 3 * sizeof(float)));
-    NRC_CUDA(cudaMalloc(&r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMemsetAsync(r->tp.pos, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->tp.dir, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->trainCounters, 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
-    // worst case: 8 paths x 64 lit vertices per training sample -- this pool cannot overflow
-    size_t cap = (size_t)n * (8 * 64 + 2 * 16);   // + the two partly used chunks a thread can end with (TRAIN_CHUNK)
+    size_t cap = (size_t)n * (8 * 64 + 2 * 16);   // worst case: 8 paths x 64 lit vertices per training sample (+ the two partly
+                                                  // used chunks a thread can end with, TRAIN_CHUNK) -- this pool cannot overflow
     NRC_REQUIRE(cap < ((size_t)1 << 31), "train grid too large for the vertex pool");
-    NRC_TRY(alloc_pool(r->tpool, (uint32_t)cap, false, r->scalars + 2, r->scalars + 3));
+    for (int b = 0; b < 2; b++) {
+        TrainPaths& tp = r->tpb[b];
+        NRC_CUDA(cudaMalloc(&tp.head, (size_t)n * 8 * sizeof(int)));
+        NRC_CUDA(cudaMalloc(&tp.pos, (size_t)n * 3 * sizeof(float)));
+        NRC_CUDA(cudaMalloc(&tp.dir, (size_t)n * 3 * sizeof(float)));
+        NRC_CUDA(cudaMalloc(&tp.target, (size_t)n * 3 * sizeof(float)));
+        NRC_CUDA(cudaMemsetAsync(tp.pos, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
+        NRC_CUDA(cudaMemsetAsync(tp.dir, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
+        NRC_CUDA(cudaMemsetAsync(tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
+        // device scalars of the two sets: {2,3} and {6,7}
+        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, false, r->scalars + 2 + 4 * b, r->scalars + 3 + 4 * b));
+    }
+    NRC_CUDA(cudaMalloc(&r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMemsetAsync(r->trainCounters, 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
+    r->trainBuf = 1;
+    r->tp = r->tpb[1]; r->tpool = r->tpoolb[1];
     r->trainAlloc = n;
     return NRC_OK;
 }
@@ -149,18 +191,23 @@ extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t
     memset(&r->ptLight, 0, sizeof(r->ptLight));
     memset(&r->rp, 0, sizeof(r->rp)); memset(&r->rpool, 0, sizeof(r->rpool)); memset(&r->ql, 0, sizeof(r->ql));
     memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
-    NRC_CUDA(cudaMalloc(&r->scalars, 8 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMalloc(&r->taps, 2 * sizeof(unsigned long long)));
+    memset(r->tpb, 0, sizeof(r->tpb)); memset(r->tpoolb, 0, sizeof(r->tpoolb));
+    NRC_CUDA(cudaMalloc(&r->scalars, 16 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMalloc(&r->taps, 4 * sizeof(unsigned long long)));   // [0] render, [1], [2] the two train sets
     NRC_CUDA(cudaMalloc(&r->totals, 6 * sizeof(unsigned long long)));
     NRC_CUDA(cudaMemsetAsync(r->totals, 0, 6 * sizeof(unsigned long long), ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 8 * sizeof(uint32_t), ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 16 * sizeof(uint32_t), ctx->stream));
+    memset(r->rs, 0, sizeof(r->rs));
+    for (int b = 0; b < 2; b++) NRC_CUDA(cudaEventCreateWithFlags(&r->evSetFree[b], cudaEventDisableTiming));
+    NRC_CUDA(cudaEventCreateWithFlags(&r->evScalars, cudaEventDisableTiming));
+    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 4 * sizeof(unsigned long long), ctx->stream));
     NRC_CUDA(cudaMallocHost(&r->hostScalars, 8 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMallocHost(&r->hostTaps, 2 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMallocHost(&r->hostTaps, 4 * sizeof(unsigned long long)));
     memset(r->hostScalars, 0, 8 * sizeof(uint32_t));
-    memset(r->hostTaps, 0, 2 * sizeof(unsigned long long));
+    memset(r->hostTaps, 0, 4 * sizeof(unsigned long long));
     NRC_TRY(alloc_frame(r, 1, (uint32_t)((size_t)width * height * 4)));
     NRC_TRY(alloc_train(r));
+    ctx->renderers.push_back(r);
     *out = r;
     return NRC_OK;
 }
@@ -168,12 +215,17 @@ extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t
 extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
 {
     if (!r) return NRC_OK;
+    for (size_t i = 0; i < r->ctx->renderers.size(); i++)
+        if (r->ctx->renderers[i] == r) { r->ctx->renderers.erase(r->ctx->renderers.begin() + i); break; }
     cudaStreamSynchronize(r->ctx->stream);
     cudaStreamSynchronize(r->ctx->stream2);
     cudaStreamSynchronize(r->ctx->stream3);
+    cudaStreamSynchronize(r->ctx->stream4);
     free_frame(r);
     free_train(r);
     FREE(r->scalars); FREE(r->taps); FREE(r->totals);
+    for (int b = 0; b < 2; b++) if (r->evSetFree[b]) cudaEventDestroy(r->evSetFree[b]);
+    if (r->evScalars) cudaEventDestroy(r->evScalars);
     if (r->hostScalars) cudaFreeHost(r->hostScalars);
     if (r->hostTaps) cudaFreeHost(r->hostTaps);
     delete r;
@@ -220,6 +272,7 @@ extern "C" nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32
     return NRC_OK;
 }
 
+static nrc_status resolve_overflow_fwd(nrc_renderer* r);
 static inline uint32_t part_count(uint32_t first, uint32_t end, uint32_t stride) { return first >= end ? 0u : (end - first + stride - 1) / stride; }
 
 extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t height)
@@ -228,9 +281,29 @@ extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t heigh
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
     r->width = width; r->height = height;
     r->y0 = r->ystride > 1 ? r->y0 : 0; r->y1 = height;
     return alloc_frame(r, r->sppAlloc ? r->sppAlloc : 1, (uint32_t)((size_t)width * height * 4));
+}
+
+// Initial capacity of the render vertex pool while the cache is on (0 = the default of 4 vertices per path; 32 per path
+// cannot overflow).  A frame that overflows a smaller pool is traced again with the worst-case pool before its results are
+// handed out.
+extern "C" nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t vertices)
+{
+    NRC_REQUIRE(r, "null renderer");
+    NRC_REQUIRE(vertices < 0x7fffffffull, "pool capacity out of range");
+    NRC_TRY(resolve_overflow_fwd(r));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    r->poolCapHint = (size_t)vertices;
+    uint32_t spp = r->sppAlloc ? r->sppAlloc : 1;
+    size_t cap = vertices ? (size_t)vertices : (size_t)r->width * r->height * spp * 4;
+    if (cap > 0x7fffffffu) cap = 0x7fffffffu;
+    return alloc_frame(r, spp, (uint32_t)cap);
 }
 
 static TraceParams make_params(const nrc_renderer* r)
@@ -285,20 +358,33 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     uint32_t n = part_count(r->i0, r->i1, r->istride);
     if (n == 0) return NRC_OK;
     TraceParams P = make_params(r);
-    // The trace half (walk, lights, combine) reads no weights: it runs on stream3 and may start while the previous frame's
-    // steps, inference and composite are still on the main stream -- and, on several GPUs, while that frame's exchange
-    // waits for the slowest rank.  It only needs the previous train kernel to have consumed the records.
-    static int noOverlap = -1;
+    // The trace half (walk, lights, combine) reads no weights, so it runs AHEAD of the main stream, on two streams of its own:
+    //   stream3: walk(k)                       -- the long pole; walk(k+1) starts as soon as walk(k) is done
+    //   stream4: light(k) -> combine(k)        -- overlaps walk(k+1), which fills the other buffer set
+    //   main   : train kernel(k) -> [exchange] -> steps -> inference -> composite
+    // so frame k+1's trace overlaps frame k's steps / inference / composite and, on several GPUs, the exchange's wait for
+    // the slowest rank.  A buffer set is reused once the train kernel that read it has finished (evTrainFree[b]).
+    static int noOverlap = -1, noAhead = -1;
     if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
-    cudaStream_t tt = (noOverlap || getenv("NRC_NO_TRAIN_AHEAD")) ? st : ctx->stream3;
-    if (tt != st && r->trainPending) NRC_CUDA(cudaStreamWaitEvent(tt, ctx->evTrainFree, 0));
-    NRC_CUDA(cudaMemsetAsync(r->scalars + 2, 0, 2 * sizeof(uint32_t), tt));
-    NRC_CUDA(cudaMemsetAsync(r->taps + 1, 0, sizeof(unsigned long long), tt));
-    NRC_TRY(launch_train_walk(ctx, tt, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
-    NRC_TRY(launch_light(ctx, tt, P, r->tpool, false, r->taps + 1));
-    NRC_TRY(launch_train_combine(ctx, tt, n, r->tpool, r->tp, r->taps, r->totals));
-    if (tt != st) {
-        NRC_CUDA(cudaEventRecord(ctx->evTrainTrace, tt));
+    if (noAhead < 0) { const char* e = getenv("NRC_NO_TRAIN_AHEAD"); noAhead = (e && atoi(e)) ? 1 : 0; }
+    const bool ahead = !(noOverlap || noAhead);
+    cudaStream_t tw = ahead ? ctx->stream3 : st;
+    cudaStream_t tl = ahead ? ctx->stream4 : st;
+    const int b = ahead ? (r->trainBuf ^ 1) : r->trainBuf;
+    r->trainBuf = b;
+    r->tp = r->tpb[b]; r->tpool = r->tpoolb[b];
+    if (ahead && r->trainPending[b]) NRC_CUDA(cudaStreamWaitEvent(tw, ctx->evTrainFree[b], 0));
+    NRC_CUDA(cudaMemsetAsync(r->tpool.count, 0, 2 * sizeof(uint32_t), tw));          // count + overflow of this set
+    NRC_CUDA(cudaMemsetAsync(r->taps + 1 + b, 0, sizeof(unsigned long long), tw));
+    NRC_TRY(launch_train_walk(ctx, tw, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
+    if (ahead) {
+        NRC_CUDA(cudaEventRecord(ctx->evTrainWalk, tw));
+        NRC_CUDA(cudaStreamWaitEvent(tl, ctx->evTrainWalk, 0));
+    }
+    NRC_TRY(launch_light(ctx, tl, P, r->tpool, false, r->taps + 1 + b));
+    NRC_TRY(launch_train_combine(ctx, tl, n, r->tpool, r->tp, r->taps + b, r->totals));   // reads taps[1] of the pointer it gets
+    if (ahead) {
+        NRC_CUDA(cudaEventRecord(ctx->evTrainTrace, tl));
         NRC_CUDA(cudaStreamWaitEvent(st, ctx->evTrainTrace, 0));
     }
     float lossScale = P.widthFactor * P.heightFactor;   // ONE_OVER_PIXEL_COUNT (nrc-train.comp:210)
@@ -306,12 +392,82 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
         NRC_TRY(launch_train_tc(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
     else
         NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
-    if (tt != st) {
-        NRC_CUDA(cudaEventRecord(ctx->evTrainFree, st));
-        r->trainPending = true;
+    if (ahead) {
+        NRC_CUDA(cudaEventRecord(ctx->evTrainFree[b], st));
+        r->trainPending[b] = true;
     }
     return NRC_OK;
 }
+
+static nrc_status drain_streams(nrc_ctx* ctx)
+{
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NRC_OK;
+}
+
+// Enqueue one render pass with the parameters in r->lastP into the other buffer set.
+static nrc_status render_pass(nrc_renderer* r)
+{
+    nrc_ctx* ctx = r->ctx;
+    const TraceParams& P = r->lastP;
+    const uint32_t rows = part_count(r->y0, r->y1, r->ystride);
+    const uint32_t spp = r->lastSpp;
+    static int noOverlap = -1;
+    if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
+    cudaStream_t s2 = noOverlap ? ctx->stream : ctx->stream2;
+    const int b = noOverlap ? r->renderBuf : (r->renderBuf ^ 1);
+    use_render_set(r, b);
+    uint32_t* sc = r->scalars + 8 * b;
+    unsigned long long* tapc = r->taps + 3 * b;
+    // the composite that last read this set (two frames ago) must be done before the walk overwrites it
+    if (s2 != ctx->stream && r->setPending[b]) NRC_CUDA(cudaStreamWaitEvent(s2, r->evSetFree[b], 0));
+    NRC_CUDA(cudaMemsetAsync(sc + 0, 0, 2 * sizeof(uint32_t), s2));
+    NRC_CUDA(cudaMemsetAsync(sc + 4, 0, sizeof(uint32_t), s2));
+    NRC_CUDA(cudaMemsetAsync(tapc, 0, sizeof(unsigned long long), s2));
+    NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
+    NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, tapc));
+    NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
+    NRC_CUDA(cudaMemcpyAsync(r->hostScalars, sc, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s2));
+    NRC_CUDA(cudaEventRecord(r->evScalars, s2));
+    if (s2 != ctx->stream) {
+        NRC_CUDA(cudaEventRecord(ctx->evJoin, s2));
+        NRC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->evJoin, 0));
+    }
+    if (r->lastInfer) NRC_TRY(infer_queries(r, ctx->stream));
+    NRC_TRY(launch_composite(ctx, ctx->stream, P, r->y0, rows, r->ystride, spp, r->rp, r->ql, r->background, r->frame, r->frame8, r->queryProbe,
+                             sc, tapc, r->totals));
+    NRC_CUDA(cudaEventRecord(r->evSetFree[b], ctx->stream));
+    r->setPending[b] = true;
+    // Only a pool below the worst case can overflow.  The flag is read LATER (resolve_overflow): a host wait here would keep
+    // the next frame's train trace from being queued while this frame is still tracing.
+    size_t px = (size_t)r->width * r->height;
+    r->overflowPending = (size_t)r->rpool.cap < px * spp * 32;
+    return NRC_OK;
+}
+
+// The vertex-pool overflow flag of the last frame.  redo: the caller is about to hand that frame's results out, so a truncated
+// frame is traced again with the worst-case pool (same parameters; the weights are the frame's own as long as no later
+// training was queued, which is the Render() -> read order).  Otherwise the frame was never looked at: just grow the pool.
+static nrc_status resolve_overflow(nrc_renderer* r, bool redo)
+{
+    if (!r->overflowPending) return NRC_OK;
+    NRC_CUDA(cudaEventSynchronize(r->evScalars));
+    r->overflowPending = false;
+    if (r->hostScalars[1] == 0) return NRC_OK;
+    size_t cap = (size_t)r->width * r->height * r->lastSpp * 32;
+    if (cap > 0x7fffffffu) cap = 0x7fffffffu;
+    NRC_REQUIRE((size_t)r->rpool.cap < cap, "vertex pool overflow with the worst-case pool");
+    NRC_TRY(drain_streams(r->ctx));
+    NRC_TRY(alloc_frame(r, r->lastSpp, (uint32_t)cap));
+    if (redo) NRC_TRY(render_pass(r));
+    return NRC_OK;
+}
+
+nrc_status nrc_renderer_resolve_pending(nrc_renderer* r) { return resolve_overflow(r, true); }
+static nrc_status resolve_overflow_fwd(nrc_renderer* r) { return resolve_overflow(r, false); }
 
 // nrc-forward.{vert,frag} over this rank's rows.  The trace part runs on stream2 and may overlap whatever is
 // still queued on the main stream (training, steps); inference waits for both.
@@ -321,53 +477,22 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
     nrc_ctx* ctx = r->ctx;
     const uint32_t rows = part_count(r->y0, r->y1, r->ystride);
     if (rows == 0) return NRC_OK;
+    NRC_TRY(resolve_overflow(r, false));   // the previous frame (costs nothing: this frame's trace queues behind that one anyway)
     const nrc_volume_params& v = r->vol->params;
     const bool useNN = (v.useNN == 1u);
     uint32_t spp = (uint32_t)(useNN ? v.withNnSpp : v.noNnSpp);
     size_t px = (size_t)r->width * r->height;
     size_t wantCap = px * spp * (useNN ? 4 : 32);
+    if (useNN && r->poolCapHint) wantCap = r->poolCapHint < px * spp * 32 ? r->poolCapHint : px * spp * 32;
     if (wantCap > 0x7fffffffu) wantCap = 0x7fffffffu;
     if (spp != r->sppAlloc || r->rpool.cap < wantCap) {
-        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
-        NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
+        NRC_TRY(drain_streams(ctx));
         NRC_TRY(alloc_frame(r, spp, (uint32_t)wantCap));
-        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     }
-    TraceParams P = make_params(r);
-    for (int attempt = 0; attempt < 2; attempt++) {
-        static int noOverlap = -1;
-        if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
-        cudaStream_t s2 = noOverlap ? ctx->stream : ctx->stream2;
-        // the previous frame's composite (main stream) still reads the buffers this walk overwrites
-        if (r->framePending) NRC_CUDA(cudaStreamWaitEvent(s2, ctx->evFork, 0));
-        // order stream2 after the allocations/memsets above, not after the training work
-        NRC_CUDA(cudaMemsetAsync(r->scalars + 0, 0, 2 * sizeof(uint32_t), s2));
-        NRC_CUDA(cudaMemsetAsync(r->scalars + 4, 0, sizeof(uint32_t), s2));
-        NRC_CUDA(cudaMemsetAsync(r->taps + 0, 0, sizeof(unsigned long long), s2));
-        NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
-        NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, r->taps + 0));
-        NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
-        NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s2));
-        NRC_CUDA(cudaEventRecord(ctx->evJoin, s2));
-        NRC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->evJoin, 0));
-        if (useNN && v.showNonNN == 0u) NRC_TRY(infer_queries(r, ctx->stream));
-        NRC_TRY(launch_composite(ctx, ctx->stream, P, r->y0, rows, r->ystride, spp, r->rp, r->ql, r->background, r->frame, r->frame8, r->queryProbe,
-                                 r->scalars, r->taps, r->totals));
-        NRC_CUDA(cudaEventRecord(ctx->evFork, ctx->stream));
-        r->framePending = true;
-        // Overflow of the vertex pool is checked lazily: only a pool smaller than the worst case can overflow,
-        // and then the frame is redone once with the worst-case pool.
-        if ((size_t)r->rpool.cap >= px * spp * 32) break;
-        NRC_CUDA(cudaEventSynchronize(ctx->evJoin));
-        if (r->hostScalars[1] == 0) break;
-        NRC_REQUIRE(attempt == 0, "vertex pool overflow after growing it");
-        size_t cap = px * spp * 32;
-        if (cap > 0x7fffffffu) cap = 0x7fffffffu;
-        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
-        NRC_TRY(alloc_frame(r, spp, (uint32_t)cap));
-        NRC_CUDA(cudaStreamSynchronize(ctx->stream));
-    }
-    return NRC_OK;
+    r->lastP = make_params(r);
+    r->lastSpp = spp;
+    r->lastInfer = useNN && v.showNonNN == 0u;
+    return render_pass(r);
 }
 
 // Render(): train -> nrc-step -> mrhe-step -> render, like the recorded command buffer.
@@ -406,6 +531,7 @@ extern "C" nrc_status nrc_read_frame(nrc_renderer* r, void* dst, nrc_frame_forma
 {
     NRC_REQUIRE(r && dst, "null argument");
     NRC_REQUIRE(fmt == NRC_FRAME_RGBA32F || fmt == NRC_FRAME_BGRA8, "unknown frame format");
+    NRC_TRY(resolve_overflow(r, true));
     return read_back(r->ctx, dst, nrc_frame_ptr(r, fmt), nrc_frame_bytes(r, fmt));
 }
 
@@ -416,6 +542,7 @@ extern "C" nrc_status nrc_read_frame_partition(nrc_renderer* r, void* dst, nrc_f
     NRC_REQUIRE(fmt == NRC_FRAME_RGBA32F || fmt == NRC_FRAME_BGRA8, "unknown frame format");
     uint32_t rows = part_count(r->y0, r->y1, r->ystride);
     if (rows == 0) return NRC_OK;
+    NRC_TRY(resolve_overflow(r, true));
     size_t rowBytes = (size_t)r->width * (fmt == NRC_FRAME_RGBA32F ? 16 : 4);
     const char* src = (const char*)nrc_frame_ptr(r, fmt) + (size_t)r->y0 * rowBytes;
     cudaMemcpyKind k = nrc_is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
@@ -433,6 +560,7 @@ extern "C" size_t nrc_frame_partition_bytes(nrc_renderer* r, nrc_frame_format fm
 extern "C" nrc_status nrc_read_render_probes(nrc_renderer* r, uint32_t* counters, float* query)
 {
     NRC_REQUIRE(r, "null renderer");
+    NRC_TRY(resolve_overflow(r, true));
     size_t px = (size_t)r->width * r->height;
     if (counters) NRC_TRY(read_back(r->ctx, counters, r->counters, px * 4 * sizeof(uint32_t)));
     if (query) NRC_TRY(read_back(r->ctx, query, r->queryProbe, px * 8 * sizeof(float)));
@@ -488,6 +616,7 @@ extern "C" nrc_status nrc_frame_totals(nrc_renderer* r, uint64_t totals[6], int 
     NRC_REQUIRE(r && totals, "null argument");
     nrc_ctx* ctx = r->ctx;
     NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     unsigned long long t[6];
@@ -501,14 +630,16 @@ extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, u
 {
     NRC_REQUIRE(r, "null renderer");
     nrc_ctx* ctx = r->ctx;
+    NRC_TRY(resolve_overflow(r, true));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
-    NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars + 8 * r->renderBuf, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     if (inferQueries) *inferQueries = r->hostScalars[4];
     if (trainSamples) *trainSamples = part_count(r->i0, r->i1, r->istride);
     // + one tap per walk step is not counted here: densityTaps are the light kernels' taps (the bulk)
-    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[0] + (uint64_t)r->hostTaps[1];
+    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[3 * r->renderBuf] + (uint64_t)r->hostTaps[1 + r->trainBuf];
     return NRC_OK;
 }

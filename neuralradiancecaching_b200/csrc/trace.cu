@@ -255,14 +255,19 @@ __device__ __forceinline__ TapCtx make_tap(const TraceParams& P)
     return t;
 }
 
-// texel sum (0..255 scale) at texel-space position (u, v, s); the caller guarantees -1 < u < nx etc.
-__device__ __forceinline__ float tap_texel(const TapCtx& t, float u, float v, float s)
+// A tap in two halves so that a batch of taps can have all its brick loads in flight before the first blend:
+// tap_cell  : texel-space position (u, v, s), -1 < u < nx etc. guaranteed by the caller -> brick index + the three fractions
+// tap_blend : brick + fractions -> texel sum (0..255 scale)
+__device__ __forceinline__ int tap_cell(const TapCtx& t, float u, float v, float s, float& a, float& b, float& c)
 {
     float fu = floorf(u), fv = floorf(v), fs = floorf(s);
-    float a = u - fu, b = v - fv, c = s - fs;
+    a = u - fu; b = v - fv; c = s - fs;
     int ix = __float_as_int(fu + TAP_MAGIC), iy = __float_as_int(fv + TAP_MAGIC), iz = __float_as_int(fs + TAP_MAGIC);
-    int cell = iz * t.strideZ + iy * t.strideY + ix + t.bias;
-    uint2 q = __ldg(t.bricks + cell);
+    return iz * t.strideZ + iy * t.strideY + ix + t.bias;
+}
+
+__device__ __forceinline__ float tap_blend(uint2 q, float a, float b, float c)
+{
     // byte k of the word -> float bits 0x4B0000kk = 2^23 + k
     float b000 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7650)), b100 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7651));
     float b010 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7652)), b110 = __uint_as_float(__byte_perm(q.x, 0x4B000000u, 0x7653));
@@ -273,6 +278,15 @@ __device__ __forceinline__ float tap_texel(const TapCtx& t, float u, float v, fl
     float y0 = fmaf(b, x10 - x00, x00), y1 = fmaf(b, x11 - x01, x01);
     return fmaf(c, y1 - y0, y0);
 }
+
+__device__ __forceinline__ float tap_texel(const TapCtx& t, float u, float v, float s)
+{
+    float a, b, c;
+    int cell = tap_cell(t, u, v, s, a, b, c);
+    return tap_blend(__ldg(t.bricks + cell), a, b, c);
+}
+
+#define TAP_BATCH 8   // brick loads in flight per thread (ncu r01f: one load at a time left the light kernels 35-57 % long-scoreboard)
 
 // GetTransmittance(start, end, count) (nrc-forward.frag:641-662): prod exp(-d_i*step) = exp(-step * sum d_i).
 // One property of the reference's product IS control flow: the fragment shader replaces the pixel by the
@@ -294,12 +308,22 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
     float sum = 0.0f, dmax = 0.0f;
     if (inside) {
         float fi = 0.0f;
-#pragma unroll 8
-        for (int i = 0; i < COUNT; i++) {
-            float d = tap_texel(t, fmaf(fi, du, u0), fmaf(fi, dv, v0), fmaf(fi, ds, s0));
-            fi += 1.0f;
-            sum += d;
-            dmax = fmaxf(dmax, d);
+#pragma unroll 1
+        for (int i = 0; i < COUNT; i += TAP_BATCH) {
+            uint2 q[TAP_BATCH];
+            float fa[TAP_BATCH], fb[TAP_BATCH], fc[TAP_BATCH];
+#pragma unroll
+            for (int j = 0; j < TAP_BATCH; j++) {
+                int cell = tap_cell(t, fmaf(fi, du, u0), fmaf(fi, dv, v0), fmaf(fi, ds, s0), fa[j], fb[j], fc[j]);
+                q[j] = __ldg(t.bricks + cell);
+                fi += 1.0f;
+            }
+#pragma unroll
+            for (int j = 0; j < TAP_BATCH; j++) {
+                float d = tap_blend(q[j], fa[j], fb[j], fc[j]);
+                sum += d;
+                dmax = fmaxf(dmax, d);
+            }
         }
     } else {   // segment leaves the sampled region (or is not finite): test every tap
         float fi = 0.0f;
@@ -320,8 +344,10 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
     return fminf(__expf(-(sum * k) * stepSize), 0.99999994f);
 }
 
-template <bool RENDER>
-__global__ void __launch_bounds__(128) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
+// MB = resident blocks ptxas must allow: WITHOUT a minimum it chases occupancy and sinks every brick load next to its use (one
+// load in flight per thread, ncu r01f: 35-57 % long-scoreboard); with a register budget it keeps the batch of loads together.
+template <bool RENDER, int MB>
+__global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
 {
     const uint32_t count = min(*pool.count, pool.cap);
     const Box box = make_box(P);
@@ -607,8 +633,21 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
     unsigned cap = (unsigned)ctx->smCount * 16;
     unsigned blocks = want < cap ? want : cap;
     if (blocks == 0) return NRC_OK;
-    if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, k_light<true><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter));
-    else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, k_light<false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter));
+    static int mb = -1;
+    if (mb < 0) { const char* e = getenv("NRC_LIGHT_MB"); mb = e ? atoi(e) : 8; }
+#define LIGHT_CASE(MBV)                                                                                                              \
+    case MBV:                                                                                                                        \
+        if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, (k_light<true, MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, (k_light<false, MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
+        break;
+    switch (mb) {
+        LIGHT_CASE(4)
+        LIGHT_CASE(5)
+        LIGHT_CASE(6)
+        default:   // 64 registers, 32 resident warps, loads in groups of 2-3: the fastest of the four on the frame (profiles/r01f)
+        LIGHT_CASE(8)
+    }
+#undef LIGHT_CASE
     return NRC_OK;
 }
 

@@ -51,6 +51,10 @@ class NrcHpmRenderer:
         L.check(L.lib().nrc_renderer_set_partition_strided(self.h, C.c_uint32(y_first), C.c_uint32(y_stride), C.c_uint32(i_first),
                                                            C.c_uint32(i_stride)))
 
+    def SetPoolCapacity(self, vertices):
+        """Initial render vertex pool capacity (0 = default); an overflowing frame is redone with the worst-case pool."""
+        L.check(L.lib().nrc_renderer_set_pool_capacity(self.h, C.c_uint64(vertices)))
+
     def partition_bytes(self, fmt=L.FRAME_BGRA8):
         return int(L.lib().nrc_frame_partition_bytes(self.h, C.c_int(fmt)))
 
