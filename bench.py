@@ -140,6 +140,8 @@ def run_b200(args):
     r = N.NrcHpmRenderer(W, H, TW, TH, inp["cam"], vol, dl, pl, env, nrc, mrhe)
     if world > 1:
         r.SetPartitionStrided(rank, world, rank, world)
+    if os.environ.get("NRC_BENCH_POOL"):          # experiment: vertices per path of the render pool (32 = cannot overflow)
+        r.SetPoolCapacity((W * H // world) * int(os.environ["NRC_BENCH_POOL"]))
 
     from neuralradiancecaching_b200.dist import GradientExchange, FusedExchange
     exchange = GradientExchange(ctx, nrc, mrhe, torch.device("cuda", local))
@@ -199,21 +201,40 @@ def run_b200(args):
 
     # ---- end to end: the host-facing call sequence; per step the scene/camera/RNG structs go host->device (kernel
     # parameters) and this rank's rows of the BGRA8 frame plus the loss come back to pinned host memory ----
+    # Like the reference's main loop (frame k is presented while frame k+1 is recorded, src/main.cpp:197-230) the read-back
+    # is asynchronous and double-buffered: step k queues frame k and its copy, then takes delivery of frame k-1.  Every
+    # frame and every loss value crosses PCIe inside the timed region; the last one is awaited before the stop event.
     d2h_bytes = r.partition_bytes(L.FRAME_BGRA8)
-    host_frame = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
-    hf = host_frame.numpy()
-    for _ in range(3):
-        frame(next(ri))
-        r.read_frame_partition(hf, L.FRAME_BGRA8)
+    host_frames = [torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    host_loss = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    hfs = [h.numpy() for h in host_frames]
+    hls = [h.numpy() for h in host_loss]
+    sync_e2e = bool(os.environ.get("NRC_E2E_SYNC"))
+
+    def e2e_steps(count):
+        pending = None
+        for k in range(count):
+            frame(next(ri))
+            if sync_e2e:
+                r.read_frame_partition(hfs[0], L.FRAME_BGRA8)    # synchronous D2H of this rank's rows
+                _ = nrc.GetStats().mseLoss                        # D2H of the loss (src/main.cpp:220-224)
+                continue
+            nrc.get_stats_async(hls[k & 1])
+            t = r.read_frame_partition_async(hfs[k & 1], L.FRAME_BGRA8)
+            if pending is not None:
+                r.readback_wait(pending)                          # frame k-1 and its loss are in host memory now
+            pending = t
+        if pending is not None:
+            r.readback_wait(pending)
+
+    e2e_steps(3)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     with torch.cuda.stream(ext):
         e0.record()
-    for _ in range(K):
-        frame(next(ri))
-        r.read_frame_partition(hf, L.FRAME_BGRA8)    # synchronous D2H of this rank's rows
-        _ = nrc.GetStats().mseLoss                    # D2H of the loss (src/main.cpp:220-224)
+    e2e_steps(K)
+    ctx.sync()
     with torch.cuda.stream(ext):
         e1.record()
     barrier()
@@ -556,7 +577,7 @@ def main():
                     help="MLP arithmetic: bf16 = tcgen05 tensor cores (bf16 operands, fp32 accumulate; north_star's tensor-core path), "
                          "fp32 = CUDA-core 1e-3 parity path.  Tracing is fp32 either way.")
     ap.add_argument("--no-fp32-line", action="store_true", help="skip the extra fp32-path measurement")
-    ap.add_argument("--exchange", default=os.environ.get("NRC_EXCHANGE", "nccl"), choices=["nccl", "fused"],
+    ap.add_argument("--exchange", default=os.environ.get("NRC_EXCHANGE", "fused"), choices=["nccl", "fused"],
                     help="multi-GPU gradient exchange: two NCCL all-reduces + step kernels, or the fused peer-memory kernel (csrc/dp.cu)")
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)

@@ -139,6 +139,9 @@ NRC_API nrc_status nrc_mlp_reset_stats(nrc_mlp* mlp);             /* ResetStats(
 NRC_API nrc_status nrc_mlp_get_stats(nrc_mlp* mlp, float* mseLoss /*host*/); /* GetStats(), :552-556 */
 /* device address of the gradient arena handed to the collective: 20995 negative-gradient floats followed by
  * the mseLoss accumulator (20996 floats in all). */
+/* GetStats() queued on the context's stream, no host wait: *mseLoss (page-locked host memory) is valid after a later
+ * nrc_readback_wait / nrc_sync. */
+NRC_API nrc_status nrc_mlp_get_stats_async(nrc_mlp* mlp, float* mseLoss);
 NRC_API float* nrc_mlp_grad_ptr(nrc_mlp* mlp);
 NRC_API size_t nrc_mlp_grad_count(nrc_mlp* mlp);
 
@@ -227,6 +230,11 @@ NRC_API nrc_status nrc_read_frame(nrc_renderer* r, void* dst /*[h|d]*/, nrc_fram
 /* this rank's rows only, compacted (row k of dst = frame row y0 + k*stride); nrc_frame_partition_bytes is its size */
 NRC_API nrc_status nrc_read_frame_partition(nrc_renderer* r, void* dst /*[h|d]*/, nrc_frame_format fmt);
 NRC_API size_t nrc_frame_partition_bytes(nrc_renderer* r, nrc_frame_format fmt);
+/* The same copy without the host wait (the reference presents frame k while it records frame k+1, src/main.cpp:197-230):
+ * queued behind the frame just rendered, on a copy stream; dst (page-locked host or device memory) is valid after
+ * nrc_readback_wait(ticket).  Up to 4 read-backs may be outstanding. */
+NRC_API nrc_status nrc_read_frame_partition_async(nrc_renderer* r, void* dst, nrc_frame_format fmt, int* ticket);
+NRC_API nrc_status nrc_readback_wait(nrc_renderer* r, int ticket);
 
 /* ---- data-parallel exchange fused with the optimiser steps (the reference is single-GPU) ----
  * One process per GPU.  Every rank creates an nrc_dp for its replica, publishes nrc_dp_handle_bytes() opaque bytes

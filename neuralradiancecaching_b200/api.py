@@ -114,6 +114,10 @@ class NeuralRadianceCache:
         L.check(L.lib().nrc_mlp_get_stats(self.h, C.byref(v)))
         return NeuralRadianceCache.StatsData(v.value)
 
+    def get_stats_async(self, out):
+        """Queue the copy of mseLoss into out[0] (a page-locked float32 array); valid after readback_wait()/sync()."""
+        L.check(L.lib().nrc_mlp_get_stats_async(self.h, _ptr(out)))
+
     def PrintWeights(self):
         p = self.get_params()[0]
         for i in range(6):

@@ -215,6 +215,7 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream3, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainTrace, cudaEventDisableTiming));
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream4, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
+    NRC_CUDA(cudaStreamCreateWithFlags(&c->streamCopy, cudaStreamNonBlocking));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainWalk, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[0], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[1], cudaEventDisableTiming));
@@ -232,6 +233,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamSynchronize(c->stream2);
     cudaStreamSynchronize(c->stream3);
     cudaStreamSynchronize(c->stream4);
+    cudaStreamSynchronize(c->streamCopy);
     for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
     if (c->pinned) cudaFreeHost(c->pinned);
     prof_drain(c);
@@ -246,6 +248,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaEventDestroy(c->evTrainFree[0]);
     cudaEventDestroy(c->evTrainFree[1]);
     cudaStreamDestroy(c->stream4);
+    cudaStreamDestroy(c->streamCopy);
     delete c;
     return NRC_OK;
 }
@@ -350,6 +353,15 @@ extern "C" nrc_status nrc_mlp_get_stats(nrc_mlp* m, float* mseLoss)
     NRC_REQUIRE(m && mseLoss, "null argument");
     NRC_CUDA(cudaMemcpyAsync(mseLoss, m->grad + NRC_MLP_PARAM_COUNT, sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return NRC_OK;
+}
+
+// GetStats() without the host wait: the copy is queued on the main stream; dst (page-locked host memory) holds the value
+// once a later nrc_readback_wait / nrc_sync has returned.
+extern "C" nrc_status nrc_mlp_get_stats_async(nrc_mlp* m, float* mseLoss)
+{
+    NRC_REQUIRE(m && mseLoss, "null argument");
+    NRC_CUDA(cudaMemcpyAsync(mseLoss, m->grad + NRC_MLP_PARAM_COUNT, sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
     return NRC_OK;
 }
 

@@ -42,6 +42,8 @@ struct nrc_renderer {
     bool overflowPending = false;         // the last frame used a pool below the worst case and its overflow flag is unread
     TraceParams lastP;                    // what the last frame was traced with (a redo after an overflow repeats it)
     uint32_t lastSpp = 0;
+    cudaEvent_t evCopyReady = nullptr, evCopyDone[4] = {nullptr, nullptr, nullptr, nullptr};   // asynchronous read-back
+    int copyNext = 0, copyLast = -1;
     size_t poolCapHint = 0;               // initial vertex-pool capacity with the cache on (0: 4 vertices per path; worst case: 32)
     bool lastInfer = false;
     // train
@@ -200,6 +202,8 @@ extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t
     memset(r->rs, 0, sizeof(r->rs));
     for (int b = 0; b < 2; b++) NRC_CUDA(cudaEventCreateWithFlags(&r->evSetFree[b], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&r->evScalars, cudaEventDisableTiming));
+    NRC_CUDA(cudaEventCreateWithFlags(&r->evCopyReady, cudaEventDisableTiming));
+    for (int k = 0; k < 4; k++) NRC_CUDA(cudaEventCreateWithFlags(&r->evCopyDone[k], cudaEventDisableTiming));
     NRC_CUDA(cudaMemsetAsync(r->taps, 0, 4 * sizeof(unsigned long long), ctx->stream));
     NRC_CUDA(cudaMallocHost(&r->hostScalars, 8 * sizeof(uint32_t)));
     NRC_CUDA(cudaMallocHost(&r->hostTaps, 4 * sizeof(unsigned long long)));
@@ -221,11 +225,14 @@ extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
     cudaStreamSynchronize(r->ctx->stream2);
     cudaStreamSynchronize(r->ctx->stream3);
     cudaStreamSynchronize(r->ctx->stream4);
+    cudaStreamSynchronize(r->ctx->streamCopy);
     free_frame(r);
     free_train(r);
     FREE(r->scalars); FREE(r->taps); FREE(r->totals);
     for (int b = 0; b < 2; b++) if (r->evSetFree[b]) cudaEventDestroy(r->evSetFree[b]);
     if (r->evScalars) cudaEventDestroy(r->evScalars);
+    if (r->evCopyReady) cudaEventDestroy(r->evCopyReady);
+    for (int k = 0; k < 4; k++) if (r->evCopyDone[k]) cudaEventDestroy(r->evCopyDone[k]);
     if (r->hostScalars) cudaFreeHost(r->hostScalars);
     if (r->hostTaps) cudaFreeHost(r->hostTaps);
     delete r;
@@ -282,6 +289,7 @@ extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t heigh
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->streamCopy));
     r->width = width; r->height = height;
     r->y0 = r->ystride > 1 ? r->y0 : 0; r->y1 = height;
     return alloc_frame(r, r->sppAlloc ? r->sppAlloc : 1, (uint32_t)((size_t)width * height * 4));
@@ -299,6 +307,7 @@ extern "C" nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t v
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->streamCopy));
     r->poolCapHint = (size_t)vertices;
     uint32_t spp = r->sppAlloc ? r->sppAlloc : 1;
     size_t cap = vertices ? (size_t)vertices : (size_t)r->width * r->height * spp * 4;
@@ -405,6 +414,7 @@ static nrc_status drain_streams(nrc_ctx* ctx)
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(ctx->streamCopy));
     return NRC_OK;
 }
 
@@ -437,13 +447,15 @@ static nrc_status render_pass(nrc_renderer* r)
         NRC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->evJoin, 0));
     }
     if (r->lastInfer) NRC_TRY(infer_queries(r, ctx->stream));
+    // an asynchronous read-back of the previous frame may still be copying out of the frame buffers
+    if (r->copyLast >= 0) NRC_CUDA(cudaStreamWaitEvent(ctx->stream, r->evCopyDone[r->copyLast], 0));
     NRC_TRY(launch_composite(ctx, ctx->stream, P, r->y0, rows, r->ystride, spp, r->rp, r->ql, r->background, r->frame, r->frame8, r->queryProbe,
                              sc, tapc, r->totals));
     NRC_CUDA(cudaEventRecord(r->evSetFree[b], ctx->stream));
     r->setPending[b] = true;
     // Only a pool below the worst case can overflow.  The flag is read LATER (resolve_overflow): a host wait here would keep
     // the next frame's train trace from being queued while this frame is still tracing.
-    size_t px = (size_t)r->width * r->height;
+    size_t px = (size_t)rows * r->width;   // this rank's pixels: the pool holds only their vertices
     r->overflowPending = (size_t)r->rpool.cap < px * spp * 32;
     return NRC_OK;
 }
@@ -457,7 +469,7 @@ static nrc_status resolve_overflow(nrc_renderer* r, bool redo)
     NRC_CUDA(cudaEventSynchronize(r->evScalars));
     r->overflowPending = false;
     if (r->hostScalars[1] == 0) return NRC_OK;
-    size_t cap = (size_t)r->width * r->height * r->lastSpp * 32;
+    size_t cap = (size_t)part_count(r->y0, r->y1, r->ystride) * r->width * r->lastSpp * 32;
     if (cap > 0x7fffffffu) cap = 0x7fffffffu;
     NRC_REQUIRE((size_t)r->rpool.cap < cap, "vertex pool overflow with the worst-case pool");
     NRC_TRY(drain_streams(r->ctx));
@@ -481,7 +493,7 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
     const nrc_volume_params& v = r->vol->params;
     const bool useNN = (v.useNN == 1u);
     uint32_t spp = (uint32_t)(useNN ? v.withNnSpp : v.noNnSpp);
-    size_t px = (size_t)r->width * r->height;
+    size_t px = (size_t)rows * r->width;   // the vertex pool is sized for this rank's rows
     size_t wantCap = px * spp * (useNN ? 4 : 32);
     if (useNN && r->poolCapHint) wantCap = r->poolCapHint < px * spp * 32 ? r->poolCapHint : px * spp * 32;
     if (wantCap > 0x7fffffffu) wantCap = 0x7fffffffu;
@@ -548,6 +560,39 @@ extern "C" nrc_status nrc_read_frame_partition(nrc_renderer* r, void* dst, nrc_f
     cudaMemcpyKind k = nrc_is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
     NRC_CUDA(cudaMemcpy2DAsync(dst, rowBytes, src, rowBytes * r->ystride, rowBytes, rows, k, r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
+    return NRC_OK;
+}
+
+// The same copy, queued on the copy stream behind everything the main stream holds now; returns at once.  dst must be
+// page-locked host memory (or device memory) that stays valid until nrc_readback_wait(ticket) returns.  The next frame's
+// composite waits for the copy, so the frame buffers are never overwritten under it.
+extern "C" nrc_status nrc_read_frame_partition_async(nrc_renderer* r, void* dst, nrc_frame_format fmt, int* ticket)
+{
+    NRC_REQUIRE(r && dst && ticket, "null argument");
+    NRC_REQUIRE(fmt == NRC_FRAME_RGBA32F || fmt == NRC_FRAME_BGRA8, "unknown frame format");
+    nrc_ctx* ctx = r->ctx;
+    NRC_TRY(resolve_overflow(r, true));   // waits for this frame's TRACE only (long done in steady state), not for the frame
+    int slot = r->copyNext;
+    r->copyNext = (r->copyNext + 1) & 3;
+    uint32_t rows = part_count(r->y0, r->y1, r->ystride);
+    NRC_CUDA(cudaEventRecord(r->evCopyReady, ctx->stream));
+    NRC_CUDA(cudaStreamWaitEvent(ctx->streamCopy, r->evCopyReady, 0));
+    if (rows) {
+        size_t rowBytes = (size_t)r->width * (fmt == NRC_FRAME_RGBA32F ? 16 : 4);
+        const char* src = (const char*)nrc_frame_ptr(r, fmt) + (size_t)r->y0 * rowBytes;
+        cudaMemcpyKind k = nrc_is_device_ptr(dst) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+        NRC_CUDA(cudaMemcpy2DAsync(dst, rowBytes, src, rowBytes * r->ystride, rowBytes, rows, k, ctx->streamCopy));
+    }
+    NRC_CUDA(cudaEventRecord(r->evCopyDone[slot], ctx->streamCopy));
+    r->copyLast = slot;
+    *ticket = slot;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_readback_wait(nrc_renderer* r, int ticket)
+{
+    NRC_REQUIRE(r && ticket >= 0 && ticket < 4, "bad ticket");
+    NRC_CUDA(cudaEventSynchronize(r->evCopyDone[ticket]));
     return NRC_OK;
 }
 

@@ -74,6 +74,15 @@ class NrcHpmRenderer:
         """Device address of the frame (stands in for the VkImage)."""
         return L.lib().nrc_frame_ptr(self.h, C.c_int(fmt))
 
+    def read_frame_partition_async(self, out, fmt=L.FRAME_BGRA8):
+        """Queue the copy of this rank's rows into `out` (page-locked host memory); returns a ticket for readback_wait()."""
+        t = C.c_int(-1)
+        L.check(L.lib().nrc_read_frame_partition_async(self.h, _ptr(out), C.c_int(fmt), C.byref(t)))
+        return t.value
+
+    def readback_wait(self, ticket):
+        L.check(L.lib().nrc_readback_wait(self.h, C.c_int(ticket)))
+
     def read_frame(self, fmt=L.FRAME_RGBA32F, out=None):
         if out is None:
             out = (np.empty((self.height, self.width, 4), np.float32) if fmt == L.FRAME_RGBA32F

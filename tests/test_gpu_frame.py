@@ -235,3 +235,36 @@ def test_queued_frames_equal_frames_read_one_by_one(N, ctx):
     assert _relmax(out[1][1], out[0][1]) < 1e-4
     assert _relmax(out[1][2], out[0][2]) < 1e-4
     assert abs(out[0][3] - out[1][3]) <= 1e-3 * abs(out[0][3])
+
+
+def test_async_readback_delivers_the_same_frames(N, ctx):
+    """Render(k); async copy of frame k; Render(k+1) queued before frame k is awaited: each delivered frame and loss equals
+    what the synchronous calls return for the same frame (the next composite must not overwrite a frame under its copy)."""
+    import torch
+    W, H, tw, th = 64, 48, 16, 16
+    cfg = Cm.scene_cfg(aspect=W / H)
+    rnd = [(0.37, 0.61, 0.13, 0.89), (0.11, 0.93, 0.5, 0.2), (0.71, 0.29, 0.4, 0.6)]
+    r, nrc, m, vol = build(N, ctx, cfg, W, H, tw, th)
+    p0, t0 = nrc.get_params()[0].copy(), m.get_tables()[0].copy()
+    want, want_loss = [], []
+    for f in range(3):
+        vol.random = np.asarray(rnd[f], np.float32)
+        nrc.ResetStats(); r.Render(); ctx.sync()
+        want.append(r.read_frame(N._lib.FRAME_BGRA8).copy()); want_loss.append(nrc.GetStats().mseLoss)
+    # same three frames again from the same start, delivered asynchronously
+    nrc.set_params(p0); nrc.set_state(delta=np.zeros(20995, np.float32), momentum=np.zeros(20995, np.float32)); m.set_tables(t0)
+    bufs = [torch.empty(H * W * 4, dtype=torch.uint8).pin_memory() for _ in range(3)]
+    loss = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(3)]
+    tickets = []
+    for f in range(3):
+        vol.random = np.asarray(rnd[f], np.float32)
+        nrc.ResetStats(); r.Render()
+        nrc.get_stats_async(loss[f].numpy())
+        tickets.append(r.read_frame_partition_async(bufs[f].numpy(), N._lib.FRAME_BGRA8))
+    for f in range(3):
+        r.readback_wait(tickets[f])
+        got = bufs[f].numpy().reshape(H, W, 4)
+        # 8-bit frames: identical up to the last-bit effects of atomically accumulated gradients on later frames
+        assert int(np.abs(got.astype(np.int32) - want[f].astype(np.int32)).max()) <= 1, f
+        assert abs(float(loss[f][0]) - want_loss[f]) <= 1e-3 * abs(want_loss[f]) + 1e-12
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
