@@ -229,6 +229,7 @@ def run_b200(args):
 
     e2e_steps(3)
     barrier()
+    r.totals(reset=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     with torch.cuda.stream(ext):
@@ -378,6 +379,15 @@ FLOP_INFER = 41344.0         # 2 * 20 672 MAC per query
 FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
 
 
+# ncu --set full capture of the default N=1 workload (profiles/r01f_ncu_summary.md): DRAM bytes (read + write) and executed warp
+# instructions per launch.  Only quoted when the run IS that workload.
+NCU_R01F = {
+    "k_train_walk": (108.7e6, 181.07e6), "k_light<train>": (196.5e6, 504.42e6), "k_train_combine": (167.7e6, 2.65e6),
+    "k_train_tc": (1.9e6, 5.33e6), "k_render_walk": (185.9e6, 1152.19e6), "k_light<render>": (128.7e6, 527.32e6),
+    "k_render_combine": (120.3e6, 6.98e6), "k_infer_tc": (13.3e6, 108.44e6), "k_composite": (223.8e6, 19.20e6),
+}
+
+
 def kernel_work(name, tot, pixels, table_floats):
     """(bound, algorithmic units per timed region, unit) of one kernel, from the run's exact counters"""
     if name == "k_light<render>":
@@ -425,8 +435,12 @@ def finish_b200(args, v):
             "traffic": None, "peak_source": which, "launches": kcount, "avg_launch_ms": kms / max(kcount, 1),
             "share_of_step": kms / max(v["ms_total"], 1e-9),
             "note": "share = this kernel's event-timed duration / step time; the two streams overlap, so shares add up to more than 1. "
-                    "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/), so their HBM fraction is low by construction; "
-                    "per-kernel figures for every kernel are under 'kernels'."}
+                    "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/r01f), so their HBM fraction is low by construction: "
+                    "'issue_roofline' is the bound that explains the frame time; per-kernel figures for every kernel are under 'kernels'."}
+    default_workload = (world == 1 and (W, H, v["TW"], v["TH"]) == (1920, 1080, 100, 100) and args.precision == "bf16")
+    if default_workload and name in NCU_R01F:
+        roof["traffic"] = NCU_R01F[name][0]
+        roof["traffic_source"] = "profiles/r01f_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     if work is not None and kms > 0:
         ach = work / (kms * 1e-3) / (1e9 if bound == "hbm" else 1e12)
         roof["achieved"] = ach
@@ -443,6 +457,16 @@ def finish_b200(args, v):
             e["frac_of_peak"] = e[un] / (hbm if b == "hbm" else tflops)
         kernels[kn] = e
     clocks = v["sampler"].summary()
+    # What actually bounds the frame: instruction issue.  Warp instructions per frame from the ncu capture over the peak issue rate
+    # of the machine at the clock sampled during this run.
+    issue = None
+    if default_workload:
+        winst = sum(x[1] for x in NCU_R01F.values())
+        mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0
+        peak_issue = v["ctx"].sm_count * 4 * mhz * 1e6
+        issue = {"warp_instructions_per_step": winst, "peak_warp_instructions_per_s": peak_issue,
+                 "floor_ms_per_step": winst / peak_issue * 1e3, "frac": (winst / peak_issue * 1e3) / (ms_total / K),
+                 "source": "profiles/r01f_ncu_summary.md (smsp__inst_executed.sum of the nine frame kernels)"}
     line = {
         "metric": METRIC, "value": units / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": v["Wm"],
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -457,7 +481,7 @@ def finish_b200(args, v):
                          "the density grid (3.4 MB) is L2-resident by design" % (W * H * 120 / 1e6)},
         "e2e": {"value": units_e2e / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / K,
                 "h2d_bytes_per_step": 40 + 140 + 36 + 28 + 8, "d2h_bytes_per_step": v["d2h_bytes"] + 4},
-        "gpu_launches": launches, "roofline": roof, "kernels": kernels, "clocks": clocks,
+        "gpu_launches": launches, "roofline": roof, "issue_roofline": issue, "kernels": kernels, "clocks": clocks,
         "queries_per_step": {"infer": tot["infer_queries"] / K, "train": tot["train_samples"] / K,
                              "density_taps": (tot["render_taps"] + tot["train_taps"]) / K},
         "mse_loss_last": v["mse"],
