@@ -339,6 +339,17 @@ public:
     void* GetImage() const { return nrc_frame_ptr(m_Handle, NRC_FRAME_BGRA8); }            // device address (stands in for the VkImage)
     size_t GetImageDataSize() const { return nrc_frame_bytes(m_Handle, NRC_FRAME_BGRA8); }  // width*height*4
     void ReadImage(void* dst, nrc_frame_format fmt = NRC_FRAME_BGRA8) const { Check(nrc_read_frame(m_Handle, dst, fmt), "nrc_read_frame"); }
+    // Presenting frame k while frame k+1 is recorded (src/main.cpp:197-230): queue the copy of this rank's rows into page-locked
+    // host memory, keep calling Render(), collect with WaitReadback(ticket).
+    int ReadImageAsync(void* dst, nrc_frame_format fmt = NRC_FRAME_BGRA8) const
+    {
+        int ticket = -1;
+        Check(nrc_read_frame_partition_async(m_Handle, dst, fmt, &ticket), "nrc_read_frame_partition_async");
+        return ticket;
+    }
+    void WaitReadback(int ticket) const { Check(nrc_readback_wait(m_Handle, ticket), "nrc_readback_wait"); }
+    // initial capacity of the render vertex pool (0 = default); an overflowing frame is traced again before it is handed out
+    void SetPoolCapacity(uint64_t vertices) { Check(nrc_renderer_set_pool_capacity(m_Handle, vertices), "nrc_renderer_set_pool_capacity"); }
     void Destroy() { nrc_renderer_destroy(m_Handle); m_Handle = nullptr; }
     nrc_renderer* Get() const { return m_Handle; }
 private:
