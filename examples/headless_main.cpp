@@ -58,6 +58,7 @@ int main(int argc, char** argv)
         en::MRHE mrhe(ctx, 0.01f, 0.0f);                                      // main.cpp:157
         volumeData.Params().useNN = 1;
         en::NrcHpmRenderer renderer(ctx, width, height, 100, 100, camera, volumeData, dirLight, pointLight, hdrEnvMap, nrc, mrhe);   // main.cpp:159-166
+        if (const char* ck = std::getenv("NRC_LOAD_CHECKPOINT")) en::LoadCheckpoint(ck, nrc, mrhe);   // resume a trained cache (not in the reference)
         for (int frame = 0; frame < frames; frame++) {                        // main.cpp:181-248
             if (frame % 100 == 0 && std::getenv("NRC_PRINT_WEIGHTS")) nrc.PrintWeights();   // main.cpp:183-187
             camera.RotateAroundOrigin({0.0f, 1.0f, 0.0f}, 0.01f);             // "camera training" orbit, main.cpp:200-203
@@ -74,6 +75,7 @@ int main(int argc, char** argv)
         std::ofstream f(out, std::ios::binary);
         f << "P6\n" << width << " " << height << "\n255\n";
         for (size_t i = 0; i < (size_t)width * height; i++) { char rgb[3] = {(char)bgra[4 * i + 2], (char)bgra[4 * i + 1], (char)bgra[4 * i]}; f.write(rgb, 3); }
+        if (const char* ck = std::getenv("NRC_SAVE_CHECKPOINT")) en::SaveCheckpoint(ck, nrc, mrhe);
         renderer.Destroy(); mrhe.Destroy(); nrc.Destroy(); hdrEnvMap.Destroy(); volumeData.Destroy();   // main.cpp:253-274
         std::cout << "wrote " << out << std::endl;
     } catch (const std::exception& e) {

@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -293,7 +294,9 @@ public:
     {
         Check(nrc_mrhe_create(ctx.Get(), learningRate, weightDecay, levelCount, hashTableSize, featureCount, minRes, maxRes, resolutions, seed,
                               &m_Handle), "nrc_mrhe_create");
+        m_Shape[0] = levelCount; m_Shape[1] = hashTableSize; m_Shape[2] = featureCount;
     }
+    const uint32_t* GetShape() const { return m_Shape; }   // {levels, entries per level, features}
     void Destroy() { nrc_mrhe_destroy(m_Handle); m_Handle = nullptr; }
     size_t GetHashTableSize() const { return nrc_mrhe_table_bytes(m_Handle); }   // bytes, MRHE.cpp:267-270
     void PrintHashTables() const   // MRHE.cpp:234-260
@@ -307,6 +310,7 @@ public:
     nrc_mrhe* Get() const { return m_Handle; }
 private:
     nrc_mrhe* m_Handle = nullptr;
+    uint32_t m_Shape[3] = {0, 0, 0};
 };
 
 // ---- NrcHpmRenderer (NrcHpmRenderer.hpp:17-96) --------------------------------------------------------------------------
@@ -363,5 +367,46 @@ private:
     const NeuralRadianceCache& m_Nrc;
     const MRHE& m_Mrhe;
 };
+
+// ---- checkpoint of the learnt state (the reference has none).  Same file layout as
+// neuralradiancecaching_b200/checkpoint.py: "NRCB200\0", u32 {version, nParams, nTables, L, T, F}, then float32 params, momentum, tables.
+inline void SaveCheckpoint(const std::string& path, const NeuralRadianceCache& nrc, const MRHE& mrhe)
+{
+    const uint32_t* sh = mrhe.GetShape();
+    std::vector<float> p(NRC_MLP_PARAM_COUNT), m(NRC_MLP_PARAM_COUNT), t((size_t)sh[0] * sh[1] * sh[2]);
+    Check(nrc_mlp_get_params(nrc.Get(), p.data(), nullptr, m.data()), "nrc_mlp_get_params");
+    Check(nrc_mrhe_get_tables(mrhe.Get(), t.data(), nullptr), "nrc_mrhe_get_tables");
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("SaveCheckpoint: cannot open " + path);
+    const uint32_t head[6] = {1u, (uint32_t)p.size(), (uint32_t)t.size(), sh[0], sh[1], sh[2]};
+    bool ok = std::fwrite("NRCB200\0", 1, 8, f) == 8 && std::fwrite(head, 4, 6, f) == 6 && std::fwrite(p.data(), 4, p.size(), f) == p.size() &&
+              std::fwrite(m.data(), 4, m.size(), f) == m.size() && std::fwrite(t.data(), 4, t.size(), f) == t.size();
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) throw std::runtime_error("SaveCheckpoint: short write to " + path);
+}
+
+inline void LoadCheckpoint(const std::string& path, NeuralRadianceCache& nrc, MRHE& mrhe)
+{
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("LoadCheckpoint: cannot open " + path);
+    char magic[8];
+    uint32_t head[6];
+    bool ok = std::fread(magic, 1, 8, f) == 8 && std::memcmp(magic, "NRCB200\0", 8) == 0 && std::fread(head, 4, 6, f) == 6 && head[0] == 1u;
+    const uint32_t* sh = mrhe.GetShape();
+    ok = ok && head[1] == (uint32_t)NRC_MLP_PARAM_COUNT && head[3] == sh[0] && head[4] == sh[1] && head[5] == sh[2] &&
+         head[2] == sh[0] * sh[1] * sh[2];
+    std::vector<float> p, m, t;
+    if (ok) {
+        p.resize(head[1]); m.resize(head[1]); t.resize(head[2]);
+        ok = std::fread(p.data(), 4, p.size(), f) == p.size() && std::fread(m.data(), 4, m.size(), f) == m.size() &&
+             std::fread(t.data(), 4, t.size(), f) == t.size();
+    }
+    std::fclose(f);
+    if (!ok) throw std::runtime_error("LoadCheckpoint: " + path + " is not a checkpoint of this cache shape");
+    std::vector<float> zp(p.size(), 0.0f), zt(t.size(), 0.0f);
+    Check(nrc_mlp_set_params(nrc.Get(), p.data()), "nrc_mlp_set_params");
+    Check(nrc_mlp_set_state(nrc.Get(), zp.data(), m.data()), "nrc_mlp_set_state");
+    Check(nrc_mrhe_set_tables(mrhe.Get(), t.data(), zt.data()), "nrc_mrhe_set_tables");
+}
 
 }   // namespace en

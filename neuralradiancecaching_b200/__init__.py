@@ -13,3 +13,4 @@ from .api import (Context, NeuralRadianceCache, MRHE, mrhe_resolutions, encode, 
 from .objects import Camera, DirLight, PointLight, VolumeData, HdrEnvMap, hdr4f_to_cdf, vec_from_angles
 from .renderer import NrcHpmRenderer
 from .loaders import ReadFileDensity3D, ReadFileHdr4f
+from .checkpoint import save_checkpoint, load_checkpoint

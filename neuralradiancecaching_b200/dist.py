@@ -100,6 +100,31 @@ class FusedExchange:
             self.h = None
 
 
+def gather_rows(part, height, rank, world, dst=0):
+    """Frame assembly: every rank holds its interleaved rows (rank, rank+world, ...) compacted in `part`
+    ([rows, width, channels] torch tensor, CPU for gloo or CUDA for NCCL); rank `dst` gets the [height, width, channels] frame,
+    the others None.  Row counts differ by at most one between ranks: parts are padded to the longest."""
+    import torch
+    import torch.distributed as dist
+    rows_max = strided_count(0, height, world)
+    pad = part
+    if part.shape[0] < rows_max:
+        pad = torch.zeros((rows_max,) + tuple(part.shape[1:]), dtype=part.dtype, device=part.device)
+        pad[:part.shape[0]] = part
+    pad = pad.contiguous()
+    if world == 1:
+        return pad[:height]
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad)            # 4 B/pixel at BGRA8: small next to a frame's work; gather-to-one is not in every backend
+    if rank != dst:
+        return None
+    full = torch.empty((height,) + tuple(part.shape[1:]), dtype=part.dtype, device=part.device)
+    for k in range(world):
+        n = strided_count(k, height, world)
+        full[k::world] = parts[k][:n]
+    return full
+
+
 def allreduce_host(arrays):
     """gloo/CPU variant used by the world_size-2 tests: numpy arrays summed over ranks in place."""
     import torch

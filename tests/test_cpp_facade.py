@@ -37,3 +37,20 @@ def test_headless_main_renders(tmp_path):
     data = open(out, "rb").read()
     assert data.startswith(b"P6\n160 96\n255\n") and len(data) == len(b"P6\n160 96\n255\n") + 160 * 96 * 3
     assert len(set(data[15:])) > 8   # not a constant image
+
+
+@pytest.mark.gpu
+def test_checkpoint_written_by_cpp_is_read_by_python_and_back(tmp_path):
+    """headless_main saves a checkpoint after 10 frames; the Python reader parses it; a second run resumes from it."""
+    from neuralradiancecaching_b200 import checkpoint as K
+    exe = _build()
+    ck = str(tmp_path / "cache.nrc")
+    env = dict(os.environ, NRC_SAVE_CHECKPOINT=ck)
+    p = subprocess.run([exe, "10", "96", "64", str(tmp_path / "a.ppm")], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stderr
+    c = K.read_checkpoint(ck)
+    assert (c["L"], c["T"], c["F"]) == (16, 16384, 2) and c["params"].size == 20995
+    assert c["momentum"].any() and c["tables"].any()
+    env = dict(os.environ, NRC_LOAD_CHECKPOINT=ck)
+    p = subprocess.run([exe, "1", "96", "64", str(tmp_path / "b.ppm")], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stderr

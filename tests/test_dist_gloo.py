@@ -73,3 +73,30 @@ def test_weak_scaling_frame_shapes():
         assert abs(w * h / (1920 * 1080) - n) < 0.02 * n and tw * th == 10000 * n
     rows = [D.shard_rows(k, 3, 10) for k in range(3)]
     assert sorted(np.concatenate(rows).tolist()) == list(range(10))
+
+
+def _gather_worker(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch
+    import torch.distributed as dist
+    from neuralradiancecaching_b200 import dist as D
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    H, W = 7, 5                                   # odd height: rank 0 has one row more than rank 1
+    frame = torch.arange(H * W * 4, dtype=torch.int32).reshape(H, W, 4)
+    part = frame[rank::world].contiguous()        # what nrc_read_frame_partition hands a rank
+    assert part.shape[0] == D.strided_count(rank, H, world)
+    full = D.gather_rows(part, H, rank, world)
+    if rank == 0:
+        np.save(os.path.join(out, "full.npy"), full.numpy())
+    else:
+        assert full is None
+    dist.destroy_process_group()
+
+
+def test_frame_assembly_from_interleaved_rows(tmp_path):
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(_gather_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    full = np.load(tmp_path / "full.npy")
+    np.testing.assert_array_equal(full, np.arange(7 * 5 * 4, dtype=np.int32).reshape(7, 5, 4))
