@@ -191,6 +191,10 @@ NRC_API nrc_status nrc_envmap_create(nrc_ctx* ctx, uint32_t width, uint32_t heig
                                      const float* invCdfY, nrc_envmap** out);
 NRC_API nrc_status nrc_envmap_destroy(nrc_envmap* env);
 NRC_API nrc_status nrc_envmap_set_strengths(nrc_envmap* env, float directStrength, float hpmStrength);  /* HdrEnvMap.cpp:108, 259-279 */
+/* Opt-in estimator, not the shipped behaviour: `halfSampleCount = sampleCount / 2` as left commented out at
+ * nrc-forward.frag:715 -- 4 of the 8 env directions per lit vertex are drawn from the map's inverse CDFs
+ * (nrc-forward.frag:727-744).  Needs an env map created with both inverse-CDF images. */
+NRC_API nrc_status nrc_envmap_set_importance_sampling(nrc_envmap* env, int on);
 /* Hdr4fToCdf (src/read_file.cpp:141-206) on the device. */
 NRC_API nrc_status nrc_hdr4f_to_cdf(nrc_ctx* ctx, const float* rgba, uint32_t width, uint32_t height, float* invCdfX, float* invCdfY);
 

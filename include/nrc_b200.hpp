@@ -236,6 +236,7 @@ public:
                                 hdrCdfY.empty() ? nullptr : hdrCdfY.data(), &m_Handle), "nrc_envmap_create");
     }
     void SetStrengths(float directStrength, float hpmStrength) { Check(nrc_envmap_set_strengths(m_Handle, directStrength, hpmStrength), "nrc_envmap_set_strengths"); }
+    void SetImportanceSampling(bool on) { Check(nrc_envmap_set_importance_sampling(m_Handle, on ? 1 : 0), "nrc_envmap_set_importance_sampling"); }   // opt-in, fwd.frag:715
     nrc_envmap* Get() const { return m_Handle; }
     void Destroy() { nrc_envmap_destroy(m_Handle); m_Handle = nullptr; }
 private:

@@ -44,7 +44,7 @@ nrc_mlp_set_state nrc_mlp_get_params nrc_mlp_reset_stats nrc_mlp_get_stats nrc_m
 nrc_mrhe_resolutions nrc_mrhe_create nrc_mrhe_destroy nrc_mrhe_set_config nrc_mrhe_table_bytes nrc_mrhe_set_tables
 nrc_mrhe_get_tables nrc_mrhe_grad_ptr nrc_mrhe_grad_extent nrc_encode nrc_encode_dir nrc_infer nrc_train_accumulate
 nrc_optimizer_step nrc_volume_create nrc_volume_destroy nrc_volume_set_params nrc_volume_sample nrc_envmap_create
-nrc_envmap_destroy nrc_envmap_set_strengths nrc_hdr4f_to_cdf nrc_renderer_create nrc_renderer_destroy
+nrc_envmap_destroy nrc_envmap_set_strengths nrc_envmap_set_importance_sampling nrc_hdr4f_to_cdf nrc_renderer_create nrc_renderer_destroy
 nrc_renderer_set_camera nrc_renderer_set_dir_light nrc_renderer_set_point_light nrc_renderer_set_partition nrc_resize
 nrc_render nrc_frame_train nrc_frame_render nrc_frame_bytes nrc_frame_ptr nrc_read_frame nrc_read_render_probes
 nrc_read_train_probes nrc_frame_stats nrc_frame_totals nrc_renderer_set_partition_strided nrc_read_frame_partition

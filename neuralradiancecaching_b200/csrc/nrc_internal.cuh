@@ -119,6 +119,7 @@ struct nrc_envmap {
     float* invCdfX = nullptr;
     float* invCdfY = nullptr;
     float directStrength = 1.0f, hpmStrength = 8.0f;
+    bool cdfHalf = false;        // opt-in: half of the env gather by inverse-CDF importance sampling (fwd.frag:727-744)
 };
 
 // Everything the trace kernels need, passed by value as a __grid_constant__ kernel parameter.
@@ -138,6 +139,8 @@ struct TraceParams {
     const uint2* bricks;
     const float4* env;
     int envW, envH;
+    const float* envInvCdfX;      // [envH][envW], non-null only when the CDF half of the env gather is switched on
+    const float* envInvCdfY;      // [envH]
     uint32_t width, height;       // frame
     uint32_t trainW, trainH;
     float widthFactor, heightFactor;

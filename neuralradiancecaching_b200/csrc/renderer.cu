@@ -343,6 +343,8 @@ static TraceParams make_params(const nrc_renderer* r)
     P.nx = (int)r->vol->nx; P.ny = (int)r->vol->ny; P.nz = (int)r->vol->nz;
     P.bricks = r->vol->bricks;
     P.env = r->env->rgba; P.envW = (int)r->env->w; P.envH = (int)r->env->h;
+    const bool cdfHalf = r->env->cdfHalf && r->env->invCdfX && r->env->invCdfY;
+    P.envInvCdfX = cdfHalf ? r->env->invCdfX : nullptr; P.envInvCdfY = cdfHalf ? r->env->invCdfY : nullptr;
     P.width = r->width; P.height = r->height; P.trainW = r->trainW; P.trainH = r->trainH;
     P.widthFactor = 1.0f / (float)r->trainW;     // NrcHpmRenderer.cpp:409-411
     P.heightFactor = 1.0f / (float)r->trainH;

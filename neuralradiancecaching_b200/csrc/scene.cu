@@ -96,6 +96,17 @@ extern "C" nrc_status nrc_envmap_set_strengths(nrc_envmap* e, float directStreng
     return NRC_OK;
 }
 
+// Opt-in estimator: `halfSampleCount = sampleCount / 2` as the author left it commented out at
+// nrc-forward.frag:715 -- 4 of the 8 env directions per vertex come from the inverse CDFs of the map (fwd.frag:727-744).
+// Consumes the same 16 random numbers per vertex, so the walks (and every other pixel's RNG stream) are unchanged.
+extern "C" nrc_status nrc_envmap_set_importance_sampling(nrc_envmap* e, int on)
+{
+    NRC_REQUIRE(e, "null envmap");
+    NRC_REQUIRE(!on || (e->invCdfX && e->invCdfY), "the env map was created without inverse CDFs (nrc_hdr4f_to_cdf)");
+    e->cdfHalf = on != 0;
+    return NRC_OK;
+}
+
 // ---- Hdr4fToCdf / InvertCdf (src/read_file.cpp:123-206) --------------------------------------------------------------------
 // The reference sums each row sequentially in float; the running sums are kept sequential here too (one thread per
 // row, strict adds) so the tables are bit-identical -- a parallel scan would round differently.  Rows are independent,

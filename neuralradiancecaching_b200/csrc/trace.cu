@@ -76,6 +76,53 @@ __device__ __forceinline__ f3 env_lookup(const TraceParams& P, f3 d, float stren
                (w00 * t00.z + w10 * t10.z + w01 * t01.z + w11 * t11.z) * strength);
 }
 
+// texture(sampler, u) of a single-channel float image: linear, clamp-to-edge (the two inverse-CDF images, HdrEnvMap.cpp:126-148)
+__device__ __forceinline__ float tex1_clamp(const float* __restrict__ row, int w, float uc)
+{
+    float u = uc * (float)w - 0.5f;
+    if (!(u == u)) return 0.0f;
+    u = fminf(fmaxf(u, -1.0f), (float)w);
+    float fu = floorf(u), a = u - fu;
+    int i0 = (int)fu, i1 = i0 + 1;
+    i0 = min(max(i0, 0), w - 1); i1 = min(max(i1, 0), w - 1);
+    return (1.0f - a) * __ldg(row + i0) + a * __ldg(row + i1);
+}
+
+__device__ __forceinline__ float tex2_clamp(const float* __restrict__ img, int w, int h, float uc, float vc)
+{
+    float x = uc * (float)w - 0.5f, y = vc * (float)h - 0.5f;
+    if (!(x == x) || !(y == y)) return 0.0f;
+    x = fminf(fmaxf(x, -1.0f), (float)w);
+    y = fminf(fmaxf(y, -1.0f), (float)h);
+    float fx = floorf(x), fy = floorf(y), a = x - fx, b = y - fy;
+    int i0 = (int)fx, j0 = (int)fy;
+    int i1 = min(max(i0 + 1, 0), w - 1), j1 = min(max(j0 + 1, 0), h - 1);
+    i0 = min(max(i0, 0), w - 1); j0 = min(max(j0, 0), h - 1);
+    float t00 = __ldg(img + (size_t)j0 * w + i0), t10 = __ldg(img + (size_t)j0 * w + i1);
+    float t01 = __ldg(img + (size_t)j1 * w + i0), t11 = __ldg(img + (size_t)j1 * w + i1);
+    return ((1.0f - a) * (1.0f - b) * t00 + a * (1.0f - b) * t10) + ((1.0f - a) * b * t01 + a * b * t11);
+}
+
+// texture(hdrEnvMap, uv).xyz * strength
+__device__ __forceinline__ f3 env_texel(const TraceParams& P, float u, float v, float strength)
+{
+    float x = u * (float)P.envW - 0.5f, y = v * (float)P.envH - 0.5f;
+    if (!(x == x) || !(y == y)) return mk3(0.0f, 0.0f, 0.0f);
+    x = fminf(fmaxf(x, -1.0f), (float)P.envW);
+    y = fminf(fmaxf(y, -1.0f), (float)P.envH);
+    float fx = floorf(x), fy = floorf(y);
+    float a = x - fx, b = y - fy;
+    int i0 = (int)fx, j0 = (int)fy;
+    int i1 = min(max(i0 + 1, 0), P.envW - 1), j1 = min(max(j0 + 1, 0), P.envH - 1);
+    i0 = min(max(i0, 0), P.envW - 1); j0 = min(max(j0, 0), P.envH - 1);
+    float4 t00 = __ldg(P.env + (size_t)j0 * P.envW + i0), t10 = __ldg(P.env + (size_t)j0 * P.envW + i1);
+    float4 t01 = __ldg(P.env + (size_t)j1 * P.envW + i0), t11 = __ldg(P.env + (size_t)j1 * P.envW + i1);
+    float w00 = (1.0f - a) * (1.0f - b), w10 = a * (1.0f - b), w01 = (1.0f - a) * b, w11 = a * b;
+    return mk3((w00 * t00.x + w10 * t10.x + w01 * t01.x + w11 * t11.x) * strength,
+               (w00 * t00.y + w10 * t10.y + w01 * t01.y + w11 * t11.y) * strength,
+               (w00 * t00.z + w10 * t10.z + w01 * t01.z + w11 * t11.z) * strength);
+}
+
 __device__ __forceinline__ WalkParams make_walk(const TraceParams& P)
 {
     WalkParams w;
@@ -346,7 +393,7 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
 
 // MB = resident blocks ptxas must allow: WITHOUT a minimum it chases occupancy and sinks every brick load next to its use (one
 // load in flight per thread, ncu r01f: 35-57 % long-scoreboard); with a register budget it keeps the batch of loads together.
-template <bool RENDER, int MB>
+template <bool RENDER, int MB, bool CDF>
 __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
 {
     const uint32_t count = min(*pool.count, pool.cap);
@@ -385,11 +432,26 @@ __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ Trace
                 float4 r = pool.rnd[(size_t)vtx * 4 + k];
 #pragma unroll 1
                 for (int h = 0; h < 2; h++) {
-                    f3 rdir = new_ray_dir_given(dir, P.g, h ? r.z : r.x, h ? r.w : r.y);
+                    const float r0 = h ? r.z : r.x, r1 = h ? r.w : r.y;
+                    f3 rdir, c;
+                    float phase = 1.0f;
+                    if (CDF && k >= 2) {   // opt-in CDF half (fwd.frag:727-744): samples 4..7, draws 8..15
+                        float thetaNorm = tex1_clamp(P.envInvCdfY, P.envH, r0);
+                        float phiNorm = tex2_clamp(P.envInvCdfX, P.envW, P.envH, r1, thetaNorm);
+                        // the unit direction the map's uv convention (fwd.frag:690-708) assigns to texel (phiNorm, thetaNorm); the
+                        // expression at fwd.frag:735 is neither unit length nor that direction (dead code there, NaN phase if run)
+                        float th = thetaNorm * 3.14159265358979323846f, ph2 = phiNorm * 2.0f * 3.14159265358979323846f;
+                        float st = sinf(th);
+                        rdir = mk3(-st * cosf(ph2), -cosf(th), -st * sinf(ph2));
+                        phase = hg_phase(P.g, -dot3(rdir, dir));
+                        c = env_texel(P, phiNorm, thetaNorm, P.envHpm);
+                    } else {
+                        rdir = new_ray_dir_given(dir, P.g, r0, r1);
+                        c = env_lookup(P, rdir, P.envHpm);
+                    }
                     f3 en, ex;
                     find_entry_exit(box, pos, rdir, en, ex, sdf);
-                    float T = transmittance<16>(tc, kDensity, pos, ex, taps);
-                    f3 c = env_lookup(P, rdir, P.envHpm);
+                    float T = transmittance<16>(tc, kDensity, pos, ex, taps) * phase;
                     acc.x += c.x * T; acc.y += c.y * T; acc.z += c.z * T;
                 }
             }
@@ -637,8 +699,9 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
     if (mb < 0) { const char* e = getenv("NRC_LIGHT_MB"); mb = e ? atoi(e) : 8; }
 #define LIGHT_CASE(MBV)                                                                                                              \
     case MBV:                                                                                                                        \
-        if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, (k_light<true, MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, (k_light<false, MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
+        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, (k_light<true, MBV, true><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, (k_light<true, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, (k_light<false, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
         break;
     switch (mb) {
         LIGHT_CASE(4)

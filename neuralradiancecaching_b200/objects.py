@@ -204,6 +204,10 @@ class HdrEnvMap:
         L.check(L.lib().nrc_envmap_create(ctx.h, C.c_uint32(width), C.c_uint32(height), _ptr(rgba), _ptr(cx), _ptr(cy), C.byref(self.h)))
         self.directStrength, self.hpmStrength = 1.0, 8.0   # HdrEnvMap.cpp:108
 
+    def set_importance_sampling(self, on):
+        """Opt-in (not the shipped estimator): 4 of the 8 env directions per vertex from the inverse CDFs (fwd.frag:715, 727-744)."""
+        L.check(L.lib().nrc_envmap_set_importance_sampling(self.h, C.c_int(1 if on else 0)))
+
     def set_strengths(self, direct, hpm):
         self.directStrength, self.hpmStrength = direct, hpm
         L.check(L.lib().nrc_envmap_set_strengths(self.h, C.c_float(direct), C.c_float(hpm)))

@@ -68,6 +68,7 @@ struct Scene {
     sampler1D hdrEnvMapInvCdfY;
     std::vector<float> envStorage, cdfXStorage, cdfYStorage;
     HdrEnvMapU hdrEnvMapData;
+    bool envCdfHalf = false;   // opt-in: halfSampleCount = sampleCount / 2, the variant commented out at fwd.frag:715
     MrheU mrhe;
     std::vector<float> mrHashTable, mrDeltaHashTable;
     NrcConfig nrcConfig;
@@ -430,7 +431,7 @@ struct Invocation {
     vec3 SampleHdrEnvMapGather(const vec3 pos, const vec3 dir, uint sampleCount)
     {
         vec3 light = vec3(0.0f);
-        const uint halfSampleCount = sampleCount;   // the CDF-importance half never runs
+        const uint halfSampleCount = S.envCdfHalf ? sampleCount / 2 : sampleCount;   // as shipped the CDF-importance half never runs
         for (uint i = 0; i < halfSampleCount; i++) {
             const vec3 randomDir = NewRayDir(dir);
             const float phase = 1.0f;
@@ -443,7 +444,12 @@ struct Invocation {
         for (uint i = 0; i < sampleCount - halfSampleCount; i++) {
             const float thetaNorm = texture(S.hdrEnvMapInvCdfY, RandFloat(1.0f)).x;
             const float phiNorm = texture(S.hdrEnvMapInvCdfX, vec2(RandFloat(1.0f), thetaNorm)).x;
-            const vec3 randomDir = sin(thetaNorm * PI) * vec3(cos(phiNorm * 2.0f * PI), 1.0f, sin(phiNorm * 2.0f * PI));
+            // As written (fwd.frag:735) the direction is sin(theta) * (cos(phi), 1, sin(phi)): not a unit vector (|d| up to 1.41 makes
+            // hg_phase_func take pow of a negative number -> NaN) and not the direction of texel (phiNorm, thetaNorm) under the map's
+            // own uv convention (uv = (atan(z,x), asin(y)) * (1/2pi, 1/pi) + 0.5, fwd.frag:690-708).  The loop is dead code in the
+            // reference; the opt-in uses the unit direction that convention assigns to the texel.
+            const float th = thetaNorm * PI, ph = phiNorm * 2.0f * PI;
+            const vec3 randomDir = vec3(-sin(th) * cos(ph), -cos(th), -sin(th) * sin(ph));
             const float phase = hg_phase_func(dot(randomDir, -dir));
             vec3 ee[2];
             find_entry_exit(pos, randomDir, ee);

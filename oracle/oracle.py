@@ -96,6 +96,10 @@ class OracleScene:
         self.l.orc_set_envmap(self.h, C.c_int(w), C.c_int(h), _p(rgba), _p(cx), _p(cy), C.c_float(direct_strength),
                               C.c_float(hpm_strength))
 
+    def set_env_cdf_half(self, on):
+        """opt-in: 4 phase-sampled + 4 CDF-importance-sampled env directions per vertex (fwd.frag:715 as commented out there)"""
+        self.l.orc_set_env_cdf_half(self.h, C.c_int(1 if on else 0))
+
     def set_mlp(self, params, lr=0.001, wd=0.0, beta1=0.5):
         p = None if params is None else _f(params)
         assert p is None or p.size == PARAM_COUNT

@@ -268,3 +268,43 @@ def test_async_readback_delivers_the_same_frames(N, ctx):
         assert int(np.abs(got.astype(np.int32) - want[f].astype(np.int32)).max()) <= 1, f
         assert abs(float(loss[f][0]) - want_loss[f]) <= 1e-3 * abs(want_loss[f]) + 1e-12
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+
+
+def test_env_importance_half_matches_oracle(N, ctx):
+    """Opt-in estimator: with the CDF half of the env gather switched on, the walk's control flow is
+    unchanged (same 16 draws per vertex) and the frame matches the oracle run with the same switch."""
+    W, H = 64, 48
+    cfg = Cm.scene_cfg(use_nn=0, aspect=W / H)
+    env_rgba = Cm.envmap()
+    eh, ew = env_rgba.shape[:2]
+    cdf_x, cdf_y = N.hdr4f_to_cdf(ctx, env_rgba, ew, eh)
+    sc = Cm.oracle_scene(cfg)
+    sc.set_envmap(env_rgba, cdf_x, cdf_y, cfg["env_direct"], cfg["env_hpm"])
+    base, cnt0, _ = sc.render(W, H)
+    sc.set_env_cdf_half(True)
+    want, cnt1, _ = sc.render(W, H)
+    for col in (0, 1, 3):
+        np.testing.assert_array_equal(cnt0[..., col], cnt1[..., col])   # same RNG consumption, lit vertices and walk steps
+    assert np.isfinite(want).all()
+    assert Cm.psnr(want, base) < 50.0                            # ... but a different estimator
+    vol = N.VolumeData(ctx, Cm.density())
+    vol.useNN, vol.showNonNN, vol.densityFactor, vol.g = 0, 0, cfg["density_factor"], cfg["g"]
+    vol.random = cfg["random4"]
+    env = N.HdrEnvMap(ctx, ew, eh, env_rgba, cdf_x, cdf_y)
+    env.set_strengths(cfg["env_direct"], cfg["env_hpm"])
+    dl = N.DirLight(Cm.DIR_ZENITH, Cm.DIR_AZIMUTH, (1, 1, 1), cfg["dir_strength"])
+    pl = N.PointLight(cfg["pt_pos"], cfg["pt_color"], cfg["pt_strength"])
+    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
+    m = N.MRHE(ctx, 0.01, 0.0, seed=0)
+    r = N.NrcHpmRenderer(W, H, 8, 8, cfg["cam"], vol, dl, pl, env, nrc, m)
+    r.FrameRender(); ctx.sync()
+    assert Cm.psnr(r.read_frame(), base) >= PSNR_MIN             # off by default
+    env.set_importance_sampling(True)
+    r.FrameRender(); ctx.sync()
+    cnt, _ = r.read_render_probes()
+    np.testing.assert_array_equal(cnt[..., 0], cnt1[..., 0])
+    assert Cm.psnr(r.read_frame(), want) >= PSNR_MIN
+    plain = N.HdrEnvMap(ctx, ew, eh, env_rgba)
+    with pytest.raises(N.NrcError):
+        plain.set_importance_sampling(True)                      # no inverse CDFs: refused
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy(); env.Destroy(); plain.Destroy()
