@@ -146,7 +146,10 @@ NRC_HD float nrc_sin(float x)
 {
     int q;
     float r = nrc_reduce_pio2(x, &q);
-    float v = (q & 1) ? nrc_cos_poly(r) : nrc_sin_poly(r);
+    /* both polynomials, then a select: the same value as evaluating only the chosen one, but no divergent branch in a warp
+     * whose lanes sit in different quadrants (the RNG calls this 16 times per lit vertex) */
+    float s = nrc_sin_poly(r), c = nrc_cos_poly(r);
+    float v = (q & 1) ? c : s;
     return (q & 2) ? -v : v;
 }
 
@@ -154,7 +157,8 @@ NRC_HD float nrc_cos(float x)
 {
     int q;
     float r = nrc_reduce_pio2(x, &q);
-    float v = (q & 1) ? nrc_sin_poly(r) : nrc_cos_poly(r);
+    float s = nrc_sin_poly(r), c = nrc_cos_poly(r);
+    float v = (q & 1) ? s : c;
     return ((q + 1) & 2) ? -v : v;
 }
 

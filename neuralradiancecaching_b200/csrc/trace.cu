@@ -193,7 +193,8 @@ struct ChunkEmitter {
 };
 
 // ---- render walk (nrc-forward.vert:28-40, nrc-forward.frag:757-870 minus lighting and Forward()) ------------------
-__global__ void __launch_bounds__(128) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
                                                      uint32_t spp, VertexPool pool, RenderPaths paths, float4* __restrict__ background,
                                                      uint32_t* __restrict__ counters)
 {
@@ -650,8 +651,17 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
 {
     uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
-    NRC_LAUNCH(ctx, st, K_RENDER_WALK,
-               k_render_walk<<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters));
+    static int mb = -1;
+    if (mb < 0) { const char* e = getenv("NRC_RWALK_MB"); mb = e ? atoi(e) : 8; }
+    if (mb == 8)
+        NRC_LAUNCH(ctx, st, K_RENDER_WALK,
+                   (k_render_walk<8><<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters)));
+    else if (mb == 6)
+        NRC_LAUNCH(ctx, st, K_RENDER_WALK,
+                   (k_render_walk<6><<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters)));
+    else
+        NRC_LAUNCH(ctx, st, K_RENDER_WALK,
+                   (k_render_walk<7><<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters)));
     return NRC_OK;
 }
 
