@@ -215,6 +215,10 @@ NRC_API nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32_t 
  * bound is 32 lit vertices per path, nrc-forward.frag:772-806, and a pool of that size cannot overflow).  A frame that
  * overflows a smaller pool is traced again with the worst-case pool before any read-back or nrc_sync returns. */
 NRC_API nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t vertices);
+/* Opt-in estimator, not the shipped behaviour: the env-map term of TraceScene in the training targets, commented out at
+ * nrc-train.comp:1118 (SampleHdrEnvMap(pos, dir, 8) as in nrc-forward.frag:751-755).  Changes the train walk's RNG
+ * consumption (16 more draws per lit vertex, before the two of NewRayDir). */
+NRC_API nrc_status nrc_renderer_set_train_env_light(nrc_renderer* r, int on);
 /* ResizeFrame, NrcHpmRenderer.cpp:103-126 */
 NRC_API nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t height);
 

@@ -354,6 +354,7 @@ public:
     }
     void WaitReadback(int ticket) const { Check(nrc_readback_wait(m_Handle, ticket), "nrc_readback_wait"); }
     // initial capacity of the render vertex pool (0 = default); an overflowing frame is traced again before it is handed out
+    void SetTrainEnvLight(bool on) { Check(nrc_renderer_set_train_env_light(m_Handle, on ? 1 : 0), "nrc_renderer_set_train_env_light"); }   // opt-in, train.comp:1118
     void SetPoolCapacity(uint64_t vertices) { Check(nrc_renderer_set_pool_capacity(m_Handle, vertices), "nrc_renderer_set_pool_capacity"); }
     void Destroy() { nrc_renderer_destroy(m_Handle); m_Handle = nullptr; }
     nrc_renderer* Get() const { return m_Handle; }

@@ -219,7 +219,6 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainWalk, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[0], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[1], cudaEventDisableTiming));
-    NRC_CUDA(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
     *out = c;
     return NRC_OK;
@@ -238,7 +237,6 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     if (c->pinned) cudaFreeHost(c->pinned);
     prof_drain(c);
     for (NrcProfRec& r : c->profFree) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
-    cudaEventDestroy(c->evFork);
     cudaEventDestroy(c->evJoin);
     cudaStreamDestroy(c->stream);
     cudaStreamDestroy(c->stream2);

@@ -57,7 +57,7 @@ struct nrc_ctx {
     cudaStream_t stream2 = nullptr;       // second stream: render walk overlaps the training chain
     cudaStream_t stream3 = nullptr;       // third stream: the train TRACE of frame k+1 (needs no weights) runs ahead of frame k's MLP tail
     cudaStream_t streamCopy = nullptr;    // asynchronous read-back of finished frames
-    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    cudaEvent_t evJoin = nullptr;
     cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
     cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[2] = {nullptr, nullptr};
     nrc_mlp_precision precision = NRC_MLP_FP32;

@@ -52,6 +52,7 @@ struct nrc_renderer {
     TrainPaths tpb[2];                // double-buffered: the walk of frame k+1 fills one set while lights/combine/MLP of frame k read the other
     VertexPool tpoolb[2];
     int trainBuf = 1;
+    bool trainEnvLight = false;       // opt-in: env-map term in the training targets (train pools then carry random numbers)
     uint32_t* trainCounters = nullptr;
     uint32_t trainAlloc = 0;
     // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count; train sets: {2,3} and {6,7}
@@ -166,7 +167,7 @@ static nrc_status alloc_train(nrc_renderer* r)
         NRC_CUDA(cudaMemsetAsync(tp.dir, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
         NRC_CUDA(cudaMemsetAsync(tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
         // device scalars of the two sets: {2,3} and {6,7}
-        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, false, r->scalars + 2 + 4 * b, r->scalars + 3 + 4 * b));
+        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, r->trainEnvLight, r->scalars + 2 + 4 * b, r->scalars + 3 + 4 * b));
     }
     NRC_CUDA(cudaMalloc(&r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
     NRC_CUDA(cudaMemsetAsync(r->trainCounters, 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
@@ -315,6 +316,22 @@ extern "C" nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t v
     return alloc_frame(r, spp, (uint32_t)cap);
 }
 
+// Opt-in estimator: the env-map term of TraceScene in the TRAINING targets, which nrc-train.comp:1118 has
+// commented out.  A lit training vertex then draws the 16 random numbers of SampleHdrEnvMap first (the render walk's order),
+// the train pools carry them, and the training vertices go through the render variant of the light kernel.
+extern "C" nrc_status nrc_renderer_set_train_env_light(nrc_renderer* r, int on)
+{
+    NRC_REQUIRE(r, "null renderer");
+    if (r->trainEnvLight == (on != 0)) return NRC_OK;
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    r->trainEnvLight = on != 0;
+    r->trainPending[0] = r->trainPending[1] = false;
+    return alloc_train(r);
+}
+
 static TraceParams make_params(const nrc_renderer* r)
 {
     TraceParams P;
@@ -392,7 +409,7 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
         NRC_CUDA(cudaEventRecord(ctx->evTrainWalk, tw));
         NRC_CUDA(cudaStreamWaitEvent(tl, ctx->evTrainWalk, 0));
     }
-    NRC_TRY(launch_light(ctx, tl, P, r->tpool, false, r->taps + 1 + b));
+    NRC_TRY(launch_light(ctx, tl, P, r->tpool, r->trainEnvLight, r->taps + 1 + b, K_LIGHT_TRAIN));
     NRC_TRY(launch_train_combine(ctx, tl, n, r->tpool, r->tp, r->taps + b, r->totals));   // reads taps[1] of the pointer it gets
     if (ahead) {
         NRC_CUDA(cudaEventRecord(ctx->evTrainTrace, tl));
@@ -440,7 +457,7 @@ static nrc_status render_pass(nrc_renderer* r)
     NRC_CUDA(cudaMemsetAsync(sc + 4, 0, sizeof(uint32_t), s2));
     NRC_CUDA(cudaMemsetAsync(tapc, 0, sizeof(unsigned long long), s2));
     NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
-    NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, tapc));
+    NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, tapc, K_LIGHT_RENDER));
     NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, sc, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s2));
     NRC_CUDA(cudaEventRecord(r->evScalars, s2));

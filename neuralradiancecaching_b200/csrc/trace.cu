@@ -169,7 +169,7 @@ struct ChunkEmitter {
     uint32_t cur, end, next;
     __device__ __forceinline__ void init() { cur = 0u; end = 0u; next = atomicAdd(pool.count, TRAIN_CHUNK); }
     __device__ __forceinline__ void begin() { head = -1; prev = -1; }
-    __device__ __forceinline__ bool vertex(f3 pos, float density, f3 dir, f3 last, const float*)
+    __device__ __forceinline__ bool vertex(f3 pos, float density, f3 dir, f3 last, const float* r)
     {
         if (cur == end) {
             cur = next;
@@ -181,6 +181,8 @@ struct ChunkEmitter {
         pool.a[slot] = make_float4(pos.x, pos.y, pos.z, density);
         pool.b[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(-1));
         pool.c[slot] = make_float4(last.x, last.y, last.z, 0.0f);
+        if (r != nullptr)   // env-map term in the training targets (opt-in): the 16 draws of SampleHdrEnvMap, as in the render pool
+            for (int k = 0; k < 4; k++) pool.rnd[(size_t)slot * 4 + k] = make_float4(r[4 * k], r[4 * k + 1], r[4 * k + 2], r[4 * k + 3]);
         if (prev >= 0) pool.b[prev].w = __int_as_float((int)slot); else head = (int)slot;
         prev = (int)slot;
         return true;
@@ -238,10 +240,11 @@ __global__ void __launch_bounds__(128, MB) k_render_walk(const __grid_constant__
 
 // ---- train walk (nrc-train.comp:1122-1259 minus lighting and Backprop) ------------------------------------------------
 // A training sample is ONE long serial chain (1 + 8 walks of 64 steps, the RNG chained through all of them) and a frame
-// has only ~10^4 of them: ~300 warps, latency-bound, a few per cent of the machine -- but the frame's critical path.
-// Sharing schedulers with the render walk (which saturates issue slots) nearly doubles its latency, so the kernel is
-// given SMs of its own: `gridDim.x` blocks that each reserve the whole shared memory of an SM (dynamic smem, unused),
-// which keeps every other block off that SM; the render chain runs on the rest of the machine meanwhile.
+// has only ~10^4 of them: ~300 warps, latency-bound, a few per cent of the machine's instructions -- but the longest chain of
+// the frame.  It runs on a stream of its own, one frame ahead of the weights (renderer.cu), so only the next train walk waits
+// for it.  Optionally (NRC_TRAIN_SMS > 0) the blocks reserve whole SMs through unused dynamic shared memory, which keeps every
+// other block off those SMs: the walk gets faster, the frame does not (it is issue-throughput bound), so this is off by default.
+template <bool ENV>
 __global__ void __launch_bounds__(1024, 1) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
                                                         uint32_t lanes, VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
 {
@@ -266,7 +269,8 @@ __global__ void __launch_bounds__(1024, 1) k_train_walk(const __grid_constant__ 
     paths.dir[3 * (size_t)local] = dir.x; paths.dir[3 * (size_t)local + 1] = dir.y; paths.dir[3 * (size_t)local + 2] = dir.z;
     for (int p = 0; p < 8; p++) {   // 8 x TracePath (:1217-1222), RNG chained from one to the next
         em.begin();
-        train_walk_path(W, box, grid, cur, dir, rng, em, wc);
+        if (ENV) train_walk_path_env(W, box, grid, cur, dir, rng, em, wc);
+        else train_walk_path(W, box, grid, cur, dir, rng, em, wc);
         paths.head[(size_t)local * 8 + p] = em.head;
     }
     em.finish();
@@ -678,7 +682,8 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
         smsEnv = e ? atoi(e) : 0;
         if (smsEnv < 0 || smsEnv > ctx->smCount) smsEnv = 0;
         g_padSmem = smsEnv > 0 ? 2048 : 0;
-        NRC_CUDA(cudaFuncSetAttribute(k_train_walk, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_walk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_walk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
     const uint32_t lanes = (uint32_t)lanesEnv;
     const uint32_t totalWarps = (n + lanes - 1) / lanes;
@@ -693,12 +698,17 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
         warpsPerBlock = 4;
         blocks = (totalWarps + warpsPerBlock - 1) / warpsPerBlock;
     }
-    NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
-               k_train_walk<<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
+    if (pool.rnd != nullptr)   // the pool carries random numbers: env-map term in the training targets is on (renderer.cu)
+        NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
+                   k_train_walk<true><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
+    else
+        NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
+                   k_train_walk<false><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
     return NRC_OK;
 }
 
-nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, VertexPool pool, bool render, unsigned long long* tapCounter)
+// render = with the env-map gather (needs pool.rnd); kid = which profile slot the launch is booked under
+nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, VertexPool pool, bool render, unsigned long long* tapCounter, int kid)
 {
     // the vertex count lives on the device: a grid-stride launch sized for the machine, not for the count
     unsigned want = (pool.cap + 127) / 128;
@@ -709,9 +719,9 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
     if (mb < 0) { const char* e = getenv("NRC_LIGHT_MB"); mb = e ? atoi(e) : 8; }
 #define LIGHT_CASE(MBV)                                                                                                              \
     case MBV:                                                                                                                        \
-        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, (k_light<true, MBV, true><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else if (render) NRC_LAUNCH(ctx, st, K_LIGHT_RENDER, (k_light<true, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else NRC_LAUNCH(ctx, st, K_LIGHT_TRAIN, (k_light<false, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
+        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, true><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else NRC_LAUNCH(ctx, st, kid, (k_light<false, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
         break;
     switch (mb) {
         LIGHT_CASE(4)

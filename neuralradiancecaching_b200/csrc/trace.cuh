@@ -58,7 +58,7 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
                               VertexPool pool, RenderPaths paths, float4* background, uint32_t* counters);
 nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t i0, uint32_t n, uint32_t istride, VertexPool pool,
                              TrainPaths paths, uint32_t* counters);
-nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, VertexPool pool, bool render, unsigned long long* tapCounter);
+nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, VertexPool pool, bool render, unsigned long long* tapCounter, int kid);
 nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
                                  VertexPool pool, RenderPaths paths, QueryList q);
 nrc_status launch_train_combine(nrc_ctx* ctx, cudaStream_t st, uint32_t nLocal, VertexPool pool, TrainPaths paths,

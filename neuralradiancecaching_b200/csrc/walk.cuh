@@ -160,3 +160,27 @@ NRC_HD void train_walk_path(const WalkParams& P, const Box& box, const Grid& gri
         c = walk_advance(box, c, d, rng, wc.sdf);
     }
 }
+
+// The same walk with the env-map term of TraceScene switched on (opt-in; train.comp:1118 has it commented out): a lit vertex
+// first draws the 16 numbers of SampleHdrEnvMap's 8 NewRayDir calls, then the two of its own NewRayDir -- the render walk's order.
+template <class Emitter>
+NRC_HD void train_walk_path_env(const WalkParams& P, const Box& box, const Grid& grid, f3 startP, f3 startD, Rng& rng, Emitter& em,
+                                WalkCounters& wc)
+{
+    f3 en, ex;
+    find_entry_exit(box, startP, startD, en, ex, wc.sdf);
+    f3 c = en, last = en, d = startD;
+    for (int i = 0; i < 64; i++) {
+        wc.steps++;
+        float density = grid_density(grid, c);
+        if (density > 0.0f) {
+            float r[16];
+            for (int k = 0; k < 16; k++) r[k] = rng_next(rng);
+            if (!em.vertex(c, density, d, last, r)) return;
+            wc.lit++;
+            last = c;
+            d = new_ray_dir(d, P.g, rng);
+        }
+        c = walk_advance(box, c, d, rng, wc.sdf);
+    }
+}

@@ -51,6 +51,10 @@ class NrcHpmRenderer:
         L.check(L.lib().nrc_renderer_set_partition_strided(self.h, C.c_uint32(y_first), C.c_uint32(y_stride), C.c_uint32(i_first),
                                                            C.c_uint32(i_stride)))
 
+    def SetTrainEnvLight(self, on):
+        """Opt-in: env-map term in the training targets (train.comp:1118 has it commented out)."""
+        L.check(L.lib().nrc_renderer_set_train_env_light(self.h, C.c_int(1 if on else 0)))
+
     def SetPoolCapacity(self, vertices):
         """Initial render vertex pool capacity (0 = default); an overflowing frame is redone with the worst-case pool."""
         L.check(L.lib().nrc_renderer_set_pool_capacity(self.h, C.c_uint64(vertices)))

@@ -68,6 +68,7 @@ struct Scene {
     sampler1D hdrEnvMapInvCdfY;
     std::vector<float> envStorage, cdfXStorage, cdfYStorage;
     HdrEnvMapU hdrEnvMapData;
+    bool trainEnvLight = false;  // opt-in: the env-map term of TraceScene that train.comp:1118 has commented out
     bool envCdfHalf = false;   // opt-in: halfSampleCount = sampleCount / 2, the variant commented out at fwd.frag:715
     MrheU mrhe;
     std::vector<float> mrHashTable, mrDeltaHashTable;
@@ -471,6 +472,10 @@ struct Invocation {
     {
         vec3 a = TraceDirLight(pos, dir);
         vec3 b = TracePointLight(pos, dir);
+        if (S.trainEnvLight) {
+            vec3 c = SampleHdrEnvMapGather(pos, dir, 8);
+            return a + b + c;
+        }
         return a + b;
     }
 

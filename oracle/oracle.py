@@ -96,6 +96,10 @@ class OracleScene:
         self.l.orc_set_envmap(self.h, C.c_int(w), C.c_int(h), _p(rgba), _p(cx), _p(cy), C.c_float(direct_strength),
                               C.c_float(hpm_strength))
 
+    def set_train_env_light(self, on):
+        """opt-in: training targets include the env-map gather (the term commented out at train.comp:1118)"""
+        self.l.orc_set_train_env_light(self.h, C.c_int(1 if on else 0))
+
     def set_env_cdf_half(self, on):
         """opt-in: 4 phase-sampled + 4 CDF-importance-sampled env directions per vertex (fwd.frag:715 as commented out there)"""
         self.l.orc_set_env_cdf_half(self.h, C.c_int(1 if on else 0))

@@ -112,6 +112,7 @@ void orc_set_envmap(void* sp, int w, int h, const float* rgba, const float* invC
     S.hdrEnvMapData.directStrength = directStrength; S.hdrEnvMapData.hpmStrength = hpmStrength;
 }
 
+void orc_set_train_env_light(void* sp, int on) { ((Scene*)sp)->trainEnvLight = on != 0; }
 void orc_set_env_cdf_half(void* sp, int on) { ((Scene*)sp)->envCdfHalf = on != 0; }
 
 void orc_set_mlp(void* sp, const float* params, float lr, float wd, float beta1)

@@ -54,13 +54,13 @@ def render_walk(cfg, W, H, shape, spp=1):
     return cnt, qry
 
 
-def train_walk(cfg, tw, th, shape):
+def train_walk(cfg, tw, th, shape, env_light=False):
     cam = cfg["cam"]
     ipv, pos, rnd = _f(cam.invProjView).reshape(16), _f(cam.m_Pos), _f(cfg["random4"][:2])
     rec = np.zeros((tw * th, 6), np.float32)
     cnt = np.zeros((tw * th, 3), np.uint32)
     lib().emu_train_walk(_p(ipv), _p(pos), _p(rnd), C.c_float(cfg["g"]), C.c_uint(tw), C.c_uint(th), C.c_float(cfg["density_factor"]),
-                         C.c_int(shape[0]), C.c_int(shape[1]), C.c_int(shape[2]), _p(rec), _p(cnt))
+                         C.c_int(shape[0]), C.c_int(shape[1]), C.c_int(shape[2]), _p(rec), _p(cnt), C.c_int(1 if env_light else 0))
     return rec, cnt
 
 

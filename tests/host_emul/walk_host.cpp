@@ -78,7 +78,7 @@ void emu_render_walk(const float* invProjView, const float* camPos, const float*
 
 // records[n][6] = pos, dir ; counters[n][3] = draws, lit, steps
 void emu_train_walk(const float* invProjView, const float* camPos, const float* random2, float g, unsigned trainW, unsigned trainH,
-                    float densityFactor, int nx, int ny, int nz, float* records, unsigned* counters)
+                    float densityFactor, int nx, int ny, int nz, float* records, unsigned* counters, int envLight)
 {
     WalkParams P; Box box; Grid grid;
     setup(invProjView, camPos, random2, g, 0, 0, 1, 1, trainW, trainH, densityFactor, nx, ny, nz, P, box, grid);
@@ -89,7 +89,10 @@ void emu_train_walk(const float* invProjView, const float* camPos, const float* 
         f3 cur, dir;
         train_pick_vertex(P, box, grid, (unsigned)i, rng, wc, cur, dir);
         RecEmitter em{nullptr, 0};
-        for (int p = 0; p < 8; p++) train_walk_path(P, box, grid, cur, dir, rng, em, wc);
+        for (int p = 0; p < 8; p++) {
+            if (envLight) train_walk_path_env(P, box, grid, cur, dir, rng, em, wc);
+            else train_walk_path(P, box, grid, cur, dir, rng, em, wc);
+        }
         float* o = records + 6 * i;
         o[0] = cur.x; o[1] = cur.y; o[2] = cur.z; o[3] = dir.x; o[4] = dir.y; o[5] = dir.z;
         counters[3 * i] = rng.draws; counters[3 * i + 1] = wc.lit; counters[3 * i + 2] = wc.steps;

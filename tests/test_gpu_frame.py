@@ -308,3 +308,34 @@ def test_env_importance_half_matches_oracle(N, ctx):
     with pytest.raises(N.NrcError):
         plain.set_importance_sampling(True)                      # no inverse CDFs: refused
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy(); env.Destroy(); plain.Destroy()
+
+
+def test_train_env_light_matches_oracle(N, ctx):
+    """Opt-in estimator: env-map term in the training targets.  RNG draws, lit vertices, walk steps and the
+    records' positions/directions bit for bit; targets to 1e-4; then back to the shipped estimator."""
+    tw, th = 20, 12
+    cfg = Cm.scene_cfg()
+    sc = Cm.oracle_scene(cfg)
+    sc.set_train_size(tw, th)
+    orec0, ocnt0 = sc.train_trace(tw, th)
+    sc.set_train_env_light(True)
+    orec, ocnt = sc.train_trace(tw, th)
+    r, nrc, m, vol = build(N, ctx, cfg, 32, 32, tw, th)
+    r.SetTrainEnvLight(True)
+    r.FrameTrain(); ctx.sync()
+    rec, cnt = r.read_train_probes()
+    np.testing.assert_array_equal(cnt[:, 0], ocnt[:, 0])
+    np.testing.assert_array_equal(cnt[:, 1], ocnt[:, 1])
+    np.testing.assert_array_equal(cnt[:, 2], ocnt[:, 3])
+    np.testing.assert_array_equal(rec[:, :6].view(np.uint32), orec[:, :6].view(np.uint32))
+    assert _relmax(rec[:, 6:], orec[:, 6:]) < 1e-4
+    assert float(rec[:, 6:].sum()) > float(orec0[:, 6:].sum())          # the env term adds light
+    # two queued frames with the flag on (double-buffered pools carry the random numbers), then off again
+    r.FrameTrain(); r.FrameTrain(); ctx.sync()
+    r.SetTrainEnvLight(False)
+    nrc.set_state(delta=np.zeros(20995, np.float32)); nrc.ResetStats()
+    r.FrameTrain(); ctx.sync()
+    rec, cnt = r.read_train_probes()
+    np.testing.assert_array_equal(cnt[:, 0], ocnt0[:, 0])
+    assert _relmax(rec[:, 6:], orec0[:, 6:]) < 1e-4
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()

@@ -188,3 +188,30 @@ def test_device_pointers_accepted(N, ctx):
     ctx.sync()
     assert out.is_cuda and _rel(out.cpu().numpy(), sc.infer(pos, d)) < REL
     nrc.Destroy(); m.Destroy()
+
+
+def test_fit_loss_curve_follows_the_oracle(N, ctx):
+    """SURVEY 8d, config 2 in small: ten train steps (accumulate -> nrc-step -> mrhe-step) on seeded batches of a synthetic
+    radiance field; the loss after every step and the final weights follow the oracle's (fp32 path, 1e-3 relative)."""
+    sc, nrc, m, params, tables = _mlp_pair(N, ctx)
+    n = 2048
+    losses_o, losses_g = [], []
+    for step in range(10):
+        pos, d = Cm.rand_queries(n, seed=1000 + step)
+        # smooth closed-form field: two blobs times a directional lobe
+        r2a = ((pos - np.float32([8, 0, -5])) ** 2).sum(1) / 300.0
+        r2b = ((pos + np.float32([10, 4, 12])) ** 2).sum(1) / 500.0
+        lobe = (0.6 + 0.4 * d[:, 1]).astype(np.float32)
+        target = np.stack([np.exp(-r2a) * lobe, 0.5 * np.exp(-r2b) * lobe, 0.3 * np.exp(-r2a) + 0.2 * np.exp(-r2b)], 1).astype(np.float32)
+        scale = 1.0 / n
+        sc.set_loss_scale(scale, 1.0)
+        sc.reset_stats(); nrc.ResetStats()
+        sc.train_accumulate(pos, d, target)
+        N.train_accumulate(nrc, m, pos, d, target, scale)
+        losses_o.append(sc.mse_loss()); losses_g.append(nrc.GetStats().mseLoss)
+        sc.nrc_step(); sc.mrhe_step()
+        N.optimizer_step(nrc, m)
+    np.testing.assert_allclose(losses_g, losses_o, rtol=REL)
+    assert _rel(nrc.get_params()[0], sc.get_mlp()[0]) < REL
+    assert _rel(m.get_tables()[0][:2 * 16384], sc.get_mrhe()[0][:2 * 16384]) < REL
+    nrc.Destroy(); m.Destroy()

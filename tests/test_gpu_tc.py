@@ -84,7 +84,7 @@ def test_frame_with_tc_inference(N, ctx):
 
 
 # Stated bounds for gradients computed from bf16 operands (per tensor, max abs error relative to the tensor's largest
-# magnitude).  Measured on B200 (scratch/tc_err.py): MLP tensors 0.2-7.6 %, worst for 128-sample batches.  The hash-table
+# magnitude).  Measured on B200 (scripts/tc_err.py): MLP tensors 0.2-7.6 %, worst for 128-sample batches.  The hash-table
 # gradient is ill-conditioned BY the reference's formula -- its corner weights are products of unbounded "lerp factors"
 # (world position minus grid floor, SURVEY A2/A11: magnitudes of 10^2..10^7 with alternating signs), so the per-entry sums
 # are small differences of huge terms and amplify the ~1-2 % bf16 noise of dL/dx0 to 3-30 %.  (mrhe-step.comp then clips

@@ -46,6 +46,23 @@ def test_train_walk_bit_exact():
     np.testing.assert_array_equal(rec[:, :6].view(np.uint32), erec.view(np.uint32))
 
 
+def test_train_walk_with_env_light_bit_exact():
+    # opt-in: env-map term in the training targets -> 16 more draws per lit vertex, in the render walk's order
+    cfg = Cm.scene_cfg()
+    sc = Cm.oracle_scene(cfg)
+    shape = emul.set_volume(Cm.density())
+    tw, th = 12, 10
+    sc.set_train_size(tw, th)
+    rec0, cnt0 = sc.train_trace(tw, th)
+    sc.set_train_env_light(True)
+    rec, cnt = sc.train_trace(tw, th)
+    assert (cnt[:, 0] > cnt0[:, 0]).any()                       # more RNG draws than the shipped estimator
+    erec, ecnt = emul.train_walk(cfg, tw, th, shape, env_light=True)
+    np.testing.assert_array_equal(cnt[:, [0, 1, 3]], ecnt)
+    np.testing.assert_array_equal(rec[:, :6].view(np.uint32), erec.view(np.uint32))
+    assert np.isfinite(rec).all() and (rec[:, 6:9] >= rec0[:, 6:9] - 1e-6).mean() > 0.5
+
+
 def test_encode_bit_exact_both_resolution_tables():
     pos, d = Cm.rand_queries(2048, seed=3)
     pos[:8] = [[0, 0, 0], [31.25, 21.25, 38.25], [-31.25, -21.25, -38.25], [-31.4, 0, 0], [0, -21.4, 38.3], [31.2499, 21.2499, 38.2499],
