@@ -541,6 +541,9 @@ def cpu_reference_sample(W, H, TW, TH, budget_s=20.0, steps=1, rows_per_step=Non
     sc.set_mrhe(inp["tables"], O.mrhe_resolutions(), 0.01, 0.0, 16, 16384, 2)
     sc.set_train_size(TW, TH)
     rnd = lcg_randoms(steps + 1)
+    # all host threads: torchrun exports OMP_NUM_THREADS=1 to its workers, which would time a one-thread baseline
+    want_threads = int(os.environ.get("NRC_CPU_THREADS", "0")) or len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    O.set_num_threads(want_threads)
     threads = O.num_threads()
     import ctypes as C
     rgba = np.zeros((H, W, 4), np.float32)
@@ -551,11 +554,13 @@ def cpu_reference_sample(W, H, TW, TH, budget_s=20.0, steps=1, rows_per_step=Non
         q = 0
         t0 = time.perf_counter()
         n_train = TW * TH
-        for k in range(chunks):                       # train: trace + Backprop over evenly spread chunks
+        recs = []
+        for k in range(chunks):                       # train: trace evenly spread chunks of the grid ...
             i0 = (k * n_train) // chunks
-            rec, _ = sc.train_trace(TW, TH, i0, min(i0 + chunk, n_train))
-            sc.train_accumulate(rec[:, 0:3], rec[:, 3:6], rec[:, 6:9])
-            q += rec.shape[0]
+            recs.append(sc.train_trace(TW, TH, i0, min(i0 + chunk, n_train))[0])
+        rec = np.concatenate(recs)                    # ... and Backprop them as one batch (all threads busy)
+        sc.train_accumulate(rec[:, 0:3], rec[:, 3:6], rec[:, 6:9])
+        q += rec.shape[0]
         sc.nrc_step()
         sc.mrhe_step()
         for k in range(rows):                         # render: evenly spread rows

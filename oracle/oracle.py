@@ -249,5 +249,9 @@ def hash3(x, y, z, T):
     return int(lib().orc_hash(C.c_uint(x), C.c_uint(y), C.c_uint(z), C.c_uint(T)))
 
 
+def set_num_threads(n):
+    lib().orc_set_num_threads(C.c_int(int(n)))
+
+
 def num_threads():
     return int(lib().orc_num_threads())

@@ -24,6 +24,15 @@ extern "C" {
 void* orc_scene_create() { return new Scene(); }
 void orc_scene_destroy(void* s) { delete (Scene*)s; }
 
+void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int orc_num_threads()
 {
 #ifdef _OPENMP
@@ -240,11 +249,15 @@ void orc_train_accumulate(void* sp, const float* pos, const float* dir, const fl
                           unsigned char* dropped)
 {
     Scene& S = *(Scene*)sp;
-    const long chunk = 1024;
+    int nThreads = orc_num_threads();
+    // per-task sample count: 1024 for big batches, smaller when that would leave threads idle (sums are grouped per task, so the
+    // grouping -- like the GPU's per-CTA partials -- only moves fp32 rounding)
+    long chunk = N / ((long)nThreads * 4);
+    if (chunk > 1024) chunk = 1024;
+    if (chunk < 32) chunk = 32;
     const long nChunks = (N + chunk - 1) / chunk;
     const size_t tableN = S.mrDeltaHashTable.size();
     const size_t lvl0 = (size_t)S.mrhe.hashTableSize * 2;   // [A10]: only the first 2*T floats are ever touched
-    int nThreads = orc_num_threads();
     long group = nThreads * 4;
     std::vector<std::vector<float>> dP(group, std::vector<float>(kParamCount));
     std::vector<std::vector<float>> dT(group, std::vector<float>(lvl0 <= tableN ? lvl0 : tableN));
@@ -287,9 +300,11 @@ void orc_mrhe_step(void* sp) { MrheStep(*(Scene*)sp); }
 void orc_render(void* sp, unsigned W, unsigned H, unsigned y0, unsigned y1, float* rgba, unsigned* counters, float* query)
 {
     const Scene& S = *(Scene*)sp;
-#pragma omp parallel for schedule(dynamic, 1)
+    // pixels, not rows, are the parallel unit: a one-row call (the bench's evenly spread sample) still uses every thread
+#pragma omp parallel for collapse(2) schedule(dynamic, 16)
     for (long py = (long)y0; py < (long)y1; py++)
-        for (unsigned px = 0; px < W; px++) {
+        for (long pxl = 0; pxl < (long)W; pxl++) {
+            const unsigned px = (unsigned)pxl;
             Invocation inv(S);
             vec4 c = inv.RenderPixel(px, (unsigned)py, W, H);
             size_t p = (size_t)py * W + px;
