@@ -120,6 +120,10 @@ NRC_API uint64_t nrc_ctx_launch_count(nrc_ctx* ctx);
  * only a wall-clock FPS counter, src/Time.cpp:8-25).  While enabled every kernel launch of this context is
  * bracketed by two events; nrc_ctx_profile_read waits for them and returns accumulated milliseconds and launch
  * counts per kernel id (arrays of nrc_kernel_count() entries). */
+/* Test hook, not a product path: exhaustive device-side comparison of the guard-free division / square-root sequences used on
+ * the walks' serial chains (csrc/strict.cuh) with the IEEE routines they shortcut; mismatches[k] must all be 0. */
+NRC_API nrc_status nrc_selftest_strict_math(nrc_ctx* ctx, uint64_t mismatches[4]);
+
 NRC_API int nrc_kernel_count(void);
 NRC_API const char* nrc_kernel_name(int kernelId);
 NRC_API nrc_status nrc_ctx_profile_enable(nrc_ctx* ctx, int on);

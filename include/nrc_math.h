@@ -214,23 +214,28 @@ NRC_HD float nrc_asin(float x)
     return (x < 0.0f) ? -p : p;
 }
 
-/* acos on [-1, 1] (argument saturated). */
+/* acos on [-1, 1] (argument saturated).
+ * |x| > 0.5: h = sqrt((1 - |x|) / 2) <= 0.5, acos = 2 asin(h) or pi - 2 asin(h); otherwise pi/2 - asin(x).  Every case ends in the
+ * SAME small-argument asin kernel on t = h or |x| (t <= 0.5), so it is evaluated once on the selected t instead of in three
+ * divergent branches -- operation for operation what nrc_asin would compute in each case. */
 NRC_HD float nrc_acos(float x)
 {
-    if (x != x) return x;
     if (x > 1.0f) x = 1.0f;
     if (x < -1.0f) x = -1.0f;
-    if (x < -0.5f) {
-        float h = NRC_SQRT(NRC_MUL(0.5f, NRC_ADD(1.0f, x)));
-        float a = nrc_asin(h);
-        return NRC_SUB(3.14159274101257324f, NRC_ADD(a, a));
-    }
-    if (x > 0.5f) {
-        float h = NRC_SQRT(NRC_MUL(0.5f, NRC_SUB(1.0f, x)));
-        float a = nrc_asin(h);
-        return NRC_ADD(a, a);
-    }
-    return NRC_SUB(1.57079637050628662109375f, nrc_asin(x));
+    float ax = nrc_abs(x);
+    int outer = ax > 0.5f;
+    float h = NRC_SQRT(NRC_MUL(0.5f, NRC_SUB(1.0f, ax)));
+    float t = outer ? h : ax;
+    float z = NRC_MUL(t, t);
+    float p = NRC_FMA(4.2163199048e-2f, z, 2.4181311049e-2f);
+    p = NRC_FMA(p, z, 4.5470025998e-2f);
+    p = NRC_FMA(p, z, 7.4953002686e-2f);
+    p = NRC_FMA(p, z, 1.6666752422e-1f);
+    p = NRC_FMA(NRC_MUL(p, z), t, t);                     /* asin(t), t in [0, 0.5] */
+    float twice = NRC_ADD(p, p);
+    float inner = NRC_SUB(1.57079637050628662109375f, (x < 0.0f) ? -p : p);
+    float hi = (x < 0.0f) ? NRC_SUB(3.14159274101257324f, twice) : twice;
+    return outer ? hi : inner;                            /* NaN: outer is false, inner is NaN */
 }
 
 /* atan(x) for x >= 0 (helper). */
