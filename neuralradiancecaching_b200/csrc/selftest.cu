@@ -4,7 +4,7 @@
 #include "strict.cuh"
 
 // [0] grid_coords: (a / extent + 0.5) compared as the range test sees it, ALL 2^32 bit patterns of a, extents 62.5 / 42.5 / 76.5
-// [1] sqrt_normal(x) vs __fsqrt_rn(x), every float in [2^-60, 2^60)
+// [1] sqrt_normal(x) vs __fsqrt_rn(x), every float in [2^-101, FLT_MAX]
 // [2] div_normal(1, y) vs __fdiv_rn(1, y), every float in [2^-30, 2^30]
 // [3] the two divisions of the HG cos-theta draw: (1-g^2)/den for every den in [0.25, 2), num/(2g) for every |num| <= 2, g = 0.7
 __device__ __forceinline__ bool same_coord(float q0, float q1)
@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(256) k_selftest_strict(unsigned long long* __r
         for (int k = 0; k < 3; k++)
             if (!same_coord(__fdiv_rn(a, ext[k]), div_normal(a, ext[k]))) b0++;
     }
-    for (unsigned long long i = t0 + 0x21800000ull; i < 0x5D800000ull; i += stride) {
+    for (unsigned long long i = t0 + 0x0D000000ull; i <= 0x7F7FFFFFull; i += stride) {
         float x = __uint_as_float((unsigned)i);
         if (__float_as_uint(__fsqrt_rn(x)) != __float_as_uint(sqrt_normal(x))) b1++;
     }
