@@ -264,6 +264,8 @@ NRC_API nrc_status nrc_dp_connect(nrc_dp* dp, const void* allHandles /*host, wor
 NRC_API nrc_status nrc_dp_reduce_step(nrc_dp* dp);
 /* replicas inside one process (single-GPU parity test): phase 0 on every replica, then phase 1 on every replica */
 NRC_API nrc_status nrc_dp_reduce_step_phase(nrc_dp* dp, int phase);
+/* 1 if a handshake gave up waiting for a peer (about 10 s; a crashed rank must not hang the other GPUs) */
+NRC_API nrc_status nrc_dp_status(nrc_dp* dp, int* timedOut);
 NRC_API nrc_status nrc_dp_destroy(nrc_dp* dp);
 
 /* Parity probes of the last frame (rows/invocations of this rank's partition only are meaningful):

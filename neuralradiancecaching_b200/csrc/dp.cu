@@ -83,7 +83,15 @@ __device__ __forceinline__ void dp_barrier(const DpArgs& a, int which)
         __threadfence_system();
         unsigned slot = (blockIdx.x * NRC_DP_MAX_WORLD) * 2;
         st_release_sys(a.peerFlags[threadIdx.x] + slot + a.rank * 2 + which, a.epoch);
-        while ((int)(ld_acquire_sys(a.myFlags + slot + threadIdx.x * 2 + which) - a.epoch) < 0) __nanosleep(32);
+        // A peer that never arrives (crashed process) must not hang this GPU: give up after ~10 s and leave a mark the host reads
+        // (nrc_dp_status); the step then runs on whatever the peer's arena holds -- the run is lost, the device is not.
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int)(ld_acquire_sys(a.myFlags + slot + threadIdx.x * 2 + which) - a.epoch) < 0) {
+            __nanosleep(32);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 10000000000ull) { a.myFlags[NRC_DP_FLAG_COUNT] = 1u; break; }
+        }
     }
     __syncthreads();
 }
@@ -192,8 +200,8 @@ extern "C" nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int 
     NRC_REQUIRE(nrc_mrhe_grad_extent(mrhe) <= NRC_DP_MAX_HEAD, "delta-table head too large for the fused exchange; use the NCCL path");
     nrc_dp* d = new nrc_dp();
     d->mlp = mlp; d->mrhe = mrhe; d->rank = rank; d->world = world;
-    cudaError_t e = cudaMalloc(&d->flags, sizeof(unsigned) * NRC_DP_FLAG_COUNT);
-    if (e == cudaSuccess) e = cudaMemset(d->flags, 0, sizeof(unsigned) * NRC_DP_FLAG_COUNT);
+    cudaError_t e = cudaMalloc(&d->flags, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));
+    if (e == cudaSuccess) e = cudaMemset(d->flags, 0, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));
     if (e != cudaSuccess) {
         nrc_set_error("nrc_dp_create: %s", cudaGetErrorString(e));
         delete d;
@@ -289,6 +297,17 @@ extern "C" nrc_status nrc_dp_reduce_step_phase(nrc_dp* d, int phase)
     if (phase == 0) return dp_launch(d, 0, 0, true);
     NRC_TRY(dp_launch(d, 0, 2, false));
     return launch_mrhe_step_range(d->mrhe, nrc_mrhe_grad_extent(d->mrhe), d->mrhe->ctx->stream);
+}
+
+// *timedOut = 1 if a handshake of any earlier nrc_dp_reduce_step gave up waiting for a peer (waits for the stream).
+extern "C" nrc_status nrc_dp_status(nrc_dp* d, int* timedOut)
+{
+    NRC_REQUIRE(d && timedOut, "null argument");
+    unsigned v = 0;
+    NRC_CUDA(cudaMemcpyAsync(&v, d->flags + NRC_DP_FLAG_COUNT, sizeof(unsigned), cudaMemcpyDeviceToHost, d->mlp->ctx->stream));
+    NRC_CUDA(cudaStreamSynchronize(d->mlp->ctx->stream));
+    *timedOut = v != 0u;
+    return NRC_OK;
 }
 
 extern "C" nrc_status nrc_dp_destroy(nrc_dp* d)

@@ -94,6 +94,12 @@ class FusedExchange:
     def phase(self, k):
         self._L.check(self._L.lib().nrc_dp_reduce_step_phase(self.h, self._C.c_int(k)))
 
+    def timed_out(self):
+        """True if a handshake ever gave up waiting for a peer (waits for the stream)."""
+        v = self._C.c_int(0)
+        self._L.check(self._L.lib().nrc_dp_status(self.h, self._C.byref(v)))
+        return bool(v.value)
+
     def close(self):
         if self.h:
             self._L.check(self._L.lib().nrc_dp_destroy(self.h))

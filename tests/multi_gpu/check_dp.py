@@ -72,6 +72,7 @@ def main():
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         assert bool((lo == hi).all()), "replicas diverged"
+    assert not fused.timed_out()
     dist.barrier()
     fused.close()
     if rank == 0:
