@@ -6,6 +6,7 @@
 #include <cstring>
 #include <fstream>
 #include <iostream>
+#include <memory>
 #include "nrc_b200.hpp"
 
 // deterministic stand-ins for the blobs the reference repo does not ship (.MISSING_LARGE_BLOBS)
@@ -59,13 +60,23 @@ int main(int argc, char** argv)
         volumeData.Params().useNN = 1;
         en::NrcHpmRenderer renderer(ctx, width, height, 100, 100, camera, volumeData, dirLight, pointLight, hdrEnvMap, nrc, mrhe);   // main.cpp:159-166
         if (const char* ck = std::getenv("NRC_LOAD_CHECKPOINT")) en::LoadCheckpoint(ck, nrc, mrhe);   // resume a trained cache (not in the reference)
+        // NRC_SPLIT_FRAME=1: the frame in its data-parallel form (train | exchange+steps | render) with a world of one rank;
+        // a multi-GPU host constructs DataParallel(nrc, mrhe, rank, world), gathers Handle() over its own transport and
+        // gives every rank its rows with renderer.SetPartition.
+        const bool split = std::getenv("NRC_SPLIT_FRAME") != nullptr;
+        std::unique_ptr<en::DataParallel> dp;
+        if (split) {
+            dp.reset(new en::DataParallel(nrc, mrhe, 0, 1));
+            dp->Connect(dp->Handle());
+        }
         for (int frame = 0; frame < frames; frame++) {                        // main.cpp:181-248
             if (frame % 100 == 0 && std::getenv("NRC_PRINT_WEIGHTS")) nrc.PrintWeights();   // main.cpp:183-187
             camera.RotateAroundOrigin({0.0f, 1.0f, 0.0f}, 0.01f);             // "camera training" orbit, main.cpp:200-203
             camera.SetAspectRatio(width, height);
             camera.UpdateUniformBuffer();                                     // main.cpp:212-213
             nrc.ResetStats();                                                 // main.cpp:215
-            renderer.Render();                                                // main.cpp:216
+            if (split) { renderer.FrameTrain(); dp->ReduceStep(); renderer.FrameRender(); }
+            else renderer.Render();                                           // main.cpp:216
             ctx.WaitIdle();                                                   // main.cpp:217
             if (frame % 25 == 0) std::cout << "frame " << frame << " NRC MSE Loss: " << nrc.GetStats().mseLoss << std::endl;   // main.cpp:220-224
             volumeData.Update(true);                                          // main.cpp:230
@@ -76,6 +87,7 @@ int main(int argc, char** argv)
         f << "P6\n" << width << " " << height << "\n255\n";
         for (size_t i = 0; i < (size_t)width * height; i++) { char rgb[3] = {(char)bgra[4 * i + 2], (char)bgra[4 * i + 1], (char)bgra[4 * i]}; f.write(rgb, 3); }
         if (const char* ck = std::getenv("NRC_SAVE_CHECKPOINT")) en::SaveCheckpoint(ck, nrc, mrhe);
+        if (dp) { if (dp->TimedOut()) std::cerr << "exchange handshake timed out" << std::endl; dp->Destroy(); }
         renderer.Destroy(); mrhe.Destroy(); nrc.Destroy(); hdrEnvMap.Destroy(); volumeData.Destroy();   // main.cpp:253-274
         std::cout << "wrote " << out << std::endl;
     } catch (const std::exception& e) {

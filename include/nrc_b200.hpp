@@ -336,6 +336,18 @@ public:
         m_VolumeData.Push();
         Check(nrc_render(m_Handle), "nrc_render");
     }
+    // The same frame in its two halves, for data-parallel ranks: FrameTrain(); DataParallel::ReduceStep(); FrameRender().
+    // SetPartition gives this rank rows [y0,y1) of the frame and train invocations [i0,i1).
+    void SetPartition(uint32_t y0, uint32_t y1, uint32_t i0, uint32_t i1) { Check(nrc_renderer_set_partition(m_Handle, y0, y1, i0, i1), "nrc_renderer_set_partition"); }
+    void FrameTrain() const
+    {
+        Check(nrc_renderer_set_camera(m_Handle, &m_Camera.GetData()), "nrc_renderer_set_camera");
+        Check(nrc_renderer_set_dir_light(m_Handle, &m_DirLight.GetData()), "nrc_renderer_set_dir_light");
+        Check(nrc_renderer_set_point_light(m_Handle, &m_PointLight.GetData()), "nrc_renderer_set_point_light");
+        m_VolumeData.Push();
+        Check(nrc_frame_train(m_Handle), "nrc_frame_train");
+    }
+    void FrameRender() const { Check(nrc_frame_render(m_Handle), "nrc_frame_render"); }
     void ResizeFrame(uint32_t width, uint32_t height)   // NrcHpmRenderer.cpp:103-126
     {
         Check(nrc_resize(m_Handle, width, height), "nrc_resize");
@@ -368,6 +380,31 @@ private:
     const HdrEnvMap& m_HdrEnvMap;
     const NeuralRadianceCache& m_Nrc;
     const MRHE& m_Mrhe;
+};
+
+// ---- data-parallel exchange fused with the optimiser steps (nrc_dp_*; the reference is single-GPU) ---------------------------------
+// One process per GPU.  Construct on every rank, exchange Handle() bytes in rank order by any transport (MPI_Allgather, a file ...),
+// Connect(), then one ReduceStep() per frame between the renderer's FrameTrain() and FrameRender().
+class DataParallel {
+public:
+    DataParallel(NeuralRadianceCache& nrc, MRHE& mrhe, int rank, int world)
+    {
+        Check(nrc_dp_create(nrc.Get(), mrhe.Get(), rank, world, &m_Handle), "nrc_dp_create");
+        m_Bytes.resize(nrc_dp_handle_bytes());
+        Check(nrc_dp_export(m_Handle, m_Bytes.data()), "nrc_dp_export");
+    }
+    const std::vector<unsigned char>& Handle() const { return m_Bytes; }
+    void Connect(const std::vector<unsigned char>& allHandlesInRankOrder)
+    {
+        Check(nrc_dp_connect(m_Handle, allHandlesInRankOrder.data(), 0), "nrc_dp_connect");
+    }
+    void ReduceStep() { Check(nrc_dp_reduce_step(m_Handle), "nrc_dp_reduce_step"); }
+    bool TimedOut() const { int v = 0; Check(nrc_dp_status(m_Handle, &v), "nrc_dp_status"); return v != 0; }
+    void Destroy() { nrc_dp_destroy(m_Handle); m_Handle = nullptr; }
+
+private:
+    nrc_dp* m_Handle = nullptr;
+    std::vector<unsigned char> m_Bytes;
 };
 
 // ---- checkpoint of the learnt state (the reference has none).  Same file layout as

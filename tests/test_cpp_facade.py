@@ -40,6 +40,18 @@ def test_headless_main_renders(tmp_path):
 
 
 @pytest.mark.gpu
+def test_split_frame_with_data_parallel_facade_matches_single_submit(tmp_path):
+    """FrameTrain / DataParallel::ReduceStep / FrameRender with a world of one rank draws the same frames as Render()."""
+    exe = _build()
+    a, b = str(tmp_path / "a.ppm"), str(tmp_path / "b.ppm")
+    p = subprocess.run([exe, "12", "96", "64", a], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    p = subprocess.run([exe, "12", "96", "64", b], capture_output=True, text=True, timeout=300, env=dict(os.environ, NRC_SPLIT_FRAME="1"))
+    assert p.returncode == 0 and "timed out" not in p.stderr, p.stderr
+    assert open(a, "rb").read() == open(b, "rb").read()
+
+
+@pytest.mark.gpu
 def test_checkpoint_written_by_cpp_is_read_by_python_and_back(tmp_path):
     """headless_main saves a checkpoint after 10 frames; the Python reader parses it; a second run resumes from it."""
     from neuralradiancecaching_b200 import checkpoint as K
