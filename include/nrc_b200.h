@@ -103,6 +103,12 @@ typedef enum nrc_mlp_precision {
     NRC_MLP_BF16_TC = 1  /* tcgen05 bf16 tensor-core kernels, fp32 accumulate; looser stated bound */
 } nrc_mlp_precision;
 
+/* How the bf16 tensor-core inference is organised (no reference counterpart: fwd.frag:503-534 is one function). */
+typedef enum nrc_infer_mode {
+    NRC_INFER_FUSED = 0, /* k_infer_tc: encode + six layers in one kernel per 128-query tile */
+    NRC_INFER_SPLIT = 1  /* k_encode_tiles (gather kernel) -> bf16 operand-image tiles in HBM -> k_mlp_stream (pipelined tcgen05 MLP) */
+} nrc_infer_mode;
+
 /* ---- context ---- */
 NRC_API const char* nrc_last_error(void);
 NRC_API const char* nrc_version(void);
@@ -113,6 +119,8 @@ NRC_API nrc_status nrc_sync(nrc_ctx* ctx);          /* vkQueueWaitIdle, src/main
 NRC_API void* nrc_ctx_stream(nrc_ctx* ctx);         /* the cudaStream_t all work is issued on */
 NRC_API int nrc_ctx_sm_count(nrc_ctx* ctx);
 NRC_API nrc_status nrc_ctx_set_precision(nrc_ctx* ctx, nrc_mlp_precision p);
+/* applies to NRC_MLP_BF16_TC inference (nrc_infer and the frame); default from the environment NRC_INFER_SPLIT=0/1 */
+NRC_API nrc_status nrc_ctx_set_infer_mode(nrc_ctx* ctx, nrc_infer_mode mode);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 NRC_API uint64_t nrc_ctx_launch_count(nrc_ctx* ctx);
 
@@ -172,6 +180,13 @@ NRC_API nrc_status nrc_encode(nrc_mrhe* mrhe, const float* pos, size_t n, float*
 NRC_API nrc_status nrc_encode_dir(nrc_ctx* ctx, const float* dir, size_t n, float* feat);
 /* Forward() (nrc-forward.frag:503-534): pos,dir[N][3] -> rgb[N][3]. */
 NRC_API nrc_status nrc_infer(nrc_mlp* mlp, nrc_mrhe* mrhe, const float* pos, const float* dir, size_t n, float* rgb);
+/* The two halves of Forward() as separate operators (NRC_INFER_SPLIT): EncodeRay (nrc-train.comp:703-713) into bf16
+ * operand-image tiles -- 16 KB per 128 queries, 16-byte chunk (kc, row) at (kc*128 + row)*16, kc = 8 consecutive network
+ * inputs, rows past n zero -- and ApplyWeights0..5 / ActivateNr1..6 (nrc-train.comp:547-701) from such tiles.
+ * featTiles is DEVICE memory of nrc_feature_tile_bytes(n) bytes; pos/dir/rgb are [h|d]. */
+NRC_API size_t nrc_feature_tile_bytes(size_t n);
+NRC_API nrc_status nrc_encode_tiles(nrc_mrhe* mrhe, const float* pos, const float* dir, size_t n, void* featTiles);
+NRC_API nrc_status nrc_mlp_forward_tiles(nrc_mlp* mlp, const void* featTiles, size_t n, float* rgb);
 /* Backprop() (nrc-train.comp:985-1028) over N records: adds the negative gradients (times lossScale =
  * ONE_OVER_PIXEL_COUNT, nrc-train.comp:210) into the delta arenas and the mean-square error into mseLoss.
  * pred[N][3] (optional) receives the network outputs. */

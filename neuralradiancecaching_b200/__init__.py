@@ -9,7 +9,7 @@ loaders.py ReadFileDensity3D, ReadFileHdr4f (src/read_file.cpp); dist.py data-pa
 from . import _lib
 from ._lib import NrcError, PARAM_COUNT
 from .api import (Context, NeuralRadianceCache, MRHE, mrhe_resolutions, encode, encode_dir, infer, train_accumulate,
-                  optimizer_step)
+                  optimizer_step, feature_tile_bytes, encode_tiles, mlp_forward_tiles)
 from .objects import Camera, DirLight, PointLight, VolumeData, HdrEnvMap, hdr4f_to_cdf, vec_from_angles
 from .renderer import NrcHpmRenderer
 from .loaders import ReadFileDensity3D, ReadFileHdr4f

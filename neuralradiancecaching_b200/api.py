@@ -82,6 +82,10 @@ class Context:
     def set_precision(self, p):
         L.check(L.lib().nrc_ctx_set_precision(self.h, C.c_int(p)))
 
+    def set_infer_mode(self, split):
+        """NRC_INFER_FUSED (k_infer_tc) or NRC_INFER_SPLIT (k_encode_tiles -> k_mlp_stream) for the bf16 tensor-core inference."""
+        L.check(L.lib().nrc_ctx_set_infer_mode(self.h, C.c_int(1 if split else 0)))
+
     def destroy(self):
         if self.h:
             L.lib().nrc_ctx_destroy(self.h)
@@ -226,6 +230,27 @@ def infer(nrc, mrhe, pos, d, out=None):
     n = pos.shape[0]
     rgb = _out((n, 3), np.float32, pos) if out is None else out
     L.check(L.lib().nrc_infer(nrc.h, mrhe.h, _ptr(pos), _ptr(d), C.c_size_t(n), _ptr(rgb)))
+    return rgb
+
+
+def feature_tile_bytes(n):
+    return int(L.lib().nrc_feature_tile_bytes(C.c_size_t(n)))
+
+
+def encode_tiles(mrhe, pos, d, out=None):
+    """EncodeRay into bf16 operand-image tiles (device memory: a torch CUDA uint8 tensor of feature_tile_bytes(n))."""
+    import torch
+    pos, d = _f32(pos), _f32(d)
+    n = pos.shape[0]
+    tiles = torch.empty(feature_tile_bytes(n), dtype=torch.uint8, device="cuda") if out is None else out
+    L.check(L.lib().nrc_encode_tiles(mrhe.h, _ptr(pos), _ptr(d), C.c_size_t(n), _ptr(tiles)))
+    return tiles
+
+
+def mlp_forward_tiles(nrc, tiles, n, out=None, like=None):
+    """The six layers from bf16 operand-image tiles (k_mlp_stream): rgb[n][3], numpy unless `out`/`like` is a CUDA tensor."""
+    rgb = out if out is not None else _out((n, 3), np.float32, like)
+    L.check(L.lib().nrc_mlp_forward_tiles(nrc.h, _ptr(tiles), C.c_size_t(n), _ptr(rgb)))
     return rgb
 
 

@@ -6,8 +6,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libnrc_b200.so")
-SOURCES = ["capi.cu", "encode.cu", "mlp_fp32.cu", "mlp_tc.cu", "steps.cu", "dp.cu", "trace.cu", "scene.cu", "renderer.cu", "selftest.cu"]
-HEADERS = ["nrc_internal.cuh", "strict.cuh", "trace.cuh", "../../include/nrc_b200.h", "../../include/nrc_math.h"]
+SOURCES = ["capi.cu", "encode.cu", "mlp_fp32.cu", "mlp_tc.cu", "mlp_stream.cu", "steps.cu", "dp.cu", "trace.cu", "scene.cu", "renderer.cu", "selftest.cu"]
+HEADERS = ["nrc_internal.cuh", "strict.cuh", "trace.cuh", "tc_ptx.cuh", "../../include/nrc_b200.h", "../../include/nrc_math.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 
@@ -30,7 +30,7 @@ def build(force=False, verbose=False):
         obj = os.path.join(objdir, s.replace(".cu", ".o"))
         objs.append(obj)
         if force or _stale(obj, [src] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + ["-c", src, "-o", obj]
+            cmd = [nvcc] + NVCC_FLAGS + os.environ.get("NRC_EXTRA_NVCC_FLAGS", "").split() + ["-c", src, "-o", obj]
             if verbose:
                 print(" ".join(cmd))
             procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

@@ -97,7 +97,7 @@ static const char* const g_kernelNames[K_COUNT] = {
     "k_encode_pos", "k_encode_dir", "k_infer_fp32", "k_train_fp32", "k_reduce_partials", "k_transpose_weights", "k_nrc_step",
     "k_mrhe_step", "k_init_normal", "k_render_walk", "k_train_walk", "k_light<render>", "k_light<train>", "k_render_combine",
     "k_train_combine", "k_composite", "k_build_bricks", "k_volume_sample", "k_pack_records", "k_cdf_rows", "k_cdf_y",
-    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc", "k_dp_reduce_step"};
+    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc", "k_dp_reduce_step", "k_encode_tiles", "k_mlp_stream"};
 
 void nrc_prof_begin(nrc_ctx* ctx, cudaStream_t st, int kid)
 {
@@ -220,6 +220,7 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[0], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[1], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
+    if (const char* e = getenv("NRC_INFER_SPLIT")) c->inferMode = atoi(e) ? NRC_INFER_SPLIT : NRC_INFER_FUSED;
     *out = c;
     return NRC_OK;
 }
@@ -273,6 +274,14 @@ extern "C" nrc_status nrc_ctx_set_precision(nrc_ctx* c, nrc_mlp_precision p)
     return NRC_OK;
 }
 
+extern "C" nrc_status nrc_ctx_set_infer_mode(nrc_ctx* c, nrc_infer_mode mode)
+{
+    NRC_REQUIRE(c, "null context");
+    NRC_REQUIRE(mode == NRC_INFER_FUSED || mode == NRC_INFER_SPLIT, "unknown inference mode");
+    c->inferMode = mode;
+    return NRC_OK;
+}
+
 // ---- MLP parameter store --------------------------------------------------------------------------------------
 extern "C" nrc_status nrc_mlp_create(nrc_ctx* ctx, float lr, float wd, float beta1, uint64_t seed, nrc_mlp** out)
 {
@@ -302,6 +311,7 @@ extern "C" nrc_status nrc_mlp_destroy(nrc_mlp* m)
     cudaFree(m->params); cudaFree(m->grad); cudaFree(m->momentum); cudaFree(m->paramsT);
     if (m->partial) cudaFree(m->partial);
     if (m->paramsBf16) cudaFree(m->paramsBf16);
+    if (m->featTiles) cudaFree(m->featTiles);
     delete m;
     return NRC_OK;
 }
@@ -492,10 +502,39 @@ extern "C" nrc_status nrc_infer(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, con
     NRC_TRY(nrc_stage_in(ctx, 0, pos, n * 3 * sizeof(float), &dpos));
     NRC_TRY(nrc_stage_in(ctx, 1, dir, n * 3 * sizeof(float), &ddir));
     NRC_TRY(nrc_stage_out(ctx, 3, rgb, n * 3 * sizeof(float), &drgb));
-    if (ctx->precision == NRC_MLP_BF16_TC)
+    if (ctx->precision == NRC_MLP_BF16_TC && ctx->inferMode == NRC_INFER_SPLIT)
+        NRC_TRY(launch_infer_split(mlp, m, (const float*)dpos, (const float*)ddir, nullptr, n, (float*)drgb, ctx->stream));
+    else if (ctx->precision == NRC_MLP_BF16_TC)
         NRC_TRY(launch_infer_tc(mlp, m, (const float*)dpos, (const float*)ddir, nullptr, n, (float*)drgb, ctx->stream));
     else
         NRC_TRY(launch_infer_fp32(mlp, m, (const float*)dpos, (const float*)ddir, nullptr, n, (float*)drgb, ctx->stream));
+    NRC_TRY(nrc_stage_out_finish(ctx, rgb, drgb, n * 3 * sizeof(float)));
+    return NRC_OK;
+}
+
+extern "C" size_t nrc_feature_tile_bytes(size_t n) { return ((n + 127) / 128) * 16384; }
+
+extern "C" nrc_status nrc_encode_tiles(nrc_mrhe* m, const float* pos, const float* dir, size_t n, void* featTiles)
+{
+    NRC_REQUIRE(m && pos && dir && featTiles, "null argument");
+    NRC_REQUIRE(nrc_is_device_ptr(featTiles), "featTiles must be device memory");
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = m->ctx;
+    const void *dpos, *ddir;
+    NRC_TRY(nrc_stage_in(ctx, 0, pos, n * 3 * sizeof(float), &dpos));
+    NRC_TRY(nrc_stage_in(ctx, 1, dir, n * 3 * sizeof(float), &ddir));
+    return launch_encode_tiles(m, (const float*)dpos, (const float*)ddir, nullptr, n, featTiles, ctx->stream);
+}
+
+extern "C" nrc_status nrc_mlp_forward_tiles(nrc_mlp* mlp, const void* featTiles, size_t n, float* rgb)
+{
+    NRC_REQUIRE(mlp && featTiles && rgb, "null argument");
+    NRC_REQUIRE(nrc_is_device_ptr(featTiles), "featTiles must be device memory");
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = mlp->ctx;
+    void* drgb;
+    NRC_TRY(nrc_stage_out(ctx, 3, rgb, n * 3 * sizeof(float), &drgb));
+    NRC_TRY(launch_mlp_stream(mlp, featTiles, nullptr, n, (float*)drgb, ctx->stream));
     NRC_TRY(nrc_stage_out_finish(ctx, rgb, drgb, n * 3 * sizeof(float)));
     return NRC_OK;
 }

@@ -24,16 +24,8 @@
 #include "nrc_internal.cuh"
 #include "strict.cuh"
 
-#define TC_ROWS 128
-#define TC_THREADS 256
-#define TC_TMEM_COLS 64
+#include "tc_ptx.cuh"
 
-// ---- bf16 weight images ----------------------------------------------------------------------------------------------
-// forward image (B operand of x*W^T: rows n = out, K = in), elements:
-//   layer l < 5 at l*4096: (k/8)*512 + n*8 + k%8 ; layer 5 (3 rows padded to 16) at 20480: (k/8)*128 + n*8 + k%8
-// transposed image at TC_W_ELEMS (B operand of the back-data GEMM e*W: rows n = in, K = out):
-//   layer l < 5 at l*4096: (k/8)*512 + n*8 + k%8 with k = out ; layer 5 at 20480: K = 16 (3 real outputs), same formula
-#define TC_W_ELEMS (5 * 4096 + 1024)
 
 __global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ params, __nv_bfloat16* __restrict__ img)
 {
@@ -59,110 +51,6 @@ __global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ par
         }
     }
     img[i] = __float2bfloat16_rn(v);
-}
-
-// ---- PTX wrappers ------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t"
-        "}" ::"r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols)   // one full warp
-{
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols)   // the same warp
-{
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-}
-
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-// generic-proxy shared-memory writes -> visible to the async proxy (the tensor core reads operands through it)
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-// D[tmem] (+)= A[smem] * B[smem]^T, kind::f16 (bf16 in, fp32 accumulate), one CTA
-__device__ __forceinline__ void umma_bf16(uint32_t dTmem, uint64_t aDesc, uint64_t bDesc, uint32_t idesc, uint32_t accumulate)
-{
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "}" ::"r"(dTmem), "l"(aDesc), "l"(bDesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-
-// all MMAs issued so far by this thread -> one arrive on the mbarrier when they have completed
-__device__ __forceinline__ void umma_commit(uint64_t* bar)
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
-// shared-memory matrix descriptor, K-major, no swizzle (layout_type 0), version 1 (Blackwell)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t smemAddr, uint32_t lboBytes, uint32_t sboBytes)
-{
-    uint64_t d = 0;
-    d |= (uint64_t)((smemAddr >> 4) & 0x3fffu);
-    d |= (uint64_t)((lboBytes >> 4) & 0x3fffu) << 16;
-    d |= (uint64_t)((sboBytes >> 4) & 0x3fffu) << 32;
-    d |= (uint64_t)1 << 46;
-    return d;
-}
-
-// instruction descriptor: D fp32 (bit 4), A bf16 (bit 7), B bf16 (bit 10), both K-major, N>>3 at 17, M>>4 at 24
-__device__ __forceinline__ constexpr uint32_t umma_idesc(uint32_t M, uint32_t N)
-{
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
-}
-
-// 32 lanes x 32 consecutive fp32 columns: thread = its lane's row
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v)
-{
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
-          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
-          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
-          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t* v)
-{
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
-                 : "r"(taddr)
-                 : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
-{
-    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
 }
 
 // ---- shared-memory map ----------------------------------------------------------------------------------------------------
@@ -334,7 +222,7 @@ __global__ void __launch_bounds__(TC_THREADS, 3) k_infer_tc(const float* __restr
 }
 
 // ---- host launchers -----------------------------------------------------------------------------------------------------------
-static nrc_status tc_prepare(nrc_mlp* mlp, cudaStream_t st)
+nrc_status tc_prepare(nrc_mlp* mlp, cudaStream_t st)
 {
     if (!mlp->paramsBf16) NRC_CUDA(cudaMalloc(&mlp->paramsBf16, 2 * TC_W_ELEMS * sizeof(uint16_t)));
     if (mlp->dirtyBf16) {
@@ -363,6 +251,56 @@ nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
                k_infer_tc<<<blocks, TC_THREADS, TC_SMEM_BYTES, st>>>(pos, dir, countDev, n, reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16),
                                                                      mlp->params, make_mrhe_dev(m), rgb));
     return NRC_OK;
+}
+
+// ---- split inference: encode -> bf16 operand-image tiles in HBM -> k_mlp_stream (mlp_stream.cu) ---------------------------
+// One block per 128-query tile, no shared memory, no TMEM: a pure gather kernel at full occupancy.  The tile image in
+// global memory is byte for byte the A-operand image k_infer_tc builds in shared memory (chunk(kc,row) = 16 B at
+// (kc*128 + row)*16), so the MLP kernel brings a tile in with ONE 16 KB bulk copy and a warp's stores are 512 contiguous bytes.
+__global__ void __launch_bounds__(TC_THREADS) k_encode_tiles(const float* __restrict__ pos, const float* __restrict__ dir,
+                                                             const uint32_t* __restrict__ countDev, size_t nMax, MrheDev m,
+                                                             unsigned char* __restrict__ featTiles)
+{
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row = (warp & 3) * 32 + lane, half = warp >> 2;
+    size_t n = nMax;
+    if (countDev) { size_t c = *countDev; n = c < nMax ? c : nMax; }
+    const size_t tile = blockIdx.x;
+    if (tile * TC_ROWS >= n) return;
+    const size_t q = tile * TC_ROWS + row;
+    const bool live = q < n;
+    f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
+    if (live) {
+        p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
+        d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
+    }
+    bool nanFlag;
+    tc_encode_half(featTiles + tile * 16384, row, half, live, p, d, m, nanFlag);
+}
+
+nrc_status launch_encode_tiles(nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, void* featTiles,
+                               cudaStream_t st)
+{
+    if (n == 0) return NRC_OK;
+    NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
+    size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
+    NRC_LAUNCH(m->ctx, st, K_ENCODE_TILES,
+               k_encode_tiles<<<(unsigned)tiles, TC_THREADS, 0, st>>>(pos, dir, countDev, n, make_mrhe_dev(m), (unsigned char*)featTiles));
+    return NRC_OK;
+}
+
+nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, float* rgb,
+                              cudaStream_t st)
+{
+    if (n == 0) return NRC_OK;
+    size_t bytes = ((n + TC_ROWS - 1) / TC_ROWS) * 16384;
+    if (mlp->featBytes < bytes) {
+        if (mlp->featTiles) { NRC_CUDA(cudaDeviceSynchronize()); NRC_CUDA(cudaFree(mlp->featTiles)); mlp->featTiles = nullptr; mlp->featBytes = 0; }
+        NRC_CUDA(cudaMalloc(&mlp->featTiles, bytes));
+        mlp->featBytes = bytes;
+    }
+    NRC_TRY(launch_encode_tiles(m, pos, dir, countDev, n, mlp->featTiles, st));
+    return launch_mlp_stream(mlp, mlp->featTiles, countDev, n, rgb, st);
 }
 
 // ==================================================================================================================

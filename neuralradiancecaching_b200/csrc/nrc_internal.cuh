@@ -43,6 +43,7 @@ enum NrcKernelId {
     K_ENCODE_POS = 0, K_ENCODE_DIR, K_INFER_FP32, K_TRAIN_FP32, K_REDUCE_PARTIALS, K_TRANSPOSE_WEIGHTS, K_NRC_STEP, K_MRHE_STEP,
     K_INIT_NORMAL, K_RENDER_WALK, K_TRAIN_WALK, K_LIGHT_RENDER, K_LIGHT_TRAIN, K_RENDER_COMBINE, K_TRAIN_COMBINE, K_COMPOSITE,
     K_BUILD_BRICKS, K_VOLUME_SAMPLE, K_PACK_RECORDS, K_CDF_ROWS, K_CDF_Y, K_INFER_TC, K_TRAIN_TC, K_PACK_BF16, K_MISC, K_DP_REDUCE_STEP,
+    K_ENCODE_TILES, K_MLP_STREAM,
     K_COUNT
 };
 
@@ -61,6 +62,7 @@ struct nrc_ctx {
     cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
     cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[2] = {nullptr, nullptr};
     nrc_mlp_precision precision = NRC_MLP_FP32;
+    nrc_infer_mode inferMode = NRC_INFER_FUSED;   // nrc_ctx_create reads NRC_INFER_SPLIT
     uint64_t launches = 0;
     std::vector<nrc_renderer*> renderers;   // nrc_sync settles their deferred vertex-pool checks (renderer.cu)
     // per-kernel event timing (off by default; bench.py turns it on over its timed region)
@@ -87,6 +89,8 @@ struct nrc_mlp {
     float* partial = nullptr;    // per-block partial gradients of the train kernel [maxBlocks][NRC_PARTIAL_STRIDE]
     int partialBlocks = 0;
     uint16_t* paramsBf16 = nullptr;  // bf16 operand images for the tcgen05 path (built on demand)
+    void* featTiles = nullptr;       // bf16 operand-image tiles of the split inference path (grown on demand)
+    size_t featBytes = 0;
     bool dirtyT = true;          // paramsT needs a rebuild after params changed
     bool dirtyBf16 = true;       // paramsBf16 needs a rebuild
 };
@@ -196,3 +200,9 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
                            float* pred, cudaStream_t st);
 nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n,
                            float* rgb, cudaStream_t st);
+// split inference: k_encode_tiles (mlp_tc.cu) -> bf16 operand-image tiles -> k_mlp_stream (mlp_stream.cu)
+nrc_status launch_encode_tiles(nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, void* featTiles,
+                               cudaStream_t st);
+nrc_status launch_mlp_stream(nrc_mlp* mlp, const void* featTiles, const uint32_t* countDev, size_t n, float* rgb, cudaStream_t st);
+nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, float* rgb,
+                              cudaStream_t st);

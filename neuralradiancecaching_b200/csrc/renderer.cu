@@ -372,7 +372,8 @@ static TraceParams make_params(const nrc_renderer* r)
 static nrc_status infer_queries(nrc_renderer* r, cudaStream_t st)
 {
     if (r->ctx->precision == NRC_MLP_BF16_TC)
-        return launch_infer_tc(r->mlp, r->mrhe, r->ql.pos, r->ql.dir, r->ql.count, r->ql.cap, r->ql.rgb, st);
+        return (r->ctx->inferMode == NRC_INFER_SPLIT ? launch_infer_split : launch_infer_tc)(r->mlp, r->mrhe, r->ql.pos, r->ql.dir, r->ql.count,
+                                                                                             r->ql.cap, r->ql.rgb, st);
     return launch_infer_fp32(r->mlp, r->mrhe, r->ql.pos, r->ql.dir, r->ql.count, r->ql.cap, r->ql.rgb, st);
 }
 

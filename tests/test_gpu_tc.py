@@ -142,3 +142,75 @@ def test_tc_training_converges_like_fp32(N, ctx):
     assert lo[-1] < 0.7 * lo[0]                      # it trains
     assert abs(lg[-1] - lo[-1]) <= 0.1 * lo[-1]      # and the bf16 path lands within 10 % of the fp32 loss
     nrc.Destroy(); m.Destroy()
+
+
+# ---- split inference: k_encode_tiles -> bf16 operand-image tiles -> k_mlp_stream (pipelined, A operand from TMEM) ----------
+@pytest.mark.parametrize("wscale", [0.01, 0.1])
+def test_infer_split_matches_oracle_and_fused(N, ctx, wscale):
+    sc, nrc, m = _pair(N, ctx, wscale)
+    # 1<<18 queries = 2048 tiles: ~14 tiles per CTA, so every shared-memory stage and every TMEM slot is reused
+    for n in (1, 127, 128, 129, 5000, 148 * 128 * 5 + 77, 1 << 18):
+        pos, d = Cm.rand_queries(n, seed=500 + n)
+        ctx.set_infer_mode(False)
+        fused = N.infer(nrc, m, pos, d)
+        ctx.set_infer_mode(True)
+        got = N.infer(nrc, m, pos, d)
+        assert np.isfinite(got).all()
+        # same operands, same fp32 accumulation: the two kernels may differ only where bf16 rounding of an activation flips
+        assert _rel(got, fused) < 1e-6, (n, _rel(got, fused))
+        if n <= (1 << 16):
+            want = sc.infer(pos, d)
+            assert _rel(got, want) < TC_REL, (n, _rel(got, want))
+    ctx.set_infer_mode(False)
+    nrc.Destroy(); m.Destroy()
+
+
+@pytest.mark.parametrize("slots", [1, 2, 3, 4, 5])
+def test_mlp_stream_slots_agree(N, ctx, slots, monkeypatch):
+    import torch
+    sc, nrc, m = _pair(N, ctx, 0.1)
+    n = 148 * 128 * 11 + 5
+    pos, d = Cm.rand_queries(n, seed=77)
+    dpos, dd = torch.from_numpy(pos).cuda(), torch.from_numpy(d).cuda()
+    ctx.set_infer_mode(False)
+    fused = N.infer(nrc, m, dpos, dd)
+    tiles = N.encode_tiles(m, dpos, dd)
+    assert tiles.numel() == N.feature_tile_bytes(n) == ((n + 127) // 128) * 16384
+    monkeypatch.setenv("NRC_MLP_SLOTS", str(slots))
+    got = N.mlp_forward_tiles(nrc, tiles, n, like=dpos)
+    ctx.sync()
+    assert _rel(got.cpu().numpy(), fused.cpu().numpy()) < 1e-6
+    nrc.Destroy(); m.Destroy()
+
+
+def test_encode_tiles_layout(N, ctx):
+    """chunk (kc, row) of a tile holds network inputs 8kc..8kc+7 of query row, bf16 of the exact fp32 features."""
+    import torch
+    sc, nrc, m = _pair(N, ctx)
+    n = 300
+    pos, d = Cm.rand_queries(n, seed=3)
+    tiles = N.encode_tiles(m, torch.from_numpy(pos).cuda(), torch.from_numpy(d).cuda())
+    ctx.sync()
+    raw = tiles.cpu().numpy().view(np.uint16).reshape(-1, 8, 128, 8)          # [tile][kc][row][8]
+    feat = np.concatenate([N.encode(m, pos, want_idx=False)[0], N.encode_dir(ctx, d)], axis=1)    # [n][64] fp32
+    u = feat.view(np.uint32).astype(np.uint64)
+    want = (((u + 0x7FFF + ((u >> 16) & 1)) >> 16) & 0xFFFF).astype(np.uint16)     # round-to-nearest-even bf16 (finite inputs)
+    got = raw.transpose(0, 2, 1, 3).reshape(-1, 64)
+    assert np.array_equal(got[:n], want)
+    assert not got[n:].any()
+    nrc.Destroy(); m.Destroy()
+
+
+def test_frame_split_equals_fused(N, ctx):
+    from test_gpu_frame import build
+    W, H = 96, 64
+    cfg = Cm.scene_cfg(aspect=W / H)
+    frames = []
+    for split in (False, True):
+        ctx.set_infer_mode(split)
+        r, nrc, m, vol = build(N, ctx, cfg, W, H, 8, 8)
+        r.FrameRender(); ctx.sync()          # no training step: both runs infer with identical weights
+        frames.append(r.read_frame())
+        r.Destroy()
+    ctx.set_infer_mode(False)
+    assert Cm.psnr(frames[1], frames[0]) >= 80.0
