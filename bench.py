@@ -385,6 +385,58 @@ def run_fit(ctx, N, L, torch, steps=10, n=1 << 18):
             "train_step_ms_host_buffers": host_ms, "h2d_bytes_per_step": n * 36, "loss_first_last": [losses[0], losses[-1]], "kernels": kern}
 
 
+def run_mlp_stream(ctx, N, torch, sizes=(1 << 21, 1 << 23), reps=20):
+    """The split inference path's two kernels alone, inputs resident in HBM and larger than L2: k_encode_tiles (gather kernel,
+    bounded by L2/HBM gathers: 1 036 algorithmic bytes per query) and k_mlp_stream (the six layers on tcgen05, bounded by the
+    tensor pipe: 41 344 FLOP per query).  Durations are CUDA events on the launching stream around `reps` back-to-back launches."""
+    from neuralradiancecaching_b200 import scene as S
+    dev = torch.device("cuda", ctx.device)
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pk = {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1590.0, "hbm_gbs": 6650.0, "fallback": True}
+    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0); nrc.set_params(S.mlp_init(1))
+    m = N.MRHE(ctx, 0.01, 0.0, seed=0); m.set_tables(S.table_init(2))
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    g = torch.Generator(device=dev); g.manual_seed(0x5EED)
+    out = {"peaks": {"bf16_tflops_burst": pk.get("bf16_tflops"), "bf16_tflops_sustained": pk.get("bf16_tflops_sustained"), "hbm_gbs": pk.get("hbm_gbs")},
+           "sizes": []}
+
+    def timed(fn):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(3):
+            fn()
+        with torch.cuda.stream(ext):
+            e0.record()
+        for _ in range(reps):
+            fn()
+        with torch.cuda.stream(ext):
+            e1.record()
+        ctx.sync()
+        return e0.elapsed_time(e1) / reps
+
+    for n in sizes:
+        box = torch.tensor([62.5, 42.5, 76.5], device=dev)
+        pos = ((torch.rand((n, 3), generator=g, device=dev) - 0.5) * box).contiguous()
+        d = torch.randn((n, 3), generator=g, device=dev); d = (d / d.norm(dim=1, keepdim=True)).contiguous()
+        tiles = torch.empty(N.feature_tile_bytes(n), dtype=torch.uint8, device=dev)
+        rgb = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        torch.cuda.synchronize(dev)
+        enc_ms = timed(lambda: N.encode_tiles(m, pos, d, out=tiles))
+        mlp_ms = timed(lambda: N.mlp_forward_tiles(nrc, tiles, n, out=rgb))
+        tf = n * FLOP_INFER / (mlp_ms * 1e-3) / 1e12
+        out["sizes"].append({
+            "queries": n, "feature_tile_MB": tiles.numel() / 1e6,
+            "k_mlp_stream": {"ms": mlp_ms, "TFLOP/s": tf, "frac_of_bf16_burst": tf / pk["bf16_tflops"] if pk.get("bf16_tflops") else None,
+                             "frac_of_bf16_sustained": tf / pk["bf16_tflops_sustained"] if pk.get("bf16_tflops_sustained") else None,
+                             "GB/s": n * 140.0 / (mlp_ms * 1e-3) / 1e9, "queries_per_s": n / (mlp_ms * 1e-3)},
+            "k_encode_tiles": {"ms": enc_ms, "GB/s_algorithmic": n * 1036.0 / (enc_ms * 1e-3) / 1e9, "queries_per_s": n / (enc_ms * 1e-3),
+                               "note": "16x8 float2 table gathers + 24 B of pos/dir in, 128 B of bf16 features out per query; the 2 MiB table is L2-resident"}})
+        del pos, d, tiles, rgb
+    nrc.Destroy(); m.Destroy()
+    return out
+
+
 # algorithmic work per unit (SURVEY.md 8d; DESIGN.md "Kernels")
 TAP_BYTES = 8.0              # one density tap = one 2x2x2 UNORM8 brick
 FLOP_INFER = 41344.0         # 2 * 20 672 MAC per query
@@ -406,8 +458,10 @@ def kernel_work(name, tot, pixels, table_floats):
         return "hbm", tot["render_taps"] * TAP_BYTES + tot["render_vertices"] * 128.0, "GB/s"
     if name == "k_light<train>":
         return "hbm", tot["train_taps"] * TAP_BYTES + tot["train_vertices"] * 64.0, "GB/s"
-    if name in ("k_infer_fp32", "k_infer_tc"):
+    if name in ("k_infer_fp32", "k_infer_tc", "k_mlp_stream"):
         return "tensor", tot["infer_queries"] * FLOP_INFER, "TFLOP/s"
+    if name == "k_encode_tiles":
+        return "hbm", tot["infer_queries"] * (1036.0 + 128.0), "GB/s"      # 1 164 B/query stand-alone encode
     if name in ("k_train_fp32", "k_train_tc"):
         return "tensor", tot["train_samples"] * FLOP_TRAIN, "TFLOP/s"
     if name == "k_render_walk":
@@ -510,6 +564,10 @@ def finish_b200(args, v):
             line["fit_config2"] = run_fit(v["ctx"], N, L, torch)
         except Exception as e:
             line["fit_config2"] = {"error": repr(e)}
+        try:
+            line["mlp_stream"] = run_mlp_stream(v["ctx"], N, torch)
+        except Exception as e:
+            line["mlp_stream"] = {"error": repr(e)}
     if world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_reference_sample(W, H, v["TW"], v["TH"], budget_s=args.cpu_budget)
