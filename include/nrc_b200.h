@@ -173,6 +173,18 @@ NRC_API float* nrc_mrhe_grad_ptr(nrc_mrhe* mrhe);                  /* device add
  * because the reference's scatter address has no level term (nrc-train.comp:977-978). */
 NRC_API size_t nrc_mrhe_grad_extent(nrc_mrhe* mrhe);
 
+/* ---- opt-in "fixed" preset (NOT what the reference ships -- every call below defaults to off) ----
+ * nrc_mrhe_set_fixed_mode: EncodePosMrhe / BackpropMrhe (nrc-train.comp:266-339, 947-983) with the slips of SURVEY Appendix A2, A3, A9,
+ *   A10 corrected: lerp factors are the grid-space fractions resPos - floor(resPos) and each blends its own axis; each of a level's two
+ *   features gets its own error; gradients land in their level's table (nrc_mrhe_grad_extent becomes the whole table).
+ * nrc_*_set_adam: nrc-step.comp / mrhe-step.comp with a second moment and bias correction (the shipped "Adam" is first-moment momentum
+ *   only, A16): g' as shipped (scrub, weight decay); m = b1 m + (1-b1) g'; v = b2 v + (1-b2) g'^2; w += lr * mhat / (sqrt(vhat) + eps).
+ *   The MLP keeps the beta1 of nrc_mlp_create; the tables get their own.  Switching on (or off) resets moments and step count.
+ *   The fused data-parallel exchange (nrc_dp_*) refuses Adam; use the all-reduce path. */
+NRC_API nrc_status nrc_mrhe_set_fixed_mode(nrc_mrhe* mrhe, int on);
+NRC_API nrc_status nrc_mlp_set_adam(nrc_mlp* mlp, int on, float beta2, float eps);
+NRC_API nrc_status nrc_mrhe_set_adam(nrc_mrhe* mrhe, int on, float beta1, float beta2, float eps);
+
 /* ---- stand-alone operators (what the reference runs inside its shaders; used by parity tests and bench) ---- */
 /* EncodePosMrhe (nrc-train.comp:266-339): pos[N][3] -> feat[N][32]; idx[N][128] (level*8+corner) optional. */
 NRC_API nrc_status nrc_encode(nrc_mrhe* mrhe, const float* pos, size_t n, float* feat, uint32_t* idx);

@@ -260,6 +260,8 @@ public:
     {
         Check(nrc_mlp_create(ctx.Get(), learningRate, weightDecay, beta1, seed, &m_Handle), "nrc_mlp_create");
     }
+    // opt-in fixed preset (no reference counterpart): second moment + bias correction in nrc-step
+    void SetAdam(bool on, float beta2 = 0.999f, float eps = 1e-8f) const { Check(nrc_mlp_set_adam(m_Handle, on ? 1 : 0, beta2, eps), "nrc_mlp_set_adam"); }
     void Destroy() { nrc_mlp_destroy(m_Handle); m_Handle = nullptr; }
     void ResetStats() { Check(nrc_mlp_reset_stats(m_Handle), "nrc_mlp_reset_stats"); }
     const StatsData& GetStats() { Check(nrc_mlp_get_stats(m_Handle, &m_Stats.mseLoss), "nrc_mlp_get_stats"); return m_Stats; }
@@ -298,6 +300,12 @@ public:
         m_Shape[0] = levelCount; m_Shape[1] = hashTableSize; m_Shape[2] = featureCount;
     }
     const uint32_t* GetShape() const { return m_Shape; }   // {levels, entries per level, features}
+    // opt-in fixed preset (no reference counterpart): corrected interpolation / gradient scatter, Adam in mrhe-step
+    void SetFixedMode(bool on) const { Check(nrc_mrhe_set_fixed_mode(m_Handle, on ? 1 : 0), "nrc_mrhe_set_fixed_mode"); }
+    void SetAdam(bool on, float beta1 = 0.9f, float beta2 = 0.999f, float eps = 1e-8f) const
+    {
+        Check(nrc_mrhe_set_adam(m_Handle, on ? 1 : 0, beta1, beta2, eps), "nrc_mrhe_set_adam");
+    }
     void Destroy() { nrc_mrhe_destroy(m_Handle); m_Handle = nullptr; }
     size_t GetHashTableSize() const { return nrc_mrhe_table_bytes(m_Handle); }   // bytes, MRHE.cpp:267-270
     void PrintHashTables() const   // MRHE.cpp:234-260

@@ -110,6 +110,10 @@ class NeuralRadianceCache:
             L.lib().nrc_mlp_destroy(self.h)
             self.h = C.c_void_p()
 
+    def set_adam(self, on, beta2=0.999, eps=1e-8):
+        """opt-in fixed preset: second moment + bias correction in nrc-step (resets moments and step count)"""
+        L.check(L.lib().nrc_mlp_set_adam(self.h, C.c_int(1 if on else 0), C.c_float(beta2), C.c_float(eps)))
+
     def ResetStats(self):
         L.check(L.lib().nrc_mlp_reset_stats(self.h))
 
@@ -185,6 +189,14 @@ class MRHE:
 
     def set_config(self, lr, wd):
         L.check(L.lib().nrc_mrhe_set_config(self.h, C.c_float(lr), C.c_float(wd)))
+
+    def set_fixed_mode(self, on):
+        """opt-in fixed preset: grid-space lerp factors on their own axes, per-feature errors, per-level gradient tables"""
+        L.check(L.lib().nrc_mrhe_set_fixed_mode(self.h, C.c_int(1 if on else 0)))
+
+    def set_adam(self, on, beta1=0.9, beta2=0.999, eps=1e-8):
+        """opt-in fixed preset: Adam in mrhe-step (resets moments and step count)"""
+        L.check(L.lib().nrc_mrhe_set_adam(self.h, C.c_int(1 if on else 0), C.c_float(beta1), C.c_float(beta2), C.c_float(eps)))
 
     def set_tables(self, tables=None, delta=None):
         t = None if tables is None else _f32(tables)

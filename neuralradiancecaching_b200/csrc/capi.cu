@@ -312,6 +312,7 @@ extern "C" nrc_status nrc_mlp_destroy(nrc_mlp* m)
     if (m->partial) cudaFree(m->partial);
     if (m->paramsBf16) cudaFree(m->paramsBf16);
     if (m->featTiles) cudaFree(m->featTiles);
+    if (m->second) cudaFree(m->second);
     delete m;
     return NRC_OK;
 }
@@ -427,6 +428,8 @@ extern "C" nrc_status nrc_mrhe_destroy(nrc_mrhe* m)
     if (!m) return NRC_OK;
     cudaStreamSynchronize(m->ctx->stream);
     cudaFree(m->tables); cudaFree(m->delta);
+    if (m->m1) cudaFree(m->m1);
+    if (m->m2) cudaFree(m->m2);
     delete m;
     return NRC_OK;
 }
@@ -460,8 +463,49 @@ extern "C" float* nrc_mrhe_grad_ptr(nrc_mrhe* m) { return m ? m->delta : nullptr
 extern "C" size_t nrc_mrhe_grad_extent(nrc_mrhe* m)
 {
     if (!m) return 0;
+    if (m->fixed) return m->count;   // the fixed preset scatters into every level's table
     size_t e = (size_t)2 * m->T;
     return e < m->count ? e : m->count;
+}
+
+// ---- the opt-in "fixed" preset ------------------------------------------------------------
+extern "C" nrc_status nrc_mrhe_set_fixed_mode(nrc_mrhe* m, int on)
+{
+    NRC_REQUIRE(m, "null mrhe");
+    m->fixed = on != 0;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_set_adam(nrc_mlp* mlp, int on, float beta2, float eps)
+{
+    NRC_REQUIRE(mlp, "null mlp");
+    NRC_REQUIRE(!on || (beta2 > 0.0f && beta2 < 1.0f && eps >= 0.0f), "beta2 must be in (0, 1), eps >= 0");
+    NRC_CUDA(cudaStreamSynchronize(mlp->ctx->stream));
+    if (on) {
+        if (!mlp->second) NRC_CUDA(cudaMalloc(&mlp->second, 21504 * sizeof(float)));
+        NRC_CUDA(cudaMemset(mlp->second, 0, 21504 * sizeof(float)));
+        mlp->beta2 = beta2; mlp->eps = eps;
+    }
+    mlp->adam = on != 0;
+    mlp->steps = 0;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_set_adam(nrc_mrhe* m, int on, float beta1, float beta2, float eps)
+{
+    NRC_REQUIRE(m, "null mrhe");
+    NRC_REQUIRE(!on || (beta1 >= 0.0f && beta1 < 1.0f && beta2 > 0.0f && beta2 < 1.0f && eps >= 0.0f), "betas must be in [0, 1), eps >= 0");
+    NRC_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    if (on) {
+        if (!m->m1) NRC_CUDA(cudaMalloc(&m->m1, m->count * sizeof(float)));
+        if (!m->m2) NRC_CUDA(cudaMalloc(&m->m2, m->count * sizeof(float)));
+        NRC_CUDA(cudaMemset(m->m1, 0, m->count * sizeof(float)));
+        NRC_CUDA(cudaMemset(m->m2, 0, m->count * sizeof(float)));
+        m->beta1 = beta1; m->beta2 = beta2; m->eps = eps;
+    }
+    m->adam = on != 0;
+    m->steps = 0;
+    return NRC_OK;
 }
 
 // ---- stand-alone operators ------------------------------------------------------------------------------------

@@ -198,6 +198,7 @@ extern "C" nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int 
     NRC_REQUIRE(mlp && mrhe && out, "null argument");
     NRC_REQUIRE(world >= 1 && world <= NRC_DP_MAX_WORLD && rank >= 0 && rank < world, "rank/world out of range");
     NRC_REQUIRE(nrc_mrhe_grad_extent(mrhe) <= NRC_DP_MAX_HEAD, "delta-table head too large for the fused exchange; use the NCCL path");
+    NRC_REQUIRE(!mlp->adam && !mrhe->adam, "the fused exchange applies the reference's steps; with Adam use the NCCL path (all-reduce + nrc_optimizer_step)");
     nrc_dp* d = new nrc_dp();
     d->mlp = mlp; d->mrhe = mrhe; d->rank = rank; d->world = world;
     cudaError_t e = cudaMalloc(&d->flags, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));

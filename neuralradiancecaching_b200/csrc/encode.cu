@@ -23,7 +23,8 @@ __global__ void __launch_bounds__(256) k_encode_pos(const float* __restrict__ po
         f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
         f3 np = mrhe_norm_pos(p, sky);
         f3 lerp;
-        mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp);
+        mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp, m.fixed != 0);
+                lerp = mrhe_blend_factors(lerp, m.fixed != 0);
         const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
         float f0[8], f1[8];
 #pragma unroll
@@ -62,6 +63,7 @@ MrheDev make_mrhe_dev(const nrc_mrhe* m)
     d.delta = m->delta;
     d.L = m->L;
     d.T = m->T;
+    d.fixed = m->fixed ? 1u : 0u;
     for (int i = 0; i < 16; i++) d.res[i] = m->res[i];
     d.skySize[0] = 62.5f; d.skySize[1] = 42.5f; d.skySize[2] = 76.5f;   // vec3(125,85,153)/2, nrc-train.comp:212
     return d;

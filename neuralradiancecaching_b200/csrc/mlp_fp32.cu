@@ -76,7 +76,8 @@ __device__ __forceinline__ void encode_tile(const float* __restrict__ pos, const
         if (level < m.L) {
             uint32_t idx[8];
             f3 lerp;
-            mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp);
+            mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp, m.fixed != 0);
+                lerp = mrhe_blend_factors(lerp, m.fixed != 0);
             const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
             float f0[8], f1[8];
 #pragma unroll
@@ -392,17 +393,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_train_fp32(const float* __restr
                     if (level >= m.L) break;
                     uint32_t idx[8];
                     f3 lf;
-                    mrhe_level_indices(p, np, m.res[level], m.T, idx, lf);
+                    mrhe_level_indices(p, np, m.res[level], m.T, idx, lf, m.fixed != 0);
                     float g = es[r * 64 + 2 * level];   // feature 0's error for both features (A9)
                     float ng = -g;
+                    // fixed preset: feature 1 gets its own error and the gradient lands in its level's table
+                    float ng1 = m.fixed ? -es[r * 64 + 2 * level + 1] : ng;
+                    float2* dl = dtab + (m.fixed ? (size_t)level * m.T : 0);
 #pragma unroll
                     for (int c = 0; c < 8; c++) {
                         float xf = (c & 4) ? lf.x : (1.0f - lf.x);
                         float yf = (c & 2) ? lf.y : (1.0f - lf.y);
                         float zf = (c & 1) ? lf.z : (1.0f - lf.z);
                         float wgt = (xf * yf) * zf;
-                        float dlt = (ng * wgt) * scale;
-                        atomicAdd(dtab + idx[c], make_float2(dlt, dlt));   // no level offset (A10)
+                        atomicAdd(dl + idx[c], make_float2((ng * wgt) * scale, (ng1 * wgt) * scale));   // no level offset (A10)
                     }
                 }
             }

@@ -79,7 +79,8 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int 
             if (live && level < m.L) {
                 uint32_t idx[8];
                 f3 lerp;
-                mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp);
+                mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp, m.fixed != 0);
+                lerp = mrhe_blend_factors(lerp, m.fixed != 0);
                 const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
                 float f0[8], f1[8];
 #pragma unroll
@@ -577,7 +578,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                 if (level >= m.L) break;
                 uint32_t idx[8];
                 f3 lf;
-                mrhe_level_indices(p, np, m.res[level], m.T, idx, lf);
+                mrhe_level_indices(p, np, m.res[level], m.T, idx, lf, m.fixed != 0);
                 float ng = -gS[row * 16 + level];
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
@@ -626,6 +627,8 @@ nrc_status launch_reduce_partials(nrc_mlp* mlp, int blocks, cudaStream_t st);   
 nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
                            float* pred, cudaStream_t st)
 {
+    // the opt-in fixed preset (per-feature errors, per-level gradient tables) trains on the fp32 CUDA-core kernel
+    if (m->fixed) return launch_train_fp32(mlp, m, pos, dir, target, n, lossScale, pred, st);
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
     NRC_TRY(tc_prepare(mlp, st));

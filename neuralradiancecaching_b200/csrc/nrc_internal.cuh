@@ -89,6 +89,11 @@ struct nrc_mlp {
     float* partial = nullptr;    // per-block partial gradients of the train kernel [maxBlocks][NRC_PARTIAL_STRIDE]
     int partialBlocks = 0;
     uint16_t* paramsBf16 = nullptr;  // bf16 operand images for the tcgen05 path (built on demand)
+    // opt-in Adam: second moment + bias correction; the reference's step is first-moment momentum only (A16)
+    bool adam = false;
+    float beta2 = 0.999f, eps = 1e-8f;
+    float* second = nullptr;     // 20995 (allocated when Adam is switched on)
+    uint32_t steps = 0;
     void* featTiles = nullptr;       // bf16 operand-image tiles of the split inference path (grown on demand)
     size_t featBytes = 0;
     bool dirtyT = true;          // paramsT needs a rebuild after params changed
@@ -105,6 +110,13 @@ struct nrc_mrhe {
     float* tables = nullptr;     // [L][T][F]
     float* delta = nullptr;      // [L][T][F]
     size_t count = 0;            // L*T*F
+    // opt-in "fixed" preset: grid-space lerp factors on their own axes, per-feature errors, per-level gradient tables
+    bool fixed = false;
+    bool adam = false;
+    float beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;
+    float* m1 = nullptr;         // first / second moments, L*T*F each (allocated when Adam is switched on)
+    float* m2 = nullptr;
+    uint32_t steps = 0;
 };
 
 struct nrc_volume {
@@ -155,6 +167,7 @@ struct MrheDev {
     const float* tables;
     float* delta;
     uint32_t L, T;
+    uint32_t fixed;               // 0 = the reference's arithmetic, 1 = the opt-in fixed preset
     uint32_t res[16];
     float skySize[3];
 };

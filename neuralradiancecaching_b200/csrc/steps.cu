@@ -44,6 +44,70 @@ __global__ void __launch_bounds__(256) k_nrc_step(float* __restrict__ params, fl
     }
 }
 
+// Opt-in Adam (the oracle's NrcStep with S.adam): the same scrub / weight decay / first moment as above, then
+// v = b2*v + (1-b2)*g'^2 and w += lr * (m*c1) / (sqrt(v*c2) + eps) with the bias corrections c = 1/(1 - beta^t) computed on the host.
+__global__ void __launch_bounds__(256) k_nrc_step_adam(float* __restrict__ params, float* __restrict__ grad, float* __restrict__ momentum,
+                                                       float* __restrict__ second, float* __restrict__ paramsT, unsigned short* __restrict__ imgBf16,
+                                                       float lr, float wd, float beta1, float beta2, float eps, float c1, float c2)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NRC_MLP_PARAM_COUNT) return;
+    float w = params[i];
+    float g = grad[i];
+    if (bad_value(g)) g = __fmul_rn(1000.0f, sign_nan0(g));
+    g = __fadd_rn(g, __fmul_rn(-w, wd));
+    float d = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, beta1), g), __fmul_rn(beta1, momentum[i]));
+    momentum[i] = d;
+    float v = __fadd_rn(__fmul_rn(beta2, second[i]), __fmul_rn(__fsub_rn(1.0f, beta2), __fmul_rn(g, g)));
+    second[i] = v;
+    d = __fdiv_rn(__fmul_rn(d, c1), __fadd_rn(__fsqrt_rn(__fmul_rn(v, c2)), eps));
+    float nw = __fadd_rn(w, __fmul_rn(d, lr));
+    if (i < NRC_MLP_WEIGHT_COUNT && bad_value(nw)) nw = 0.0f;
+    params[i] = nw;
+    grad[i] = 0.0f;
+    if (i < 5 * 4096) {
+        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+        paramsT[l * 4096 + k * 64 + o] = nw;
+    }
+    if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {
+        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+        int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
+        unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
+        imgBf16[dst] = h;
+        int dstT = (5 * 4096 + 1024) + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7);
+        imgBf16[dstT] = h;
+    }
+}
+
+__device__ __forceinline__ float mrhe_update_adam(float w, float g, float& m1, float& m2, float lr, float wd, float beta1, float beta2, float eps,
+                                                  float c1, float c2)
+{
+    if (bad_value(g)) g = __fmul_rn(100.0f, sign_nan0(g));
+    g = __fadd_rn(g, __fmul_rn(-w, wd));
+    m1 = __fadd_rn(__fmul_rn(beta1, m1), __fmul_rn(__fsub_rn(1.0f, beta1), g));
+    m2 = __fadd_rn(__fmul_rn(beta2, m2), __fmul_rn(__fsub_rn(1.0f, beta2), __fmul_rn(g, g)));
+    float d = __fdiv_rn(__fmul_rn(m1, c1), __fadd_rn(__fsqrt_rn(__fmul_rn(m2, c2)), eps));
+    float nw = __fadd_rn(w, __fmul_rn(d, lr));
+    return bad_value(nw) ? 0.0f : nw;
+}
+
+// 32 B/param streamed (w, delta, m1, m2 read; w, delta, m1, m2 written)
+__global__ void __launch_bounds__(256) k_mrhe_step_adam(float4* __restrict__ tables, float4* __restrict__ delta, float4* __restrict__ m1,
+                                                        float4* __restrict__ m2, size_t n4, float lr, float wd, float beta1, float beta2, float eps,
+                                                        float c1, float c2)
+{
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 w = tables[i], g = delta[i], a = m1[i], b = m2[i];
+        w.x = mrhe_update_adam(w.x, g.x, a.x, b.x, lr, wd, beta1, beta2, eps, c1, c2);
+        w.y = mrhe_update_adam(w.y, g.y, a.y, b.y, lr, wd, beta1, beta2, eps, c1, c2);
+        w.z = mrhe_update_adam(w.z, g.z, a.z, b.z, lr, wd, beta1, beta2, eps, c1, c2);
+        w.w = mrhe_update_adam(w.w, g.w, a.w, b.w, lr, wd, beta1, beta2, eps, c1, c2);
+        tables[i] = w; m1[i] = a; m2[i] = b;
+        delta[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
 __device__ __forceinline__ float mrhe_update(float w, float g, float lr, float wd)
 {
     if (bad_value(g)) g = __fmul_rn(100.0f, sign_nan0(g));
@@ -92,6 +156,15 @@ __global__ void __launch_bounds__(256) k_init_normal(float* __restrict__ dst, si
 
 nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st)
 {
+    if (mlp->adam) {
+        mlp->steps++;
+        const float c1 = 1.0f / (1.0f - powf(mlp->beta1, (float)mlp->steps)), c2 = 1.0f / (1.0f - powf(mlp->beta2, (float)mlp->steps));
+        NRC_LAUNCH(mlp->ctx, st, K_NRC_STEP,
+                   k_nrc_step_adam<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->second, mlp->paramsT,
+                                                                                     mlp->paramsBf16, mlp->lr, mlp->wd, mlp->beta1, mlp->beta2,
+                                                                                     mlp->eps, c1, c2));
+        return NRC_OK;
+    }
     NRC_LAUNCH(mlp->ctx, st, K_NRC_STEP,
                k_nrc_step<<<(NRC_MLP_PARAM_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->grad, mlp->momentum, mlp->paramsT,
                                                                             mlp->paramsBf16, mlp->lr, mlp->wd, mlp->beta1));
@@ -105,6 +178,15 @@ nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
     size_t cap = (size_t)m->ctx->smCount * 8;
     unsigned blocks = (unsigned)(want < cap ? want : cap);
     if (blocks == 0) return NRC_OK;
+    if (m->adam) {
+        m->steps++;
+        const float c1 = 1.0f / (1.0f - powf(m->beta1, (float)m->steps)), c2 = 1.0f / (1.0f - powf(m->beta2, (float)m->steps));
+        NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
+                   k_mrhe_step_adam<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables), reinterpret_cast<float4*>(m->delta),
+                                                            reinterpret_cast<float4*>(m->m1), reinterpret_cast<float4*>(m->m2), n4, m->lr, m->wd,
+                                                            m->beta1, m->beta2, m->eps, c1, c2));
+        return NRC_OK;
+    }
     NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
                k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables), reinterpret_cast<float4*>(m->delta), n4, m->lr, m->wd));
     return NRC_OK;

@@ -70,6 +70,15 @@ struct Scene {
     HdrEnvMapU hdrEnvMapData;
     bool trainEnvLight = false;  // opt-in: the env-map term of TraceScene that train.comp:1118 has commented out
     bool envCdfHalf = false;   // opt-in: halfSampleCount = sampleCount / 2, the variant commented out at fwd.frag:715
+    // opt-in "fixed" preset (none of it is what the reference ships):
+    //   mrheFixed: grid-space lerp factors (resPos - floor(resPos)) instead of world-minus-grid [A2], each factor blends its own axis
+    //              [A3], every feature gets its own error [A9], gradients land in their level's table [A10];
+    //   adam:      second moment + bias correction in both step shaders (the shipped "Adam" is first-moment momentum only [A16]).
+    bool mrheFixed = false;
+    bool adam = false;
+    float adamBeta2 = 0.999f, adamEps = 1e-8f, mrheBeta1 = 0.9f;
+    uint32_t nrcSteps = 0, mrheSteps = 0;
+    std::vector<float> secondMoment, mrFirstMoment, mrSecondMoment;
     MrheU mrhe;
     std::vector<float> mrHashTable, mrDeltaHashTable;
     NrcConfig nrcConfig;
@@ -173,7 +182,9 @@ struct Invocation {
                 neighbourFeatures[neigh] = vec2(GetMrheFeature(level, entryIndex, 0), GetMrheFeature(level, entryIndex, 1));
             }
             vec3 lerpFactors = pos - neighbours[0];   // [A2] world pos minus grid-space floor
+            if (S.mrheFixed) lerpFactors = resPos - floorPos;
             allLerpFactors[level] = lerpFactors;
+            if (S.mrheFixed) lerpFactors = vec3(lerpFactors.z, lerpFactors.y, lerpFactors.x);   // the blend below pairs .z with the x bit [A3]
             vec2 zLerpFeatures[4];
             for (uint i = 0; i < 4; i++)              // [A3] "z" lerp blends the x bit
                 zLerpFeatures[i] = (neighbourFeatures[i] * (1.0f - lerpFactors.z)) + (neighbourFeatures[4 + i] * lerpFactors.z);
@@ -342,7 +353,8 @@ struct Invocation {
         const float opc = S.WIDTH_FACTOR * S.HEIGHT_FACTOR;
         for (uint level = 0; level < 16; level++) {
             const vec3 lerpFactors = allLerpFactors[level];
-            const vec2 error = vec2(nr0[(level * 2) + 0], nr0[(level * 2) + 0]);   // [A9]
+            const vec2 error = vec2(nr0[(level * 2) + 0], nr0[(level * 2) + (S.mrheFixed ? 1 : 0)]);   // [A9]
+            const size_t levelOffset = S.mrheFixed ? (size_t)level * S.mrhe.hashTableSize * 2 : 0;   // [A10]
             for (uint x = 0; x < 2; x++)
                 for (uint y = 0; y < 2; y++)
                     for (uint z = 0; z < 2; z++) {
@@ -353,8 +365,8 @@ struct Invocation {
                         const float zFactor = z == 1 ? lerpFactors.z : (1.0f - lerpFactors.z);
                         const float errorWeight = xFactor * yFactor * zFactor;
                         const vec2 delta = -error * errorWeight * opc;
-                        sink.mrDeltaHashTable[(2 * tableEntryIndex) + 0] += delta.x;   // [A10] no level offset
-                        sink.mrDeltaHashTable[(2 * tableEntryIndex) + 1] += delta.y;
+                        sink.mrDeltaHashTable[levelOffset + (2 * tableEntryIndex) + 0] += delta.x;   // [A10] no level offset
+                        sink.mrDeltaHashTable[levelOffset + (2 * tableEntryIndex) + 1] += delta.y;
                     }
         }
     }
@@ -648,6 +660,13 @@ inline void NrcStep(Scene& S)
 {
     const float border = 1000.0f;
     const float beta1 = S.nrcConfig.beta1;
+    float adamC1 = 1.0f, adamC2 = 1.0f;   // bias corrections 1/(1 - beta^t)
+    if (S.adam) {
+        if (S.secondMoment.size() != kParamCount) S.secondMoment.assign(kParamCount, 0.0f);
+        S.nrcSteps++;
+        adamC1 = 1.0f / (1.0f - pow(beta1, float(S.nrcSteps)));
+        adamC2 = 1.0f / (1.0f - pow(S.adamBeta2, float(S.nrcSteps)));
+    }
     for (size_t i = 0; i < kParamCount; i++) {
         const bool isWeight = i < kBiasOffset[0];
         float weight = S.params[i];
@@ -656,6 +675,11 @@ inline void NrcStep(Scene& S)
         deltaWeight += -weight * S.nrcConfig.weightDecay;
         float d = ((1.0f - beta1) * deltaWeight) + (beta1 * S.momentum[i]);
         S.momentum[i] = d;
+        if (S.adam) {   // deltas are NEGATIVE gradients: w += lr * mhat / (sqrt(vhat) + eps)
+            const float v = (S.adamBeta2 * S.secondMoment[i]) + ((1.0f - S.adamBeta2) * (deltaWeight * deltaWeight));
+            S.secondMoment[i] = v;
+            d = (d * adamC1) / (sqrt(v * adamC2) + S.adamEps);
+        }
         S.params[i] = S.params[i] + d * S.nrcConfig.learningRate;
         if (isWeight && IsNanOrInf(S.params[i])) S.params[i] = 0.0f;
         S.deltaParams[i] = 0.0f;
@@ -667,11 +691,25 @@ inline void MrheStep(Scene& S)
 {
     const float border = 100.0f;
     const size_t maxIndex = (size_t)S.mrhe.levelCount * S.mrhe.featureCount * S.mrhe.hashTableSize;
+    float adamC1 = 1.0f, adamC2 = 1.0f;
+    if (S.adam) {
+        if (S.mrFirstMoment.size() != maxIndex) { S.mrFirstMoment.assign(maxIndex, 0.0f); S.mrSecondMoment.assign(maxIndex, 0.0f); }
+        S.mrheSteps++;
+        adamC1 = 1.0f / (1.0f - pow(S.mrheBeta1, float(S.mrheSteps)));
+        adamC2 = 1.0f / (1.0f - pow(S.adamBeta2, float(S.mrheSteps)));
+    }
     for (size_t index = 0; index < maxIndex; index++) {
         float deltaWeight = S.mrDeltaHashTable[index];
         const float weight = S.mrHashTable[index];
         if (IsNanOrInf(deltaWeight)) deltaWeight = border * sign(deltaWeight);
         deltaWeight += -weight * S.mrhe.weightDecay;
+        if (S.adam) {
+            const float m = (S.mrheBeta1 * S.mrFirstMoment[index]) + ((1.0f - S.mrheBeta1) * deltaWeight);
+            const float v = (S.adamBeta2 * S.mrSecondMoment[index]) + ((1.0f - S.adamBeta2) * (deltaWeight * deltaWeight));
+            S.mrFirstMoment[index] = m;
+            S.mrSecondMoment[index] = v;
+            deltaWeight = (m * adamC1) / (sqrt(v * adamC2) + S.adamEps);
+        }
         S.mrHashTable[index] = S.mrHashTable[index] + deltaWeight * S.mrhe.learningRate;
         if (IsNanOrInf(S.mrHashTable[index])) S.mrHashTable[index] = 0.0f;
         S.mrDeltaHashTable[index] = 0.0f;

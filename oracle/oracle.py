@@ -104,6 +104,14 @@ class OracleScene:
         """opt-in: 4 phase-sampled + 4 CDF-importance-sampled env directions per vertex (fwd.frag:715 as commented out there)"""
         self.l.orc_set_env_cdf_half(self.h, C.c_int(1 if on else 0))
 
+    def set_mrhe_fixed(self, on):
+        """opt-in "fixed" preset: grid-space lerp factors on their own axes, per-feature errors, per-level gradient tables"""
+        self.l.orc_set_mrhe_fixed(self.h, C.c_int(1 if on else 0))
+
+    def set_adam(self, on, beta2=0.999, eps=1e-8, mrhe_beta1=0.9):
+        """opt-in "fixed" preset: Adam (second moment + bias correction) in both step shaders; resets the moments"""
+        self.l.orc_set_adam(self.h, C.c_int(1 if on else 0), C.c_float(beta2), C.c_float(eps), C.c_float(mrhe_beta1))
+
     def set_mlp(self, params, lr=0.001, wd=0.0, beta1=0.5):
         p = None if params is None else _f(params)
         assert p is None or p.size == PARAM_COUNT

@@ -123,6 +123,15 @@ void orc_set_envmap(void* sp, int w, int h, const float* rgba, const float* invC
 
 void orc_set_train_env_light(void* sp, int on) { ((Scene*)sp)->trainEnvLight = on != 0; }
 void orc_set_env_cdf_half(void* sp, int on) { ((Scene*)sp)->envCdfHalf = on != 0; }
+// the opt-in "fixed" preset
+void orc_set_mrhe_fixed(void* sp, int on) { ((Scene*)sp)->mrheFixed = on != 0; }
+void orc_set_adam(void* sp, int on, float beta2, float eps, float mrheBeta1)
+{
+    Scene* S = (Scene*)sp;
+    S->adam = on != 0; S->adamBeta2 = beta2; S->adamEps = eps; S->mrheBeta1 = mrheBeta1;
+    S->nrcSteps = S->mrheSteps = 0;
+    S->secondMoment.clear(); S->mrFirstMoment.clear(); S->mrSecondMoment.clear();
+}
 
 void orc_set_mlp(void* sp, const float* params, float lr, float wd, float beta1)
 {
@@ -257,7 +266,7 @@ void orc_train_accumulate(void* sp, const float* pos, const float* dir, const fl
     if (chunk < 32) chunk = 32;
     const long nChunks = (N + chunk - 1) / chunk;
     const size_t tableN = S.mrDeltaHashTable.size();
-    const size_t lvl0 = (size_t)S.mrhe.hashTableSize * 2;   // [A10]: only the first 2*T floats are ever touched
+    const size_t lvl0 = S.mrheFixed ? tableN : (size_t)S.mrhe.hashTableSize * 2;   // [A10]: only the first 2*T floats are ever touched (parity preset)
     long group = nThreads * 4;
     std::vector<std::vector<float>> dP(group, std::vector<float>(kParamCount));
     std::vector<std::vector<float>> dT(group, std::vector<float>(lvl0 <= tableN ? lvl0 : tableN));
