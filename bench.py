@@ -443,12 +443,12 @@ FLOP_INFER = 41344.0         # 2 * 20 672 MAC per query
 FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
 
 
-# ncu --set full capture of the default N=1 workload (profiles/r01k_ncu_summary.md, final round-1 build): DRAM bytes (read + write)
+# ncu --set full capture of the default N=1 workload (profiles/r01n_ncu_summary.md, final round-1 build): DRAM bytes (read + write)
 # and executed warp instructions per launch.  Only quoted when the run IS that workload.
 NCU_R01K = {
-    "k_train_walk": (108.3e6, 148.28e6), "k_light<train>": (195.9e6, 510.50e6), "k_train_combine": (167.9e6, 2.65e6),
-    "k_train_tc": (1.9e6, 5.33e6), "k_render_walk": (187.6e6, 1049.72e6), "k_light<render>": (132.6e6, 523.88e6),
-    "k_render_combine": (120.9e6, 6.98e6), "k_infer_tc": (13.3e6, 108.44e6), "k_composite": (223.1e6, 19.20e6),
+    "k_train_walk": (108.4e6, 148.28e6), "k_light<train>": (196.2e6, 363.06e6), "k_train_combine": (167.9e6, 2.65e6),
+    "k_train_tc": (1.9e6, 5.35e6), "k_render_walk": (188.0e6, 1049.72e6), "k_light<render>": (131.2e6, 434.07e6),
+    "k_render_combine": (120.7e6, 6.98e6), "k_infer_tc": (13.3e6, 110.13e6), "k_composite": (222.8e6, 19.20e6),
 }
 
 
@@ -501,12 +501,12 @@ def finish_b200(args, v):
             "traffic": None, "peak_source": which, "launches": kcount, "avg_launch_ms": kms / max(kcount, 1),
             "share_of_step": kms / max(v["ms_total"], 1e-9),
             "note": "share = this kernel's event-timed duration / step time; the two streams overlap, so shares add up to more than 1. "
-                    "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/r01k), so their HBM fraction is low by construction: "
+                    "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/r01n), so their HBM fraction is low by construction: "
                     "'issue_roofline' is the bound that explains the frame time; per-kernel figures for every kernel are under 'kernels'."}
     default_workload = (world == 1 and (W, H, v["TW"], v["TH"]) == (1920, 1080, 100, 100) and args.precision == "bf16")
     if default_workload and name in NCU_R01K:
         roof["traffic"] = NCU_R01K[name][0]
-        roof["traffic_source"] = "profiles/r01k_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+        roof["traffic_source"] = "profiles/r01n_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     if work is not None and kms > 0:
         ach = work / (kms * 1e-3) / (1e9 if bound == "hbm" else 1e12)
         roof["achieved"] = ach
@@ -532,7 +532,7 @@ def finish_b200(args, v):
         peak_issue = v["ctx"].sm_count * 4 * mhz * 1e6
         issue = {"warp_instructions_per_step": winst, "peak_warp_instructions_per_s": peak_issue,
                  "floor_ms_per_step": winst / peak_issue * 1e3, "frac": (winst / peak_issue * 1e3) / (ms_total / K),
-                 "source": "profiles/r01k_ncu_summary.md (smsp__inst_executed.sum of the nine frame kernels)"}
+                 "source": "profiles/r01n_ncu_summary.md (smsp__inst_executed.sum of the nine frame kernels)"}
     line = {
         "metric": METRIC, "value": units / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": v["Wm"],
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": v["scaling"], "vs_baseline": None,
