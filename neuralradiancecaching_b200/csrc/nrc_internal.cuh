@@ -125,6 +125,11 @@ struct nrc_volume {
     // 2x2x2 corner bricks: cell (i,j,k), i in [-1,nx-1], holds the 8 UNORM8 texels it interpolates,
     // border texels are 0 (CLAMP_TO_BORDER, opaque black): one 8-byte load per density tap.
     uint2* bricks = nullptr;     // [(nz+1)][(ny+1)][(nx+1)]
+    // opt-in: the same UNORM8 texels as a 3-D CUDA array behind a linear-filtering, border-addressing texture object (light taps only)
+    cudaArray_t texArray = nullptr;
+    cudaTextureObject_t tex = 0;
+    bool texTaps = false;
+    uint32_t texMask = 3;        // which light segments use it (NRC_TAPS_TEX_MASK; default all)
     nrc_volume_params params;
 };
 
@@ -153,6 +158,8 @@ struct TraceParams {
     float exitJump;               // length(2*skySize), find_entry_exit
     int nx, ny, nz;
     const uint2* bricks;
+    unsigned long long densityTex;   // cudaTextureObject_t, 0 unless the volume's light taps go through the texture unit (opt-in)
+    uint32_t densityTexMask;         // bit 0: dir / point light segments, bit 1: environment segments
     const float4* env;
     int envW, envH;
     const float* envInvCdfX;      // [envH][envW], non-null only when the CDF half of the env gather is switched on

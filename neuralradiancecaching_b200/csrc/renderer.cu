@@ -359,6 +359,8 @@ static TraceParams make_params(const nrc_renderer* r)
     }
     P.nx = (int)r->vol->nx; P.ny = (int)r->vol->ny; P.nz = (int)r->vol->nz;
     P.bricks = r->vol->bricks;
+    P.densityTex = r->vol->texTaps ? (unsigned long long)r->vol->tex : 0ull;
+    P.densityTexMask = r->vol->texMask;
     P.env = r->env->rgba; P.envW = (int)r->env->w; P.envH = (int)r->env->h;
     const bool cdfHalf = r->env->cdfHalf && r->env->invCdfX && r->env->invCdfY;
     P.envInvCdfX = cdfHalf ? r->env->invCdfX : nullptr; P.envInvCdfY = cdfHalf ? r->env->invCdfY : nullptr;
