@@ -385,7 +385,7 @@ def run_fit(ctx, N, L, torch, steps=10, n=1 << 18):
             "train_step_ms_host_buffers": host_ms, "h2d_bytes_per_step": n * 36, "loss_first_last": [losses[0], losses[-1]], "kernels": kern}
 
 
-def run_mlp_stream(ctx, N, torch, sizes=(1 << 21, 1 << 23), reps=20):
+def run_mlp_stream(ctx, N, torch, sizes=(1 << 19, 1 << 21, 1 << 23), reps=20):
     """The split inference path's two kernels alone, inputs resident in HBM and larger than L2: k_encode_tiles (gather kernel,
     bounded by L2/HBM gathers: 1 036 algorithmic bytes per query) and k_mlp_stream (the six layers on tcgen05, bounded by the
     tensor pipe: 41 344 FLOP per query).  Durations are CUDA events on the launching stream around `reps` back-to-back launches."""
