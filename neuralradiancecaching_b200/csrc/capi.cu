@@ -217,6 +217,8 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream4, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
     NRC_CUDA(cudaStreamCreateWithFlags(&c->streamCopy, cudaStreamNonBlocking));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainWalk, cudaEventDisableTiming));
+    NRC_CUDA(cudaStreamCreateWithPriority(&c->stream5, cudaStreamNonBlocking, prLow));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evRenderWalk, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[0], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[1], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
@@ -233,6 +235,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamSynchronize(c->stream2);
     cudaStreamSynchronize(c->stream3);
     cudaStreamSynchronize(c->stream4);
+    cudaStreamSynchronize(c->stream5);
     cudaStreamSynchronize(c->streamCopy);
     for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
     if (c->pinned) cudaFreeHost(c->pinned);
@@ -244,9 +247,11 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamDestroy(c->stream3);
     cudaEventDestroy(c->evTrainTrace);
     cudaEventDestroy(c->evTrainWalk);
+    cudaEventDestroy(c->evRenderWalk);
     cudaEventDestroy(c->evTrainFree[0]);
     cudaEventDestroy(c->evTrainFree[1]);
     cudaStreamDestroy(c->stream4);
+    cudaStreamDestroy(c->stream5);
     cudaStreamDestroy(c->streamCopy);
     delete c;
     return NRC_OK;

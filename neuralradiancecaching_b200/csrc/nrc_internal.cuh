@@ -60,6 +60,8 @@ struct nrc_ctx {
     cudaStream_t streamCopy = nullptr;    // asynchronous read-back of finished frames
     cudaEvent_t evJoin = nullptr;
     cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
+    cudaStream_t stream5 = nullptr;       // fifth stream: lights + combine of the RENDER trace, beside the next frame's render walk
+    cudaEvent_t evRenderWalk = nullptr;
     cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[2] = {nullptr, nullptr};
     nrc_mlp_precision precision = NRC_MLP_FP32;
     nrc_infer_mode inferMode = NRC_INFER_FUSED;   // nrc_ctx_create reads NRC_INFER_SPLIT

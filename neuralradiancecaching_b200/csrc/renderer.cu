@@ -435,6 +435,7 @@ static nrc_status drain_streams(nrc_ctx* ctx)
     NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->streamCopy));
     return NRC_OK;
@@ -460,12 +461,21 @@ static nrc_status render_pass(nrc_renderer* r)
     NRC_CUDA(cudaMemsetAsync(sc + 4, 0, sizeof(uint32_t), s2));
     NRC_CUDA(cudaMemsetAsync(tapc, 0, sizeof(unsigned long long), s2));
     NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
-    NRC_TRY(launch_light(ctx, s2, P, r->rpool, true, tapc, K_LIGHT_RENDER));
-    NRC_TRY(launch_render_combine(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
-    NRC_CUDA(cudaMemcpyAsync(r->hostScalars, sc, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s2));
-    NRC_CUDA(cudaEventRecord(r->evScalars, s2));
-    if (s2 != ctx->stream) {
-        NRC_CUDA(cudaEventRecord(ctx->evJoin, s2));
+    // NRC_RENDER_LIGHT_STREAM=1: lights + combine on a stream of their own (as on the train side), so that the NEXT frame's render
+    // walk, which fills the other buffer set, may start while this frame's lights are still running
+    static int lightStream = -1;
+    if (lightStream < 0) { const char* e = getenv("NRC_RENDER_LIGHT_STREAM"); lightStream = (e && atoi(e)) ? 1 : 0; }
+    cudaStream_t sl = (lightStream && s2 != ctx->stream) ? ctx->stream5 : s2;
+    if (sl != s2) {
+        NRC_CUDA(cudaEventRecord(ctx->evRenderWalk, s2));
+        NRC_CUDA(cudaStreamWaitEvent(sl, ctx->evRenderWalk, 0));
+    }
+    NRC_TRY(launch_light(ctx, sl, P, r->rpool, true, tapc, K_LIGHT_RENDER));
+    NRC_TRY(launch_render_combine(ctx, sl, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
+    NRC_CUDA(cudaMemcpyAsync(r->hostScalars, sc, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, sl));
+    NRC_CUDA(cudaEventRecord(r->evScalars, sl));
+    if (sl != ctx->stream) {
+        NRC_CUDA(cudaEventRecord(ctx->evJoin, sl));
         NRC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->evJoin, 0));
     }
     if (r->lastInfer) NRC_TRY(infer_queries(r, ctx->stream));

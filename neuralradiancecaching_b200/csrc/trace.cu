@@ -783,7 +783,9 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
 {
     // the vertex count lives on the device: a grid-stride launch sized for the machine, not for the count
     unsigned want = (pool.cap + 127) / 128;
-    unsigned cap = (unsigned)ctx->smCount * 16;
+    static int perSm = -1;   // NRC_LIGHT_BLOCKS_PER_SM: grid cap of the grid-stride light kernels (default 16 = two waves of 8)
+    if (perSm < 0) { const char* e = getenv("NRC_LIGHT_BLOCKS_PER_SM"); perSm = e ? atoi(e) : 16; if (perSm < 1) perSm = 1; }
+    unsigned cap = (unsigned)ctx->smCount * (unsigned)perSm;
     unsigned blocks = want < cap ? want : cap;
     if (blocks == 0) return NRC_OK;
     static int mb = -1;
