@@ -191,6 +191,12 @@ NRC_API size_t nrc_mrhe_grad_extent(nrc_mrhe* mrhe);
 NRC_API nrc_status nrc_mrhe_set_fixed_mode(nrc_mrhe* mrhe, int on);
 NRC_API nrc_status nrc_mlp_set_adam(nrc_mlp* mlp, int on, float beta2, float eps);
 NRC_API nrc_status nrc_mrhe_set_adam(nrc_mrhe* mrhe, int on, float beta1, float beta2, float eps);
+/* Adam moments and step counts, for checkpoints ([h|d] float arrays of 20 995 / L*T*F elements; any pointer may be NULL).  The MLP's
+ * first moment is the reference's momentum arena (nrc_mlp_get_params / nrc_mlp_set_state).  NRC_ERR_INVALID unless Adam is on. */
+NRC_API nrc_status nrc_mlp_get_adam_state(nrc_mlp* mlp, float* second, uint32_t* steps);
+NRC_API nrc_status nrc_mlp_set_adam_state(nrc_mlp* mlp, const float* second, uint32_t steps);
+NRC_API nrc_status nrc_mrhe_get_adam_state(nrc_mrhe* mrhe, float* m1, float* m2, uint32_t* steps);
+NRC_API nrc_status nrc_mrhe_set_adam_state(nrc_mrhe* mrhe, const float* m1, const float* m2, uint32_t steps);
 
 /* ---- stand-alone operators (what the reference runs inside its shaders; used by parity tests and bench) ---- */
 /* EncodePosMrhe (nrc-train.comp:266-339): pos[N][3] -> feat[N][32]; idx[N][128] (level*8+corner) optional. */

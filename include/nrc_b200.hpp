@@ -419,6 +419,8 @@ private:
 
 // ---- checkpoint of the learnt state (the reference has none).  Same file layout as
 // neuralradiancecaching_b200/checkpoint.py: "NRCB200\0", u32 {version, nParams, nTables, L, T, F}, then float32 params, momentum, tables.
+// Version 2 (written only when Adam of the fixed preset is on) appends u32 flags {1 MLP, 2 tables}, then per set bit u32 steps and
+// the moments (MLP: second; tables: first, second).  LoadCheckpoint restores them into objects that have Adam switched on.
 inline void SaveCheckpoint(const std::string& path, const NeuralRadianceCache& nrc, const MRHE& mrhe)
 {
     const uint32_t* sh = mrhe.GetShape();
@@ -427,9 +429,23 @@ inline void SaveCheckpoint(const std::string& path, const NeuralRadianceCache& n
     Check(nrc_mrhe_get_tables(mrhe.Get(), t.data(), nullptr), "nrc_mrhe_get_tables");
     FILE* f = std::fopen(path.c_str(), "wb");
     if (!f) throw std::runtime_error("SaveCheckpoint: cannot open " + path);
-    const uint32_t head[6] = {1u, (uint32_t)p.size(), (uint32_t)t.size(), sh[0], sh[1], sh[2]};
+    uint32_t stepsMlp = 0, stepsTab = 0;
+    const uint32_t flags = (nrc_mlp_get_adam_state(nrc.Get(), nullptr, &stepsMlp) == NRC_OK ? 1u : 0u) |
+                           (nrc_mrhe_get_adam_state(mrhe.Get(), nullptr, nullptr, &stepsTab) == NRC_OK ? 2u : 0u);
+    std::vector<float> second, m1, m2;
+    if (flags & 1u) { second.resize(p.size()); Check(nrc_mlp_get_adam_state(nrc.Get(), second.data(), nullptr), "nrc_mlp_get_adam_state"); }
+    if (flags & 2u) {
+        m1.resize(t.size()); m2.resize(t.size());
+        Check(nrc_mrhe_get_adam_state(mrhe.Get(), m1.data(), m2.data(), nullptr), "nrc_mrhe_get_adam_state");
+    }
+    const uint32_t head[6] = {flags ? 2u : 1u, (uint32_t)p.size(), (uint32_t)t.size(), sh[0], sh[1], sh[2]};
     bool ok = std::fwrite("NRCB200\0", 1, 8, f) == 8 && std::fwrite(head, 4, 6, f) == 6 && std::fwrite(p.data(), 4, p.size(), f) == p.size() &&
               std::fwrite(m.data(), 4, m.size(), f) == m.size() && std::fwrite(t.data(), 4, t.size(), f) == t.size();
+    if (flags) ok = ok && std::fwrite(&flags, 4, 1, f) == 1;
+    if (flags & 1u) ok = ok && std::fwrite(&stepsMlp, 4, 1, f) == 1 && std::fwrite(second.data(), 4, second.size(), f) == second.size();
+    if (flags & 2u)
+        ok = ok && std::fwrite(&stepsTab, 4, 1, f) == 1 && std::fwrite(m1.data(), 4, m1.size(), f) == m1.size() &&
+             std::fwrite(m2.data(), 4, m2.size(), f) == m2.size();
     ok = (std::fclose(f) == 0) && ok;
     if (!ok) throw std::runtime_error("SaveCheckpoint: short write to " + path);
 }
@@ -440,7 +456,7 @@ inline void LoadCheckpoint(const std::string& path, NeuralRadianceCache& nrc, MR
     if (!f) throw std::runtime_error("LoadCheckpoint: cannot open " + path);
     char magic[8];
     uint32_t head[6];
-    bool ok = std::fread(magic, 1, 8, f) == 8 && std::memcmp(magic, "NRCB200\0", 8) == 0 && std::fread(head, 4, 6, f) == 6 && head[0] == 1u;
+    bool ok = std::fread(magic, 1, 8, f) == 8 && std::memcmp(magic, "NRCB200\0", 8) == 0 && std::fread(head, 4, 6, f) == 6 && (head[0] == 1u || head[0] == 2u);
     const uint32_t* sh = mrhe.GetShape();
     ok = ok && head[1] == (uint32_t)NRC_MLP_PARAM_COUNT && head[3] == sh[0] && head[4] == sh[1] && head[5] == sh[2] &&
          head[2] == sh[0] * sh[1] * sh[2];
@@ -450,12 +466,28 @@ inline void LoadCheckpoint(const std::string& path, NeuralRadianceCache& nrc, MR
         ok = std::fread(p.data(), 4, p.size(), f) == p.size() && std::fread(m.data(), 4, m.size(), f) == m.size() &&
              std::fread(t.data(), 4, t.size(), f) == t.size();
     }
+    uint32_t flags = 0, stepsMlp = 0, stepsTab = 0;
+    std::vector<float> second, m1, m2;
+    if (ok && head[0] == 2u) {
+        ok = std::fread(&flags, 4, 1, f) == 1;
+        if (ok && (flags & 1u)) { second.resize(p.size()); ok = std::fread(&stepsMlp, 4, 1, f) == 1 && std::fread(second.data(), 4, second.size(), f) == second.size(); }
+        if (ok && (flags & 2u)) {
+            m1.resize(t.size()); m2.resize(t.size());
+            ok = std::fread(&stepsTab, 4, 1, f) == 1 && std::fread(m1.data(), 4, m1.size(), f) == m1.size() &&
+                 std::fread(m2.data(), 4, m2.size(), f) == m2.size();
+        }
+    }
     std::fclose(f);
     if (!ok) throw std::runtime_error("LoadCheckpoint: " + path + " is not a checkpoint of this cache shape");
     std::vector<float> zp(p.size(), 0.0f), zt(t.size(), 0.0f);
     Check(nrc_mlp_set_params(nrc.Get(), p.data()), "nrc_mlp_set_params");
     Check(nrc_mlp_set_state(nrc.Get(), zp.data(), m.data()), "nrc_mlp_set_state");
     Check(nrc_mrhe_set_tables(mrhe.Get(), t.data(), zt.data()), "nrc_mrhe_set_tables");
+    // Adam state goes into objects that have Adam switched on (SetAdam before LoadCheckpoint); otherwise it is skipped
+    if ((flags & 1u) && nrc_mlp_get_adam_state(nrc.Get(), nullptr, nullptr) == NRC_OK)
+        Check(nrc_mlp_set_adam_state(nrc.Get(), second.data(), stepsMlp), "nrc_mlp_set_adam_state");
+    if ((flags & 2u) && nrc_mrhe_get_adam_state(mrhe.Get(), nullptr, nullptr, nullptr) == NRC_OK)
+        Check(nrc_mrhe_set_adam_state(mrhe.Get(), m1.data(), m2.data(), stepsTab), "nrc_mrhe_set_adam_state");
 }
 
 }   // namespace en

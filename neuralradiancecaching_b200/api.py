@@ -104,6 +104,7 @@ class NeuralRadianceCache:
         self.h = C.c_void_p()
         L.check(L.lib().nrc_mlp_create(ctx.h, C.c_float(learning_rate), C.c_float(weight_decay), C.c_float(beta1),
                                        C.c_uint64(seed), C.byref(self.h)))
+        self.adam = False
 
     def Destroy(self):
         if self.h:
@@ -113,6 +114,17 @@ class NeuralRadianceCache:
     def set_adam(self, on, beta2=0.999, eps=1e-8):
         """opt-in fixed preset: second moment + bias correction in nrc-step (resets moments and step count)"""
         L.check(L.lib().nrc_mlp_set_adam(self.h, C.c_int(1 if on else 0), C.c_float(beta2), C.c_float(eps)))
+        self.adam = bool(on)
+
+    def get_adam_state(self):
+        """(second moment [20995], step count); only while Adam is on"""
+        v = np.empty(L.PARAM_COUNT, np.float32)
+        n = C.c_uint32()
+        L.check(L.lib().nrc_mlp_get_adam_state(self.h, _ptr(v), C.byref(n)))
+        return v, int(n.value)
+
+    def set_adam_state(self, second, steps):
+        L.check(L.lib().nrc_mlp_set_adam_state(self.h, _ptr(_f32(second)), C.c_uint32(steps)))
 
     def ResetStats(self):
         L.check(L.lib().nrc_mlp_reset_stats(self.h))
@@ -170,6 +182,7 @@ class MRHE:
         L.check(L.lib().nrc_mrhe_create(ctx.h, C.c_float(learning_rate), C.c_float(weight_decay), C.c_uint32(level_count),
                                         C.c_uint32(hash_table_size), C.c_uint32(feature_count), C.c_uint32(min_res),
                                         C.c_uint32(max_res), _ptr(res), C.c_uint64(seed), C.byref(self.h)))
+        self.adam = False
 
     def Destroy(self):
         if self.h:
@@ -197,6 +210,17 @@ class MRHE:
     def set_adam(self, on, beta1=0.9, beta2=0.999, eps=1e-8):
         """opt-in fixed preset: Adam in mrhe-step (resets moments and step count)"""
         L.check(L.lib().nrc_mrhe_set_adam(self.h, C.c_int(1 if on else 0), C.c_float(beta1), C.c_float(beta2), C.c_float(eps)))
+        self.adam = bool(on)
+
+    def get_adam_state(self):
+        """(first moment, second moment [L*T*F each], step count); only while Adam is on"""
+        m1, m2 = np.empty(self.count, np.float32), np.empty(self.count, np.float32)
+        n = C.c_uint32()
+        L.check(L.lib().nrc_mrhe_get_adam_state(self.h, _ptr(m1), _ptr(m2), C.byref(n)))
+        return m1, m2, int(n.value)
+
+    def set_adam_state(self, m1, m2, steps):
+        L.check(L.lib().nrc_mrhe_set_adam_state(self.h, _ptr(_f32(m1)), _ptr(_f32(m2)), C.c_uint32(steps)))
 
     def set_tables(self, tables=None, delta=None):
         t = None if tables is None else _f32(tables)

@@ -513,6 +513,41 @@ extern "C" nrc_status nrc_mrhe_set_adam(nrc_mrhe* m, int on, float beta1, float 
     return NRC_OK;
 }
 
+// Adam moments for checkpoints (the first moment of the MLP is the reference's momentum: nrc_mlp_get_params / nrc_mlp_set_state)
+extern "C" nrc_status nrc_mlp_get_adam_state(nrc_mlp* mlp, float* second, uint32_t* steps)
+{
+    NRC_REQUIRE(mlp && mlp->adam && mlp->second, "Adam is not switched on for this MLP");
+    if (second) NRC_TRY(copy_out(mlp->ctx, second, mlp->second, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    if (steps) *steps = mlp->steps;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mlp_set_adam_state(nrc_mlp* mlp, const float* second, uint32_t steps)
+{
+    NRC_REQUIRE(mlp && mlp->adam && mlp->second, "Adam is not switched on for this MLP");
+    if (second) NRC_TRY(copy_in(mlp->ctx, mlp->second, second, NRC_MLP_PARAM_COUNT * sizeof(float)));
+    mlp->steps = steps;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_get_adam_state(nrc_mrhe* m, float* m1, float* m2, uint32_t* steps)
+{
+    NRC_REQUIRE(m && m->adam && m->m1 && m->m2, "Adam is not switched on for these tables");
+    if (m1) NRC_TRY(copy_out(m->ctx, m1, m->m1, m->count * sizeof(float)));
+    if (m2) NRC_TRY(copy_out(m->ctx, m2, m->m2, m->count * sizeof(float)));
+    if (steps) *steps = m->steps;
+    return NRC_OK;
+}
+
+extern "C" nrc_status nrc_mrhe_set_adam_state(nrc_mrhe* m, const float* m1, const float* m2, uint32_t steps)
+{
+    NRC_REQUIRE(m && m->adam && m->m1 && m->m2, "Adam is not switched on for these tables");
+    if (m1) NRC_TRY(copy_in(m->ctx, m->m1, m1, m->count * sizeof(float)));
+    if (m2) NRC_TRY(copy_in(m->ctx, m->m2, m2, m->count * sizeof(float)));
+    m->steps = steps;
+    return NRC_OK;
+}
+
 // ---- stand-alone operators ------------------------------------------------------------------------------------
 extern "C" nrc_status nrc_encode(nrc_mrhe* m, const float* pos, size_t n, float* feat, uint32_t* idx)
 {

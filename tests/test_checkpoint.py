@@ -59,6 +59,114 @@ def test_round_trip_and_rejections(tmp_path):
         K.load_checkpoint(path, c, d)
 
 
+class _AdamMlp(_Mlp):
+    adam = True
+
+    def __init__(self):
+        super().__init__()
+        self.v = np.random.Generator(np.random.PCG64(7)).random(20995).astype(np.float32)
+        self.steps = 17
+
+    def get_adam_state(self):
+        return self.v, self.steps
+
+    def set_adam_state(self, v, steps):
+        self.v, self.steps = np.array(v, np.float32), steps
+
+
+class _AdamTab(_Tab):
+    adam = True
+
+    def __init__(self):
+        super().__init__()
+        g = np.random.Generator(np.random.PCG64(8))
+        self.m1 = g.standard_normal(self.t.size).astype(np.float32)
+        self.m2 = g.random(self.t.size).astype(np.float32)
+        self.steps = 23
+
+    def get_adam_state(self):
+        return self.m1, self.m2, self.steps
+
+    def set_adam_state(self, m1, m2, steps):
+        self.m1, self.m2, self.steps = np.array(m1, np.float32), np.array(m2, np.float32), steps
+
+
+def test_version_2_carries_the_adam_moments(tmp_path):
+    path = str(tmp_path / "ck2.nrc")
+    a, b = _AdamMlp(), _AdamTab()
+    K.save_checkpoint(path, a, b)
+    raw = open(path, "rb").read()
+    assert raw[8:12] == (2).to_bytes(4, "little")
+    c, d = _AdamMlp(), _AdamTab()
+    c.v[:] = 0; c.steps = 0; d.m1[:] = 0; d.m2[:] = 0; d.steps = 0
+    K.load_checkpoint(path, c, d)
+    np.testing.assert_array_equal(c.v.view(np.uint32), a.v.view(np.uint32))
+    np.testing.assert_array_equal(d.m1.view(np.uint32), b.m1.view(np.uint32))
+    np.testing.assert_array_equal(d.m2.view(np.uint32), b.m2.view(np.uint32))
+    assert (c.steps, d.steps) == (17, 23)
+    # objects without Adam take the version-1 part of a version-2 file and leave the moments in the returned dict
+    e, f = _Mlp(), _Tab()
+    got = K.load_checkpoint(path, e, f)
+    np.testing.assert_array_equal(e.p.view(np.uint32), a.p.view(np.uint32))
+    assert got["adam_mlp"][1] == 17 and got["adam_mrhe"][2] == 23
+    # only one of the two with Adam: flags = 2
+    K.save_checkpoint(path, _Mlp(), b)
+    got = K.read_checkpoint(path)
+    assert got["adam_mlp"] is None and got["adam_mrhe"][2] == 23
+    # a version-1 writer output is still version 1 and still loads
+    K.save_checkpoint(path, _Mlp(), _Tab())
+    assert open(path, "rb").read()[8:12] == (1).to_bytes(4, "little")
+    assert K.read_checkpoint(path)["adam_mlp"] is None
+    # truncated trailer
+    K.save_checkpoint(path, a, b)
+    raw = open(path, "rb").read()
+    open(path, "wb").write(raw[:-4])
+    with pytest.raises(ValueError):
+        K.read_checkpoint(path)
+    open(path, "wb").write(raw + b"\0\0\0\0")
+    with pytest.raises(ValueError):
+        K.read_checkpoint(path)
+
+
+@pytest.mark.gpu
+def test_gpu_adam_state_round_trip_continues_bit_exactly(tmp_path):
+    import common as Cm
+    import neuralradiancecaching_b200 as N
+    ctx = N.Context(0)
+
+    def make(s):
+        nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.9, seed=s)
+        m = N.MRHE(ctx, 0.01, 0.0, seed=s + 1)
+        m.set_fixed_mode(True)
+        nrc.set_adam(True)
+        m.set_adam(True)
+        return nrc, m
+    nrc, m = make(3)
+    pos, d = Cm.rand_queries(2000, seed=5)
+    tgt = np.random.Generator(np.random.PCG64(6)).random((2000, 3)).astype(np.float32)
+    for _ in range(3):
+        N.train_accumulate(nrc, m, pos, d, tgt, 1.0 / 2000)
+        N.optimizer_step(nrc, m)
+    path = str(tmp_path / "ck2.nrc")
+    K.save_checkpoint(path, nrc, m)
+    nrc2, m2 = make(11)
+    K.load_checkpoint(path, nrc2, m2)
+    assert nrc2.get_adam_state()[1] == 3 and m2.get_adam_state()[2] == 3
+    for a, b in ((nrc, m), (nrc2, m2)):
+        N.train_accumulate(a, b, pos[:512], d[:512], tgt[:512], 1.0 / 512)
+        N.optimizer_step(a, b)
+    np.testing.assert_array_equal(nrc.get_params()[0].view(np.uint32), nrc2.get_params()[0].view(np.uint32))
+    np.testing.assert_array_equal(m.get_tables()[0].view(np.uint32), m2.get_tables()[0].view(np.uint32))
+    np.testing.assert_array_equal(m.get_adam_state()[1].view(np.uint32), m2.get_adam_state()[1].view(np.uint32))
+    # the getters refuse when Adam is off
+    nrc3 = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.9, seed=1)
+    with pytest.raises(Exception):
+        nrc3.get_adam_state()
+    for o in (nrc, m, nrc2, m2, nrc3):
+        o.Destroy()
+    ctx.destroy()
+
+
 @pytest.mark.gpu
 def test_gpu_round_trip_gives_the_same_cache(tmp_path):
     import common as Cm
