@@ -129,7 +129,7 @@ def test_version_2_carries_the_adam_moments(tmp_path):
 
 
 @pytest.mark.gpu
-def test_gpu_adam_state_round_trip_continues_bit_exactly(tmp_path):
+def test_gpu_adam_state_round_trip_resumes_training(tmp_path):
     import common as Cm
     import neuralradiancecaching_b200 as N
     ctx = N.Context(0)
@@ -152,12 +152,18 @@ def test_gpu_adam_state_round_trip_continues_bit_exactly(tmp_path):
     nrc2, m2 = make(11)
     K.load_checkpoint(path, nrc2, m2)
     assert nrc2.get_adam_state()[1] == 3 and m2.get_adam_state()[2] == 3
+    # the restored state is the saved state, bit for bit
+    np.testing.assert_array_equal(nrc.get_adam_state()[0].view(np.uint32), nrc2.get_adam_state()[0].view(np.uint32))
+    for k in (0, 1):
+        np.testing.assert_array_equal(m.get_adam_state()[k].view(np.uint32), m2.get_adam_state()[k].view(np.uint32))
     for a, b in ((nrc, m), (nrc2, m2)):
         N.train_accumulate(a, b, pos[:512], d[:512], tgt[:512], 1.0 / 512)
         N.optimizer_step(a, b)
-    np.testing.assert_array_equal(nrc.get_params()[0].view(np.uint32), nrc2.get_params()[0].view(np.uint32))
-    np.testing.assert_array_equal(m.get_tables()[0].view(np.uint32), m2.get_tables()[0].view(np.uint32))
-    np.testing.assert_array_equal(m.get_adam_state()[1].view(np.uint32), m2.get_adam_state()[1].view(np.uint32))
+    # one more step on both: the table gradients are float atomics (summation order differs between launches), so a few ulp
+    np.testing.assert_allclose(nrc.get_params()[0], nrc2.get_params()[0], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(m.get_tables()[0], m2.get_tables()[0], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(m.get_adam_state()[1], m2.get_adam_state()[1], rtol=1e-5, atol=1e-12)
+    assert nrc2.get_adam_state()[1] == 4 and m2.get_adam_state()[2] == 4
     # the getters refuse when Adam is off
     nrc3 = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.9, seed=1)
     with pytest.raises(Exception):
