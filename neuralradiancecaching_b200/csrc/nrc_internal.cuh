@@ -43,7 +43,7 @@ enum NrcKernelId {
     K_ENCODE_POS = 0, K_ENCODE_DIR, K_INFER_FP32, K_TRAIN_FP32, K_REDUCE_PARTIALS, K_TRANSPOSE_WEIGHTS, K_NRC_STEP, K_MRHE_STEP,
     K_INIT_NORMAL, K_RENDER_WALK, K_TRAIN_WALK, K_LIGHT_RENDER, K_LIGHT_TRAIN, K_RENDER_COMBINE, K_TRAIN_COMBINE, K_COMPOSITE,
     K_BUILD_BRICKS, K_VOLUME_SAMPLE, K_PACK_RECORDS, K_CDF_ROWS, K_CDF_Y, K_INFER_TC, K_TRAIN_TC, K_PACK_BF16, K_MISC, K_DP_REDUCE_STEP,
-    K_ENCODE_TILES, K_MLP_STREAM,
+    K_ENCODE_TILES, K_MLP_STREAM, K_RENDER_WALK_TAIL,
     K_COUNT
 };
 

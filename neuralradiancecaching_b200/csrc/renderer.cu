@@ -55,7 +55,7 @@ struct nrc_renderer {
     bool trainEnvLight = false;       // opt-in: env-map term in the training targets (train pools then carry random numbers)
     uint32_t* trainCounters = nullptr;
     uint32_t trainAlloc = 0;
-    // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count; train sets: {2,3} and {6,7}
+    // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count, [5] render-walk paths handed to the tail launch; train sets: {2,3} and {6,7}
     uint32_t* scalars = nullptr;
     unsigned long long* taps = nullptr;   // [0], [3] render taps of the two sets; [1], [2] train taps of the two sets
     unsigned long long* totals = nullptr; // [6] running totals (nrc_frame_totals)
@@ -86,7 +86,7 @@ static void free_frame(nrc_renderer* r)
     for (int b = 0; b < 2; b++) {
         nrc_renderer::RenderSet& S = r->rs[b];
         FREE(S.background);
-        FREE(S.rp.head); FREE(S.rp.qposPhase); FREE(S.rp.qdirValid); FREE(S.rp.result); FREE(S.rp.qweight); FREE(S.rp.qslot);
+        FREE(S.rp.head); FREE(S.rp.qposPhase); FREE(S.rp.qdirValid); FREE(S.rp.result); FREE(S.rp.qweight); FREE(S.rp.qslot); FREE(S.rp.spill);
         FREE(S.ql.pos); FREE(S.ql.dir); FREE(S.ql.rgb);
         free_pool(S.rpool);
         r->setPending[b] = false;
@@ -126,6 +126,13 @@ static nrc_status alloc_frame(nrc_renderer* r, uint32_t spp, uint32_t poolCap)
         NRC_CUDA(cudaMalloc(&S.rp.result, paths * sizeof(float4)));
         NRC_CUDA(cudaMalloc(&S.rp.qweight, paths * sizeof(float)));
         NRC_CUDA(cudaMalloc(&S.rp.qslot, paths * sizeof(int)));
+        S.rp.spill = nullptr;                      // state of the paths the head launch of the render walk leaves alive (trace.cu)
+        S.rp.spillStride = 0;
+        S.rp.spillCount = r->scalars + 8 * b + 5;
+        if (spp == 1) {
+            NRC_CUDA(cudaMalloc(&S.rp.spill, px * 5 * sizeof(float4)));
+            S.rp.spillStride = (uint32_t)px;
+        }
         NRC_CUDA(cudaMalloc(&S.ql.pos, paths * 3 * sizeof(float)));
         NRC_CUDA(cudaMalloc(&S.ql.dir, paths * 3 * sizeof(float)));
         NRC_CUDA(cudaMalloc(&S.ql.rgb, paths * 3 * sizeof(float)));
@@ -458,7 +465,7 @@ static nrc_status render_pass(nrc_renderer* r)
     // the composite that last read this set (two frames ago) must be done before the walk overwrites it
     if (s2 != ctx->stream && r->setPending[b]) NRC_CUDA(cudaStreamWaitEvent(s2, r->evSetFree[b], 0));
     NRC_CUDA(cudaMemsetAsync(sc + 0, 0, 2 * sizeof(uint32_t), s2));
-    NRC_CUDA(cudaMemsetAsync(sc + 4, 0, sizeof(uint32_t), s2));
+    NRC_CUDA(cudaMemsetAsync(sc + 4, 0, 2 * sizeof(uint32_t), s2));   // query count, spilled paths of the render walk
     NRC_CUDA(cudaMemsetAsync(tapc, 0, sizeof(unsigned long long), s2));
     NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
     // NRC_RENDER_LIGHT_STREAM=1: lights + combine on a stream of their own (as on the train side), so that the NEXT frame's render

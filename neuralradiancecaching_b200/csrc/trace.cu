@@ -195,10 +195,30 @@ struct ChunkEmitter {
 };
 
 // ---- render walk (nrc-forward.vert:28-40, nrc-forward.frag:757-870 minus lighting and Forward()) ------------------
+// Two launches when spp == 1 and splitAt > 0.  On the bench frame 24 % of the paths end within 12 steps (they terminate into the cache)
+// and 76 % run all 32 (empty space inside the box: a step never covers more than a tenth of the way out), so with one pixel per lane
+// for the whole walk a warp carries 15 % dead lanes through the sphere traces (scripts/walk_divergence.py; ncu: 27 of 32 lanes on
+// the march lines).  The head launch walks `splitAt` steps and appends the state of every path that is still alive to a compacted list
+// (80 bytes per path, one warp-aggregated atomic); the tail launch finishes those with full warps.  The walk itself is the same code
+// on the same state (walk.cuh: render_walk_steps), so every draw and every vertex is what the single launch produces; only the
+// order of the vertices in the pool differs, and nothing reads that order.
+__device__ __forceinline__ void render_path_store(const TraceParams& P, RenderPaths paths, size_t path, int head, const WalkQuery& q)
+{
+    float4 qp = make_float4(0.0f, 0.0f, 0.0f, 0.0f), qd = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (q.valid) {
+        float ph = hg_phase(P.g, -dot3(q.dir, q.lastDir));   // dirPhase (fwd.frag:785)
+        qp = make_float4(q.pos.x, q.pos.y, q.pos.z, ph);
+        qd = make_float4(q.dir.x, q.dir.y, q.dir.z, 1.0f);
+    }
+    paths.head[path] = head;
+    paths.qposPhase[path] = qp;
+    paths.qdirValid[path] = qd;
+}
+
 template <int MB>
 __global__ void __launch_bounds__(128, MB) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
                                                      uint32_t spp, VertexPool pool, RenderPaths paths, float4* __restrict__ background,
-                                                     uint32_t* __restrict__ counters)
+                                                     uint32_t* __restrict__ counters, int splitAt)
 {
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
     if (local >= rows * P.width) return;
@@ -218,23 +238,63 @@ __global__ void __launch_bounds__(128, MB) k_render_walk(const __grid_constant__
     background[pix] = make_float4(envc.x, envc.y, envc.z, miss ? 1.0f : 0.0f);
     PoolEmitter em;
     em.pool = pool;
+    const int stepsHere = splitAt > 0 ? splitAt : NRC_RENDER_WALK_STEPS;   // splitAt > 0 only with spp == 1 (launch_render_walk)
     for (uint32_t s = 0; s < spp; s++) {
         size_t path = pix * spp + s;
         em.begin();
-        float4 qp = make_float4(0.0f, 0.0f, 0.0f, 0.0f), qd = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        WalkQuery q;
+        q.valid = false;
         if (!miss) {
-            WalkQuery q;
-            render_walk_path(W, box, grid, entry, rd, rng, em, wc, q);
-            if (q.valid) {
-                float ph = hg_phase(P.g, -dot3(q.dir, q.lastDir));   // dirPhase (fwd.frag:785)
-                qp = make_float4(q.pos.x, q.pos.y, q.pos.z, ph);
-                qd = make_float4(q.dir.x, q.dir.y, q.dir.z, 1.0f);
+            WalkState ws = walk_state_begin(entry, rd);
+            bool alive = render_walk_steps(W, box, grid, ws, 0, stepsHere, rng, em, wc, q);
+            if (alive && splitAt > 0) {
+                const unsigned m = __activemask(), lane = threadIdx.x & 31u;
+                const int leader = __ffs(m) - 1;
+                unsigned base = 0u;
+                if ((int)lane == leader) base = atomicAdd(paths.spillCount, (unsigned)__popc(m));
+                const size_t slot = __shfl_sync(m, base, leader) + __popc(m & ((1u << lane) - 1u));
+                const size_t n = paths.spillStride;
+                paths.spill[slot] = make_float4(ws.cur.x, ws.cur.y, ws.cur.z, ws.termProb);
+                paths.spill[n + slot] = make_float4(ws.last.x, ws.last.y, ws.last.z, rng.pre);
+                paths.spill[2 * n + slot] = make_float4(ws.dir.x, ws.dir.y, ws.dir.z, rng.prePre);
+                paths.spill[3 * n + slot] = make_float4(ws.lastDir.x, ws.lastDir.y, ws.lastDir.z, __uint_as_float((unsigned)pix));
+                paths.spill[4 * n + slot] = make_float4(__int_as_float(em.head), __int_as_float(em.prev), __uint_as_float(rng.draws),
+                                                        __uint_as_float(wc.lit));
+                return;   // the tail launch writes this path's outputs
             }
         }
-        paths.head[path] = em.head;
-        paths.qposPhase[path] = qp;
-        paths.qdirValid[path] = qd;
+        render_path_store(P, paths, path, em.head, q);
     }
+    if (counters) reinterpret_cast<uint4*>(counters)[pix] = make_uint4(rng.draws, wc.lit, wc.steps, wc.emitted);
+}
+
+template <int MB>
+__global__ void __launch_bounds__(128, MB) k_render_walk_tail(const __grid_constant__ TraceParams P, VertexPool pool, RenderPaths paths,
+                                                          uint32_t* __restrict__ counters, int splitAt)
+{
+    const size_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *paths.spillCount) return;
+    const size_t n = paths.spillStride;
+    const float4 a = paths.spill[t], b = paths.spill[n + t], c = paths.spill[2 * n + t], d = paths.spill[3 * n + t], e = paths.spill[4 * n + t];
+    const Box box = make_box(P);
+    const Grid grid = make_grid(P);
+    const WalkParams W = make_walk(P);
+    WalkState ws;
+    ws.cur = mk3(a.x, a.y, a.z); ws.termProb = a.w;
+    ws.last = mk3(b.x, b.y, b.z);
+    ws.dir = mk3(c.x, c.y, c.z);
+    ws.lastDir = mk3(d.x, d.y, d.z);
+    Rng rng;
+    rng.pre = b.w; rng.prePre = c.w; rng.draws = __float_as_uint(e.z);
+    const size_t pix = __float_as_uint(d.w);
+    PoolEmitter em;
+    em.pool = pool;
+    em.head = __float_as_int(e.x); em.prev = __float_as_int(e.y);
+    WalkCounters wc = {__float_as_uint(e.w), (unsigned)splitAt, 0u, 0u};
+    WalkQuery q;
+    q.valid = false;
+    render_walk_steps(W, box, grid, ws, splitAt, NRC_RENDER_WALK_STEPS, rng, em, wc, q);
+    render_path_store(P, paths, pix, em.head, q);
     if (counters) reinterpret_cast<uint4*>(counters)[pix] = make_uint4(rng.draws, wc.lit, wc.steps, wc.emitted);
 }
 
@@ -728,15 +788,22 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
     if (n == 0) return NRC_OK;
     static int mb = -1;
     if (mb < 0) { const char* e = getenv("NRC_RWALK_MB"); mb = e ? atoi(e) : 8; }
-    if (mb == 8)
-        NRC_LAUNCH(ctx, st, K_RENDER_WALK,
-                   (k_render_walk<8><<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters)));
-    else if (mb == 6)
-        NRC_LAUNCH(ctx, st, K_RENDER_WALK,
-                   (k_render_walk<6><<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters)));
-    else
-        NRC_LAUNCH(ctx, st, K_RENDER_WALK,
-                   (k_render_walk<7><<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters)));
+    // steps in the head launch; 0 = the whole walk in one launch.  Read at every launch (tests switch it)
+    const char* se = getenv("NRC_RWALK_SPLIT");
+    int splitEnv = se ? atoi(se) : 10;
+    if (splitEnv < 0 || splitEnv >= NRC_RENDER_WALK_STEPS) splitEnv = 0;
+    // the caller zeroes *paths.spillCount on this stream before the call (renderer.cu: render_pass)
+    const int split = (spp == 1 && paths.spill != nullptr && paths.spillStride >= n) ? splitEnv : 0;
+    const unsigned blocks = (n + 127) / 128;
+#define RWALK_CASE(MBV)                                                                                                                    \
+    NRC_LAUNCH(ctx, st, K_RENDER_WALK,                                                                                                     \
+               (k_render_walk<MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split))); \
+    if (split > 0)                                                                                                                         \
+        NRC_LAUNCH(ctx, st, K_RENDER_WALK_TAIL, (k_render_walk_tail<MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, paths, counters, split)));
+    if (mb == 8) { RWALK_CASE(8) }
+    else if (mb == 6) { RWALK_CASE(6) }
+    else { RWALK_CASE(7) }
+#undef RWALK_CASE
     return NRC_OK;
 }
 

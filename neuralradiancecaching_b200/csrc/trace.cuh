@@ -35,6 +35,10 @@ struct RenderPaths {
     float4* result;       // L.rgb (non-NN part), T          (combine)
     float* qweight;       // T * dirPhase                     (combine)
     int* qslot;           // index into the compacted query list or -1
+    // two-launch render walk (trace.cu): paths still alive after the head launch, compacted; 6 float4 planes of spillStride records
+    float4* spill;
+    uint32_t* spillCount;
+    uint32_t spillStride;
 };
 
 struct QueryList {

@@ -48,44 +48,69 @@ NRC_HD void render_ray(const WalkParams& P, unsigned px, unsigned py, f3& ro, f3
     rng.draws = 0;
 }
 
-#if defined(__CUDACC__)
-#pragma nv_exec_check_disable
-#endif
 // TracePath(ro, rd, useNN) of the render shader without lighting and Forward(): walks from `entry`, calls
 // em.vertex(pos, density, dir, last, rands16) for every lit vertex (false = pool full, stop) and fills `q` when the
 // path terminates into the cache.
+//
+// The loop is resumable: render_walk_steps runs steps [i0, i1) on a WalkState and says whether the path is still alive, so that
+// the render kernel can stop after a few steps, compact the surviving paths and finish them in a second launch with full warps
+// (trace.cu).  render_walk_path is the whole walk in one call (host emulation, spp > 1).
+struct WalkState { f3 cur, last, dir, lastDir; float termProb; };
+
+NRC_HD WalkState walk_state_begin(f3 entry, f3 rd)
+{
+    WalkState s;
+    s.cur = entry; s.last = entry; s.dir = rd; s.lastDir = mk3(0.0f, 0.0f, 0.0f); s.termProb = 1.0f;
+    return s;
+}
+
+#if defined(__CUDACC__)
+#pragma nv_exec_check_disable
+#endif
+template <class Emitter>
+NRC_HD bool render_walk_steps(const WalkParams& P, const Box& box, const Grid& grid, WalkState& s, int i0, int i1, Rng& rng, Emitter& em,
+                              WalkCounters& wc, WalkQuery& q)
+{
+    const bool useNN = (P.useNN == 1u);
+    for (int i = i0; i < i1; i++) {
+        wc.steps++;
+        float density = grid_density(grid, s.cur);
+        if (density > 0.0f) {
+            if (useNN) {
+                if (rng_next(rng) > s.termProb) {
+                    if (P.showNonNN == 0u) {
+                        q.pos = s.cur; q.dir = s.dir; q.lastDir = s.lastDir; q.valid = true;   // A19: lastDir = 0 before the first scatter
+                        wc.emitted++;
+                    }
+                    return false;
+                }
+                s.termProb = NRC_MUL(s.termProb, 0.5f);
+            }
+            float r[16];
+            for (int k = 0; k < 16; k++) r[k] = rng_next(rng);   // the 8 NewRayDir calls of SampleHdrEnvMap (fwd.frag:717-725)
+            if (!em.vertex(s.cur, density, s.dir, s.last, r)) return false;
+            wc.lit++;
+            s.last = s.cur;
+            s.lastDir = s.dir;
+            s.dir = new_ray_dir(s.dir, P.g, rng);
+        }
+        s.cur = walk_advance(box, s.cur, s.dir, rng, wc.sdf);
+    }
+    return true;
+}
+
+#define NRC_RENDER_WALK_STEPS 32
+
+#if defined(__CUDACC__)
+#pragma nv_exec_check_disable
+#endif
 template <class Emitter>
 NRC_HD void render_walk_path(const WalkParams& P, const Box& box, const Grid& grid, f3 entry, f3 rd, Rng& rng, Emitter& em,
                              WalkCounters& wc, WalkQuery& q)
 {
-    const bool useNN = (P.useNN == 1u);
-    f3 cur = entry, last = entry, dir = rd, lastDir = mk3(0.0f, 0.0f, 0.0f);
-    float termProb = 1.0f;
+    WalkState s = walk_state_begin(entry, rd);
     q.valid = false;
-    for (int i = 0; i < 32; i++) {
-        wc.steps++;
-        float density = grid_density(grid, cur);
-        if (density > 0.0f) {
-            if (useNN) {
-                if (rng_next(rng) > termProb) {
-                    if (P.showNonNN == 0u) {
-                        q.pos = cur; q.dir = dir; q.lastDir = lastDir; q.valid = true;   // A19: lastDir = 0 before the first scatter
-                        wc.emitted++;
-                    }
-                    return;
-                }
-                termProb = NRC_MUL(termProb, 0.5f);
-            }
-            float r[16];
-            for (int k = 0; k < 16; k++) r[k] = rng_next(rng);   // the 8 NewRayDir calls of SampleHdrEnvMap (fwd.frag:717-725)
-            if (!em.vertex(cur, density, dir, last, r)) return;
-            wc.lit++;
-            last = cur;
-            lastDir = dir;
-            dir = new_ray_dir(dir, P.g, rng);
-        }
-        cur = walk_advance(box, cur, dir, rng, wc.sdf);
-    }
+    render_walk_steps(P, box, grid, s, 0, NRC_RENDER_WALK_STEPS, rng, em, wc, q);
 }
 
 // main() of nrc-train.comp (:1228-1259) + the vertex-picking walk of TracePathAndLearn (:1173-1215): returns the

@@ -76,6 +76,50 @@ void emu_render_walk(const float* invProjView, const float* camPos, const float*
     }
 }
 
+// Divergence study (scripts/walk_divergence.py): per pixel {walk steps, SDF evaluations of the walk, SDF evaluations of the camera ray}
+void emu_render_walk_cost(const float* invProjView, const float* camPos, const float* random2, float g, unsigned useNN, unsigned W, unsigned H,
+                          float densityFactor, int nx, int ny, int nz, unsigned* cost, unsigned char* perStep)
+{
+    WalkParams P; Box box; Grid grid;
+    setup(invProjView, camPos, random2, g, useNN, 0, W, H, 1, 1, densityFactor, nx, ny, nz, P, box, grid);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (long py = 0; py < (long)H; py++) for (unsigned px = 0; px < W; px++) {
+        f3 ro, rd; Rng rng;
+        render_ray(P, px, (unsigned)py, ro, rd, rng);
+        WalkCounters wc = {0, 0, 0, 0};
+        f3 entry, ex;
+        find_entry_exit(box, ro, rd, entry, ex, wc.sdf);
+        unsigned cam = wc.sdf;
+        bool miss = sky_sdf(box, entry) > NRC_MAX_RAY_DISTANCE;
+        WalkQuery q; q.valid = false;
+        RecEmitter em{nullptr, 0};
+        size_t p = (size_t)py * W + px;
+        if (!miss && perStep) {
+            // the same walk one step at a time: SDF evaluations of step i (render_walk_path's loop body, lighting left out)
+            const bool nn = (P.useNN == 1u);
+            f3 cur = entry, dir = rd;
+            float termProb = 1.0f;
+            for (int i = 0; i < 32; i++) {
+                wc.steps++;
+                float density = grid_density(grid, cur);
+                if (density > 0.0f) {
+                    if (nn) {
+                        if (rng_next(rng) > termProb) break;
+                        termProb = NRC_MUL(termProb, 0.5f);
+                    }
+                    for (int k = 0; k < 16; k++) rng_next(rng);
+                    wc.lit++;
+                    dir = new_ray_dir(dir, P.g, rng);
+                }
+                unsigned before = wc.sdf;
+                cur = walk_advance(box, cur, dir, rng, wc.sdf);
+                perStep[32 * p + i] = (unsigned char)(wc.sdf - before > 255 ? 255 : wc.sdf - before);
+            }
+        } else if (!miss) render_walk_path(P, box, grid, entry, rd, rng, em, wc, q);
+        cost[4 * p] = wc.steps; cost[4 * p + 1] = wc.sdf - cam; cost[4 * p + 2] = cam; cost[4 * p + 3] = wc.lit;
+    }
+}
+
 // records[n][6] = pos, dir ; counters[n][3] = draws, lit, steps
 void emu_train_walk(const float* invProjView, const float* camPos, const float* random2, float g, unsigned trainW, unsigned trainH,
                     float densityFactor, int nx, int ny, int nz, float* records, unsigned* counters, int envLight)

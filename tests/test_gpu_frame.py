@@ -75,6 +75,37 @@ def test_render_pass_parity(N, ctx, use_nn):
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
 
 
+def test_split_render_walk_is_the_single_launch_walk(N, ctx, monkeypatch):
+    """NRC_RWALK_SPLIT: the head launch walks k steps, the tail launch finishes the compacted survivors.  Every split point gives the
+    counters, queries and frame of the single-launch walk (k = 0), bit for bit; the default (10) is what the other tests run with."""
+    W, H = 160, 96
+    cfg = Cm.scene_cfg(use_nn=1, aspect=W / H)
+    got = {}
+    for k in (0, 1, 10, 31):
+        monkeypatch.setenv("NRC_RWALK_SPLIT", str(k))
+        r, nrc, m, vol = build(N, ctx, cfg, W, H, 8, 8)
+        r.FrameRender()
+        ctx.sync()
+        cnt, qry = r.read_render_probes()
+        got[k] = (cnt.copy(), qry.copy(), r.read_frame().copy(), r.stats())
+        r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+    monkeypatch.delenv("NRC_RWALK_SPLIT")
+    cnt0, qry0, frame0, st0 = got[0]
+    assert cnt0[..., 2].max() == 32 and (cnt0[..., 2] < 8).any()          # both kinds of path are in the frame
+    for k in (1, 10, 31):
+        cnt, qry, frame, st = got[k]
+        np.testing.assert_array_equal(cnt, cnt0)
+        np.testing.assert_array_equal(qry.view(np.uint32), qry0.view(np.uint32))
+        np.testing.assert_array_equal(frame.view(np.uint32), frame0.view(np.uint32))
+        assert st["density_taps"] == st0["density_taps"] and st["infer_queries"] == st0["infer_queries"]
+    # against the oracle as well, at the default split
+    sc = Cm.oracle_scene(cfg)
+    orgba, ocnt, oqry = sc.render(W, H)
+    np.testing.assert_array_equal(got[10][0][..., 0], ocnt[..., 0])
+    np.testing.assert_array_equal(got[10][0][..., 2], ocnt[..., 3])
+    assert Cm.psnr(got[10][2], orgba) >= PSNR_MIN
+
+
 def test_train_pass_parity(N, ctx):
     tw, th = 20, 12
     cfg = Cm.scene_cfg()
