@@ -443,12 +443,13 @@ FLOP_INFER = 41344.0         # 2 * 20 672 MAC per query
 FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
 
 
-# ncu --set full capture of the default N=1 workload (profiles/r01n_ncu_summary.md, final round-1 build): DRAM bytes (read + write)
+# ncu --set full capture of the default N=1 workload (profiles/r01p_ncu_summary.md, final round-1 build): DRAM bytes (read + write)
 # and executed warp instructions per launch.  Only quoted when the run IS that workload.
 NCU_R01K = {
-    "k_train_walk": (108.4e6, 148.28e6), "k_light<train>": (196.2e6, 363.06e6), "k_train_combine": (167.9e6, 2.65e6),
-    "k_train_tc": (1.9e6, 5.35e6), "k_render_walk": (188.0e6, 1049.72e6), "k_light<render>": (131.2e6, 434.07e6),
-    "k_render_combine": (120.7e6, 6.98e6), "k_infer_tc": (13.3e6, 110.13e6), "k_composite": (222.8e6, 19.20e6),
+    "k_train_walk": (111.3e6, 142.76e6), "k_light<train>": (196.4e6, 362.48e6), "k_train_combine": (168.1e6, 2.65e6),
+    "k_train_tc": (1.9e6, 5.35e6), "k_render_walk": (240.8e6, 423.18e6), "k_render_walk_tail": (199.5e6, 508.84e6),
+    "k_light<render>": (132.9e6, 424.43e6), "k_render_combine": (119.2e6, 6.98e6), "k_infer_tc": (13.3e6, 110.13e6),
+    "k_composite": (223.5e6, 19.13e6),
 }
 
 
@@ -464,7 +465,7 @@ def kernel_work(name, tot, pixels, table_floats):
         return "hbm", tot["infer_queries"] * (1036.0 + 128.0), "GB/s"      # 1 164 B/query stand-alone encode
     if name in ("k_train_fp32", "k_train_tc"):
         return "tensor", tot["train_samples"] * FLOP_TRAIN, "TFLOP/s"
-    if name == "k_render_walk":
+    if name == "k_render_walk":      # head launch: background + path outputs per pixel, the vertices it emits; the spill is not algorithmic
         return "hbm", pixels * 68.0 + tot["render_vertices"] * 112.0, "GB/s"
     if name == "k_train_walk":
         return "hbm", tot["train_samples"] * 72.0 + tot["train_vertices"] * 48.0, "GB/s"
@@ -501,12 +502,12 @@ def finish_b200(args, v):
             "traffic": None, "peak_source": which, "launches": kcount, "avg_launch_ms": kms / max(kcount, 1),
             "share_of_step": kms / max(v["ms_total"], 1e-9),
             "note": "share = this kernel's event-timed duration / step time; the two streams overlap, so shares add up to more than 1. "
-                    "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/r01n), so their HBM fraction is low by construction: "
+                    "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/r01p), so their HBM fraction is low by construction: "
                     "'issue_roofline' is the bound that explains the frame time; per-kernel figures for every kernel are under 'kernels'."}
     default_workload = (world == 1 and (W, H, v["TW"], v["TH"]) == (1920, 1080, 100, 100) and args.precision == "bf16")
     if default_workload and name in NCU_R01K:
         roof["traffic"] = NCU_R01K[name][0]
-        roof["traffic_source"] = "profiles/r01n_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+        roof["traffic_source"] = "profiles/r01p_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     if work is not None and kms > 0:
         ach = work / (kms * 1e-3) / (1e9 if bound == "hbm" else 1e12)
         roof["achieved"] = ach
@@ -532,7 +533,7 @@ def finish_b200(args, v):
         peak_issue = v["ctx"].sm_count * 4 * mhz * 1e6
         issue = {"warp_instructions_per_step": winst, "peak_warp_instructions_per_s": peak_issue,
                  "floor_ms_per_step": winst / peak_issue * 1e3, "frac": (winst / peak_issue * 1e3) / (ms_total / K),
-                 "source": "profiles/r01n_ncu_summary.md (smsp__inst_executed.sum of the nine frame kernels)"}
+                 "source": "profiles/r01p_ncu_summary.md (smsp__inst_executed.sum of the ten frame kernels)"}
     line = {
         "metric": METRIC, "value": units / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": v["Wm"],
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": v["scaling"], "vs_baseline": None,
