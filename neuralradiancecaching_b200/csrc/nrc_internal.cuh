@@ -127,6 +127,10 @@ struct nrc_volume {
     // 2x2x2 corner bricks: cell (i,j,k), i in [-1,nx-1], holds the 8 UNORM8 texels it interpolates,
     // border texels are 0 (CLAMP_TO_BORDER, opaque black): one 8-byte load per density tap.
     uint2* bricks = nullptr;     // [(nz+1)][(ny+1)][(nx+1)]
+    // occupancy of the bricks for the light kernels: bit r = some brick of cells [r << occShift, (r+1) << occShift) (linear index,
+    // runs along x) is non-zero.  A tap whose run is empty needs no load.  occShift = 0: not built (switched off or volume too large)
+    uint32_t* occ = nullptr;
+    uint32_t occWords = 0, occShift = 0;
     // opt-in: the same UNORM8 texels as a 3-D CUDA array behind a linear-filtering, border-addressing texture object (light taps only)
     cudaArray_t texArray = nullptr;
     cudaTextureObject_t tex = 0;
@@ -160,6 +164,8 @@ struct TraceParams {
     float exitJump;               // length(2*skySize), find_entry_exit
     int nx, ny, nz;
     const uint2* bricks;
+    const uint32_t* occ;             // brick-run occupancy bits (nrc_volume), null = off
+    uint32_t occWords, occShift;
     unsigned long long densityTex;   // cudaTextureObject_t, 0 unless the volume's light taps go through the texture unit (opt-in)
     uint32_t densityTexMask;         // bit 0: dir / point light segments, bit 1: environment segments
     const float4* env;

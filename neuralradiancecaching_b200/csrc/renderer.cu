@@ -366,6 +366,7 @@ static TraceParams make_params(const nrc_renderer* r)
     }
     P.nx = (int)r->vol->nx; P.ny = (int)r->vol->ny; P.nz = (int)r->vol->nz;
     P.bricks = r->vol->bricks;
+    P.occ = r->vol->occ; P.occWords = r->vol->occWords; P.occShift = r->vol->occShift;
     P.densityTex = r->vol->texTaps ? (unsigned long long)r->vol->tex : 0ull;
     P.densityTexMask = r->vol->texMask;
     P.env = r->env->rgba; P.envW = (int)r->env->w; P.envH = (int)r->env->h;

@@ -23,6 +23,7 @@ extern "C" nrc_status nrc_volume_create(nrc_ctx* ctx, const float* density, uint
     const void* dgrid;
     NRC_TRY(nrc_stage_in(ctx, 5, density, (size_t)nx * ny * nz * sizeof(float), &dgrid));
     NRC_TRY(launch_build_bricks(v, (const float*)dgrid));
+    NRC_TRY(launch_build_occupancy(v));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     *out = v;
     if (const char* e = getenv("NRC_TAPS_TEX")) {
@@ -90,6 +91,7 @@ extern "C" nrc_status nrc_volume_destroy(nrc_volume* v)
     if (v->tex) cudaDestroyTextureObject(v->tex);
     if (v->texArray) cudaFreeArray(v->texArray);
     cudaFree(v->bricks);
+    cudaFree(v->occ);
     delete v;
     return NRC_OK;
 }

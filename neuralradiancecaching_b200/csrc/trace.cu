@@ -352,6 +352,7 @@ struct TapCtx {
     const uint2* bricks;
     unsigned long long tex;         // cudaTextureObject_t of the UNORM8 grid (0 = off): opt-in hardware-filtered light taps
     unsigned texMask;               // bit 0: dir / point light segments, bit 1: environment segments
+    unsigned occShift;              // cells per occupancy bit = 1 << occShift (tap_load<true>)
 };
 
 #define TAP_MAGIC 12582912.0f   // 1.5 * 2^23: float bits of (k + TAP_MAGIC) = 0x4B400000 + k for integer |k| < 2^22
@@ -368,6 +369,7 @@ __device__ __forceinline__ TapCtx make_tap(const TraceParams& P)
     t.bricks = P.bricks;
     t.tex = P.densityTex;
     t.texMask = P.densityTexMask;
+    t.occShift = P.occShift;
     return t;
 }
 
@@ -457,7 +459,21 @@ __device__ __forceinline__ f2pair tap_blend2(uint2 q0, uint2 q1, f2pair a, f2pai
 // the texture unit: border addressing = clamp-to-border(0), the hardware's trilinear filter with 9-bit fixed-point weights instead of
 // the fp32 lerps: ~7 instructions per tap instead of 32, values within ~1e-4 relative.  The vertex-to-vertex segment never takes this
 // path: its `== 1.0` outcome is control flow (see above) and must be the exact fp32 result.
-template <int COUNT>
+// OCC: the block holds the volume's brick-run occupancy bits in shared memory (k_light copies them in): a tap whose run of cells has
+// no non-zero brick skips its load and blends a zero brick -- the same value, one L1/L2 sector request less.
+template <bool OCC>
+__device__ __forceinline__ uint2 tap_load(const TapCtx& t, int c)
+{
+    if (!OCC) return __ldg(t.bricks + c);
+    extern __shared__ uint32_t s_occ[];
+    const unsigned r = (unsigned)c >> t.occShift;
+    const unsigned w = s_occ[r >> 5];
+    uint2 q = make_uint2(0u, 0u);
+    if ((int)__funnelshift_l(0u, w, r) < 0) q = __ldg(t.bricks + c);   // run r is bit 31 - (r & 31) of its word: shifted into the sign
+    return q;
+}
+
+template <int COUNT, bool OCC>
 __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFactor, f3 a, f3 b, unsigned& taps, bool allowTex = false)
 {
     float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
@@ -492,8 +508,8 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
             for (int j = 0; j < TAP_BATCH / 2; j++) {
                 int c0, c1;
                 tap_cell2(t, fma2(fi, du2, u02), fma2(fi, dv2, v02), fma2(fi, ds2, s02), c0, c1, fa[j], fb[j], fc[j]);
-                q[2 * j] = __ldg(t.bricks + c0);
-                q[2 * j + 1] = __ldg(t.bricks + c1);
+                q[2 * j] = tap_load<OCC>(t, c0);
+                q[2 * j + 1] = tap_load<OCC>(t, c1);
                 fi = add2(fi, two);
             }
 #pragma unroll
@@ -529,9 +545,14 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
 
 // MB = resident blocks ptxas must allow: WITHOUT a minimum it chases occupancy and sinks every brick load next to its use (one
 // load in flight per thread, ncu r01f: 35-57 % long-scoreboard); with a register budget it keeps the batch of loads together.
-template <bool RENDER, int MB, bool CDF>
+template <bool RENDER, int MB, bool CDF, bool OCC>
 __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
 {
+    if (OCC) {
+        extern __shared__ uint32_t s_occ[];
+        for (uint32_t i = threadIdx.x; i < P.occWords; i += blockDim.x) s_occ[i] = P.occ[i];
+        __syncthreads();
+    }
     const uint32_t count = min(*pool.count, pool.cap);
     const Box box = make_box(P);
     const TapCtx tc = make_tap(P);
@@ -548,13 +569,13 @@ __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ Trace
             f3 L = mk3(P.dirDir[0], P.dirDir[1], P.dirDir[2]);
             f3 en, ex;
             find_entry_exit(box, pos, s_neg(s_normalize(L)), en, ex, sdf);
-            float T = transmittance<32>(tc, kDensity, pos, ex, taps, (tc.texMask & 1u) != 0);
+            float T = transmittance<32, OCC>(tc, kDensity, pos, ex, taps, (tc.texMask & 1u) != 0);
             float l = T * P.dirStrength * hg_phase(P.g, -dot3(L, dir));
             light.x += l; light.y += l; light.z += l;
         }
         if (P.ptStrength != 0.0f) {    // TracePointLight (fwd.frag:677-688)
             f3 lp = mk3(P.ptPos[0], P.ptPos[1], P.ptPos[2]);
-            float T = transmittance<32>(tc, kDensity, lp, pos, taps, (tc.texMask & 1u) != 0);
+            float T = transmittance<32, OCC>(tc, kDensity, lp, pos, taps, (tc.texMask & 1u) != 0);
             f3 tl = mk3(lp.x - pos.x, lp.y - pos.y, lp.z - pos.z);
             float inv = rsqrtf(dot3(tl, tl));
             float ph = hg_phase(P.g, -dot3(tl, dir) * inv);
@@ -587,13 +608,13 @@ __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ Trace
                     }
                     f3 en, ex;
                     find_entry_exit(box, pos, rdir, en, ex, sdf);
-                    float T = transmittance<16>(tc, kDensity, pos, ex, taps, (tc.texMask & 2u) != 0) * phase;
+                    float T = transmittance<16, OCC>(tc, kDensity, pos, ex, taps, (tc.texMask & 2u) != 0) * phase;
                     acc.x += c.x * T; acc.y += c.y * T; acc.z += c.z * T;
                 }
             }
             light.x += acc.x * 0.125f; light.y += acc.y * 0.125f; light.z += acc.z * 0.125f;
         }
-        float tr = transmittance<32>(tc, kDensity, pos, last, taps);
+        float tr = transmittance<32, OCC>(tc, kDensity, pos, last, taps);
         pool.out[vtx] = make_float4(light.x, light.y, light.z, tr);
     }
     if (tapCounter) {
@@ -758,7 +779,47 @@ __global__ void __launch_bounds__(256) k_volume_sample(Grid g, const float* __re
     out[i] = grid_density(g, mk3(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]));
 }
 
+// bit 31 - (r & 31) of word r >> 5 of occ = some brick of the cells [r << shift, (r + 1) << shift) is non-zero; one thread per bit, one ballot per word
+__global__ void __launch_bounds__(256) k_brick_occupancy(const uint2* __restrict__ bricks, size_t cells, uint32_t shift, uint32_t bits,
+                                                         uint32_t* __restrict__ occ)
+{
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;   // the grid covers whole words
+    bool any = false;
+    if (r < bits) {
+        const size_t c0 = (size_t)r << shift;
+        const size_t c1 = min(c0 + ((size_t)1 << shift), cells);
+        for (size_t c = c0; c < c1; c++) {
+            const uint2 q = bricks[c];
+            any |= (q.x | q.y) != 0u;
+        }
+    }
+    const unsigned w = __ballot_sync(0xffffffffu, any);
+    if ((threadIdx.x & 31u) == 0u) occ[r >> 5] = __brev(w);   // first run of the word in the top bit (tap_load tests the sign)
+}
+
 // ---- launchers -----------------------------------------------------------------------------------------------------------
+#define NRC_OCC_MAX_WORDS 8192u   // 32 KB of shared memory per block at most
+nrc_status launch_build_occupancy(nrc_volume* vol)
+{
+    // NRC_LIGHT_OCC_SHIFT: cells per occupancy bit = 2^shift; 0 = no occupancy test in the light kernels, the default: measured on the
+    // bench frame the test skips a third of the brick loads but costs 8 instructions per tap, and the frame is issue-bound
+    // (2.97 ms with shift 5 against 2.84 ms without)
+    const char* e = getenv("NRC_LIGHT_OCC_SHIFT");
+    const int shift = e ? atoi(e) : 0;
+    vol->occShift = 0; vol->occWords = 0;
+    if (shift < 1 || shift > 8) return NRC_OK;
+    const size_t cells = (size_t)(vol->nx + 1) * (vol->ny + 1) * (vol->nz + 1);
+    const size_t bits = (cells + ((size_t)1 << shift) - 1) >> shift;
+    const size_t words = (bits + 31) / 32;
+    if (words > NRC_OCC_MAX_WORDS) return NRC_OK;   // a larger volume would need coarser runs than are worth testing
+    NRC_CUDA(cudaMalloc(&vol->occ, words * sizeof(uint32_t)));
+    cudaStream_t st = vol->ctx->stream;
+    NRC_LAUNCH(vol->ctx, st, K_MISC,
+               k_brick_occupancy<<<(unsigned)((words * 32 + 255) / 256), 256, 0, st>>>(vol->bricks, cells, (uint32_t)shift, (uint32_t)bits, vol->occ));
+    vol->occShift = (uint32_t)shift; vol->occWords = (uint32_t)words;
+    return NRC_OK;
+}
+
 nrc_status launch_build_bricks(nrc_volume* vol, const float* densityDev)
 {
     size_t cells = (size_t)(vol->nx + 1) * (vol->ny + 1) * (vol->nz + 1);
@@ -859,10 +920,18 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
     if (mb < 0) { const char* e = getenv("NRC_LIGHT_MB"); mb = e ? atoi(e) : 8; }
 #define LIGHT_CASE(MBV)                                                                                                              \
     case MBV:                                                                                                                        \
-        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, true><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else NRC_LAUNCH(ctx, st, kid, (k_light<false, MBV, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
+        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, true, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, false, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
+        else NRC_LAUNCH(ctx, st, kid, (k_light<false, MBV, false, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
         break;
+    if (P.occ != nullptr && P.occShift > 0 && mb == 8) {   // occupancy-tested taps: the bits travel in dynamic shared memory
+        size_t smem = (size_t)P.occWords * sizeof(uint32_t);   // <= 32 KB (NRC_OCC_MAX_WORDS)
+        if (smem < NRC_PAD_SMEM) smem = NRC_PAD_SMEM;
+        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, 8, true, true><<<blocks, 128, smem, st>>>(P, pool, tapCounter)));
+        else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, 8, false, true><<<blocks, 128, smem, st>>>(P, pool, tapCounter)));
+        else NRC_LAUNCH(ctx, st, kid, (k_light<false, 8, false, true><<<blocks, 128, smem, st>>>(P, pool, tapCounter)));
+        return NRC_OK;
+    }
     switch (mb) {
         LIGHT_CASE(4)
         LIGHT_CASE(5)
