@@ -6,8 +6,10 @@ timeout 100 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}
 timeout 400 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err
 timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err
 A="--steps 2 --warmup 3 --no-fit --no-cpu-baseline --no-fp32-line"
+if [ -z "$SKIP_NCU" ]; then
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py $A > gpurun_out/${T}_ncu_list.log 2>&1
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:"k_train_walk|k_render_walk|k_light|k_infer_tc|k_train_tc|k_composite|k_train_combine|k_render_combine" --launch-skip 30 --launch-count 10 -o gpurun_out/prof_${T} python bench.py $A > gpurun_out/${T}_ncu_full.log 2>&1
+fi
 python - <<PY
 import json
 T = "${T}"
