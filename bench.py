@@ -445,7 +445,7 @@ FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
 
 # ncu --set full capture of the default N=1 workload (profiles/r01p_ncu_summary.md, final round-1 build): DRAM bytes (read + write)
 # and executed warp instructions per launch.  Only quoted when the run IS that workload.
-NCU_R01K = {
+NCU_FRAME = {
     "k_train_walk": (111.3e6, 142.76e6), "k_light<train>": (196.4e6, 362.48e6), "k_train_combine": (168.1e6, 2.65e6),
     "k_train_tc": (1.9e6, 5.35e6), "k_render_walk": (240.8e6, 423.18e6), "k_render_walk_tail": (199.5e6, 508.84e6),
     "k_light<render>": (132.9e6, 424.43e6), "k_render_combine": (119.2e6, 6.98e6), "k_infer_tc": (13.3e6, 110.13e6),
@@ -505,8 +505,8 @@ def finish_b200(args, v):
                     "The walk kernels are latency/issue-bound on an L2-resident grid (profiles/r01p), so their HBM fraction is low by construction: "
                     "'issue_roofline' is the bound that explains the frame time; per-kernel figures for every kernel are under 'kernels'."}
     default_workload = (world == 1 and (W, H, v["TW"], v["TH"]) == (1920, 1080, 100, 100) and args.precision == "bf16")
-    if default_workload and name in NCU_R01K:
-        roof["traffic"] = NCU_R01K[name][0]
+    if default_workload and name in NCU_FRAME:
+        roof["traffic"] = NCU_FRAME[name][0]
         roof["traffic_source"] = "profiles/r01p_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
     if work is not None and kms > 0:
         ach = work / (kms * 1e-3) / (1e9 if bound == "hbm" else 1e12)
@@ -528,7 +528,7 @@ def finish_b200(args, v):
     # of the machine at the clock sampled during this run.
     issue = None
     if default_workload:
-        winst = sum(x[1] for x in NCU_R01K.values())
+        winst = sum(x[1] for x in NCU_FRAME.values())
         mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0
         peak_issue = v["ctx"].sm_count * 4 * mhz * 1e6
         issue = {"warp_instructions_per_step": winst, "peak_warp_instructions_per_s": peak_issue,

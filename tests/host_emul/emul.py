@@ -54,6 +54,19 @@ def render_walk(cfg, W, H, shape, spp=1):
     return cnt, qry
 
 
+def render_walk_split(cfg, W, H, shape, split_at):
+    """the walk as the head + tail launches of trace.cu run it; returns counters, queries and the number of paths handed over"""
+    cam = cfg["cam"]
+    ipv, pos, rnd = _f(cam.invProjView).reshape(16), _f(cam.m_Pos), _f(cfg["random4"][:2])
+    cnt = np.zeros((H, W, 4), np.uint32)
+    qry = np.zeros((H, W, 7), np.float32)
+    n = C.c_uint(0)
+    lib().emu_render_walk_split(_p(ipv), _p(pos), _p(rnd), C.c_float(cfg["g"]), C.c_uint(cfg["use_nn"]), C.c_uint(cfg["show_non_nn"]),
+                                C.c_uint(W), C.c_uint(H), C.c_int(split_at), C.c_float(cfg["density_factor"]),
+                                C.c_int(shape[0]), C.c_int(shape[1]), C.c_int(shape[2]), _p(cnt), _p(qry), C.byref(n))
+    return cnt, qry, n.value
+
+
 def train_walk(cfg, tw, th, shape, env_light=False):
     cam = cfg["cam"]
     ipv, pos, rnd = _f(cam.invProjView).reshape(16), _f(cam.m_Pos), _f(cfg["random4"][:2])

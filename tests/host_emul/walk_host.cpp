@@ -76,6 +76,54 @@ void emu_render_walk(const float* invProjView, const float* camPos, const float*
     }
 }
 
+// The render walk as the two launches of trace.cu run it: `splitAt` steps, the state of a surviving path packed into the 20-word spill
+// record (same fields, same order as k_render_walk writes them), unpacked, the remaining steps.  Outputs as emu_render_walk (spp = 1).
+void emu_render_walk_split(const float* invProjView, const float* camPos, const float* random2, float g, unsigned useNN, unsigned showNonNN,
+                           unsigned W, unsigned H, int splitAt, float densityFactor, int nx, int ny, int nz, unsigned* counters, float* query,
+                           unsigned* spilled)
+{
+    WalkParams P; Box box; Grid grid;
+    setup(invProjView, camPos, random2, g, useNN, showNonNN, W, H, 1, 1, densityFactor, nx, ny, nz, P, box, grid);
+    unsigned nSpilled = 0;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : nSpilled)
+    for (long py = 0; py < (long)H; py++) for (unsigned px = 0; px < W; px++) {
+        f3 ro, rd; Rng rng;
+        render_ray(P, px, (unsigned)py, ro, rd, rng);
+        WalkCounters wc = {0, 0, 0, 0};
+        f3 entry, ex;
+        find_entry_exit(box, ro, rd, entry, ex, wc.sdf);
+        bool miss = sky_sdf(box, entry) > NRC_MAX_RAY_DISTANCE;
+        WalkQuery q; q.valid = false; q.pos = q.dir = q.lastDir = mk3(0, 0, 0);
+        RecEmitter em{nullptr, 0};
+        if (!miss) {
+            WalkState ws = walk_state_begin(entry, rd);
+            if (render_walk_steps(P, box, grid, ws, 0, splitAt, rng, em, wc, q)) {
+                float rec[20] = {ws.cur.x, ws.cur.y, ws.cur.z, ws.termProb, ws.last.x, ws.last.y, ws.last.z, rng.pre,
+                                 ws.dir.x, ws.dir.y, ws.dir.z, rng.prePre, ws.lastDir.x, ws.lastDir.y, ws.lastDir.z, 0.0f,
+                                 0.0f, 0.0f, 0.0f, 0.0f};
+                unsigned draws = rng.draws, lit = wc.lit;
+                nSpilled++;
+                // ---- tail launch: nothing but the record, the draw count and the lit count survives
+                WalkState t;
+                t.cur = mk3(rec[0], rec[1], rec[2]); t.termProb = rec[3];
+                t.last = mk3(rec[4], rec[5], rec[6]);
+                t.dir = mk3(rec[8], rec[9], rec[10]);
+                t.lastDir = mk3(rec[12], rec[13], rec[14]);
+                Rng r2; r2.pre = rec[7]; r2.prePre = rec[11]; r2.draws = draws;
+                WalkCounters w2 = {lit, (unsigned)splitAt, 0, 0};
+                WalkQuery q2; q2.valid = false; q2.pos = q2.dir = q2.lastDir = mk3(0, 0, 0);
+                render_walk_steps(P, box, grid, t, splitAt, NRC_RENDER_WALK_STEPS, r2, em, w2, q2);
+                rng = r2; wc = w2; q = q2;
+            }
+        }
+        size_t p = (size_t)py * W + px;
+        counters[4 * p] = rng.draws; counters[4 * p + 1] = wc.lit; counters[4 * p + 2] = wc.steps; counters[4 * p + 3] = wc.emitted;
+        float* o = query + 7 * p;
+        o[0] = q.pos.x; o[1] = q.pos.y; o[2] = q.pos.z; o[3] = q.dir.x; o[4] = q.dir.y; o[5] = q.dir.z; o[6] = q.valid ? 1.0f : 0.0f;
+    }
+    *spilled = nSpilled;
+}
+
 // Divergence study (scripts/walk_divergence.py): per pixel {walk steps, SDF evaluations of the walk, SDF evaluations of the camera ray}
 void emu_render_walk_cost(const float* invProjView, const float* camPos, const float* random2, float g, unsigned useNN, unsigned W, unsigned H,
                           float densityFactor, int nx, int ny, int nz, unsigned* cost, unsigned char* perStep)

@@ -22,6 +22,24 @@ def test_render_walk_bit_exact():
     assert qry[..., 7].mean() > 0.2   # the scene does exercise the cache
 
 
+def test_render_walk_in_two_launches_is_the_same_walk():
+    """trace.cu stops the render walk after NRC_RWALK_SPLIT steps and finishes the surviving paths in a second launch from a 20-word
+    record: the record carries everything the remaining steps read (every split point gives the single walk's draws, vertices,
+    steps and queries), for the cache on and off."""
+    shape = emul.set_volume(Cm.density())
+    W, H = 64, 40
+    for cfg in (Cm.scene_cfg(), Cm.scene_cfg(use_nn=0)):
+        cnt, qry = emul.render_walk(cfg, W, H, shape)
+        handed = []
+        for k in (1, 4, 10, 31):
+            scnt, sqry, n = emul.render_walk_split(cfg, W, H, shape, k)
+            np.testing.assert_array_equal(scnt, cnt)
+            np.testing.assert_array_equal(sqry.view(np.uint32), qry.view(np.uint32))
+            handed.append(n)
+        assert handed[0] >= handed[1] >= handed[2] >= handed[3] > 0          # fewer paths survive a later split
+        assert handed[0] == int((cnt[..., 2] > 1).sum())                      # exactly the paths with a second step
+
+
 def test_render_walk_frame0_and_no_nn():
     # frame 0: random = 0 -> every draw is 0 (SURVEY A17); and the non-NN path (useNN = 0)
     for cfg in (Cm.scene_cfg(random4=(0, 0, 0, 0)), Cm.scene_cfg(use_nn=0)):
