@@ -3,7 +3,8 @@
 #include "nrc_internal.cuh"
 #include "strict.cuh"
 
-// [0] grid_coords: (a / extent + 0.5) compared as the range test sees it, ALL 2^32 bit patterns of a, extents 62.5 / 42.5 / 76.5
+// [0] grid_coords: (a / extent + 0.5) compared as the range test sees it, ALL 2^32 bit patterns of a, extents 62.5 / 42.5 / 76.5,
+//     for div_normal and for the three-instruction div_extent
 // [1] sqrt_normal(x) vs __fsqrt_rn(x), every float in [2^-101, FLT_MAX]
 // [2] div_normal(1, y) vs __fdiv_rn(1, y), every float in [2^-30, 2^30]
 // [3] the two divisions of the HG cos-theta draw: (1-g^2)/den for every den in [0.25, 2), num/(2g) for every |num| <= 2, g = 0.7
@@ -24,8 +25,10 @@ __global__ void __launch_bounds__(256) k_selftest_strict(unsigned long long* __r
     for (unsigned long long i = t0; i < (1ull << 32); i += stride) {
         float a = __uint_as_float((unsigned)i);
 #pragma unroll
-        for (int k = 0; k < 3; k++)
+        for (int k = 0; k < 3; k++) {
             if (!same_coord(__fdiv_rn(a, ext[k]), div_normal(a, ext[k]))) b0++;
+            if (!same_coord(__fdiv_rn(a, ext[k]), div_extent(a, ext[k], __frcp_rn(ext[k])))) b0++;   // the form grid_coords uses
+        }
     }
     for (unsigned long long i = t0 + 0x0D000000ull; i <= 0x7F7FFFFFull; i += stride) {
         float x = __uint_as_float((unsigned)i);

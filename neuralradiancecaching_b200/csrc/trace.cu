@@ -28,6 +28,7 @@ __device__ __forceinline__ Grid make_grid(const TraceParams& P)
     g.nx = P.nx; g.ny = P.ny; g.nz = P.nz;
     g.bricks = P.bricks;
     g.skySize = mk3(P.skySize[0], P.skySize[1], P.skySize[2]);
+    g.invSize = mk3(__frcp_rn(g.skySize.x), __frcp_rn(g.skySize.y), __frcp_rn(g.skySize.z));
     g.densityFactor = P.densityFactor;
     return g;
 }
@@ -836,6 +837,7 @@ nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, flo
     g.nx = (int)vol->nx; g.ny = (int)vol->ny; g.nz = (int)vol->nz;
     g.bricks = vol->bricks;
     g.skySize = mk3(62.5f, 42.5f, 76.5f);
+    g.invSize = mk3(1.0f / 62.5f, 1.0f / 42.5f, 1.0f / 76.5f);   // IEEE single division on the host = __frcp_rn
     g.densityFactor = vol->params.densityFactor;
     cudaStream_t st = vol->ctx->stream;
     NRC_LAUNCH(vol->ctx, st, K_VOLUME_SAMPLE, k_volume_sample<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(g, pos, n, out));
