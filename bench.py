@@ -214,30 +214,32 @@ def run_b200(args):
     # ---- end to end: the host-facing call sequence; per step the scene/camera/RNG structs go host->device (kernel
     # parameters) and this rank's rows of the BGRA8 frame plus the loss come back to pinned host memory ----
     # Like the reference's main loop (frame k is presented while frame k+1 is recorded, src/main.cpp:197-230) the read-back
-    # is asynchronous and double-buffered: step k queues frame k and its copy, then takes delivery of frame k-1.  Every
-    # frame and every loss value crosses PCIe inside the timed region; the last one is awaited before the stop event.
+    # is asynchronous and buffered: step k queues frame k and its copy, then takes delivery of frame k-D (D = NRC_E2E_DEPTH, default 2:
+    # the host stays two frames ahead of the frame it consumes, like the device-timed loop, whose frame graph overlaps the next
+    # frame's tracing with this frame's lighting and inference; D = 1 is the plain double buffer).  Every frame and every loss value
+    # crosses PCIe inside the timed region; the last ones are awaited before the stop event.
     d2h_bytes = r.partition_bytes(L.FRAME_BGRA8)
-    host_frames = [torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory() for _ in range(2)]
-    host_loss = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    depth = min(max(int(os.environ.get("NRC_E2E_DEPTH", "2")), 1), 3)      # the renderer keeps 4 read-back tickets
+    host_frames = [torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory() for _ in range(depth + 1)]
+    host_loss = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(depth + 1)]
     hfs = [h.numpy() for h in host_frames]
     hls = [h.numpy() for h in host_loss]
     sync_e2e = bool(os.environ.get("NRC_E2E_SYNC"))
 
     def e2e_steps(count):
-        pending = None
+        pending = []
         for k in range(count):
             frame(next(ri))
             if sync_e2e:
                 r.read_frame_partition(hfs[0], L.FRAME_BGRA8)    # synchronous D2H of this rank's rows
                 _ = nrc.GetStats().mseLoss                        # D2H of the loss (src/main.cpp:220-224)
                 continue
-            nrc.get_stats_async(hls[k & 1])
-            t = r.read_frame_partition_async(hfs[k & 1], L.FRAME_BGRA8)
-            if pending is not None:
-                r.readback_wait(pending)                          # frame k-1 and its loss are in host memory now
-            pending = t
-        if pending is not None:
-            r.readback_wait(pending)
+            nrc.get_stats_async(hls[k % (depth + 1)])
+            pending.append(r.read_frame_partition_async(hfs[k % (depth + 1)], L.FRAME_BGRA8))
+            if len(pending) > depth:
+                r.readback_wait(pending.pop(0))                   # frame k-D and its loss are in host memory now
+        for t in pending:
+            r.readback_wait(t)
 
     e2e_steps(3)
     barrier()
