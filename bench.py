@@ -150,8 +150,12 @@ def run_b200(args):
     r = N.NrcHpmRenderer(W, H, TW, TH, inp["cam"], vol, dl, pl, env, nrc, mrhe)
     if world > 1:
         r.SetPartitionStrided(rank, world, rank, world)
-    if os.environ.get("NRC_BENCH_POOL"):          # experiment: vertices per path of the render pool (32 = cannot overflow)
-        r.SetPoolCapacity((W * H // world) * int(os.environ["NRC_BENCH_POOL"]))
+    # Render vertex pool, vertices per path (NRC_BENCH_POOL; 0 = the library default of 4, grown and re-traced on overflow).  32 cannot
+    # overflow, so no read has to wait on the host for the overflow flag of the frame it hands out: e2e 2.93 instead of 3.00 ms/frame;
+    # 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are for.  Larger per-rank frames keep the library default.
+    pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "32" if (W * H // world) <= 2304 * 1296 else "0"))
+    if pool_per_path > 0:
+        r.SetPoolCapacity((W * H // world) * pool_per_path)
 
     from neuralradiancecaching_b200.dist import GradientExchange, FusedExchange
     exchange = GradientExchange(ctx, nrc, mrhe, torch.device("cuda", local))
@@ -548,6 +552,7 @@ def finish_b200(args, v):
                    "parallelism": "rows interleaved over %d GPU(s), train samples sharded, %s" % (
                        world, "gradients summed over NVLink peer memory inside the fused step kernel" if (world > 1 and args.exchange == "fused")
                        else "NCCL all-reduce of gradients"),
+                   "vertex_pool": "%d vertices per path%s" % (v["pool_per_path"] or 4, " (worst case: cannot overflow)" if v["pool_per_path"] >= 32 else ""),
                    "l2": "fresh per-frame RNG seed: every frame traces new paths; per-frame buffers (%.0f MB) exceed nothing but are rewritten, "
                          "the density grid (%s) %s" % (W * H * 120 / 1e6, "13 MB of bricks" if v["grid_scale"] == 1 else "838 MB of bricks",
                                                       "is L2-resident by design" if v["grid_scale"] == 1 else "does not fit L2: taps gather from HBM")},
