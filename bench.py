@@ -155,7 +155,7 @@ def run_b200(args):
     # 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are for.  Larger per-rank frames keep the library default.
     pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "32" if (W * H // world) <= 2304 * 1296 else "0"))
     if pool_per_path > 0:
-        r.SetPoolCapacity((W * H // world) * pool_per_path)
+        r.SetPoolCapacity(-(-H // world) * W * pool_per_path)      # the rank with the most rows
 
     from neuralradiancecaching_b200.dist import GradientExchange, FusedExchange
     exchange = GradientExchange(ctx, nrc, mrhe, torch.device("cuda", local))
