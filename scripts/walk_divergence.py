@@ -23,11 +23,8 @@ def main():
     shape = E.set_volume(inp["density"])
     cam = inp["cam"]
     rnd = bench.lcg_randoms(2)[1]
-    cost = np.zeros((H, W, 4), np.uint32)
-    per = np.zeros((H, W, 32), np.uint8)
-    f = E._f
-    E.lib().emu_render_walk_cost(E._p(f(cam.invProjView).reshape(16)), E._p(f(cam.m_Pos)), E._p(f(rnd[:2])), C.c_float(0.7), C.c_uint(1),
-                                 C.c_uint(W), C.c_uint(H), C.c_float(0.4), C.c_int(shape[0]), C.c_int(shape[1]), C.c_int(shape[2]), E._p(cost), E._p(per))
+    cfg = dict(cam=cam, random4=rnd, g=0.7, use_nn=1, density_factor=0.4)
+    cost, per = E.render_walk_cost(cfg, W, H, shape)
     steps, sdf, camsdf, lit = [cost[..., k].astype(np.int64) for k in range(4)]
     print("pixels %d, in the box %.1f %%, mean walk steps %.2f (of those in the box %.2f), SDF evaluations per step %.2f, camera ray %.2f"
           % (W * H, 100.0 * (steps > 0).mean(), steps.mean(), steps[steps > 0].mean(), sdf.sum() / max(steps.sum(), 1), camsdf.mean()))

@@ -67,6 +67,18 @@ def render_walk_split(cfg, W, H, shape, split_at):
     return cnt, qry, n.value
 
 
+def render_walk_cost(cfg, W, H, shape):
+    """divergence study (scripts/walk_divergence.py): per pixel {walk steps, SDF evaluations of the walk, of the camera ray, lit
+    vertices} and the SDF evaluations of every walk step"""
+    cam = cfg["cam"]
+    ipv, pos, rnd = _f(cam.invProjView).reshape(16), _f(cam.m_Pos), _f(cfg["random4"][:2])
+    cost = np.zeros((H, W, 4), np.uint32)
+    per = np.zeros((H, W, 32), np.uint8)
+    lib().emu_render_walk_cost(_p(ipv), _p(pos), _p(rnd), C.c_float(cfg["g"]), C.c_uint(cfg["use_nn"]), C.c_uint(W), C.c_uint(H),
+                               C.c_float(cfg["density_factor"]), C.c_int(shape[0]), C.c_int(shape[1]), C.c_int(shape[2]), _p(cost), _p(per))
+    return cost, per
+
+
 def train_walk(cfg, tw, th, shape, env_light=False):
     cam = cfg["cam"]
     ipv, pos, rnd = _f(cam.invProjView).reshape(16), _f(cam.m_Pos), _f(cfg["random4"][:2])

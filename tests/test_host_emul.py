@@ -40,6 +40,20 @@ def test_render_walk_in_two_launches_is_the_same_walk():
         assert handed[0] == int((cnt[..., 2] > 1).sum())                      # exactly the paths with a second step
 
 
+def test_walk_cost_counters_describe_the_same_walk():
+    """the per-step SDF counts behind scripts/walk_divergence.py come from a step-by-step copy of the walk loop: its steps and lit
+    vertices must be those of render_walk_path, and the per-step counts must add up to the walk's total"""
+    cfg = Cm.scene_cfg()
+    shape = emul.set_volume(Cm.density())
+    W, H = 48, 30
+    cnt, _ = emul.render_walk(cfg, W, H, shape)
+    cost, per = emul.render_walk_cost(cfg, W, H, shape)
+    np.testing.assert_array_equal(cost[..., 0], cnt[..., 2])                 # walk steps
+    np.testing.assert_array_equal(cost[..., 3], cnt[..., 1])                 # lit vertices
+    np.testing.assert_array_equal(per.sum(axis=2), cost[..., 1])             # SDF evaluations, step by step
+    assert (per[(cost[..., 0] == 32) & (cnt[..., 3] == 0)] > 0).all()         # a walk that runs out of steps marched in every one
+
+
 def test_render_walk_frame0_and_no_nn():
     # frame 0: random = 0 -> every draw is 0 (SURVEY A17); and the non-NN path (useNN = 0)
     for cfg in (Cm.scene_cfg(random4=(0, 0, 0, 0)), Cm.scene_cfg(use_nn=0)):
