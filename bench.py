@@ -696,6 +696,7 @@ def main():
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fit", action="store_true", help="skip the BASELINE config-2 (2^18-query MRHE+MLP fit) side measurement")
+    ap.add_argument("--no-side", action="store_true", help="skip the side measurements of the other BASELINE configs (config3 / strong_4k / config5) and the parity check")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

@@ -213,14 +213,16 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prLow));
     // the train trace is the long pole of the frame: just below the main stream (whose kernels are short), above the render trace
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream3, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
+    c->streamWalk[0] = c->stream3;
+    for (int i = 1; i < NRC_TRAIN_WALK_STREAMS; i++)
+        NRC_CUDA(cudaStreamCreateWithPriority(&c->streamWalk[i], cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainTrace, cudaEventDisableTiming));
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream4, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
     NRC_CUDA(cudaStreamCreateWithFlags(&c->streamCopy, cudaStreamNonBlocking));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainWalk, cudaEventDisableTiming));
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream5, cudaStreamNonBlocking, prLow));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evRenderWalk, cudaEventDisableTiming));
-    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[0], cudaEventDisableTiming));
-    NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[1], cudaEventDisableTiming));
+    for (int i = 0; i < NRC_TRAIN_SETS; i++) NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[i], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
     if (const char* e = getenv("NRC_INFER_SPLIT")) c->inferMode = atoi(e) ? NRC_INFER_SPLIT : NRC_INFER_FUSED;
     *out = c;
@@ -233,7 +235,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     cudaStreamSynchronize(c->stream2);
-    cudaStreamSynchronize(c->stream3);
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) cudaStreamSynchronize(c->streamWalk[i]);
     cudaStreamSynchronize(c->stream4);
     cudaStreamSynchronize(c->stream5);
     cudaStreamSynchronize(c->streamCopy);
@@ -244,12 +246,11 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaEventDestroy(c->evJoin);
     cudaStreamDestroy(c->stream);
     cudaStreamDestroy(c->stream2);
-    cudaStreamDestroy(c->stream3);
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) cudaStreamDestroy(c->streamWalk[i]);
     cudaEventDestroy(c->evTrainTrace);
     cudaEventDestroy(c->evTrainWalk);
     cudaEventDestroy(c->evRenderWalk);
-    cudaEventDestroy(c->evTrainFree[0]);
-    cudaEventDestroy(c->evTrainFree[1]);
+    for (int i = 0; i < NRC_TRAIN_SETS; i++) cudaEventDestroy(c->evTrainFree[i]);
     cudaStreamDestroy(c->stream4);
     cudaStreamDestroy(c->stream5);
     cudaStreamDestroy(c->streamCopy);

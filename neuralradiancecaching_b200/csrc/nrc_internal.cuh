@@ -48,6 +48,11 @@ enum NrcKernelId {
 };
 
 struct NrcProfRec { int kid; cudaEvent_t a, b; };
+// The train trace (walk -> light -> combine) reads no weights, so consecutive frames' traces are independent of each other: up to
+// NRC_TRAIN_WALK_STREAMS train walks are in flight at once (a walk is ~300 warps of pure dependent latency, so several of them take
+// barely longer than one), each filling its own buffer set; a set is reused once the train kernel that read it has finished.
+#define NRC_TRAIN_SETS 4
+#define NRC_TRAIN_WALK_STREAMS 3
 nrc_status nrc_renderer_resolve_pending(nrc_renderer* r);   // renderer.cu
 
 // ---- handles ---------------------------------------------------------------------------------------
@@ -62,7 +67,8 @@ struct nrc_ctx {
     cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
     cudaStream_t stream5 = nullptr;       // fifth stream: lights + combine of the RENDER trace, beside the next frame's render walk
     cudaEvent_t evRenderWalk = nullptr;
-    cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[2] = {nullptr, nullptr};
+    cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[NRC_TRAIN_SETS] = {nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t streamWalk[NRC_TRAIN_WALK_STREAMS] = {nullptr, nullptr, nullptr};   // [0] = stream3: consecutive frames' train walks on alternating streams
     nrc_mlp_precision precision = NRC_MLP_FP32;
     nrc_infer_mode inferMode = NRC_INFER_FUSED;   // nrc_ctx_create reads NRC_INFER_SPLIT
     uint64_t launches = 0;

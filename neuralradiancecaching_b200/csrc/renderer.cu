@@ -1,8 +1,9 @@
 // renderer.cu -- nrc_renderer: the frame graph that replaces NrcHpmRenderer's recorded command buffer
 // (src/NrcHpmRenderer.cpp:571-730): train -> nrc-step -> mrhe-step -> render.
 //
-//   stream3 : train walk                 } independent of the weights: run AHEAD on double-buffered pools -- walk(k+1) overlaps
-//   stream4 : train light -> combine     } light(k), and both overlap frame k's steps / exchange wait / inference / composite
+//   walk streams : train walk            } independent of the weights AND of each other: consecutive frames' walks run on alternating
+//                                        } streams into NRC_TRAIN_SETS buffer sets, so up to three of these latency-bound chains are in flight
+//   stream4 : train light -> combine     } at once; all of it overlaps frame k's steps / exchange wait / inference / composite
 //   stream  : fused encode+MLP fwd/bwd -> [gradient exchange] -> steps -> batched inference -> composite
 //   stream2 : render walk -> light -> combine (compacts the NRC queries)           (independent of the weights)
 #include <math.h>
@@ -49,19 +50,22 @@ struct nrc_renderer {
     // train
     TrainPaths tp;                    // = tpb[trainBuf]: the buffers of the last nrc_frame_train (what the probes read)
     VertexPool tpool;
-    TrainPaths tpb[2];                // double-buffered: the walk of frame k+1 fills one set while lights/combine/MLP of frame k read the other
-    VertexPool tpoolb[2];
-    int trainBuf = 1;
+    TrainPaths tpb[NRC_TRAIN_SETS];   // multi-buffered: the walks of frames k+1.. fill other sets while lights/combine/MLP of frame k read theirs
+    VertexPool tpoolb[NRC_TRAIN_SETS];
+    int trainBuf = NRC_TRAIN_SETS - 1;
+    unsigned trainSeq = 0;            // train frames queued so far: picks the walk stream
     bool trainEnvLight = false;       // opt-in: env-map term in the training targets (train pools then carry random numbers)
-    uint32_t* trainCounters = nullptr;
+    uint32_t* trainCounters = nullptr;             // = trainCountersB[trainBuf]
+    uint32_t* trainCountersB[NRC_TRAIN_SETS] = {nullptr, nullptr, nullptr, nullptr};   // per set: walks of different frames run concurrently
     uint32_t trainAlloc = 0;
-    // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count, [5] render-walk paths handed to the tail launch; train sets: {2,3} and {6,7}
+    // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count, [5] render-walk paths handed to the tail launch;
+    // train set b: {16 + 2b, 17 + 2b} = vertex count, overflow
     uint32_t* scalars = nullptr;
-    unsigned long long* taps = nullptr;   // [0], [3] render taps of the two sets; [1], [2] train taps of the two sets
+    unsigned long long* taps = nullptr;   // [0], [3] render taps of the two sets; [4 + b] train taps of set b
     unsigned long long* totals = nullptr; // [6] running totals (nrc_frame_totals)
     uint32_t* hostScalars = nullptr;      // pinned mirror
     unsigned long long* hostTaps = nullptr;
-    bool trainPending[2] = {false, false};  // evTrainFree[b] marks the end of the train kernel that last consumed buffer set b
+    bool trainPending[NRC_TRAIN_SETS] = {false, false, false, false};  // evTrainFree[b] marks the end of the train kernel that last consumed buffer set b
 };
 
 #define FREE(p) do { if (p) { cudaFree(p); (p) = nullptr; } } while (0)
@@ -148,11 +152,12 @@ static nrc_status alloc_frame(nrc_renderer* r, uint32_t spp, uint32_t poolCap)
 
 static void free_train(nrc_renderer* r)
 {
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < NRC_TRAIN_SETS; b++) {
         FREE(r->tpb[b].head); FREE(r->tpb[b].pos); FREE(r->tpb[b].dir); FREE(r->tpb[b].target);
         free_pool(r->tpoolb[b]);
+        FREE(r->trainCountersB[b]);
     }
-    FREE(r->trainCounters);
+    r->trainCounters = nullptr;
     memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
     r->trainAlloc = 0;
 }
@@ -164,7 +169,7 @@ static nrc_status alloc_train(nrc_renderer* r)
     size_t cap = (size_t)n * (8 * 64 + 2 * 16);   // worst case: 8 paths x 64 lit vertices per training sample (+ the two partly
                                                   // used chunks a thread can end with, TRAIN_CHUNK) -- this pool cannot overflow
     NRC_REQUIRE(cap < ((size_t)1 << 31), "train grid too large for the vertex pool");
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < NRC_TRAIN_SETS; b++) {
         TrainPaths& tp = r->tpb[b];
         NRC_CUDA(cudaMalloc(&tp.head, (size_t)n * 8 * sizeof(int)));
         NRC_CUDA(cudaMalloc(&tp.pos, (size_t)n * 3 * sizeof(float)));
@@ -173,13 +178,14 @@ static nrc_status alloc_train(nrc_renderer* r)
         NRC_CUDA(cudaMemsetAsync(tp.pos, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
         NRC_CUDA(cudaMemsetAsync(tp.dir, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
         NRC_CUDA(cudaMemsetAsync(tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
-        // device scalars of the two sets: {2,3} and {6,7}
-        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, r->trainEnvLight, r->scalars + 2 + 4 * b, r->scalars + 3 + 4 * b));
+        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, r->trainEnvLight, r->scalars + 16 + 2 * b, r->scalars + 17 + 2 * b));
     }
-    NRC_CUDA(cudaMalloc(&r->trainCounters, (size_t)n * 4 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMemsetAsync(r->trainCounters, 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
-    r->trainBuf = 1;
-    r->tp = r->tpb[1]; r->tpool = r->tpoolb[1];
+    for (int b = 0; b < NRC_TRAIN_SETS; b++) {
+        NRC_CUDA(cudaMalloc(&r->trainCountersB[b], (size_t)n * 4 * sizeof(uint32_t)));
+        NRC_CUDA(cudaMemsetAsync(r->trainCountersB[b], 0, (size_t)n * 4 * sizeof(uint32_t), r->ctx->stream));
+    }
+    r->trainBuf = NRC_TRAIN_SETS - 1;
+    r->tp = r->tpb[r->trainBuf]; r->tpool = r->tpoolb[r->trainBuf]; r->trainCounters = r->trainCountersB[r->trainBuf];
     r->trainAlloc = n;
     return NRC_OK;
 }
@@ -202,21 +208,21 @@ extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t
     memset(&r->rp, 0, sizeof(r->rp)); memset(&r->rpool, 0, sizeof(r->rpool)); memset(&r->ql, 0, sizeof(r->ql));
     memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
     memset(r->tpb, 0, sizeof(r->tpb)); memset(r->tpoolb, 0, sizeof(r->tpoolb));
-    NRC_CUDA(cudaMalloc(&r->scalars, 16 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMalloc(&r->taps, 4 * sizeof(unsigned long long)));   // [0] render, [1], [2] the two train sets
+    NRC_CUDA(cudaMalloc(&r->scalars, 32 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMalloc(&r->taps, 8 * sizeof(unsigned long long)));
     NRC_CUDA(cudaMalloc(&r->totals, 6 * sizeof(unsigned long long)));
     NRC_CUDA(cudaMemsetAsync(r->totals, 0, 6 * sizeof(unsigned long long), ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 16 * sizeof(uint32_t), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 32 * sizeof(uint32_t), ctx->stream));
     memset(r->rs, 0, sizeof(r->rs));
     for (int b = 0; b < 2; b++) NRC_CUDA(cudaEventCreateWithFlags(&r->evSetFree[b], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&r->evScalars, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&r->evCopyReady, cudaEventDisableTiming));
     for (int k = 0; k < 4; k++) NRC_CUDA(cudaEventCreateWithFlags(&r->evCopyDone[k], cudaEventDisableTiming));
-    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 8 * sizeof(unsigned long long), ctx->stream));
     NRC_CUDA(cudaMallocHost(&r->hostScalars, 8 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMallocHost(&r->hostTaps, 4 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMallocHost(&r->hostTaps, 8 * sizeof(unsigned long long)));
     memset(r->hostScalars, 0, 8 * sizeof(uint32_t));
-    memset(r->hostTaps, 0, 4 * sizeof(unsigned long long));
+    memset(r->hostTaps, 0, 8 * sizeof(unsigned long long));
     NRC_TRY(alloc_frame(r, 1, (uint32_t)((size_t)width * height * 4)));
     NRC_TRY(alloc_train(r));
     ctx->renderers.push_back(r);
@@ -231,7 +237,7 @@ extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
         if (r->ctx->renderers[i] == r) { r->ctx->renderers.erase(r->ctx->renderers.begin() + i); break; }
     cudaStreamSynchronize(r->ctx->stream);
     cudaStreamSynchronize(r->ctx->stream2);
-    cudaStreamSynchronize(r->ctx->stream3);
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) cudaStreamSynchronize(r->ctx->streamWalk[i]);
     cudaStreamSynchronize(r->ctx->stream4);
     cudaStreamSynchronize(r->ctx->streamCopy);
     free_frame(r);
@@ -295,7 +301,7 @@ extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t heigh
     NRC_REQUIRE(r && width > 0 && height > 0, "bad size");
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
-    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(r->ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->streamCopy));
     r->width = width; r->height = height;
@@ -313,7 +319,7 @@ extern "C" nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t v
     NRC_TRY(resolve_overflow_fwd(r));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
-    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(r->ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->streamCopy));
     r->poolCapHint = (size_t)vertices;
@@ -332,10 +338,10 @@ extern "C" nrc_status nrc_renderer_set_train_env_light(nrc_renderer* r, int on)
     if (r->trainEnvLight == (on != 0)) return NRC_OK;
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
-    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream3));
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(r->ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
     r->trainEnvLight = on != 0;
-    r->trainPending[0] = r->trainPending[1] = false;
+    for (int b = 0; b < NRC_TRAIN_SETS; b++) r->trainPending[b] = false;
     return alloc_train(r);
 }
 
@@ -398,8 +404,9 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     if (n == 0) return NRC_OK;
     TraceParams P = make_params(r);
     // The trace half (walk, lights, combine) reads no weights, so it runs AHEAD of the main stream, on two streams of its own:
-    //   stream3: walk(k)                       -- the long pole; walk(k+1) starts as soon as walk(k) is done
-    //   stream4: light(k) -> combine(k)        -- overlaps walk(k+1), which fills the other buffer set
+    //   walk streams: walk(k)                  -- the long pole (one serial chain per sample); walk(k+1), walk(k+2) run beside it on the
+    //                                             other walk streams (NRC_TRAIN_WALK=n: walks in flight, default 3; 1 = one after the other)
+    //   stream4: light(k) -> combine(k)        -- overlaps the later walks, which fill other buffer sets
     //   main   : train kernel(k) -> [exchange] -> steps -> inference -> composite
     // so frame k+1's trace overlaps frame k's steps / inference / composite and, on several GPUs, the exchange's wait for
     // the slowest rank.  A buffer set is reused once the train kernel that read it has finished (evTrainFree[b]).
@@ -407,21 +414,28 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
     if (noAhead < 0) { const char* e = getenv("NRC_NO_TRAIN_AHEAD"); noAhead = (e && atoi(e)) ? 1 : 0; }
     const bool ahead = !(noOverlap || noAhead);
-    cudaStream_t tw = ahead ? ctx->stream3 : st;
+    static int walkStreams = -1;
+    if (walkStreams < 0) {
+        const char* e = getenv("NRC_TRAIN_WALK");
+        walkStreams = e ? atoi(e) : NRC_TRAIN_WALK_STREAMS;
+        if (walkStreams < 1 || walkStreams > NRC_TRAIN_WALK_STREAMS) walkStreams = NRC_TRAIN_WALK_STREAMS;
+    }
+    cudaStream_t tw = ahead ? ctx->streamWalk[r->trainSeq % (unsigned)walkStreams] : st;
     cudaStream_t tl = ahead ? ctx->stream4 : st;
-    const int b = ahead ? (r->trainBuf ^ 1) : r->trainBuf;
+    r->trainSeq++;
+    const int b = ahead ? (r->trainBuf + 1) % NRC_TRAIN_SETS : r->trainBuf;
     r->trainBuf = b;
-    r->tp = r->tpb[b]; r->tpool = r->tpoolb[b];
+    r->tp = r->tpb[b]; r->tpool = r->tpoolb[b]; r->trainCounters = r->trainCountersB[b];
     if (ahead && r->trainPending[b]) NRC_CUDA(cudaStreamWaitEvent(tw, ctx->evTrainFree[b], 0));
     NRC_CUDA(cudaMemsetAsync(r->tpool.count, 0, 2 * sizeof(uint32_t), tw));          // count + overflow of this set
-    NRC_CUDA(cudaMemsetAsync(r->taps + 1 + b, 0, sizeof(unsigned long long), tw));
+    NRC_CUDA(cudaMemsetAsync(r->taps + 4 + b, 0, sizeof(unsigned long long), tw));
     NRC_TRY(launch_train_walk(ctx, tw, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
     if (ahead) {
         NRC_CUDA(cudaEventRecord(ctx->evTrainWalk, tw));
         NRC_CUDA(cudaStreamWaitEvent(tl, ctx->evTrainWalk, 0));
     }
-    NRC_TRY(launch_light(ctx, tl, P, r->tpool, r->trainEnvLight, r->taps + 1 + b, K_LIGHT_TRAIN));
-    NRC_TRY(launch_train_combine(ctx, tl, n, r->tpool, r->tp, r->taps + b, r->totals));   // reads taps[1] of the pointer it gets
+    NRC_TRY(launch_light(ctx, tl, P, r->tpool, r->trainEnvLight, r->taps + 4 + b, K_LIGHT_TRAIN));
+    NRC_TRY(launch_train_combine(ctx, tl, n, r->tpool, r->tp, r->taps + 4 + b, r->totals));
     if (ahead) {
         NRC_CUDA(cudaEventRecord(ctx->evTrainTrace, tl));
         NRC_CUDA(cudaStreamWaitEvent(st, ctx->evTrainTrace, 0));
@@ -440,7 +454,7 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
 
 static nrc_status drain_streams(nrc_ctx* ctx)
 {
-    NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
@@ -700,7 +714,7 @@ extern "C" nrc_status nrc_frame_totals(nrc_renderer* r, uint64_t totals[6], int 
 {
     NRC_REQUIRE(r && totals, "null argument");
     nrc_ctx* ctx = r->ctx;
-    NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -716,15 +730,15 @@ extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, u
     NRC_REQUIRE(r, "null renderer");
     nrc_ctx* ctx = r->ctx;
     NRC_TRY(resolve_overflow(r, true));
-    NRC_CUDA(cudaStreamSynchronize(ctx->stream3));
+    for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars + 8 * r->renderBuf, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     if (inferQueries) *inferQueries = r->hostScalars[4];
     if (trainSamples) *trainSamples = part_count(r->i0, r->i1, r->istride);
     // + one tap per walk step is not counted here: densityTaps are the light kernels' taps (the bulk)
-    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[3 * r->renderBuf] + (uint64_t)r->hostTaps[1 + r->trainBuf];
+    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[3 * r->renderBuf] + (uint64_t)r->hostTaps[4 + r->trainBuf];
     return NRC_OK;
 }

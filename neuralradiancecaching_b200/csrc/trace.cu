@@ -678,7 +678,7 @@ __global__ void __launch_bounds__(128) k_train_combine(uint32_t nLocal, VertexPo
     uint32_t i = t >> 3, p = t & 7u;
     if (t == 0 && totals) {   // running totals of this rank (nrc_frame_totals)
         totals[1] += nLocal;
-        totals[3] += taps[1];
+        totals[3] += taps[0];
         totals[5] += min(*pool.count, pool.cap);
     }
     f3 L = mk3(0.0f, 0.0f, 0.0f);
