@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libnrc_b200.so")
 SOURCES = ["capi.cu", "encode.cu", "mlp_fp32.cu", "mlp_tc.cu", "mlp_stream.cu", "steps.cu", "dp.cu", "trace.cu", "scene.cu", "renderer.cu", "selftest.cu"]
-HEADERS = ["nrc_internal.cuh", "strict.cuh", "walk.cuh", "trace.cuh", "tc_ptx.cuh", "../../include/nrc_b200.h", "../../include/nrc_math.h"]
+HEADERS = ["nrc_internal.cuh", "strict.cuh", "walk.cuh", "trace.cuh", "tc_ptx.cuh", "mrhe_scatter.cuh", "../../include/nrc_b200.h", "../../include/nrc_math.h"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

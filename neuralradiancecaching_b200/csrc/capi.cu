@@ -316,6 +316,8 @@ extern "C" nrc_status nrc_mlp_destroy(nrc_mlp* m)
     cudaStreamSynchronize(m->ctx->stream);
     cudaFree(m->params); cudaFree(m->grad); cudaFree(m->momentum); cudaFree(m->paramsT);
     if (m->partial) cudaFree(m->partial);
+    if (m->gScratch) cudaFree(m->gScratch);
+    if (m->histPartial) cudaFree(m->histPartial);
     if (m->paramsBf16) cudaFree(m->paramsBf16);
     if (m->featTiles) cudaFree(m->featTiles);
     if (m->second) cudaFree(m->second);

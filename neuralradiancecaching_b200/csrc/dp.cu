@@ -18,6 +18,7 @@
 #include <cuda_bf16.h>
 #include <string.h>
 #include "nrc_internal.cuh"
+#include "tc_ptx.cuh"
 
 #define NRC_DP_MAX_WORLD 16
 #define NRC_DP_MAX_HEAD (1u << 20)
@@ -124,13 +125,7 @@ __device__ __forceinline__ void dp_nrc_update(const DpArgs& a, int i, float g)
         int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
         a.paramsT[l * 4096 + k * 64 + o] = nw;
     }
-    if (a.imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {   // both operand images of the tcgen05 path, as k_nrc_step
-        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
-        int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
-        unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
-        a.imgBf16[dst] = h;
-        a.imgBf16[(5 * 4096 + 1024) + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7)] = h;
-    }
+    if (a.imgBf16 && i < NRC_MLP_WEIGHT_COUNT) tc_store_weight(a.imgBf16, i, nw);   // the operand images of the tcgen05 path, as k_nrc_step
 }
 
 __device__ __forceinline__ float dp_mrhe_update(float w, float g, float lr, float wd)

@@ -19,8 +19,10 @@
 // the reference's scatter (one red.global.add.v2.f32 per corner).
 #include "nrc_internal.cuh"
 #include "strict.cuh"
+#include "mrhe_scatter.cuh"
 
 #define TILE 64          // samples per CTA tile
+#define NRC_HIST_FIRST 21248   // first thread of k_reduce_partials that reduces a histogram entry (a multiple of the block size past the arena)
 #define NTHREADS 256
 
 struct MlpDev {
@@ -201,7 +203,7 @@ __device__ __forceinline__ void zero_acc(float acc[4][4])
 __global__ void __launch_bounds__(NTHREADS, 1) k_train_fp32(const float* __restrict__ pos, const float* __restrict__ dir,
                                                             const float* __restrict__ target, const uint32_t* __restrict__ countDev,
                                                             size_t nMax, float scale, MlpDev w, MrheDev m, float* __restrict__ partialAll,
-                                                            float* __restrict__ predOut)
+                                                            float* __restrict__ predOut, float* gAll, float* __restrict__ histAll)
 {
     extern __shared__ __align__(16) float smem[];
     float* As = smem;                     // [6][64][64]
@@ -379,50 +381,45 @@ __global__ void __launch_bounds__(NTHREADS, 1) k_train_fp32(const float* __restr
             float* t1 = et; et = etn; etn = t1;
             float* t2 = es; es = esn; esn = t2;
         }
-        // ---- hash-table gradient (BackpropMrhe, nrc-train.comp:947-983) ----
+        // ---- dL/dx0 of the 32 hash features -> this sample's scratch row (mrhe_scatter.cuh, phase 1); zeros for dropped samples ----
         {
             int r = tid & 63, h = tid >> 6;
             size_t q = base + r;
-            if (!dropS[r]) {
-                f3 p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
-                f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
-                f3 np = mrhe_norm_pos(p, sky);
-                float2* dtab = reinterpret_cast<float2*>(m.delta);
-                for (int li = 0; li < 4; li++) {
-                    uint32_t level = 4 * h + li;
-                    if (level >= m.L) break;
-                    uint32_t idx[8];
-                    f3 lf;
-                    mrhe_level_indices(p, np, m.res[level], m.T, idx, lf, m.fixed != 0);
-                    float g = es[r * 64 + 2 * level];   // feature 0's error for both features (A9)
-                    float ng = -g;
-                    // fixed preset: feature 1 gets its own error and the gradient lands in its level's table
-                    float ng1 = m.fixed ? -es[r * 64 + 2 * level + 1] : ng;
-                    float2* dl = dtab + (m.fixed ? (size_t)level * m.T : 0);
-#pragma unroll
-                    for (int c = 0; c < 8; c++) {
-                        float xf = (c & 4) ? lf.x : (1.0f - lf.x);
-                        float yf = (c & 2) ? lf.y : (1.0f - lf.y);
-                        float zf = (c & 1) ? lf.z : (1.0f - lf.z);
-                        float wgt = (xf * yf) * zf;
-                        atomicAdd(dl + idx[c], make_float2((ng * wgt) * scale, (ng1 * wgt) * scale));   // no level offset (A10)
-                    }
-                }
+            if (q < n) {
+                const bool dead = dropS[r] != 0;
+                float4* go = reinterpret_cast<float4*>(gAll + q * 32 + 8 * h);
+                const float4* e = reinterpret_cast<const float4*>(es + r * 64 + 8 * h);
+                go[0] = dead ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : e[0];
+                go[1] = dead ? make_float4(0.0f, 0.0f, 0.0f, 0.0f) : e[1];
             }
         }
         __syncthreads();
     }
+    // ---- hash-table gradient (BackpropMrhe, nrc-train.comp:947-983): phase 2, over all tiles of this CTA.
+    // The histogram (parity preset, T <= NRC_HIST_MAX_T) takes over the activation buffers, which are dead now. ----
+    mrhe_scatter_tiles<TILE>(pos, gAll, n, m, scale, histAll ? smem : nullptr, histAll ? histAll + (size_t)blockIdx.x * m.T : nullptr);
     if (tid == 0) partial[20995] = lossAcc;
 }
 
-// grad[i] += sum over CTAs (fixed order) of partial[b][i]; i == 20995 is the mseLoss accumulator.
-__global__ void __launch_bounds__(256) k_reduce_partials(const float* __restrict__ partial, int nb, float* __restrict__ grad)
+// grad[i] += sum over CTAs (fixed order) of partial[b][i]; i == 20995 is the mseLoss accumulator.  Threads past the MLP arena add the
+// CTAs' hash-gradient histograms (mrhe_scatter.cuh) into the head of the delta table: entry h receives the same sum in both features (A9).
+__global__ void __launch_bounds__(256) k_reduce_partials(const float* __restrict__ partial, int nb, float* __restrict__ grad,
+                                                         const float* __restrict__ hist, uint32_t T, float2* __restrict__ delta)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= NRC_MLP_PARAM_COUNT + 1) return;
+    if (i < NRC_MLP_PARAM_COUNT + 1) {
+        float s = 0.0f;
+        for (int b = 0; b < nb; b++) s += partial[(size_t)b * NRC_PARTIAL_STRIDE + i];
+        grad[i] += s;
+        return;
+    }
+    const uint32_t h = (uint32_t)i - NRC_HIST_FIRST;
+    if (hist == nullptr || i < NRC_HIST_FIRST || h >= T) return;
     float s = 0.0f;
-    for (int b = 0; b < nb; b++) s += partial[(size_t)b * NRC_PARTIAL_STRIDE + i];
-    grad[i] += s;
+    for (int b = 0; b < nb; b++) s += hist[(size_t)b * T + h];
+    float2 d = delta[h];
+    d.x += s; d.y += s;
+    delta[h] = d;
 }
 
 // Wt[l][in][out] = W[l][out][in] for the five hidden layers.
@@ -465,10 +462,44 @@ nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
     return NRC_OK;
 }
 
-nrc_status launch_reduce_partials(nrc_mlp* mlp, int blocks, cudaStream_t st)
+nrc_status launch_reduce_partials(nrc_mlp* mlp, nrc_mrhe* m, int blocks, bool hist, cudaStream_t st)
 {
+    const uint32_t T = hist ? m->T : 0u;
+    const unsigned threads = hist ? (NRC_HIST_FIRST + T) : (NRC_MLP_PARAM_COUNT + 1);
     NRC_LAUNCH(mlp->ctx, st, K_REDUCE_PARTIALS,
-               k_reduce_partials<<<(NRC_MLP_PARAM_COUNT + 1 + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad));
+               k_reduce_partials<<<(threads + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad, hist ? mlp->histPartial : nullptr, T,
+                                                                        reinterpret_cast<float2*>(m->delta)));
+    return NRC_OK;
+}
+
+// Scratch of one train launch: the per-CTA partial arenas, one dL/dx0 row per sample, and (parity preset with a table that fits shared
+// memory) one histogram row per CTA.  Grown on demand; a growth waits for the device (the buffers may be in use by a queued launch).
+nrc_status train_scratch(nrc_mlp* mlp, nrc_mrhe* m, size_t n, bool* useHist)
+{
+    const int sms = mlp->ctx->smCount;
+    if (mlp->partialBlocks < sms) {
+        NRC_CUDA(cudaDeviceSynchronize());
+        if (mlp->partial) NRC_CUDA(cudaFree(mlp->partial));
+        mlp->partial = nullptr;
+        NRC_CUDA(cudaMalloc(&mlp->partial, (size_t)sms * NRC_PARTIAL_STRIDE * sizeof(float)));
+        mlp->partialBlocks = sms;
+    }
+    if (mlp->gScratchRows < n) {
+        NRC_CUDA(cudaDeviceSynchronize());
+        if (mlp->gScratch) NRC_CUDA(cudaFree(mlp->gScratch));
+        mlp->gScratch = nullptr; mlp->gScratchRows = 0;
+        const size_t rows = n + n / 4 + 1024;
+        NRC_CUDA(cudaMalloc(&mlp->gScratch, rows * 32 * sizeof(float)));
+        mlp->gScratchRows = rows;
+    }
+    *useHist = !m->fixed && m->T <= NRC_HIST_MAX_T && (m->T % 4u) == 0u;
+    if (*useHist && mlp->histPartialFloats < (size_t)sms * m->T) {
+        NRC_CUDA(cudaDeviceSynchronize());
+        if (mlp->histPartial) NRC_CUDA(cudaFree(mlp->histPartial));
+        mlp->histPartial = nullptr; mlp->histPartialFloats = 0;
+        NRC_CUDA(cudaMalloc(&mlp->histPartial, (size_t)sms * m->T * sizeof(float)));
+        mlp->histPartialFloats = (size_t)sms * m->T;
+    }
     return NRC_OK;
 }
 
@@ -484,18 +515,13 @@ nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
         NRC_CUDA(cudaFuncSetAttribute(k_train_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
+    bool useHist = false;
+    NRC_TRY(train_scratch(mlp, m, n, &useHist));
     size_t tiles = (n + TILE - 1) / TILE;
     int blocks = (int)(tiles < (size_t)mlp->ctx->smCount ? tiles : (size_t)mlp->ctx->smCount);
-    if (blocks > mlp->partialBlocks) {
-        if (mlp->partial) NRC_CUDA(cudaFree(mlp->partial));
-        mlp->partial = nullptr;
-        NRC_CUDA(cudaMalloc(&mlp->partial, (size_t)mlp->ctx->smCount * NRC_PARTIAL_STRIDE * sizeof(float)));
-        mlp->partialBlocks = mlp->ctx->smCount;
-    }
     MlpDev w{mlp->params, mlp->paramsT};
     NRC_LAUNCH(mlp->ctx, st, K_TRAIN_FP32,
-               k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), mlp->partial, pred));
-    NRC_LAUNCH(mlp->ctx, st, K_REDUCE_PARTIALS,
-               k_reduce_partials<<<(NRC_MLP_PARAM_COUNT + 1 + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad));
-    return NRC_OK;
+               k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), mlp->partial, pred,
+                                                            mlp->gScratch, useHist ? mlp->histPartial : nullptr));
+    return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }

@@ -21,36 +21,18 @@
 // bound is 3e-2 of the largest output magnitude (tests/test_gpu_tc.py); the fp32 CUDA-core kernels (mlp_fp32.cu) stay
 // the 1e-3 parity path.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include "nrc_internal.cuh"
 #include "strict.cuh"
 
 #include "tc_ptx.cuh"
 
 
-__global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ params, __nv_bfloat16* __restrict__ img)
+// all four operand images from the packed fp32 arena (the padding of the layer-5 images stays zero from the allocation's memset)
+__global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ params, unsigned short* __restrict__ img)
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 2 * TC_W_ELEMS) return;
-    float v = 0.0f;
-    if (i < TC_W_ELEMS) {
-        if (i < 5 * 4096) {
-            int l = i >> 12, rem = i & 4095, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7;
-            v = params[l * 4096 + n * 64 + kc * 8 + kk];
-        } else {
-            int rem = i - 5 * 4096, kc = rem >> 7, n = (rem >> 3) & 15, kk = rem & 7;
-            if (n < 3) v = params[NRC_W_OFF(5) + n * 64 + kc * 8 + kk];
-        }
-    } else {
-        int j = i - TC_W_ELEMS;
-        if (j < 5 * 4096) {
-            int l = j >> 12, rem = j & 4095, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7;
-            v = params[l * 4096 + (kc * 8 + kk) * 64 + n];
-        } else {
-            int rem = j - 5 * 4096, kc = rem >> 9, n = (rem >> 3) & 63, kk = rem & 7, o = kc * 8 + kk;
-            if (o < 3) v = params[NRC_W_OFF(5) + o * 64 + n];
-        }
-    }
-    img[i] = __float2bfloat16_rn(v);
+    if (i < NRC_MLP_WEIGHT_COUNT) tc_store_weight(img, i, params[i]);
 }
 
 // ---- shared-memory map ----------------------------------------------------------------------------------------------------
@@ -60,13 +42,38 @@ __global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ par
 #define TC_SMEM_BAR (TC_SMEM_BIAS + 336 * 4)      // mbarrier (8 B) + TMEM base slot (4 B)
 #define TC_SMEM_BYTES (TC_SMEM_BAR + 16)
 
-// Encode half of row `r`'s network inputs into the A tile.  half 0: MRHE levels 0-7 + OneBlob theta; half 1: levels
+// Encode half of row `r`'s network inputs into the A tile (SPLIT: into the hi / mid / lo tiles).  half 0: MRHE levels 0-7 + OneBlob theta; half 1: levels
 // 8-15 + OneBlob phi.  Index arithmetic and blends are the strict ones (bit-identical hash indices); only the final
 // rounding to bf16 differs from the fp32 path.
-__device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int half, bool live, f3 p, f3 d, const MrheDev& m, bool& nanIn04)
+// 8 consecutive network inputs of one row as one 16-byte chunk: bf16 (SPLIT = false) or the three bf16 parts hi / mid / lo of the fp32
+// values into three tiles of the same layout (the split-precision forward pass of the train kernel)
+template <bool SPLIT>
+__device__ __forceinline__ void tc_store_chunk(uint4* hi, uint4* mid, uint4* lo, int index, const float* o)
 {
+    if (!SPLIT) {
+        hi[index] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+        return;
+    }
+    uint32_t h[4], m[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) split2_bf16x3(o[2 * j], o[2 * j + 1], h[j], m[j], l[j]);
+    hi[index] = make_uint4(h[0], h[1], h[2], h[3]);
+    mid[index] = make_uint4(m[0], m[1], m[2], m[3]);
+    lo[index] = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+template <bool SPLIT>
+__device__ __forceinline__ void tc_encode_half(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int r, int half, bool live, f3 p, f3 d,
+                                               const MrheDev& m, bool& nanIn04, unsigned short* gate0 = nullptr)
+{
+    // gate0 (training): gate0[4 r + f / 16] bit f % 16 = (network input f > 0) on the fp32 value -- the layer-0 ReLU gate of the reference
+    // (the error of layer 1 is gated by the raw input features).  It cannot be read off the bf16 operand: OneBlob bins a few
+    // sigma away from the angle are fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.
+    unsigned gm = 0u, gb = 0u;
     nanIn04 = false;
     uint4* chunk = reinterpret_cast<uint4*>(aTile);   // chunk(kc, row) = chunk[kc * 128 + row]
+    uint4* chunkM = reinterpret_cast<uint4*>(aMid);
+    uint4* chunkL = reinterpret_cast<uint4*>(aLo);
     f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
     f3 np = mrhe_norm_pos(p, sky);
 #pragma unroll
@@ -96,7 +103,9 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int 
             o[2 * li + 1] = o1;
         }
         if (half == 0 && g == 0) nanIn04 = (o[0] != o[0]) | (o[1] != o[1]) | (o[2] != o[2]) | (o[3] != o[3]) | (o[4] != o[4]);   // train.comp:993-999
-        chunk[(2 * half + g) * TC_ROWS + r] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+#pragma unroll
+        for (int j = 0; j < 8; j++) gm |= (o[j] > 0.0f ? 1u : 0u) << (8 * g + j);
+        tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (2 * half + g) * TC_ROWS + r, o);
     }
     float ang;
     if (half == 0) {
@@ -116,7 +125,13 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, int r, int 
             float t2 = NRC_DIV(NRC_SUB(fi, ang), sigma);
             o[i] = live ? NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2))) : 0.0f;
         }
-        chunk[(4 + 2 * half + g) * TC_ROWS + r] = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+#pragma unroll
+        for (int i = 0; i < 8; i++) gb |= (o[i] > 0.0f ? 1u : 0u) << (8 * g + i);
+        tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (4 + 2 * half + g) * TC_ROWS + r, o);
+    }
+    if (gate0) {
+        gate0[4 * r + half] = (unsigned short)gm;
+        gate0[4 * r + 2 + half] = (unsigned short)gb;
     }
 }
 
@@ -167,7 +182,7 @@ __global__ void __launch_bounds__(TC_THREADS, 3) k_infer_tc(const float* __restr
             d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
         }
         bool nanFlag;
-        tc_encode_half(aTile, row, half, live, p, d, m, nanFlag);
+        tc_encode_half<false>(aTile, nullptr, nullptr, row, half, live, p, d, m, nanFlag);
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
@@ -225,10 +240,14 @@ __global__ void __launch_bounds__(TC_THREADS, 3) k_infer_tc(const float* __restr
 // ---- host launchers -----------------------------------------------------------------------------------------------------------
 nrc_status tc_prepare(nrc_mlp* mlp, cudaStream_t st)
 {
-    if (!mlp->paramsBf16) NRC_CUDA(cudaMalloc(&mlp->paramsBf16, 2 * TC_W_ELEMS * sizeof(uint16_t)));
+    if (!mlp->paramsBf16) {
+        NRC_CUDA(cudaMalloc(&mlp->paramsBf16, TC_IMG_ELEMS * sizeof(uint16_t)));
+        NRC_CUDA(cudaMemsetAsync(mlp->paramsBf16, 0, TC_IMG_ELEMS * sizeof(uint16_t), st));
+        mlp->dirtyBf16 = true;
+    }
     if (mlp->dirtyBf16) {
         NRC_LAUNCH(mlp->ctx, st, K_PACK_BF16,
-                   k_pack_bf16<<<(2 * TC_W_ELEMS + 255) / 256, 256, 0, st>>>(mlp->params, reinterpret_cast<__nv_bfloat16*>(mlp->paramsBf16)));
+                   k_pack_bf16<<<(NRC_MLP_WEIGHT_COUNT + 255) / 256, 256, 0, st>>>(mlp->params, mlp->paramsBf16));
         mlp->dirtyBf16 = false;
     }
     return NRC_OK;
@@ -276,7 +295,7 @@ __global__ void __launch_bounds__(TC_THREADS) k_encode_tiles(const float* __rest
         d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
     }
     bool nanFlag;
-    tc_encode_half(featTiles + tile * 16384, row, half, live, p, d, m, nanFlag);
+    tc_encode_half<false>(featTiles + tile * 16384, nullptr, nullptr, row, half, live, p, d, m, nanFlag);
 }
 
 nrc_status launch_encode_tiles(nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, void* featTiles,
@@ -307,9 +326,22 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 // ==================================================================================================================
 // Training on the tensor cores: EncodeRay + Forward + Backprop (train.comp:703-741, 743-1028) for a tile of 128 samples.
 //
-//   forward   A_{l+1} = relu(A_l W_l^T + b_l)                  tcgen05.mma M=128 (samples) N=64 K=64, as in k_infer_tc;
-//                                                              every A_l stays in shared memory (bf16) for the backward
-//   back-data E_l     = gate(E_{l+1} W_l)                      M=128 N=64 K=64, B = the TRANSPOSED weight image
+//   forward   A_{l+1} = relu(A_l W_l^T + b_l)                  tcgen05.mma M=128 (samples) N=64 K=64 in SPLIT PRECISION: activations and
+//                                                              weights are kept as three bf16 parts (x = hi + mid + lo) and a K step is
+//                                                              six MMAs (hi*hi, hi*mid, mid*hi, hi*lo, lo*hi, mid*mid) into one fp32
+//                                                              accumulator -- the fp32 product to ~2^-24.  Why the forward pass: the
+//                                                              ReLU gates of the WHOLE backward pass are read off the forward
+//                                                              activations, and a plain bf16 forward flips enough of them (|z| below
+//                                                              the rounding noise) to put 8-30 % of error on the hash-table gradient,
+//                                                              whose corner weights are unbounded so that a few samples
+//                                                              dominate an entry.  Measured by emulation (scripts/tc_split_emul.py):
+//                                                              bf16 forward 12-30 %, two-part split 0.4-6 %, three-part split <= 0.75 %
+//                                                              = the floor set by the bf16 backward pass; making the last back-data GEMM
+//                                                              precise instead changes nothing.  The tensor pipe idles in this kernel
+//                                                              (gathers and epilogues bound it), so 6x the forward MMAs are free.
+//                                                              The hi part of every A_l stays in shared memory for the backward pass
+//                                                              (gates, dW operands); mid / lo live only until the next layer has read them.
+//   back-data E_l     = gate(E_{l+1} W_l)                      M=128 N=64 K=64, bf16, B = the TRANSPOSED weight image
 //   dW_l, db_l        = E_{l+1}^T [A_l | 1]                    M=128 (64 out rows + 64 zero rows) N=80 K=128 (the samples):
 //                                                              both operands are written transposed (K = sample) by the
 //                                                              epilogues; the accumulators of all five hidden layers live in
@@ -317,13 +349,19 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 //                                                              once at the end -> per-CTA partials, summed in fixed order by
 //                                                              k_reduce_partials.  No atomics on the MLP parameters.
 //   layer 5 (64 -> 3): forward and back-data on the tensor cores (N = 16 / K = 16 padded), dW5/db5 on CUDA cores.
-//   gates, loss, clamp, NaN guard, the feature-0-for-both / no-level-offset hash scatter: the reference's.
+//   gates, loss, clamp, NaN guard: the reference's.
+//   hash-table gradient: dL/dx0 of every sample goes to a global scratch row; after the last tile the CTA scatters its samples into a
+//   shared-memory histogram (mrhe_scatter.cuh) -- no global atomics in the parity preset.
 // TMEM: columns 0-63 forward/back-data accumulator, 64 + 80*l .. dW_l | db_l (464 of 512 columns).
 // ==================================================================================================================
-#define TT_WF 0                                    // forward weight stage (8 KB); reused for the hash-gradient staging
-#define TT_WB 8192                                 // transposed weight stage (8 KB)
-#define TT_ACT 16384                               // A_0..A_5, 16 KB each, K-major (K = feature)
-#define TT_E (TT_ACT + 6 * 16384)                  // E tile, K-major (K = feature): A operand of the back-data GEMM
+#include "mrhe_scatter.cuh"
+
+#define TT_WF 0                                    // forward weight stages hi | mid | lo, 8 KB each
+#define TT_WB 24576                                // transposed weight stage (8 KB)
+#define TT_ACT 32768                               // A_0..A_5 (hi parts), 16 KB each, K-major (K = feature)
+#define TT_AM (TT_ACT + 6 * 16384)                 // mid part of the current layer's input
+#define TT_E (TT_AM + 16384)                       // E tile, K-major (K = feature): A operand of the back-data GEMM.  During the forward
+#define TT_AL TT_E                                 //   pass the same 16 KB hold the lo part of the current layer's input
 #define TT_ET_LBO (128 * 16 + 16)                  // padded so that the transposing 2-byte stores spread over the banks
 #define TT_ET (TT_E + 16384)                       // E^T, K = sample: 16 chunks x (128 rows x 16 B + pad)
 #define TT_AT_LBO (80 * 16 + 16)
@@ -333,15 +371,29 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 #define TT_PRED (TT_E6 + 2048)                     // [128][4] fp32 predictions
 #define TT_DROP (TT_PRED + 2048)                   // [128] int
 #define TT_LOSS (TT_DROP + 512)                    // [8] float
-#define TT_BAR (TT_LOSS + 64)
+#define TT_GATE0 (TT_LOSS + 64)                    // [128][4] ushort: sign bits of the 64 fp32 network inputs (layer-0 gate)
+#define TT_BAR (TT_GATE0 + 1024)
 #define TT_SMEM_BYTES (TT_BAR + 16)
+#define TT_HIST TT_ACT                             // after the last tile: the hash-gradient histogram (up to 128 KiB = TT_ACT .. TT_ET)
 #define TT_DW_COL(l) (64u + 80u * (uint32_t)(l))
+static_assert(TT_SMEM_BYTES <= 227 * 1024, "k_train_tc shared memory");
+static_assert(TT_HIST + NRC_HIST_MAX_T * 4 <= TT_ET, "histogram overlaps live buffers");
 
 __device__ __forceinline__ void tt_stage8k(unsigned char* dst, const __nv_bfloat16* __restrict__ src, int bytes)
 {
     const uint4* s = reinterpret_cast<const uint4*>(src);
     uint4* d = reinterpret_cast<uint4*>(dst);
     for (int i = threadIdx.x; i < bytes / 16; i += TC_THREADS) d[i] = __ldg(s + i);
+}
+
+// the three parts of layer l's forward weights into the three stages
+__device__ __forceinline__ void tt_stage_fwd(unsigned char* smem, const __nv_bfloat16* __restrict__ wimg, int l)
+{
+    const int bytes = (l < 5) ? 8192 : 2048;
+    const int off = (l < 5) ? l * 4096 : 5 * 4096;
+    tt_stage8k(smem + TT_WF, wimg + off, bytes);
+    tt_stage8k(smem + TT_WF + 8192, wimg + TC_IMG_MID + off, bytes);
+    tt_stage8k(smem + TT_WF + 16384, wimg + TC_IMG_LO + off, bytes);
 }
 
 // element (feature m, sample k) of a K=sample operand
@@ -353,7 +405,8 @@ __device__ __forceinline__ void tt_store_t(unsigned char* base, uint32_t lbo, in
 __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restrict__ pos, const float* __restrict__ dir,
                                                             const float* __restrict__ target, size_t n, float scale,
                                                             const __nv_bfloat16* __restrict__ wimg, const float* __restrict__ params, MrheDev m,
-                                                            float* __restrict__ partialAll, float* __restrict__ predOut)
+                                                            float* __restrict__ partialAll, float* __restrict__ predOut, float* gAll,
+                                                            float* __restrict__ histAll)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     float* biasS = reinterpret_cast<float*>(smem + TT_BIAS);
@@ -363,7 +416,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     float* lossS = reinterpret_cast<float*>(smem + TT_LOSS);
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + TT_BAR);
     uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(smem + TT_BAR + 8);
-    float* gS = reinterpret_cast<float*>(smem + TT_WF);   // [128][16] hash-gradient staging (the forward stage is idle then)
+    unsigned short* gate0S = reinterpret_cast<unsigned short*>(smem + TT_GATE0);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int quad = warp & 3, half = warp >> 2;
@@ -401,55 +454,66 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
             p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
             d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
         }
-        // ---- encode into A_0 (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
+        // ---- encode into A_0 = hi + mid + lo (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
         bool nanFlag;
-        tc_encode_half(smem + TT_ACT, row, half, inRange, p, d, m, nanFlag);
+        tc_encode_half<true>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, row, half, inRange, p, d, m, nanFlag, gate0S);
         if (half == 0) dropS[row] = (!inRange || nanFlag) ? 1 : 0;
-        tt_stage8k(smem + TT_WF, wimg, 8192);
+        tt_stage_fwd(smem, wimg, 0);
         __syncthreads();
         const bool dropped = dropS[row] != 0;
         if (dropped) {   // a dropped sample contributes nothing: zero its inputs (its error rows are zeroed below)
-            uint4* chunk = reinterpret_cast<uint4*>(smem + TT_ACT);
-            for (int c = 4 * half; c < 4 * half + 4; c++) chunk[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+            for (int c = 4 * half; c < 4 * half + 4; c++) {
+                reinterpret_cast<uint4*>(smem + TT_ACT)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+                reinterpret_cast<uint4*>(smem + TT_AM)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+                reinterpret_cast<uint4*>(smem + TT_AL)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+            }
         }
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
-        // ---- forward (train.comp:715-741) ----
+        // ---- forward (train.comp:715-741), split precision ----
 #pragma unroll 1
         for (int l = 0; l < 6; l++) {
-            const uint32_t actIn = sBase + TT_ACT + (uint32_t)l * 16384u;
             if (tid == 0) {
                 tc_fence_after();
                 const uint32_t nOut = (l < 5) ? 64u : 16u;
                 const uint32_t idesc = umma_idesc(TC_ROWS, nOut);
                 const uint32_t wLbo = nOut * 16u;
+                const uint32_t aH = sBase + TT_ACT + (uint32_t)l * 16384u, aM = sBase + TT_AM, aL = sBase + TT_AL;
+                const uint32_t wH = sBase + TT_WF, wM = wH + 8192u, wL = wH + 16384u;
 #pragma unroll
-                for (int ks = 0; ks < 4; ks++)
-                    umma_bf16(tmemBase, umma_desc(actIn + ks * 4096, 2048, 128), umma_desc(sBase + TT_WF + ks * 2 * wLbo, wLbo, 128), idesc,
-                              ks > 0 ? 1u : 0u);
+                for (int ks = 0; ks < 4; ks++) {
+                    const uint32_t ao = (uint32_t)ks * 4096u, wo = (uint32_t)ks * 2u * wLbo;
+                    // smallest partial products first
+                    umma_bf16(tmemBase, umma_desc(aM + ao, 2048, 128), umma_desc(wM + wo, wLbo, 128), idesc, ks > 0 ? 1u : 0u);
+                    umma_bf16(tmemBase, umma_desc(aL + ao, 2048, 128), umma_desc(wH + wo, wLbo, 128), idesc, 1u);
+                    umma_bf16(tmemBase, umma_desc(aH + ao, 2048, 128), umma_desc(wL + wo, wLbo, 128), idesc, 1u);
+                    umma_bf16(tmemBase, umma_desc(aM + ao, 2048, 128), umma_desc(wH + wo, wLbo, 128), idesc, 1u);
+                    umma_bf16(tmemBase, umma_desc(aH + ao, 2048, 128), umma_desc(wM + wo, wLbo, 128), idesc, 1u);
+                    umma_bf16(tmemBase, umma_desc(aH + ao, 2048, 128), umma_desc(wH + wo, wLbo, 128), idesc, 1u);
+                }
                 umma_commit(bar);
             }
             mbar_wait(bar, phase);
             phase ^= 1u;
             tc_fence_after();
-            // the forward stage is free again: fetch the next layer's weights (or the first backward stage) behind the epilogue
-            if (l < 4) tt_stage8k(smem + TT_WF, wimg + (l + 1) * 4096, 8192);
-            else if (l == 4) tt_stage8k(smem + TT_WF, wimg + 5 * 4096, 2048);
-            else tt_stage8k(smem + TT_WB, wimg + TC_W_ELEMS + 5 * 4096, 2048);     // W5^T: 64 rows x K 16
+            // the forward stages are free again: fetch the next layer's weights (or the first backward stage) behind the epilogue
+            if (l < 5) tt_stage_fwd(smem, wimg, l + 1);
+            else tt_stage8k(smem + TT_WB, wimg + TC_IMG_T + 5 * 4096, 2048);     // W5^T: 64 rows x K 16
             if (l < 5) {
                 uint32_t v[32];
                 tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
                 tmem_ld_wait();
                 const float* b = biasS + l * 64 + half * 32;
-                uint4* chunk = reinterpret_cast<uint4*>(smem + TT_ACT + (l + 1) * 16384);
+                uint4* cH = reinterpret_cast<uint4*>(smem + TT_ACT + (l + 1) * 16384);
+                uint4* cM = reinterpret_cast<uint4*>(smem + TT_AM);
+                uint4* cL = reinterpret_cast<uint4*>(smem + TT_AL);
 #pragma unroll
                 for (int c = 0; c < 4; c++) {
                     float x[8];
 #pragma unroll
                     for (int j = 0; j < 8; j++) x[j] = fmaxf(__uint_as_float(v[8 * c + j]) + b[8 * c + j], 0.0f);
-                    chunk[(4 * half + c) * TC_ROWS + row] =
-                        make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]), pack_bf16(x[6], x[7]));
+                    tc_store_chunk<true>(cH, cM, cL, (4 * half + c) * TC_ROWS + row, x);
                 }
             } else if (half == 0) {
                 // ---- output, loss, output error with the layer-5 gate (train.comp:1002-1012, 746-749) ----
@@ -467,7 +531,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                         float tg = fminf(__ldg(target + 3 * q + j), 1024.0f);
                         err = y - tg;
                         lsum += err * err;
-                        bool gate = (a5[j] & 0x7fffu) != 0u && (a5[j] & 0x8000u) == 0u;     // bf16 value > 0
+                        bool gate = (a5[j] & 0x7fffu) != 0u && (a5[j] & 0x8000u) == 0u;     // hi part > 0  <=>  value > 0
                         e[j] = gate ? 2.0f * err : 0.0f;
                     }
                     predS[row * 4 + j] = dropped ? 0.0f : y;
@@ -478,7 +542,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
 #pragma unroll
                     for (int j = 0; j < 3; j++) predOut[3 * q + j] = predS[row * 4 + j];
                 }
-                // E_6 as the A operand of the layer-5 back-data GEMM (K = 16: two chunks)
+                // E_6 as the A operand of the layer-5 back-data GEMM (K = 16: two chunks); the lo part that lived here is dead
                 uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
                 echunk[row] = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], 0.0f), 0u, 0u);
                 echunk[TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
@@ -536,9 +600,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
             tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
             tmem_ld_wait();
             if (L >= 1) {
-                tt_stage8k(smem + TT_WB, wimg + TC_W_ELEMS + (L - 1) * 4096, 8192);
+                tt_stage8k(smem + TT_WB, wimg + TC_IMG_T + (L - 1) * 4096, 8192);
                 const uint4* aprev = reinterpret_cast<const uint4*>(smem + TT_ACT + (L - 1) * 16384);
                 uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
+                // gates: A_{L-1} > 0.  Hidden activations: the sign of the hi part; the network inputs (L == 1): the exact fp32 signs
+                const uint32_t g0 = (uint32_t)gate0S[4 * row + 2 * half] | ((uint32_t)gate0S[4 * row + 2 * half + 1] << 16);
 #pragma unroll
                 for (int c = 0; c < 4; c++) {
                     uint4 a = aprev[(4 * half + c) * TC_ROWS + row];       // A_{L-1}[row][32h + 8c .. +7]
@@ -548,8 +614,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                     for (int j2 = 0; j2 < 4; j2++) {
                         unsigned short alo = (unsigned short)(aw[j2] & 0xffffu), ahi = (unsigned short)(aw[j2] >> 16);
                         float elo = __uint_as_float(v[8 * c + 2 * j2]), ehi = __uint_as_float(v[8 * c + 2 * j2 + 1]);
-                        if (!((alo & 0x7fffu) != 0u && (alo & 0x8000u) == 0u)) elo = 0.0f;    // gate: A_{L-1} > 0
-                        if (!((ahi & 0x7fffu) != 0u && (ahi & 0x8000u) == 0u)) ehi = 0.0f;
+                        bool openLo = (alo & 0x7fffu) != 0u && (alo & 0x8000u) == 0u, openHi = (ahi & 0x7fffu) != 0u && (ahi & 0x8000u) == 0u;
+                        if (L == 1) { openLo = (g0 >> (8 * c + 2 * j2)) & 1u; openHi = (g0 >> (8 * c + 2 * j2 + 1)) & 1u; }
+                        if (!openLo) elo = 0.0f;
+                        if (!openHi) ehi = 0.0f;
                         ew[j2] = pack_bf16(elo, ehi);
                         const int f = 32 * half + 8 * c + 2 * j2;
                         tt_store_t(smem + TT_ET, TT_ET_LBO, f, row, (unsigned short)(ew[j2] & 0xffffu));
@@ -559,39 +627,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                     }
                     echunk[(4 * half + c) * TC_ROWS + row] = make_uint4(ew[0], ew[1], ew[2], ew[3]);
                 }
-            } else if (half == 0) {
-                // dX_0: the hash encoding's gradient lives in features 0..31 (feature 2*level is used for both features, A9)
+            } else if (half == 0 && inRange) {
+                // dX_0: the hash encoding's gradient lives in features 0..31 -> this sample's scratch row (mrhe_scatter.cuh, phase 1)
+                float4* go = reinterpret_cast<float4*>(gAll + q * 32);
 #pragma unroll
-                for (int lv = 0; lv < 16; lv++) gS[row * 16 + lv] = __uint_as_float(v[2 * lv]);
+                for (int j = 0; j < 8; j++)
+                    go[j] = dropped ? make_float4(0.0f, 0.0f, 0.0f, 0.0f)
+                                    : make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                                                  __uint_as_float(v[4 * j + 3]));
             }
             fence_async_smem();
             tc_fence_before();
             __syncthreads();
         }
-        // ---- hash-table gradient (BackpropMrhe, train.comp:947-983): thread (row, half) -> 8 levels ----
-        if (!dropped) {
-            f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
-            f3 np = mrhe_norm_pos(p, sky);
-            float2* dtab = reinterpret_cast<float2*>(m.delta);
-            for (int li = 0; li < 8; li++) {
-                uint32_t level = 8 * half + li;
-                if (level >= m.L) break;
-                uint32_t idx[8];
-                f3 lf;
-                mrhe_level_indices(p, np, m.res[level], m.T, idx, lf, m.fixed != 0);
-                float ng = -gS[row * 16 + level];
-#pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    float xf = (c & 4) ? lf.x : (1.0f - lf.x);
-                    float yf = (c & 2) ? lf.y : (1.0f - lf.y);
-                    float zf = (c & 1) ? lf.z : (1.0f - lf.z);
-                    float dlt = (ng * ((xf * yf) * zf)) * scale;
-                    atomicAdd(dtab + idx[c], make_float2(dlt, dlt));   // no level offset (A10)
-                }
-            }
-        }
-        __syncthreads();   // gS (the forward weight stage) is rewritten by the next tile
     }
+    // ---- hash-table gradient (BackpropMrhe, train.comp:947-983): phase 2, over all tiles of this CTA ----
+    mrhe_scatter_tiles<TC_ROWS>(pos, gAll, n, m, scale, histAll ? reinterpret_cast<float*>(smem + TT_HIST) : nullptr,
+                                histAll ? histAll + (size_t)blockIdx.x * m.T : nullptr);
     // ---- gradients out: TMEM -> this CTA's partial arena (negative gradient times ONE_OVER_PIXEL_COUNT, A8) ----
     tc_fence_after();
     if (quad < 2) {
@@ -622,7 +674,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     if (warp == 0) tmem_dealloc(tmemBase, 512);
 }
 
-nrc_status launch_reduce_partials(nrc_mlp* mlp, int blocks, cudaStream_t st);   // mlp_fp32.cu
+nrc_status launch_reduce_partials(nrc_mlp* mlp, nrc_mrhe* m, int blocks, bool hist, cudaStream_t st);   // mlp_fp32.cu
+nrc_status train_scratch(nrc_mlp* mlp, nrc_mrhe* m, size_t n, bool* useHist);                            // mlp_fp32.cu
 
 nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
                            float* pred, cudaStream_t st)
@@ -637,17 +690,17 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
         NRC_CUDA(cudaFuncSetAttribute(k_train_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
         attr = true;
     }
+    bool useHist = false;
+    NRC_TRY(train_scratch(mlp, m, n, &useHist));
     size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     int blocks = (int)(tiles < (size_t)mlp->ctx->smCount ? tiles : (size_t)mlp->ctx->smCount);
-    if (blocks > mlp->partialBlocks) {
-        if (mlp->partial) NRC_CUDA(cudaFree(mlp->partial));
-        mlp->partial = nullptr;
-        NRC_CUDA(cudaMalloc(&mlp->partial, (size_t)mlp->ctx->smCount * NRC_PARTIAL_STRIDE * sizeof(float)));
-        mlp->partialBlocks = mlp->ctx->smCount;
-    }
+    static int capEnv = -1;   // NRC_TRAIN_TC_BLOCKS: cap on the CTAs of the train kernel (experiments)
+    if (capEnv < 0) { const char* e = getenv("NRC_TRAIN_TC_BLOCKS"); capEnv = e ? atoi(e) : 0; }
+    if (capEnv > 0 && blocks > capEnv) blocks = capEnv;
     NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
                k_train_tc<<<blocks, TC_THREADS, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale,
                                                                      reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16), mlp->params,
-                                                                     make_mrhe_dev(m), mlp->partial, pred));
-    return launch_reduce_partials(mlp, blocks, st);
+                                                                     make_mrhe_dev(m), mlp->partial, pred, mlp->gScratch,
+                                                                     useHist ? mlp->histPartial : nullptr));
+    return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }

@@ -96,6 +96,10 @@ struct nrc_mlp {
     float* paramsT = nullptr;    // transposed weight copy Wt[l][in][out] for the forward GEMMs (5*4096 + 64*4)
     float* partial = nullptr;    // per-block partial gradients of the train kernel [maxBlocks][NRC_PARTIAL_STRIDE]
     int partialBlocks = 0;
+    float* gScratch = nullptr;   // [rows][32] dL/dx0 of the hash features, phase 1 -> phase 2 of the train kernels (mrhe_scatter.cuh)
+    size_t gScratchRows = 0;
+    float* histPartial = nullptr;   // [smCount][T] per-CTA hash-gradient histograms of the last train launch (parity preset, small T)
+    size_t histPartialFloats = 0;
     uint16_t* paramsBf16 = nullptr;  // bf16 operand images for the tcgen05 path (built on demand)
     // opt-in Adam: second moment + bias correction; the reference's step is first-moment momentum only (A16)
     bool adam = false;
@@ -225,6 +229,9 @@ nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
                              float* rgb, cudaStream_t st);
 nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n,
                              float lossScale, float* pred, cudaStream_t st);
+// per-launch scratch of both train kernels: partial arenas, the dL/dx0 rows, the per-CTA histograms (useHist: the shared-memory path applies)
+nrc_status train_scratch(nrc_mlp* mlp, nrc_mrhe* m, size_t n, bool* useHist);
+nrc_status launch_reduce_partials(nrc_mlp* mlp, nrc_mrhe* m, int blocks, bool hist, cudaStream_t st);
 // steps.cu
 nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st);
 nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st);

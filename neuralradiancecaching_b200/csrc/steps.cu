@@ -7,6 +7,7 @@
 // Both are pure streaming kernels: grid sized in multiples of the SM count, float4 accesses, no reuse.
 #include <cuda_bf16.h>
 #include "nrc_internal.cuh"
+#include "tc_ptx.cuh"
 
 __device__ __forceinline__ bool bad_value(float x) { return (x != x) || (fabsf(x) == INFINITY) || (fabsf(x) > 1000.0f); }
 __device__ __forceinline__ float sign_nan0(float x) { return (x > 0.0f) ? 1.0f : ((x < 0.0f) ? -1.0f : 0.0f); }
@@ -33,15 +34,7 @@ __global__ void __launch_bounds__(256) k_nrc_step(float* __restrict__ params, fl
         int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
         paramsT[l * 4096 + k * 64 + o] = nw;
     }
-    if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {   // operand image of the tcgen05 path (layout: mlp_tc.cu)
-        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
-        int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
-        unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
-        imgBf16[dst] = h;
-        // transposed image (rows = in, K = out); layer 5 has K = 16
-        int dstT = (5 * 4096 + 1024) + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7);
-        imgBf16[dstT] = h;
-    }
+    if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) tc_store_weight(imgBf16, i, nw);   // operand images of the tcgen05 path (tc_ptx.cuh)
 }
 
 // Opt-in Adam (the oracle's NrcStep with S.adam): the same scrub / weight decay / first moment as above, then
@@ -69,14 +62,7 @@ __global__ void __launch_bounds__(256) k_nrc_step_adam(float* __restrict__ param
         int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
         paramsT[l * 4096 + k * 64 + o] = nw;
     }
-    if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) {
-        int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
-        int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
-        unsigned short h = __bfloat16_as_ushort(__float2bfloat16_rn(nw));
-        imgBf16[dst] = h;
-        int dstT = (5 * 4096 + 1024) + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7);
-        imgBf16[dstT] = h;
-    }
+    if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) tc_store_weight(imgBf16, i, nw);
 }
 
 __device__ __forceinline__ float mrhe_update_adam(float w, float g, float& m1, float& m2, float lr, float wd, float beta1, float beta2, float eps,

@@ -14,6 +14,12 @@
 // transposed image at TC_W_ELEMS (B operand of the back-data GEMM e*W: rows n = in, K = out):
 //   layer l < 5 at l*4096: (k/8)*512 + n*8 + k%8 with k = out ; layer 5 at 20480: K = 16 (3 real outputs), same formula
 #define TC_W_ELEMS (5 * 4096 + 1024)
+// The training kernel's FORWARD pass runs in split precision (bf16x3: w = hi + mid + lo, each a bf16; six partial products per K step
+// reproduce the fp32 product to ~2^-24): two more forward images, same layout as the first, hold the mid and lo parts.
+#define TC_IMG_T TC_W_ELEMS              // transposed image
+#define TC_IMG_MID (2 * TC_W_ELEMS)      // forward image, mid part
+#define TC_IMG_LO (3 * TC_W_ELEMS)       // forward image, lo part
+#define TC_IMG_ELEMS (4 * TC_W_ELEMS)
 
 // ---- PTX wrappers ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -117,5 +123,39 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
 {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// x = hi + mid + lo with three bf16 parts (round to nearest each; the residuals are exact in fp32)
+__device__ __forceinline__ void split_bf16x3(float x, unsigned short& hi, unsigned short& mid, unsigned short& lo)
+{
+    hi = __bfloat16_as_ushort(__float2bfloat16_rn(x));
+    const float r1 = x - __uint_as_float((uint32_t)hi << 16);
+    mid = __bfloat16_as_ushort(__float2bfloat16_rn(r1));
+    const float r2 = r1 - __uint_as_float((uint32_t)mid << 16);
+    lo = __bfloat16_as_ushort(__float2bfloat16_rn(r2));
+}
+
+// the same for a pair, packed like pack_bf16 (first value in the low half)
+__device__ __forceinline__ void split2_bf16x3(float a, float b, uint32_t& hi, uint32_t& mid, uint32_t& lo)
+{
+    hi = pack_bf16(a, b);
+    const float ra = a - __uint_as_float(hi << 16), rb = b - __uint_as_float(hi & 0xffff0000u);
+    mid = pack_bf16(ra, rb);
+    const float sa = ra - __uint_as_float(mid << 16), sb = rb - __uint_as_float(mid & 0xffff0000u);
+    lo = pack_bf16(sa, sb);
+}
+
+// One MLP weight (packed arena index i < 20 672, value w) into all four operand images (layouts above): the forward image and its
+// mid / lo parts, and the transposed image.  Called by k_pack_bf16 and by every optimiser-step kernel, so the images never go stale.
+__device__ __forceinline__ void tc_store_weight(unsigned short* __restrict__ img, int i, float w)
+{
+    const int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+    const int dst = (l < 5) ? (l * 4096 + (k >> 3) * 512 + o * 8 + (k & 7)) : (5 * 4096 + (k >> 3) * 128 + o * 8 + (k & 7));
+    unsigned short hi, mid, lo;
+    split_bf16x3(w, hi, mid, lo);
+    img[dst] = hi;
+    img[TC_IMG_MID + dst] = mid;
+    img[TC_IMG_LO + dst] = lo;
+    img[TC_IMG_T + l * 4096 + (o >> 3) * 512 + k * 8 + (o & 7)] = hi;   // rows = in, K = out; layer 5 has K = 16
 }
 

@@ -4,7 +4,7 @@ run() {
   local spec="$1"
   local envs="${spec%%--*}"
   local args=""
-  if [[ "$spec" == *"--"* ]]; then args="--${spec#*--}"; fi
+  if [[ "$spec" == *" -- "* ]]; then args="${spec#* -- }"; envs="${spec%% -- *}"; fi
   echo "== env[$envs] args[$args]"
   env $envs timeout 300 python bench.py --steps 20 --warmup 3 --no-cpu-baseline --no-fp32-line --no-fit --no-side $args 2>gpurun_out/sweep_last.err | tail -1 | python -c "
 import json,sys
