@@ -414,11 +414,19 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
     if (noAhead < 0) { const char* e = getenv("NRC_NO_TRAIN_AHEAD"); noAhead = (e && atoi(e)) ? 1 : 0; }
     const bool ahead = !(noOverlap || noAhead);
-    static int walkStreams = -1;
-    if (walkStreams < 0) {
+    // Walks in flight: enough to hide the walk's latency (~2.5 ms beside the other kernels) behind the frame time, no more -- measured
+    // (profiles/r02_walks_in_flight.md): a 1080p frame (2.9 ms) is fastest with one walk at a time (2.92 vs 3.26 ms with three), a 720p
+    // frame (1.8-1.9 ms) with two or three (1.82-1.9 vs 2.15 ms with one).  NRC_TRAIN_WALK=n overrides the choice.
+    static int walkEnv = -1;
+    if (walkEnv < 0) {
         const char* e = getenv("NRC_TRAIN_WALK");
-        walkStreams = e ? atoi(e) : NRC_TRAIN_WALK_STREAMS;
-        if (walkStreams < 1 || walkStreams > NRC_TRAIN_WALK_STREAMS) walkStreams = NRC_TRAIN_WALK_STREAMS;
+        walkEnv = e ? atoi(e) : 0;
+        if (walkEnv < 0 || walkEnv > NRC_TRAIN_WALK_STREAMS) walkEnv = 0;
+    }
+    int walkStreams = walkEnv;
+    if (walkStreams == 0) {
+        const size_t px = (size_t)part_count(r->y0, r->y1, r->ystride) * r->width;
+        walkStreams = px >= 1500000 ? 1 : (px >= 600000 ? 2 : 3);
     }
     cudaStream_t tw = ahead ? ctx->streamWalk[r->trainSeq % (unsigned)walkStreams] : st;
     cudaStream_t tl = ahead ? ctx->stream4 : st;
