@@ -217,6 +217,14 @@ NRC_API nrc_status nrc_mlp_forward_tiles(nrc_mlp* mlp, const void* featTiles, si
  * pred[N][3] (optional) receives the network outputs. */
 NRC_API nrc_status nrc_train_accumulate(nrc_mlp* mlp, nrc_mrhe* mrhe, const float* pos, const float* dir, const float* target, size_t n,
                                         float lossScale, float* pred);
+/* No counterpart in the reference.  nrc_train_accumulate for callers that cannot call
+ * cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it): always the fp32 kernel, pos / dir / target / pred
+ * must be DEVICE memory, n <= nrc_train_accumulate_static_max_samples() (8192; larger n is rejected with NRC_ERR_INVALID).  Calls no
+ * cudaMalloc / cudaFree: its scratch is one file-scope __device__ array (~3.4 MB per GPU, held until the process exits) shared by every
+ * call -- calls whose kernels overlap on one GPU (different contexts / streams) race on it; calls on one context are stream-ordered. */
+NRC_API size_t nrc_train_accumulate_static_max_samples(void);
+NRC_API nrc_status nrc_train_accumulate_static(nrc_mlp* mlp, nrc_mrhe* mrhe, const float* pos, const float* dir, const float* target, size_t n,
+                                               float lossScale, float* pred);
 /* nrc-step.comp:394-406 then mrhe-step.comp:63-74 (either handle may be NULL to skip it). */
 NRC_API nrc_status nrc_optimizer_step(nrc_mlp* mlp, nrc_mrhe* mrhe);
 

@@ -525,3 +525,74 @@ nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
                                                             mlp->gScratch, useHist ? mlp->histPartial : nullptr));
     return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }
+
+// ---- allocation-free training entry point (no counterpart in the reference) ----------
+// nrc_train_accumulate_static: Backprop() over up to NRC_STATIC_MAX_SAMPLES device-resident records with the fp32 kernel above, for
+// callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  The scratch the train
+// kernel needs -- per-CTA partial gradient arenas, one dL/dx0 row per sample, per-CTA hash-gradient histograms -- lives in ONE
+// file-scope __device__ array of fixed size (about 3.4 MB, held by every GPU that loads the library until the process exits).
+// Every call shares that array and it keeps the last call's contents: the kernel itself rewrites every word it later reads (each CTA
+// zeroes its partial arena first, writes the dL/dx0 rows of all samples < n before phase 2 reads them, and stores its whole histogram
+// row), so nothing has to be cleared between calls -- but two calls whose kernels overlap on the GPU (different streams / contexts of
+// one device) race on it.  Calls on one context are stream-ordered and safe.
+#define NRC_STATIC_MAX_BLOCKS 16
+#define NRC_STATIC_MAX_SAMPLES 8192
+#define NRC_STATIC_MAX_T 16384
+#define NRC_STATIC_PARTIAL_FLOATS (NRC_STATIC_MAX_BLOCKS * NRC_PARTIAL_STRIDE)
+#define NRC_STATIC_G_FLOATS (NRC_STATIC_MAX_SAMPLES * 32)
+#define NRC_STATIC_HIST_FLOATS (NRC_STATIC_MAX_BLOCKS * NRC_STATIC_MAX_T)
+#define NRC_STATIC_FLOATS (NRC_STATIC_PARTIAL_FLOATS + NRC_STATIC_G_FLOATS + NRC_STATIC_HIST_FLOATS)
+static __device__ __align__(256) float g_staticTrainScratch[NRC_STATIC_FLOATS];
+
+// In host code the array's name is only a stand-in: the device address comes from cudaGetSymbolAddress, once per device, with that
+// device current.
+#define NRC_STATIC_MAX_DEVICES 64
+static float* g_staticTrainScratchDev[NRC_STATIC_MAX_DEVICES] = {nullptr};
+
+extern "C" size_t nrc_train_accumulate_static_max_samples(void) { return NRC_STATIC_MAX_SAMPLES; }
+
+extern "C" nrc_status nrc_train_accumulate_static(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n,
+                                                  float lossScale, float* pred)
+{
+    NRC_REQUIRE(mlp && m && pos && dir && target, "null argument");
+    NRC_REQUIRE(mlp->ctx == m->ctx, "mlp and mrhe belong to different contexts");
+    NRC_REQUIRE(n <= NRC_STATIC_MAX_SAMPLES, "nrc_train_accumulate_static: more than 8192 samples (the static scratch is sized for that); "
+                                             "use nrc_train_accumulate or split the batch");
+    NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
+    NRC_REQUIRE(nrc_is_device_ptr(pos) && nrc_is_device_ptr(dir) && nrc_is_device_ptr(target) && (!pred || nrc_is_device_ptr(pred)),
+                "nrc_train_accumulate_static takes device memory only (staging host buffers would allocate)");
+    if (n == 0) return NRC_OK;
+    nrc_ctx* ctx = mlp->ctx;
+    NRC_REQUIRE(ctx->device >= 0 && ctx->device < NRC_STATIC_MAX_DEVICES, "device index out of range for the static scratch");
+    NRC_CUDA(cudaSetDevice(ctx->device));
+    if (!g_staticTrainScratchDev[ctx->device]) {
+        float* p = nullptr;
+        NRC_CUDA(cudaGetSymbolAddress((void**)&p, g_staticTrainScratch));
+        g_staticTrainScratchDev[ctx->device] = p;
+    }
+    float* scratch = g_staticTrainScratchDev[ctx->device];
+    float* partial = scratch;
+    float* gRows = scratch + NRC_STATIC_PARTIAL_FLOATS;
+    float* hist = gRows + NRC_STATIC_G_FLOATS;
+    const bool useHist = !m->fixed && m->T <= NRC_STATIC_MAX_T && (m->T % 4u) == 0u;   // larger tables / fixed preset: global atomics
+    cudaStream_t st = ctx->stream;
+    NRC_TRY(launch_mlp_prepare(mlp));
+    static bool attr = false;
+    const size_t smem = TRAIN_SMEM_FLOATS * sizeof(float);
+    if (!attr) {
+        NRC_CUDA(cudaFuncSetAttribute(k_train_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = true;
+    }
+    const size_t tiles = (n + TILE - 1) / TILE;
+    const int blocks = (int)(tiles < NRC_STATIC_MAX_BLOCKS ? tiles : NRC_STATIC_MAX_BLOCKS);
+    MlpDev w{mlp->params, mlp->paramsT};
+    NRC_LAUNCH(ctx, st, K_TRAIN_FP32,
+               k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), partial, pred, gRows,
+                                                            useHist ? hist : nullptr));
+    const uint32_t T = useHist ? m->T : 0u;
+    const unsigned threads = useHist ? (NRC_HIST_FIRST + T) : (NRC_MLP_PARAM_COUNT + 1);
+    NRC_LAUNCH(ctx, st, K_REDUCE_PARTIALS,
+               k_reduce_partials<<<(threads + 255) / 256, 256, 0, st>>>(partial, blocks, mlp->grad, useHist ? hist : nullptr, T,
+                                                                        reinterpret_cast<float2*>(m->delta)));
+    return NRC_OK;
+}
