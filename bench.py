@@ -88,8 +88,7 @@ def scene_inputs(width, height, grid_scale=1, table_size=16384):
     from neuralradiancecaching_b200.objects import Camera, vec_from_angles
     dens = S.cloud_density()                      # 125 x 85 x 153, deterministic (SHA-256 in BASELINE.md)
     if grid_scale > 1:                            # config 5: the "full" cloud = the sixteenth-size grid refined per axis
-        from scipy import ndimage
-        dens = np.clip(ndimage.zoom(dens, grid_scale, order=1), 0.0, 1.0).astype(np.float32)
+        dens = S.refined_density(grid_scale)
     env = S.sky_envmap(1024, 512)                 # the shape of data/image/photostudio.hdr
     cam = Camera((0.0, 0.0, -64.0), (0.0, 0.0, 1.0), (0.0, 1.0, 0.0), width / float(height), np.radians(60.0), 0.1, 100.0)
     return dict(density=dens, env=env, cam=cam, dir_dir=vec_from_angles(-1.57, 0.0), params=S.mlp_init(1), tables=S.table_init(2, 16, table_size, 2))
@@ -108,6 +107,137 @@ def lcg_randoms(n, seed=0x2545F491):
 
 
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
+class Workload:
+    """One BASELINE configuration set up on this rank's GPU: scene objects, renderer, this rank's partition, the gradient exchange."""
+
+    def __init__(self, args, ctx, rank, world, local, W, H, TW, TH, grid_scale=1, table_size=16384, exchange=None):
+        import torch
+        import neuralradiancecaching_b200 as N
+        from neuralradiancecaching_b200 import _lib as L
+        from neuralradiancecaching_b200.dist import GradientExchange, FusedExchange
+        self.N, self.L, self.ctx, self.rank, self.world, self.local = N, L, ctx, rank, world, local
+        self.W, self.H, self.TW, self.TH, self.grid_scale, self.table_size = W, H, TW, TH, grid_scale, table_size
+        self.inp = inp = scene_inputs(W, H, grid_scale, table_size)
+        self.vol = N.VolumeData(ctx, inp["density"])
+        self.vol.useNN = 1
+        self.env = N.HdrEnvMap(ctx, 1024, 512, inp["env"])
+        self.dl = N.DirLight(-1.57, 0.0, (1, 1, 1), 1.0)      # strengths 1.0: the reference default 0 makes the target == 0 (SURVEY finding 9)
+        self.pl = N.PointLight((0, 0, 0), (1, 1, 1), 1.0)
+        self.nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
+        self.nrc.set_params(inp["params"])
+        self.mrhe = N.MRHE(ctx, 0.01, 0.0, 16, table_size, 2, seed=0)
+        self.mrhe.set_tables(inp["tables"])
+        self.r = N.NrcHpmRenderer(W, H, TW, TH, inp["cam"], self.vol, self.dl, self.pl, self.env, self.nrc, self.mrhe)
+        if world > 1:
+            self.r.SetPartitionStrided(rank, world, rank, world)
+        # Render vertex pool, vertices per path (NRC_BENCH_POOL; 0 = the library default of 4, grown and re-traced on overflow).  32 cannot
+        # overflow, so no read has to wait on the host for the overflow flag of the frame it hands out: e2e 2.93 instead of 3.00 ms/frame;
+        # 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are for.  Larger per-rank frames keep the library default.
+        self.pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "32" if (W * H // world) <= 2304 * 1296 else "0"))
+        if self.pool_per_path > 0:
+            self.r.SetPoolCapacity(-(-H // world) * W * self.pool_per_path)      # the rank with the most rows
+        dev = torch.device("cuda", local)
+        self.exchange = GradientExchange(ctx, self.nrc, self.mrhe, dev)
+        self.ext = self.exchange.stream
+        kind = exchange or args.exchange
+        if 2 * table_size > (1 << 20) and not os.environ.get("NRC_DP_BIG"):
+            kind = "nccl"                         # heads beyond 2^20 floats go through NCCL unless the sharded fused exchange is asked for
+        self.exchange_kind = kind if world > 1 else "none"
+        self.fused = FusedExchange(self.nrc, self.mrhe, rank, world, dev) if (world > 1 and kind == "fused") else None
+
+    def frame(self, random4):
+        self.vol.Update(random4=random4)
+        self.nrc.ResetStats()
+        if self.world == 1:
+            self.r.Render()
+        else:
+            self.r.FrameTrain()
+            if self.fused is not None:
+                self.fused()                 # one kernel: peer-memory sum over NVLink + nrc-step + mrhe-step (csrc/dp.cu)
+            else:
+                self.exchange()              # NCCL all-reduce of the MLP gradient arena (+loss) and the delta-table head
+                self.N.optimizer_step(self.nrc, self.mrhe)
+            self.r.FrameRender()
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        self.ctx.sync()
+        torch.cuda.synchronize()
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(self, K, warm, rnd_iter, profile=False):
+        """`warm` untimed frames, then K frames between two events on the main stream, barrier + synchronize on both sides; returns
+        (ms of the K frames on this rank, this rank's counters over them, per-kernel profile or None, kernel launches)."""
+        import torch
+        ctx = self.ctx
+        for _ in range(warm):
+            self.frame(next(rnd_iter))
+        self.barrier()
+        self.r.totals(reset=True)
+        launches0 = ctx.launch_count()
+        if profile:
+            ctx.profile(True)
+            ctx.profile_read(reset=True)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(self.ext):
+            ev0.record()
+        for _ in range(K):
+            self.frame(next(rnd_iter))
+        with torch.cuda.stream(self.ext):
+            ev1.record()
+        self.barrier()
+        ms = ev0.elapsed_time(ev1)
+        prof = None
+        if profile:
+            prof = ctx.profile_read(reset=True)
+            ctx.profile(False)
+        return ms, self.r.totals(reset=True), prof, ctx.launch_count() - launches0
+
+    def check_exchange(self):
+        if self.fused is not None and self.fused.timed_out():
+            raise SystemExit("bench.py: a handshake of the fused gradient exchange timed out; the replicas may have diverged -- no result")
+
+    def destroy(self):
+        self.ctx.sync()
+        if self.fused is not None:
+            self.fused.close()
+        for o in (self.r, self.nrc, self.mrhe, self.vol, self.env):
+            o.Destroy()
+
+
+def side_measure(args, ctx, rank, world, local, W, H, TW, TH, grid_scale, table_size, scaling, steps=10, warm=3, label=""):
+    """A short measurement of another BASELINE configuration after the headline loop (own objects, same context): ms/frame, queries/s
+    over all ranks (max-over-ranks device time), the slowest kernels of this rank, and its own oracle parity flags."""
+    import torch
+    import torch.distributed as dist
+    wl = Workload(args, ctx, rank, world, local, W, H, TW, TH, grid_scale, table_size)
+    rnd = iter(lcg_randoms(steps + warm + 4, seed=0x1F123BB5))
+    ms, tot, prof, launches = wl.timed(steps, warm, rnd, profile=True)
+    wl.check_exchange()
+    dev = torch.device("cuda", local)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    c = torch.tensor([tot["infer_queries"] + tot["train_samples"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c)
+    out = {"workload": label, "frame": [W, H], "train_grid": [TW, TH], "hash_table": [16, table_size, 2], "grid_scale": grid_scale,
+           "n_gpus": world, "scaling": scaling, "steps": steps, "warmup": warm, "ms_per_step": float(t[0]) / steps,
+           "queries_per_s": float(c[0]) / (float(t[0]) * 1e-3), "exchange": wl.exchange_kind,
+           "kernels_ms_per_step": {k: ms_ / steps for k, (ms_, _) in sorted(prof.items(), key=lambda kv: -kv[1][0])[:8]}}
+    if not args.no_parity:
+        try:
+            v = {"r": wl.r, "nrc": wl.nrc, "mrhe": wl.mrhe, "vol": wl.vol, "ctx": ctx, "inp": wl.inp, "world": world, "rank": rank, "local": local,
+                 "W": W, "H": H, "TW": TW, "TH": TH, "table_size": table_size}
+            out["parity"] = parity_check(v, args)
+        except Exception as e:
+            out["parity"] = {"error": repr(e)}
+    wl.destroy()
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -133,86 +263,44 @@ def run_b200(args):
         grid_scale, table_size = 4, 1 << 22
     if args.width:
         W, H = args.width, args.height
-    inp = scene_inputs(W, H, grid_scale, table_size)
 
     ctx = N.Context(local)
-    vol = N.VolumeData(ctx, inp["density"])
-    vol.useNN = 1
-    env = N.HdrEnvMap(ctx, 1024, 512, inp["env"])
-    dl = N.DirLight(-1.57, 0.0, (1, 1, 1), 1.0)      # strengths 1.0: the reference default 0 makes the target == 0 (SURVEY finding 9)
-    pl = N.PointLight((0, 0, 0), (1, 1, 1), 1.0)
-    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
-    nrc.set_params(inp["params"])
-    mrhe = N.MRHE(ctx, 0.01, 0.0, 16, table_size, 2, seed=0)
-    mrhe.set_tables(inp["tables"])
     if args.precision == "bf16":
         ctx.set_precision(L.MLP_BF16_TC)
-    r = N.NrcHpmRenderer(W, H, TW, TH, inp["cam"], vol, dl, pl, env, nrc, mrhe)
-    if world > 1:
-        r.SetPartitionStrided(rank, world, rank, world)
-    # Render vertex pool, vertices per path (NRC_BENCH_POOL; 0 = the library default of 4, grown and re-traced on overflow).  32 cannot
-    # overflow, so no read has to wait on the host for the overflow flag of the frame it hands out: e2e 2.93 instead of 3.00 ms/frame;
-    # 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are for.  Larger per-rank frames keep the library default.
-    pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "32" if (W * H // world) <= 2304 * 1296 else "0"))
-    if pool_per_path > 0:
-        r.SetPoolCapacity(-(-H // world) * W * pool_per_path)      # the rank with the most rows
-
-    from neuralradiancecaching_b200.dist import GradientExchange, FusedExchange
-    exchange = GradientExchange(ctx, nrc, mrhe, torch.device("cuda", local))
-    ext = exchange.stream
-    if 2 * table_size > (1 << 20):
-        args.exchange = "nccl"                    # the fused kernel is for the latency regime (csrc/dp.cu); big tables go through NCCL
-    fused = FusedExchange(nrc, mrhe, rank, world, torch.device("cuda", local)) if (world > 1 and args.exchange == "fused") else None
-
-    def frame(random4):
-        vol.Update(random4=random4)
-        nrc.ResetStats()
-        if world == 1:
-            r.Render()
-        else:
-            r.FrameTrain()
-            if fused is not None:
-                fused()                      # one kernel: peer-memory sum over NVLink + nrc-step + mrhe-step (csrc/dp.cu)
-            else:
-                exchange()                   # NCCL all-reduce of the MLP gradient arena (+loss) and the delta-table head
-                N.optimizer_step(nrc, mrhe)
-            r.FrameRender()
-
-    def barrier():
-        ctx.sync()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    wl = Workload(args, ctx, rank, world, local, W, H, TW, TH, grid_scale, table_size)
+    inp, vol, env, nrc, mrhe, r = wl.inp, wl.vol, wl.env, wl.nrc, wl.mrhe, wl.r
+    exchange, ext, fused, pool_per_path = wl.exchange, wl.ext, wl.fused, wl.pool_per_path
+    args.exchange = wl.exchange_kind if world > 1 else args.exchange
+    frame, barrier = wl.frame, wl.barrier
 
     K, Wm = args.steps, args.warmup
-    rnd = lcg_randoms(2 * (K + Wm) + 40)
+    REPS = max(1, args.repeats)
+    rnd = lcg_randoms((2 * REPS + 2) * (K + Wm) + 60)
     ri = iter(rnd)
-    # ---- device-resident timing (value) ----
-    for _ in range(Wm):
-        frame(next(ri))
-    barrier()
-    r.totals(reset=True)
-    launches0 = ctx.launch_count()
-    ctx.profile(True)
-    ctx.profile_read(reset=True)
+    dev = torch.device("cuda", local)
+
+    def median_repeat(ms_list):
+        """index of the median repeat by the max-over-ranks time (the same on every rank) and the reduced times"""
+        t = torch.tensor(ms_list, dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        order = sorted(range(len(ms_list)), key=lambda i: float(t[i]))
+        return order[len(order) // 2], [float(x) for x in t]
+
+    # ---- device-resident timing (value): REPS repeats of exactly K frames each, the median repeat is reported ----
     sampler = ClockSampler(local)      # rank 0 only: N concurrent nvidia-smi pollers perturb the ranks they poll
-    if rank == 0:
-        sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with torch.cuda.stream(ext):
-        ev0.record()
-    for _ in range(K):
-        frame(next(ri))
-    with torch.cuda.stream(ext):
-        ev1.record()
-    barrier()
+    reps = []
+    for rep in range(REPS):
+        if rep == 0:
+            for _ in range(Wm):
+                frame(next(ri))
+            if rank == 0:
+                sampler.start()
+        reps.append(wl.timed(K, 0, ri, profile=True))
     sampler.stop_flag = True
-    ms_total = ev0.elapsed_time(ev1)
-    prof = ctx.profile_read(reset=True)
-    ctx.profile(False)
-    launches = ctx.launch_count() - launches0
-    tot = r.totals(reset=True)
+    wl.check_exchange()
+    mid, rep_ms = median_repeat([x[0] for x in reps])
+    ms_total, tot, prof, launches = reps[mid]
     mse = nrc.GetStats().mseLoss
 
     # ---- end to end: the host-facing call sequence; per step the scene/camera/RNG structs go host->device (kernel
@@ -246,20 +334,22 @@ def run_b200(args):
             r.readback_wait(t)
 
     e2e_steps(3)
-    barrier()
-    r.totals(reset=True)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0 = time.perf_counter()
-    with torch.cuda.stream(ext):
-        e0.record()
-    e2e_steps(K)
-    ctx.sync()
-    with torch.cuda.stream(ext):
-        e1.record()
-    barrier()
-    e2e_wall_ms = (time.perf_counter() - t0) * 1e3
-    e2e_ms = max(e0.elapsed_time(e1), 0.0)
-    tot_e2e = r.totals(reset=True)
+    e2e_reps = []
+    for rep in range(REPS):
+        barrier()
+        r.totals(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(ext):
+            e0.record()
+        e2e_steps(K)
+        ctx.sync()
+        with torch.cuda.stream(ext):
+            e1.record()
+        barrier()
+        e2e_reps.append((max(e0.elapsed_time(e1), 0.0), r.totals(reset=True)))
+    wl.check_exchange()
+    emid, e2e_rep_ms = median_repeat([x[0] for x in e2e_reps])
+    e2e_ms, tot_e2e = e2e_reps[emid]
     if os.environ.get("NRC_BENCH_TIMELINE") and rank == 0:      # kernel timeline of two more frames (both streams), to stderr
         ctx.profile(True)
     if os.environ.get("NRC_BENCH_TIMELINE"):
@@ -449,14 +539,18 @@ FLOP_INFER = 41344.0         # 2 * 20 672 MAC per query
 FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
 
 
-# ncu --set full capture of the default N=1 workload (profiles/r01p_ncu_summary.md, final round-1 build): DRAM bytes (read + write)
-# and executed warp instructions per launch.  Only quoted when the run IS that workload.
-NCU_FRAME = {
-    "k_train_walk": (111.3e6, 142.76e6), "k_light<train>": (196.4e6, 362.48e6), "k_train_combine": (168.1e6, 2.65e6),
-    "k_train_tc": (1.9e6, 5.35e6), "k_render_walk": (240.8e6, 423.18e6), "k_render_walk_tail": (199.5e6, 508.84e6),
-    "k_light<render>": (132.9e6, 424.43e6), "k_render_combine": (119.2e6, 6.98e6), "k_infer_tc": (13.3e6, 110.13e6),
-    "k_composite": (223.5e6, 19.13e6),
-}
+# ncu --set full capture of the default N=1 workload: DRAM bytes (read + write) and executed warp instructions per launch of every
+# frame kernel, read from the committed summary profiles/ncu_frame.json (written by scripts/ncu_summary.py --json from the capture named
+# in its "source"); only quoted when the run IS that workload.
+def load_ncu_frame():
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_frame.json")))
+        return {k: (float(x[0]), float(x[1])) for k, x in d["kernels"].items()}, d.get("source", "profiles/ncu_frame.json")
+    except Exception:
+        return {}, None
+
+
+NCU_FRAME, NCU_SOURCE = load_ncu_frame()
 
 
 def kernel_work(name, tot, pixels, table_floats):
@@ -478,6 +572,118 @@ def kernel_work(name, tot, pixels, table_floats):
     if name == "k_mrhe_step":
         return "hbm", None, "GB/s"      # filled by the caller: 16 B/param/launch
     return "hbm", None, "GB/s"
+
+
+def parity_check(v, args):
+    """Oracle parity of the very workload the line times: the bench scene at its initial weights, one frame with a
+    fixed `random` vec4, rendered once more on the GPU OUTSIDE the timed region and compared with the CPU oracle -- control flow bit for
+    bit (RNG draws, lit vertices, walk steps, emitted queries, query / record positions and directions), the frame by PSNR, the
+    gradients by max-norm.  N = 1: every train invocation and every `row_step`-th frame row; N > 1: every rank checks a sample of its
+    own rows and of its own train invocations, and all ranks compare a hash of their parameters and tables (replicas_identical)."""
+    import hashlib
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    r, nrc, mrhe, vol, ctx, inp = v["r"], v["nrc"], v["mrhe"], v["vol"], v["ctx"], v["inp"]
+    world, rank, W, H, TW, TH = v["world"], v["rank"], v["W"], v["H"], v["TW"], v["TH"]
+    out = {}
+    # ---- replicas after the timed frames ----
+    ctx.sync()
+    if world > 1:
+        hsh = hashlib.sha256(nrc.get_params()[0].tobytes() + mrhe.get_tables()[0].tobytes()).digest()[:8]
+        mine = torch.tensor(list(hsh), dtype=torch.uint8, device=torch.device("cuda", v["local"]))
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine)
+        out["replicas_identical"] = all(bool((p == parts[0]).all()) for p in parts)
+    # ---- the parity frame: initial weights, fixed seed ----
+    rnd = np.asarray([0.37, 0.61, 0.13, 0.89], np.float32)
+    nrc.set_params(inp["params"])
+    nrc.set_state(delta=np.zeros(20995, np.float32), momentum=np.zeros(20995, np.float32))
+    mrhe.set_tables(inp["tables"], delta=np.zeros(mrhe.count, np.float32))
+    vol.Update(random4=rnd)
+    nrc.ResetStats()
+    r.FrameTrain()
+    ctx.sync()
+    rec, tcnt = r.read_train_probes()
+    g_mlp = nrc.get_params()[1].copy()
+    g_tab = mrhe.get_tables()[1][:2 * v["table_size"]].copy()
+    if world == 1:
+        import neuralradiancecaching_b200 as N
+        N.optimizer_step(nrc, mrhe)
+    else:      # the parity frame is per rank: no exchange; render with the initial weights
+        nrc.set_state(delta=np.zeros(20995, np.float32)); mrhe.set_tables(delta=np.zeros(mrhe.count, np.float32))
+    r.FrameRender()
+    ctx.sync()
+    cnt, qry = r.read_render_probes()
+    frame = r.read_frame()
+    # ---- the oracle on the same scene ----
+    threads = max(1, (len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)) // world)
+    O.set_num_threads(threads)
+    sc = O.OracleScene()
+    cam = inp["cam"]
+    sc.set_camera(cam.projView, cam.invProjView, cam.m_Pos)
+    sc.set_volume(inp["density"])
+    sc.set_dir_light((1, 1, 1), -1.57, inp["dir_dir"], 0.0, 1.0)
+    sc.set_point_light((0, 0, 0), 1.0, (1, 1, 1))
+    sc.set_envmap(inp["env"], None, None, 1.0, 8.0)
+    sc.set_mlp(inp["params"], 0.001, 0.0, 0.5)
+    sc.set_mrhe(inp["tables"], O.mrhe_resolutions(), 0.01, 0.0, 16, v["table_size"], 2)
+    sc.set_train_size(TW, TH)
+    sc.set_volume_params(rnd, 1, 0, 0.4, 0.7, 1, 1)
+    n_train = TW * TH
+    if world == 1:
+        idx = np.arange(n_train)
+        orec, ocnt = sc.train_trace(TW, TH)
+    else:      # a contiguous block of invocations, of which this rank traced every world-th
+        b0 = (rank * 977) % max(n_train - 128 * world, 1)
+        orec, ocnt = sc.train_trace(TW, TH, b0, b0 + 128 * world)
+        sel = np.arange(b0, b0 + 128 * world)
+        keep = (sel % world) == rank
+        idx, orec, ocnt = sel[keep], orec[keep], ocnt[keep]
+    out["train_samples_checked"] = int(idx.size)
+    out["train_counters_equal"] = bool(np.array_equal(tcnt[idx][:, :3], ocnt[:, [0, 1, 3]]))
+    out["records_bits_equal"] = bool(np.array_equal(rec[idx][:, :6].view(np.uint32), orec[:, :6].view(np.uint32)))
+    out["target_rel"] = float(np.abs(rec[idx][:, 6:] - orec[:, 6:]).max() / max(float(np.abs(orec[:, 6:]).max()), 1e-30))
+    if world == 1:
+        sc.train_accumulate(orec[:, 0:3], orec[:, 3:6], orec[:, 6:9])
+        od, ot = sc.get_mlp()[1], sc.get_mrhe()[1][:2 * v["table_size"]]
+        out["grad_rel"] = float(np.abs(g_mlp - od).max() / max(float(np.abs(od).max()), 1e-30))
+        out["table_grad_rel"] = float(np.abs(g_tab - ot).max() / max(float(np.abs(ot).max()), 1e-30))
+        sc.nrc_step(); sc.mrhe_step()
+    my_rows = np.arange(rank, H, world)
+    step = max(1, int(args.parity_row_step) if world == 1 else -(-len(my_rows) // 48))
+    rows = my_rows[step // 2::step]
+    eq = {"draws_equal": True, "lit_equal": True, "steps_equal": True, "queries_equal": True, "query_bits_equal": True}
+    se, peak, npx = 0.0, 1e-12, 0
+    for y in rows:
+        y = int(y)
+        orgba, oc, oq = sc.render(W, H, y, y + 1)
+        eq["draws_equal"] &= bool(np.array_equal(cnt[y, :, 0], oc[y, :, 0]))
+        eq["lit_equal"] &= bool(np.array_equal(cnt[y, :, 1], oc[y, :, 1]))
+        eq["steps_equal"] &= bool(np.array_equal(cnt[y, :, 2], oc[y, :, 3]))
+        eq["queries_equal"] &= bool(np.array_equal(cnt[y, :, 3], oq[y, :, 7].astype(np.uint32)))
+        eq["query_bits_equal"] &= bool(np.array_equal(qry[y, :, :6].view(np.uint32), oq[y, :, :6].view(np.uint32)))
+        dlt = frame[y].astype(np.float64) - orgba[y].astype(np.float64)
+        se += float((dlt * dlt).sum()); npx += dlt.size
+        peak = max(peak, float(np.abs(orgba[y]).max()))
+    out.update(eq)
+    out["rows"] = int(len(rows))
+    out["row_step"] = int(step)
+    mse = se / max(npx, 1)
+    out["frame_psnr_db"] = 99.0 if mse == 0 else float(10.0 * np.log10(peak * peak / mse))
+    out["mlp_precision"] = args.precision
+    out["note"] = ("GPU frame vs the CPU oracle on the timed scene at its initial weights, random=(0.37,0.61,0.13,0.89); the walk's control flow "
+                   "is independent of the MLP precision; frame_psnr_db / grad_rel are for the precision the line times")
+    if world > 1:      # all flags must hold on every rank
+        flags = [k for k, x in out.items() if isinstance(x, bool)]
+        t = torch.tensor([1.0 if out[k] else 0.0 for k in flags] + [-out["frame_psnr_db"]], dtype=torch.float64, device=torch.device("cuda", v["local"]))
+        tmin = t.clone(); dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        for i, k in enumerate(flags):
+            out[k] = bool(tmin[i] > 0.5)
+        out["frame_psnr_db"] = float(-tmax[-1])      # the worst rank
+        out["ranks_checked"] = world
+    return out
 
 
 def finish_b200(args, v):
@@ -513,7 +719,7 @@ def finish_b200(args, v):
     default_workload = (world == 1 and (W, H, v["TW"], v["TH"]) == (1920, 1080, 100, 100) and args.precision == "bf16")
     if default_workload and name in NCU_FRAME:
         roof["traffic"] = NCU_FRAME[name][0]
-        roof["traffic_source"] = "profiles/r01p_ncu_summary.md (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+        roof["traffic_source"] = "%s (dram__bytes_read.sum + dram__bytes_write.sum, one launch)" % NCU_SOURCE
     if work is not None and kms > 0:
         ach = work / (kms * 1e-3) / (1e9 if bound == "hbm" else 1e12)
         roof["achieved"] = ach
@@ -533,13 +739,13 @@ def finish_b200(args, v):
     # What actually bounds the frame: instruction issue.  Warp instructions per frame from the ncu capture over the peak issue rate
     # of the machine at the clock sampled during this run.
     issue = None
-    if default_workload:
+    if default_workload and NCU_FRAME:
         winst = sum(x[1] for x in NCU_FRAME.values())
         mhz = clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 1965.0
         peak_issue = v["ctx"].sm_count * 4 * mhz * 1e6
         issue = {"warp_instructions_per_step": winst, "peak_warp_instructions_per_s": peak_issue,
                  "floor_ms_per_step": winst / peak_issue * 1e3, "frac": (winst / peak_issue * 1e3) / (ms_total / K),
-                 "source": "profiles/r01p_ncu_summary.md (smsp__inst_executed.sum of the ten frame kernels)"}
+                 "source": "%s (smsp__inst_executed.sum of the frame kernels)" % NCU_SOURCE}
     line = {
         "metric": METRIC, "value": units / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": v["Wm"],
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": v["scaling"], "vs_baseline": None,
@@ -581,9 +787,40 @@ def finish_b200(args, v):
             line["cpu_baseline"] = cpu_reference_sample(W, H, v["TW"], v["TH"], budget_s=args.cpu_budget)
         except Exception as e:   # the checker failing must not hide the GPU number
             line["cpu_baseline"] = {"error": repr(e)}
+    if not args.no_side and not args.no_parity:
+        try:
+            line["parity"] = parity_check(v, args)
+        except Exception as e:   # the checker failing must not hide the GPU number
+            line["parity"] = {"error": repr(e)}
+    line["repeats"] = {"count": len(v["rep_ms"]), "steps_each": K, "ms_per_step": [x / K for x in v["rep_ms"]],
+                       "e2e_ms_per_step": [x / K for x in v["e2e_rep_ms"]], "reported": "median repeat (max over ranks per repeat)"}
+    v["wl"].destroy()
+    # ---- the other BASELINE configurations, measured briefly behind the headline so that they appear in driver-run lines ----
+    if not args.no_side and args.config == "default" and not args.width:
+        ctx_, local = v["ctx"], v["local"]
+        side = []
+        if world == 1:
+            side.append(("config3", (1280, 720, 100, 100, 1, 16384, "none"), "BASELINE configs[2]: 1280x720, 1 spp, online training, env map, 1 GPU"))
+            side.append(("config5_n1", (1920, 1080, 100, 100, 4, 1 << 22, "none"),
+                         "BASELINE configs[4] on one GPU: refined 500x340x612 cloud, 2^22-entry hash tables, 1080p"))
+        else:
+            side.append(("strong_4k", (3840, 2160, 100, 100, 1, 16384, "strong"),
+                         "BASELINE configs[3]: ONE 3840x2160 frame + 10^4 samples split over the ranks (strong scaling)"))
+            if world >= 8:
+                Ws, Hs, TWs, THs = frame_shape(world)
+                side.append(("config5", (Ws, Hs, TWs, THs, 4, 1 << 22, "weak"),
+                             "BASELINE configs[4]: refined cloud, 2^22-entry hash tables, %d GPUs (weak-scaling frame)" % world))
+        for key, (w_, h_, tw_, th_, gs_, ts_, sc_), label in side:
+            if key in (os.environ.get("NRC_BENCH_SKIP", "") or "").split(","):
+                continue
+            try:
+                line[key] = side_measure(args, ctx_, rank, world, local, w_, h_, tw_, th_, gs_, ts_, sc_, label=label)
+            except SystemExit:
+                raise
+            except Exception as e:
+                line[key] = {"error": repr(e)}
     if rank == 0:
         print(json.dumps(line))
-    v["r"].Destroy()
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -670,7 +907,9 @@ def run_reference(args):
             "ms_per_step": cb["seconds"] / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "cloud_sixteenth (synthetic 125x85x153 stand-in) %dx%d 1 spp, online NRC training %dx%d samples/frame, "
-                                   "dir+point+env lights, useNN=1; CPU, bounded sample of each frame" % (W, H, TW, TH)},
+                                   "dir+point+env lights, useNN=1" % (W, H, TW, TH),
+                       "baseline_config": "default", "frame": [W, H], "train_grid": [TW, TH], "hash_table": [16, 16384, 2], "mlp": "64x5->3 relu",
+                       "parallelism": "CPU oracle on the host cores of rank 0: a bounded, evenly spread sample of each frame (see cpu_baseline.sample)"},
             "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
@@ -698,6 +937,9 @@ def main():
     ap.add_argument("--no-fit", action="store_true", help="skip the BASELINE config-2 (2^18-query MRHE+MLP fit) side measurement")
     ap.add_argument("--no-side", action="store_true", help="skip the side measurements of the other BASELINE configs (config3 / strong_4k / config5) and the parity check")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--repeats", type=int, default=3, help="the K timed steps are repeated this many times; the median repeat is reported")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle parity check of the timed workload")
+    ap.add_argument("--parity-row-step", type=int, default=4, help="N = 1: the parity check compares every k-th frame row with the oracle")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -8,7 +8,8 @@
  * nrc_status; the text of the last failure on the calling thread is nrc_last_error().
  *
  * Pointer arguments marked [h|d] may be host or device memory; the library detects which
- * (cudaPointerGetAttributes) and stages host buffers through pinned memory itself.  All work is
+ * (cudaPointerGetAttributes) and copies host buffers to device scratch before it returns (pageable or page-locked alike: the
+ * caller may reuse or free a host buffer as soon as the call returns).  All work is
  * issued on the context's stream; calls that return data to host memory synchronise that stream.
  *
  * There is NO CPU fallback: without a CUDA device nrc_ctx_create fails with NRC_ERR_NO_DEVICE.
@@ -313,7 +314,9 @@ NRC_API nrc_status nrc_dp_connect(nrc_dp* dp, const void* allHandles /*host, wor
 NRC_API nrc_status nrc_dp_reduce_step(nrc_dp* dp);
 /* replicas inside one process (single-GPU parity test): phase 0 on every replica, then phase 1 on every replica */
 NRC_API nrc_status nrc_dp_reduce_step_phase(nrc_dp* dp, int phase);
-/* 1 if a handshake gave up waiting for a peer (about 10 s; a crashed rank must not hang the other GPUs) */
+/* 1 if a handshake gave up waiting for a peer (about 30 s; a crashed rank must not hang the other GPUs).  The exchange FAILS CLOSED:
+ * the block that gave up skips its step and its clear, the mark is written into every rank's flag block, and from then on
+ * nrc_dp_reduce_step, nrc_sync and nrc_readback_wait of every rank return NRC_ERR_CUDA. */
 NRC_API nrc_status nrc_dp_status(nrc_dp* dp, int* timedOut);
 NRC_API nrc_status nrc_dp_destroy(nrc_dp* dp);
 

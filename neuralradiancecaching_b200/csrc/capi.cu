@@ -53,8 +53,12 @@ nrc_status nrc_stage_in(nrc_ctx* ctx, int slot, const void* p, size_t bytes, con
     }
     void* d;
     NRC_TRY(nrc_scratch(ctx, slot, bytes, &d));
-    // pageable or pinned host memory: cudaMemcpyAsync is stream-ordered and truly asynchronous for pinned sources
+    // pageable host memory is staged by the runtime before cudaMemcpyAsync returns; a PAGE-LOCKED source is read by the DMA engine
+    // later, so wait for it: the caller may reuse or free the buffer as soon as the entry point returns
     NRC_CUDA(cudaMemcpyAsync(d, p, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) cudaGetLastError();
+    else if (at.type == cudaMemoryTypeHost) NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     *dev = d;
     return NRC_OK;
 }
@@ -258,10 +262,22 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     return NRC_OK;
 }
 
+nrc_status nrc_ctx_check_dp(nrc_ctx* c)
+{
+    for (size_t i = 0; i < c->dpFailWords.size(); i++)
+        if (*c->dpFailWords[i] != 0u) {
+            nrc_set_error("a fused data-parallel exchange timed out waiting for a peer rank and failed closed (step and clear skipped); "
+                          "the replicas have diverged -- restart the job");
+            return NRC_ERR_CUDA;
+        }
+    return NRC_OK;
+}
+
 extern "C" nrc_status nrc_sync(nrc_ctx* c)
 {
     NRC_REQUIRE(c, "null context");
     NRC_CUDA(cudaStreamSynchronize(c->stream));
+    NRC_TRY(nrc_ctx_check_dp(c));
     // a frame traced with a vertex pool below the worst case is checked now (and redone if it overflowed)
     for (size_t i = 0; i < c->renderers.size(); i++) NRC_TRY(nrc_renderer_resolve_pending(c->renderers[i]));
     NRC_CUDA(cudaStreamSynchronize(c->stream));

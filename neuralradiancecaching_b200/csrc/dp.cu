@@ -17,6 +17,7 @@
 // mrhe-step.comp:27-74).
 #include <cuda_bf16.h>
 #include <string.h>
+#include <stdlib.h>
 #include "nrc_internal.cuh"
 #include "tc_ptx.cuh"
 
@@ -35,6 +36,7 @@ struct nrc_dp {
     const float* peerDelta[NRC_DP_MAX_WORLD] = {nullptr};
     unsigned* peerFlags[NRC_DP_MAX_WORLD] = {nullptr};
     void* opened[NRC_DP_MAX_WORLD][3] = {{nullptr}};
+    unsigned* hostFail = nullptr;              // pinned mirror of the sticky time-out word, refreshed behind every launch
 };
 
 struct DpHandle {   // what one rank publishes to the others
@@ -56,6 +58,7 @@ struct DpArgs {
     float lr, wd, beta1;
     float* tables; float* delta; unsigned extent;
     float mlr, mwd;
+    unsigned long long timeoutNs;   // how long a handshake waits for a peer before the exchange fails closed
 };
 
 __device__ __forceinline__ float4 ld_sys4(const float* p)
@@ -77,21 +80,29 @@ __device__ __forceinline__ float dp_sign(float x) { return (x > 0.0f) ? 1.0f : (
 
 // Block b of every rank owns the same slice of both arenas, so the handshakes are per block: block b signals slot
 // (b, rank, which) of every peer and waits until block b of every peer has signalled its own.  No grid-wide barrier.
-__device__ __forceinline__ void dp_barrier(const DpArgs& a, int which)
+// A peer that never arrives (crashed process) must not hang this GPU: the wait gives up after ~30 s and the exchange FAILS CLOSED --
+// s_fail is raised, the caller skips its step and its clear for this launch, and the sticky word NRC_DP_FLAG_COUNT is set in this
+// rank's flag block AND in every peer's, so that every rank's next nrc_dp_reduce_step / nrc_sync / nrc_readback_wait reports it.
+// A block that has already failed only signals (its peers must not wait out their own time-out for it) and does not wait.
+__device__ __forceinline__ void dp_barrier(const DpArgs& a, int which, int* s_fail)
 {
     __syncthreads();
     if ((int)threadIdx.x < a.world) {
         __threadfence_system();
         unsigned slot = (blockIdx.x * NRC_DP_MAX_WORLD) * 2;
         st_release_sys(a.peerFlags[threadIdx.x] + slot + a.rank * 2 + which, a.epoch);
-        // A peer that never arrives (crashed process) must not hang this GPU: give up after ~10 s and leave a mark the host reads
-        // (nrc_dp_status); the step then runs on whatever the peer's arena holds -- the run is lost, the device is not.
-        unsigned long long t0, t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        while ((int)(ld_acquire_sys(a.myFlags + slot + threadIdx.x * 2 + which) - a.epoch) < 0) {
-            __nanosleep(32);
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > 10000000000ull) { a.myFlags[NRC_DP_FLAG_COUNT] = 1u; break; }
+        if (!*s_fail) {
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while ((int)(ld_acquire_sys(a.myFlags + slot + threadIdx.x * 2 + which) - a.epoch) < 0) {
+                __nanosleep(32);
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > a.timeoutNs) {
+                    atomicExch(s_fail, 1);
+                    for (int r = 0; r < a.world; r++) st_release_sys(a.peerFlags[r] + NRC_DP_FLAG_COUNT, 1u);
+                    break;
+                }
+            }
         }
     }
     __syncthreads();
@@ -144,9 +155,12 @@ __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_cons
 {
     const int t = blockIdx.x * DP_THREADS + threadIdx.x;
     const int stride = DP_BLOCKS * DP_THREADS;
-    if (a.barriers) dp_barrier(a, 0);
+    __shared__ int s_fail;
+    if (threadIdx.x == 0) s_fail = a.barriers ? (ld_acquire_sys(a.myFlags + NRC_DP_FLAG_COUNT) != 0u) : 0;   // an earlier launch (here or on a peer) gave up
+    __syncthreads();
+    if (a.barriers) dp_barrier(a, 0, &s_fail);
     float lossSum = 0.0f;
-    if (a.doStep) {
+    if (a.doStep && !s_fail) {
         // ---- MLP arena: sum over ranks in rank order, then nrc-step.comp for this replica ----
         for (int i4 = t; i4 < DP_MLP_VEC; i4 += stride) {
             float4 g = dp_sum4(a.peerGrad, a.world, i4);
@@ -169,8 +183,8 @@ __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_cons
             reinterpret_cast<float4*>(a.tables)[i4] = w;
         }
     }
-    if (a.barriers) dp_barrier(a, 1);     // block b of every peer has read my slice b
-    if (a.clear) {
+    if (a.barriers) dp_barrier(a, 1, &s_fail);     // block b of every peer has read my slice b
+    if (a.clear && !s_fail) {
         for (int i4 = t; i4 < DP_MLP_VEC; i4 += stride) {
             float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
             if (i4 == DP_MLP_VEC - 1) {   // {b5[0..2] gradients, loss}: every rank reports the global loss
@@ -203,6 +217,14 @@ extern "C" nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int 
         delete d;
         return NRC_ERR_CUDA;
     }
+    if (cudaMallocHost(&d->hostFail, sizeof(unsigned)) != cudaSuccess) {
+        nrc_set_error("nrc_dp_create: cudaMallocHost failed");
+        cudaFree(d->flags);
+        delete d;
+        return NRC_ERR_CUDA;
+    }
+    *d->hostFail = 0u;
+    mlp->ctx->dpFailWords.push_back(d->hostFail);
     *out = d;
     return NRC_OK;
 }
@@ -270,7 +292,14 @@ static nrc_status dp_launch(nrc_dp* d, int barriers, int clear, bool reduce)
     a.lr = d->mlp->lr; a.wd = d->mlp->wd; a.beta1 = d->mlp->beta1;
     a.tables = d->mrhe->tables; a.delta = d->mrhe->delta; a.extent = (unsigned)nrc_mrhe_grad_extent(d->mrhe);
     a.mlr = d->mrhe->lr; a.mwd = d->mrhe->wd;
+    {
+        const char* e = getenv("NRC_DP_TIMEOUT_MS");   // default 30 s: longer than any stall of a healthy rank (pool regrowth + re-trace, checkpoint load)
+        const long ms = e ? atol(e) : 30000;
+        a.timeoutNs = (unsigned long long)(ms > 0 ? ms : 30000) * 1000000ull;
+    }
     NRC_LAUNCH(ctx, ctx->stream, K_DP_REDUCE_STEP, k_dp_reduce_step<<<DP_BLOCKS, DP_THREADS, 0, ctx->stream>>>(a));
+    // the sticky time-out word follows every launch to pinned host memory: the next call / nrc_sync / nrc_readback_wait sees it
+    if (barriers) NRC_CUDA(cudaMemcpyAsync(d->hostFail, d->flags + NRC_DP_FLAG_COUNT, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
     return NRC_OK;
 }
 
@@ -280,6 +309,7 @@ extern "C" nrc_status nrc_dp_reduce_step(nrc_dp* d)
 {
     NRC_REQUIRE(d && d->connected, "nrc_dp_connect first");
     NRC_REQUIRE(!d->sameProcess || d->world == 1, "same-process replicas: use nrc_dp_reduce_step_phase");
+    NRC_TRY(nrc_ctx_check_dp(d->mlp->ctx));
     NRC_TRY(dp_launch(d, d->world > 1, 1, true));
     return launch_mrhe_step_range(d->mrhe, nrc_mrhe_grad_extent(d->mrhe), d->mrhe->ctx->stream);
 }
@@ -289,7 +319,8 @@ extern "C" nrc_status nrc_dp_reduce_step(nrc_dp* d)
 extern "C" nrc_status nrc_dp_reduce_step_phase(nrc_dp* d, int phase)
 {
     NRC_REQUIRE(d && d->connected, "nrc_dp_connect first");
-    NRC_REQUIRE(phase == 0 || phase == 1, "phase must be 0 or 1");
+    NRC_REQUIRE(phase == 0 || phase == 1 || phase == 2, "phase must be 0, 1 or 2");
+    if (phase == 2) return dp_launch(d, 1, 1, true);   // test hook: the real kernel with handshakes, on this replica only (time-out test)
     if (phase == 0) return dp_launch(d, 0, 0, true);
     NRC_TRY(dp_launch(d, 0, 2, false));
     return launch_mrhe_step_range(d->mrhe, nrc_mrhe_grad_extent(d->mrhe), d->mrhe->ctx->stream);
@@ -314,6 +345,12 @@ extern "C" nrc_status nrc_dp_destroy(nrc_dp* d)
         for (int k = 0; k < 3; k++)
             if (d->opened[r][k]) cudaIpcCloseMemHandle(d->opened[r][k]);
     cudaFree(d->flags);
+    {
+        std::vector<const volatile unsigned*>& w = d->mlp->ctx->dpFailWords;
+        for (size_t i = 0; i < w.size(); i++)
+            if (w[i] == d->hostFail) { w.erase(w.begin() + i); break; }
+    }
+    if (d->hostFail) cudaFreeHost(d->hostFail);
     delete d;
     return NRC_OK;
 }

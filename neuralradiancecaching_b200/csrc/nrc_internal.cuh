@@ -73,6 +73,7 @@ struct nrc_ctx {
     nrc_infer_mode inferMode = NRC_INFER_FUSED;   // nrc_ctx_create reads NRC_INFER_SPLIT
     uint64_t launches = 0;
     std::vector<nrc_renderer*> renderers;   // nrc_sync settles their deferred vertex-pool checks (renderer.cu)
+    std::vector<const volatile unsigned*> dpFailWords;   // pinned time-out words of this context's nrc_dp objects (dp.cu): non-zero = a fused exchange failed closed
     // per-kernel event timing (off by default; bench.py turns it on over its timed region)
     bool profiling = false;
     std::vector<NrcProfRec> profOpen;       // recorded, not yet read
@@ -212,6 +213,9 @@ void nrc_prof_end(nrc_ctx* ctx, cudaStream_t st);
         NRC_CUDA(cudaGetLastError());            \
     } while (0)
 bool nrc_is_device_ptr(const void* p);
+// NRC_ERR_CUDA (with a message) once a fused data-parallel exchange of this context has given up on a peer (dp.cu): the replicas can
+// no longer be trusted to be identical
+nrc_status nrc_ctx_check_dp(nrc_ctx* ctx);
 nrc_status nrc_scratch(nrc_ctx* ctx, int slot, size_t bytes, void** out);
 // returns a device pointer holding the data of `p` (p itself when it already is one)
 nrc_status nrc_stage_in(nrc_ctx* ctx, int slot, const void* p, size_t bytes, const void** dev);

@@ -655,7 +655,7 @@ extern "C" nrc_status nrc_readback_wait(nrc_renderer* r, int ticket)
 {
     NRC_REQUIRE(r && ticket >= 0 && ticket < 4, "bad ticket");
     NRC_CUDA(cudaEventSynchronize(r->evCopyDone[ticket]));
-    return NRC_OK;
+    return nrc_ctx_check_dp(r->ctx);
 }
 
 extern "C" size_t nrc_frame_partition_bytes(nrc_renderer* r, nrc_frame_format fmt)

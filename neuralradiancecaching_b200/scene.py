@@ -42,6 +42,13 @@ def cloud_density(nx=125, ny=85, nz=153, seed=7):
     return np.clip(d, 0.0, 1.0).astype(np.float32)
 
 
+def refined_density(scale=4):
+    """BASELINE config 5's "full-density cloud": the sixteenth-size grid refined `scale` times per axis by linear interpolation
+    (500 x 340 x 612 at scale 4; the full-size file is not in the reference)."""
+    from scipy import ndimage
+    return np.clip(ndimage.zoom(cloud_density(), scale, order=1), 0.0, 1.0).astype(np.float32)
+
+
 def sha256(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 

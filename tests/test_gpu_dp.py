@@ -104,6 +104,50 @@ def test_fused_rejects_unconnected_and_oversized(N, ctx):
     nrc.Destroy(); m.Destroy(); big.Destroy()
 
 
+def test_fused_exchange_fails_closed_when_a_peer_never_arrives(N, ctx, monkeypatch):
+    """A rank whose peer never launches gives up after the time-out (NRC_DP_TIMEOUT_MS; default 30 s) and FAILS CLOSED: no step, no
+    clear, the mark lands in every rank's flag block, and nrc_sync reports it from then on (the old kernel stepped on
+    whatever the late peer's arena held and zeroed gradients the peer had not read)."""
+    from neuralradiancecaching_b200 import _lib as L
+    from neuralradiancecaching_b200.dist import FusedExchange
+    monkeypatch.setenv("NRC_DP_TIMEOUT_MS", "200")
+    params = Cm.S.mlp_init(1)
+    tables = Cm.S.table_init()
+    reps = []
+    for r in range(2):
+        nrc = N.NeuralRadianceCache(ctx, 0.05, 0.0, 0.5, seed=0)
+        nrc.set_params(params)
+        m = N.MRHE(ctx, 0.1, 0.0, seed=0)
+        g = Cm.S.init_params(100 + r, 20995, 0.3)
+        t = np.zeros_like(tables)
+        t[:2 * 16384] = Cm.S.init_params(200 + r, 2 * 16384, 0.2)
+        nrc.set_state(delta=g)
+        m.set_tables(tables, t)
+        reps.append((nrc, m, g, t))
+    dps = [FusedExchange(nrc, m, r, 2, connect=False) for r, (nrc, m, _, _) in enumerate(reps)]
+    for d in dps:
+        d.connect([x.handle for x in dps], same_process=True)
+    assert not dps[0].timed_out() and not dps[1].timed_out()
+    dps[0].phase(2)                       # rank 0's kernel with the real handshakes; "rank 1" never launches
+    with pytest.raises(L.NrcError, match="failed closed"):
+        ctx.sync()
+    assert dps[0].timed_out() and dps[1].timed_out()          # the mark reached the peer's flag block too
+    nrc, m, g, t = reps[0]
+    gp, gd, _ = nrc.get_params()
+    np.testing.assert_array_equal(gp.view(np.uint32), params.view(np.uint32))        # no step
+    np.testing.assert_array_equal(gd.view(np.uint32), g.view(np.uint32))             # no clear
+    tt, td = m.get_tables()
+    np.testing.assert_array_equal(tt.view(np.uint32), tables.view(np.uint32))
+    np.testing.assert_array_equal(td.view(np.uint32), t.view(np.uint32))
+    with pytest.raises(L.NrcError, match="failed closed"):
+        dps[0].phase(2) if False else L.check(L.lib().nrc_sync(ctx.h))
+    for d in dps:
+        d.close()
+    ctx.sync()                            # the context is usable again once the failed exchange objects are gone
+    for nrc, m, _, _ in reps:
+        nrc.Destroy(); m.Destroy()
+
+
 def test_fused_exchange_across_gpus():
     """Spawns tests/multi_gpu/check_dp.py on 2 GPUs (skipped on a single-GPU box)."""
     import os
