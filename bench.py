@@ -89,7 +89,14 @@ def scene_inputs(width, height, grid_scale=1, table_size=16384):
     dens = S.cloud_density()                      # 125 x 85 x 153, deterministic (SHA-256 in BASELINE.md)
     if grid_scale > 1:                            # config 5: the "full" cloud = the sixteenth-size grid refined per axis
         dens = S.refined_density(grid_scale)
-    env = S.sky_envmap(1024, 512)                 # the shape of data/image/photostudio.hdr
+    env_path = os.environ.get("NRC_ENVMAP")       # e.g. the reference's data/image/photostudio.hdr (1024 x 512 RGBE); not present on the GPU box
+    if env_path:
+        from neuralradiancecaching_b200 import loaders as Ld
+        env, ew, eh = Ld.ReadFileHdr4f(env_path)
+        if (ew, eh) != (1024, 512):
+            raise SystemExit("bench.py: NRC_ENVMAP must be a 1024x512 map (the shape of data/image/photostudio.hdr), got %dx%d" % (ew, eh))
+    else:
+        env = S.sky_envmap(1024, 512)             # the shape of data/image/photostudio.hdr
     cam = Camera((0.0, 0.0, -64.0), (0.0, 0.0, 1.0), (0.0, 1.0, 0.0), width / float(height), np.radians(60.0), 0.1, 100.0)
     return dict(density=dens, env=env, cam=cam, dir_dir=vec_from_angles(-1.57, 0.0), params=S.mlp_init(1), tables=S.table_init(2, 16, table_size, 2))
 
@@ -208,7 +215,7 @@ class Workload:
             o.Destroy()
 
 
-def side_measure(args, ctx, rank, world, local, W, H, TW, TH, grid_scale, table_size, scaling, steps=10, warm=3, label=""):
+def side_measure(args, ctx, rank, world, local, W, H, TW, TH, grid_scale, table_size, scaling, steps=20, warm=6, label=""):
     """A short measurement of another BASELINE configuration after the headline loop (own objects, same context): ms/frame, queries/s
     over all ranks (max-over-ranks device time), the slowest kernels of this rank, and its own oracle parity flags."""
     import torch
@@ -754,6 +761,7 @@ def finish_b200(args, v):
                        "cloud_sixteenth (synthetic 125x85x153 stand-in)" if v["grid_scale"] == 1 else
                        "full cloud (synthetic 125x85x153 grid refined x%d per axis)" % v["grid_scale"], W, H, v["TW"], v["TH"]),
                    "baseline_config": args.config,
+                   "envmap": ("file " + os.path.basename(os.environ["NRC_ENVMAP"])) if os.environ.get("NRC_ENVMAP") else "synthetic sky 1024x512 (the shape of data/image/photostudio.hdr; set NRC_ENVMAP=<file.hdr> to load it)",
                    "frame": [W, H], "train_grid": [v["TW"], v["TH"]], "hash_table": [16, v["table_size"], 2], "mlp": "64x5->3 relu",
                    "parallelism": "rows interleaved over %d GPU(s), train samples sharded, %s" % (
                        world, "gradients summed over NVLink peer memory inside the fused step kernel" if (world > 1 and args.exchange == "fused")

@@ -212,6 +212,7 @@ public:
         Push();
     }
     void Update(const float random4[4]) { for (int i = 0; i < 4; i++) m_Params.random[i] = random4[i]; Push(); }
+    void SetSeed(uint32_t seed) { m_Lcg = 0x2545F491u ^ (seed * 2654435761u); }   // of the LCG behind Update(bool)
     nrc_volume_params& Params() { return m_Params; }   // useNN, showNonNN, densityFactor, g, spp: the ImGui sliders (VolumeData.cpp:116-128)
     void Push() const { Check(nrc_volume_set_params(m_Handle, &m_Params), "nrc_volume_set_params"); }
     nrc_volume* Get() const { return m_Handle; }
@@ -349,6 +350,11 @@ public:
     // The same frame in its two halves, for data-parallel ranks: FrameTrain(); DataParallel::ReduceStep(); FrameRender().
     // SetPartition gives this rank rows [y0,y1) of the frame and train invocations [i0,i1).
     void SetPartition(uint32_t y0, uint32_t y1, uint32_t i0, uint32_t i1) { Check(nrc_renderer_set_partition(m_Handle, y0, y1, i0, i1), "nrc_renderer_set_partition"); }
+    // interleaved partition (rows yFirst, yFirst + yStride, ...; train invocations likewise): the load-balanced split data-parallel hosts use
+    void SetPartitionStrided(uint32_t yFirst, uint32_t yStride, uint32_t iFirst, uint32_t iStride)
+    {
+        Check(nrc_renderer_set_partition_strided(m_Handle, yFirst, yStride, iFirst, iStride), "nrc_renderer_set_partition_strided");
+    }
     void FrameTrain() const
     {
         Check(nrc_renderer_set_camera(m_Handle, &m_Camera.GetData()), "nrc_renderer_set_camera");
