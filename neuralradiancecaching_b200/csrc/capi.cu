@@ -462,6 +462,7 @@ extern "C" nrc_status nrc_mrhe_set_config(nrc_mrhe* m, float lr, float wd)
 {
     NRC_REQUIRE(m, "null mrhe");
     m->lr = lr; m->wd = wd;
+    m->tailClean = false;
     return NRC_OK;
 }
 
@@ -472,6 +473,7 @@ extern "C" nrc_status nrc_mrhe_set_tables(nrc_mrhe* m, const float* tables, cons
     NRC_REQUIRE(m, "null mrhe");
     if (tables) NRC_TRY(copy_in(m->ctx, m->tables, tables, m->count * sizeof(float)));
     if (delta) NRC_TRY(copy_in(m->ctx, m->delta, delta, m->count * sizeof(float)));
+    m->tailClean = false;   // the next step must visit every entry again (steps.cu)
     return NRC_OK;
 }
 
@@ -497,6 +499,7 @@ extern "C" nrc_status nrc_mrhe_set_fixed_mode(nrc_mrhe* m, int on)
 {
     NRC_REQUIRE(m, "null mrhe");
     m->fixed = on != 0;
+    m->tailClean = false;
     return NRC_OK;
 }
 
@@ -528,6 +531,7 @@ extern "C" nrc_status nrc_mrhe_set_adam(nrc_mrhe* m, int on, float beta1, float 
         m->beta1 = beta1; m->beta2 = beta2; m->eps = eps;
     }
     m->adam = on != 0;
+    m->tailClean = false;
     m->steps = 0;
     return NRC_OK;
 }

@@ -11,19 +11,26 @@
 //   3. tells every peer "I have read your gradients", waits for all, and clears its own arenas.
 // The exchange is 84 KB + 2*T*4 B: latency-bound (the two NCCL all-reduces alone measure 60 us at 4 GPUs), so the kernel is
 // 16 small blocks that each own a fixed slice of both arenas and handshake with the same block of the peers -- small
-// blocks get an SM slot at once while the render chain fills the GPU, and nothing needs a grid-wide barrier.  For hash tables whose touched head is larger than NRC_DP_MAX_HEAD floats the
-// host falls back to the NCCL path (bandwidth-bound regime).
+// blocks get an SM slot at once while the render chain fills the GPU, and nothing needs a grid-wide barrier.
+// Bandwidth regime (heads above NRC_DP_SHARD_FLOATS: T = 2^22 tables, 33.5 MB; the fixed preset, 512 MiB): the same kernel in
+// SHARDED form -- reduce-scatter + sharded step + all-gather in one launch.  Rank r owns slice r of the head: it reads the W gradient
+// slices over NVLink, adds them in rank order, applies mrhe-step.comp (or the opt-in Adam) to its slice and WRITES the new table
+// values (and Adam moments) into every replica (st.relaxed.sys.v4).  Per rank 2 x (W-1)/W x head bytes cross NVLink instead of
+// (W-1) x head; the grid grows to 64 blocks.  The handshakes are the same two: "gradients complete" before, "I have read yours and
+// written my slice of your table" after -- the second one is what makes the peers' table writes visible before the next kernel here.
 // The reference has no multi-GPU path at all; the step arithmetic is the one of steps.cu (nrc-step.comp:200-406,
 // mrhe-step.comp:27-74).
 #include <cuda_bf16.h>
 #include <string.h>
+#include <math.h>
 #include <stdlib.h>
 #include "nrc_internal.cuh"
 #include "tc_ptx.cuh"
 
 #define NRC_DP_MAX_WORLD 16
-#define NRC_DP_MAX_HEAD (1u << 20)
-#define NRC_DP_FLAG_COUNT (16 * NRC_DP_MAX_WORLD * 2)
+#define NRC_DP_SHARD_FLOATS (1u << 20)   // heads above this many floats are exchanged in sharded form (NRC_DP_SHARD=1 forces it)
+#define NRC_DP_MAX_BLOCKS 64
+#define NRC_DP_FLAG_COUNT (NRC_DP_MAX_BLOCKS * NRC_DP_MAX_WORLD * 2)
 
 struct nrc_dp {
     nrc_mlp* mlp = nullptr;
@@ -35,15 +42,20 @@ struct nrc_dp {
     const float* peerGrad[NRC_DP_MAX_WORLD] = {nullptr};
     const float* peerDelta[NRC_DP_MAX_WORLD] = {nullptr};
     unsigned* peerFlags[NRC_DP_MAX_WORLD] = {nullptr};
-    void* opened[NRC_DP_MAX_WORLD][3] = {{nullptr}};
+    float* peerTables[NRC_DP_MAX_WORLD] = {nullptr};   // sharded form: the owner of a slice writes it into every replica
+    float* peerM1[NRC_DP_MAX_WORLD] = {nullptr};
+    float* peerM2[NRC_DP_MAX_WORLD] = {nullptr};
+    void* opened[NRC_DP_MAX_WORLD][6] = {{nullptr}};
+    bool sharded = false;
+    bool mlpAdam = false, mrheAdam = false;    // as they were when the exchange was created (the moments' buffers are mapped then)
     unsigned* hostFail = nullptr;              // pinned mirror of the sticky time-out word, refreshed behind every launch
 };
 
 struct DpHandle {   // what one rank publishes to the others
-    cudaIpcMemHandle_t grad, delta, flags;
-    unsigned long long rawGrad, rawDelta, rawFlags;   // same-process emulation
+    cudaIpcMemHandle_t grad, delta, flags, tables, m1, m2;
+    unsigned long long rawGrad, rawDelta, rawFlags, rawTables, rawM1, rawM2;   // same-process emulation
     unsigned long long extent;
-    int rank, pad;
+    int rank, adam;
 };
 
 struct DpArgs {
@@ -58,6 +70,13 @@ struct DpArgs {
     float lr, wd, beta1;
     float* tables; float* delta; unsigned extent;
     float mlr, mwd;
+    // sharded form: destinations of the owner's writes; nDest = world (sharded) or 1 (replicated: this replica only)
+    float* destTables[NRC_DP_MAX_WORLD]; float* destM1[NRC_DP_MAX_WORLD]; float* destM2[NRC_DP_MAX_WORLD];
+    int nDest, sharded;
+    // opt-in Adam (steps.cu: k_nrc_step_adam / k_mrhe_step_adam): moments of this replica, bias corrections computed on the host
+    int mlpAdam, mrheAdam;
+    float* second; float beta2, eps, c1, c2;
+    float* m1; float* m2; float mbeta1, mbeta2, meps, mc1, mc2;
     unsigned long long timeoutNs;   // how long a handshake waits for a peer before the exchange fails closed
 };
 
@@ -129,6 +148,11 @@ __device__ __forceinline__ void dp_nrc_update(const DpArgs& a, int i, float g)
     g = __fadd_rn(g, __fmul_rn(-w, a.wd));
     float d = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, a.beta1), g), __fmul_rn(a.beta1, a.momentum[i]));
     a.momentum[i] = d;
+    if (a.mlpAdam) {   // k_nrc_step_adam, operation for operation
+        float v = __fadd_rn(__fmul_rn(a.beta2, a.second[i]), __fmul_rn(__fsub_rn(1.0f, a.beta2), __fmul_rn(g, g)));
+        a.second[i] = v;
+        d = __fdiv_rn(__fmul_rn(d, a.c1), __fadd_rn(__fsqrt_rn(__fmul_rn(v, a.c2)), a.eps));
+    }
     float nw = __fadd_rn(w, __fmul_rn(d, a.lr));
     if (i < NRC_MLP_WEIGHT_COUNT && dp_bad(nw)) nw = 0.0f;
     a.params[i] = nw;
@@ -147,6 +171,23 @@ __device__ __forceinline__ float dp_mrhe_update(float w, float g, float lr, floa
     return dp_bad(nw) ? 0.0f : nw;
 }
 
+// mrhe_update_adam of steps.cu, operation for operation
+__device__ __forceinline__ float dp_mrhe_update_adam(const DpArgs& a, float w, float g, float& m1, float& m2)
+{
+    if (dp_bad(g)) g = __fmul_rn(100.0f, dp_sign(g));
+    g = __fadd_rn(g, __fmul_rn(-w, a.mwd));
+    m1 = __fadd_rn(__fmul_rn(a.mbeta1, m1), __fmul_rn(__fsub_rn(1.0f, a.mbeta1), g));
+    m2 = __fadd_rn(__fmul_rn(a.mbeta2, m2), __fmul_rn(__fsub_rn(1.0f, a.mbeta2), __fmul_rn(g, g)));
+    float d = __fdiv_rn(__fmul_rn(m1, a.mc1), __fadd_rn(__fsqrt_rn(__fmul_rn(m2, a.mc2)), a.meps));
+    float nw = __fadd_rn(w, __fmul_rn(d, a.mlr));
+    return dp_bad(nw) ? 0.0f : nw;
+}
+
+__device__ __forceinline__ void st_sys4(float* p, float4 v)
+{
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 #define DP_BLOCKS 16
 #define DP_THREADS 256
 #define DP_MLP_VEC ((NRC_MLP_PARAM_COUNT + 1 + 3) / 4)   // 5249 float4: 20995 gradients + the loss accumulator
@@ -154,7 +195,7 @@ __device__ __forceinline__ float dp_mrhe_update(float w, float g, float lr, floa
 __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_constant__ DpArgs a)
 {
     const int t = blockIdx.x * DP_THREADS + threadIdx.x;
-    const int stride = DP_BLOCKS * DP_THREADS;
+    const int stride = gridDim.x * DP_THREADS;
     __shared__ int s_fail;
     if (threadIdx.x == 0) s_fail = a.barriers ? (ld_acquire_sys(a.myFlags + NRC_DP_FLAG_COUNT) != 0u) : 0;   // an earlier launch (here or on a peer) gave up
     __syncthreads();
@@ -172,18 +213,35 @@ __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_cons
                 else if (i == NRC_MLP_PARAM_COUNT) lossSum = gs[c];
             }
         }
-        // ---- head of the delta hash table (all Backprop can touch): sum + mrhe-step.comp ----
-        for (unsigned i4 = t; i4 < a.extent / 4; i4 += stride) {
+        // ---- head of the delta hash table (all Backprop can touch): sum + mrhe-step.comp.  Replicated form: every rank
+        // reduces and steps the whole head for itself.  Sharded form: this rank's slice only, written into every replica. ----
+        const unsigned n4 = a.extent / 4;
+        unsigned lo = 0, hi = n4;
+        if (a.sharded) {
+            const unsigned per = (n4 + (unsigned)a.world - 1u) / (unsigned)a.world;
+            lo = min(per * (unsigned)a.rank, n4);
+            hi = min(lo + per, n4);
+        }
+        for (unsigned i4 = lo + t; i4 < hi; i4 += stride) {
             float4 g = dp_sum4(a.peerDelta, a.world, i4);
             float4 w = reinterpret_cast<const float4*>(a.tables)[i4];
-            w.x = dp_mrhe_update(w.x, g.x, a.mlr, a.mwd);
-            w.y = dp_mrhe_update(w.y, g.y, a.mlr, a.mwd);
-            w.z = dp_mrhe_update(w.z, g.z, a.mlr, a.mwd);
-            w.w = dp_mrhe_update(w.w, g.w, a.mlr, a.mwd);
-            reinterpret_cast<float4*>(a.tables)[i4] = w;
+            if (a.mrheAdam) {
+                float4 p = reinterpret_cast<const float4*>(a.m1)[i4], q = reinterpret_cast<const float4*>(a.m2)[i4];
+                w.x = dp_mrhe_update_adam(a, w.x, g.x, p.x, q.x);
+                w.y = dp_mrhe_update_adam(a, w.y, g.y, p.y, q.y);
+                w.z = dp_mrhe_update_adam(a, w.z, g.z, p.z, q.z);
+                w.w = dp_mrhe_update_adam(a, w.w, g.w, p.w, q.w);
+                for (int r = 0; r < a.nDest; r++) { st_sys4(a.destM1[r] + (size_t)i4 * 4, p); st_sys4(a.destM2[r] + (size_t)i4 * 4, q); }
+            } else {
+                w.x = dp_mrhe_update(w.x, g.x, a.mlr, a.mwd);
+                w.y = dp_mrhe_update(w.y, g.y, a.mlr, a.mwd);
+                w.z = dp_mrhe_update(w.z, g.z, a.mlr, a.mwd);
+                w.w = dp_mrhe_update(w.w, g.w, a.mlr, a.mwd);
+            }
+            for (int r = 0; r < a.nDest; r++) st_sys4(a.destTables[r] + (size_t)i4 * 4, w);
         }
     }
-    if (a.barriers) dp_barrier(a, 1, &s_fail);     // block b of every peer has read my slice b
+    if (a.barriers) dp_barrier(a, 1, &s_fail);     // block b of every peer has read my slice b (and, sharded, written its slice of my table)
     if (a.clear && !s_fail) {
         for (int i4 = t; i4 < DP_MLP_VEC; i4 += stride) {
             float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -206,10 +264,15 @@ extern "C" nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int 
 {
     NRC_REQUIRE(mlp && mrhe && out, "null argument");
     NRC_REQUIRE(world >= 1 && world <= NRC_DP_MAX_WORLD && rank >= 0 && rank < world, "rank/world out of range");
-    NRC_REQUIRE(nrc_mrhe_grad_extent(mrhe) <= NRC_DP_MAX_HEAD, "delta-table head too large for the fused exchange; use the NCCL path");
-    NRC_REQUIRE(!mlp->adam && !mrhe->adam, "the fused exchange applies the reference's steps; with Adam use the NCCL path (all-reduce + nrc_optimizer_step)");
+    NRC_REQUIRE(nrc_mrhe_grad_extent(mrhe) < ((size_t)1 << 32) && (nrc_mrhe_grad_extent(mrhe) % 4) == 0, "delta-table head out of range for the fused exchange");
     nrc_dp* d = new nrc_dp();
     d->mlp = mlp; d->mrhe = mrhe; d->rank = rank; d->world = world;
+    {
+        const char* e = getenv("NRC_DP_SHARD");   // 1 / 0 force the sharded / replicated form (tests, measurements)
+        d->sharded = e ? (atoi(e) != 0) : (nrc_mrhe_grad_extent(mrhe) > NRC_DP_SHARD_FLOATS);
+        if (world == 1) d->sharded = false;
+    }
+    d->mlpAdam = mlp->adam; d->mrheAdam = mrhe->adam;
     cudaError_t e = cudaMalloc(&d->flags, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));
     if (e == cudaSuccess) e = cudaMemset(d->flags, 0, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));
     if (e != cudaSuccess) {
@@ -240,8 +303,17 @@ extern "C" nrc_status nrc_dp_export(nrc_dp* d, void* handle)
     h.rawGrad = (unsigned long long)(uintptr_t)d->mlp->grad;
     h.rawDelta = (unsigned long long)(uintptr_t)d->mrhe->delta;
     h.rawFlags = (unsigned long long)(uintptr_t)d->flags;
+    NRC_CUDA(cudaIpcGetMemHandle(&h.tables, d->mrhe->tables));
+    h.rawTables = (unsigned long long)(uintptr_t)d->mrhe->tables;
+    if (d->mrheAdam) {
+        NRC_CUDA(cudaIpcGetMemHandle(&h.m1, d->mrhe->m1));
+        NRC_CUDA(cudaIpcGetMemHandle(&h.m2, d->mrhe->m2));
+        h.rawM1 = (unsigned long long)(uintptr_t)d->mrhe->m1;
+        h.rawM2 = (unsigned long long)(uintptr_t)d->mrhe->m2;
+    }
     h.extent = nrc_mrhe_grad_extent(d->mrhe);
     h.rank = d->rank;
+    h.adam = (d->mlpAdam ? 1 : 0) | (d->mrheAdam ? 2 : 0) | (d->sharded ? 4 : 0);
     memcpy(handle, &h, sizeof(h));
     return NRC_OK;
 }
@@ -257,9 +329,13 @@ extern "C" nrc_status nrc_dp_connect(nrc_dp* d, const void* allHandles, int same
     for (int r = 0; r < d->world; r++) {
         NRC_REQUIRE(hs[r].rank == r, "handles are not in rank order");
         NRC_REQUIRE(hs[r].extent == extent, "ranks disagree on the hash-table shape");
+        NRC_REQUIRE(hs[r].adam == ((d->mlpAdam ? 1 : 0) | (d->mrheAdam ? 2 : 0) | (d->sharded ? 4 : 0)), "ranks disagree on Adam / the exchange form");
         if (r == d->rank) {
             d->peerGrad[r] = d->mlp->grad; d->peerDelta[r] = d->mrhe->delta; d->peerFlags[r] = d->flags;
+            d->peerTables[r] = d->mrhe->tables; d->peerM1[r] = d->mrhe->m1; d->peerM2[r] = d->mrhe->m2;
         } else if (sameProcess) {
+            d->peerTables[r] = (float*)(uintptr_t)hs[r].rawTables;
+            d->peerM1[r] = (float*)(uintptr_t)hs[r].rawM1; d->peerM2[r] = (float*)(uintptr_t)hs[r].rawM2;
             d->peerGrad[r] = (const float*)(uintptr_t)hs[r].rawGrad;
             d->peerDelta[r] = (const float*)(uintptr_t)hs[r].rawDelta;
             d->peerFlags[r] = (unsigned*)(uintptr_t)hs[r].rawFlags;
@@ -270,6 +346,15 @@ extern "C" nrc_status nrc_dp_connect(nrc_dp* d, const void* allHandles, int same
             d->peerGrad[r] = (const float*)d->opened[r][0];
             d->peerDelta[r] = (const float*)d->opened[r][1];
             d->peerFlags[r] = (unsigned*)d->opened[r][2];
+            if (d->sharded) {   // the owner of a slice writes it into this peer's replica
+                NRC_CUDA(cudaIpcOpenMemHandle(&d->opened[r][3], hs[r].tables, cudaIpcMemLazyEnablePeerAccess));
+                d->peerTables[r] = (float*)d->opened[r][3];
+                if (d->mrheAdam) {
+                    NRC_CUDA(cudaIpcOpenMemHandle(&d->opened[r][4], hs[r].m1, cudaIpcMemLazyEnablePeerAccess));
+                    NRC_CUDA(cudaIpcOpenMemHandle(&d->opened[r][5], hs[r].m2, cudaIpcMemLazyEnablePeerAccess));
+                    d->peerM1[r] = (float*)d->opened[r][4]; d->peerM2[r] = (float*)d->opened[r][5];
+                }
+            }
         }
     }
     d->connected = true;
@@ -292,12 +377,33 @@ static nrc_status dp_launch(nrc_dp* d, int barriers, int clear, bool reduce)
     a.lr = d->mlp->lr; a.wd = d->mlp->wd; a.beta1 = d->mlp->beta1;
     a.tables = d->mrhe->tables; a.delta = d->mrhe->delta; a.extent = (unsigned)nrc_mrhe_grad_extent(d->mrhe);
     a.mlr = d->mrhe->lr; a.mwd = d->mrhe->wd;
+    NRC_REQUIRE(d->mlp->adam == d->mlpAdam && d->mrhe->adam == d->mrheAdam, "Adam was switched after nrc_dp_create: create the exchange again");
+    a.sharded = d->sharded ? 1 : 0;
+    if (d->sharded) {
+        a.nDest = d->world;
+        for (int r = 0; r < d->world; r++) { a.destTables[r] = d->peerTables[r]; a.destM1[r] = d->peerM1[r]; a.destM2[r] = d->peerM2[r]; }
+    } else {
+        a.nDest = 1;
+        a.destTables[0] = d->mrhe->tables; a.destM1[0] = d->mrhe->m1; a.destM2[0] = d->mrhe->m2;
+    }
+    if (reduce && d->mlpAdam) {   // launch_nrc_step's bookkeeping
+        d->mlp->steps++;
+        a.mlpAdam = 1; a.second = d->mlp->second; a.beta2 = d->mlp->beta2; a.eps = d->mlp->eps;
+        a.c1 = 1.0f / (1.0f - powf(d->mlp->beta1, (float)d->mlp->steps)); a.c2 = 1.0f / (1.0f - powf(d->mlp->beta2, (float)d->mlp->steps));
+    }
+    if (reduce && d->mrheAdam) {  // launch_mrhe_step's
+        d->mrhe->steps++;
+        a.mrheAdam = 1; a.m1 = d->mrhe->m1; a.m2 = d->mrhe->m2; a.mbeta1 = d->mrhe->beta1; a.mbeta2 = d->mrhe->beta2; a.meps = d->mrhe->eps;
+        a.mc1 = 1.0f / (1.0f - powf(d->mrhe->beta1, (float)d->mrhe->steps)); a.mc2 = 1.0f / (1.0f - powf(d->mrhe->beta2, (float)d->mrhe->steps));
+    }
     {
         const char* e = getenv("NRC_DP_TIMEOUT_MS");   // default 30 s: longer than any stall of a healthy rank (pool regrowth + re-trace, checkpoint load)
         const long ms = e ? atol(e) : 30000;
         a.timeoutNs = (unsigned long long)(ms > 0 ? ms : 30000) * 1000000ull;
     }
-    NRC_LAUNCH(ctx, ctx->stream, K_DP_REDUCE_STEP, k_dp_reduce_step<<<DP_BLOCKS, DP_THREADS, 0, ctx->stream>>>(a));
+    // latency regime: 16 small blocks; bandwidth regime (sharded): 64, so that enough NVLink loads and stores are in flight
+    const unsigned blocks = d->sharded ? NRC_DP_MAX_BLOCKS : DP_BLOCKS;
+    NRC_LAUNCH(ctx, ctx->stream, K_DP_REDUCE_STEP, k_dp_reduce_step<<<blocks, DP_THREADS, 0, ctx->stream>>>(a));
     // the sticky time-out word follows every launch to pinned host memory: the next call / nrc_sync / nrc_readback_wait sees it
     if (barriers) NRC_CUDA(cudaMemcpyAsync(d->hostFail, d->flags + NRC_DP_FLAG_COUNT, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
     return NRC_OK;
@@ -342,7 +448,7 @@ extern "C" nrc_status nrc_dp_destroy(nrc_dp* d)
     if (!d) return NRC_OK;
     cudaStreamSynchronize(d->mlp->ctx->stream);
     for (int r = 0; r < NRC_DP_MAX_WORLD; r++)
-        for (int k = 0; k < 3; k++)
+        for (int k = 0; k < 6; k++)
             if (d->opened[r][k]) cudaIpcCloseMemHandle(d->opened[r][k]);
     cudaFree(d->flags);
     {

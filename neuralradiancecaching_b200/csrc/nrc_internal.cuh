@@ -130,6 +130,11 @@ struct nrc_mrhe {
     float* m1 = nullptr;         // first / second moments, L*T*F each (allocated when Adam is switched on)
     float* m2 = nullptr;
     uint32_t steps = 0;
+    // mrhe-step.comp visits every table entry every frame (2 GiB of traffic at T = 2^22), but in the shipped arithmetic gradients only ever
+    // land in the head [0, 2T).  With weight decay 0 an entry whose delta is 0 is left bit-identical by the step
+    // (w + lr * (0 - w * 0) = w) once it has been scrubbed (bad(w) -> 0) -- so after ONE full step the tail is a fixed point and later
+    // steps visit the head only.  Anything that can change the tail or the rule (set_tables, set_config, fixed preset, Adam) clears this.
+    bool tailClean = false;
 };
 
 struct nrc_volume {

@@ -6,6 +6,7 @@
 //                          16 B/param streamed with 128-bit accesses; HBM-bound at T = 2^22 (2 GiB / step).
 // Both are pure streaming kernels: grid sized in multiples of the SM count, float4 accesses, no reuse.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include "nrc_internal.cuh"
 #include "tc_ptx.cuh"
 
@@ -157,9 +158,20 @@ nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st)
     return NRC_OK;
 }
 
+// entries beyond which the step may skip (see nrc_mrhe::tailClean): the whole table unless the tail is a proven fixed point
+static size_t mrhe_step_extent(const nrc_mrhe* m)
+{
+    const size_t head = nrc_mrhe_grad_extent(const_cast<nrc_mrhe*>(m));
+    static int noSkip = -1;   // NRC_MRHE_STEP_FULL=1: always stream the whole table like the reference's dispatch (measurements)
+    if (noSkip < 0) { const char* e = getenv("NRC_MRHE_STEP_FULL"); noSkip = (e && atoi(e)) ? 1 : 0; }
+    if (!noSkip && m->tailClean && m->wd == 0.0f && !m->adam && !m->fixed && head < m->count) return head;
+    return m->count;
+}
+
 nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
 {
-    size_t n4 = m->count / 4;   // L*T*F is a multiple of 4 for every supported shape (F == 2, T even)
+    const size_t extent = mrhe_step_extent(m);
+    size_t n4 = extent / 4;   // L*T*F is a multiple of 4 for every supported shape (F == 2, T even)
     size_t want = (n4 + 255) / 256;
     size_t cap = (size_t)m->ctx->smCount * 8;
     unsigned blocks = (unsigned)(want < cap ? want : cap);
@@ -175,6 +187,7 @@ nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
     }
     NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
                k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables), reinterpret_cast<float4*>(m->delta), n4, m->lr, m->wd));
+    if (extent == m->count && m->wd == 0.0f && !m->fixed) m->tailClean = true;   // every entry scrubbed, every delta zero: the tail is a fixed point now
     return NRC_OK;
 }
 
@@ -182,14 +195,24 @@ nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st)
 nrc_status launch_mrhe_step_range(nrc_mrhe* m, size_t firstFloat, cudaStream_t st)
 {
     if (firstFloat >= m->count) return NRC_OK;
+    if (firstFloat >= mrhe_step_extent(m)) return NRC_OK;   // the tail is a fixed point of the step (nrc_mrhe::tailClean)
     size_t n4 = (m->count - firstFloat) / 4;
     size_t want = (n4 + 255) / 256;
     size_t cap = (size_t)m->ctx->smCount * 8;
     unsigned blocks = (unsigned)(want < cap ? want : cap);
     if (blocks == 0) return NRC_OK;
+    if (m->adam) {   // the fused kernel has already counted this step (dp.cu): same bias corrections, no second increment
+        const float c1 = 1.0f / (1.0f - powf(m->beta1, (float)m->steps)), c2 = 1.0f / (1.0f - powf(m->beta2, (float)m->steps));
+        NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
+                   k_mrhe_step_adam<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables + firstFloat), reinterpret_cast<float4*>(m->delta + firstFloat),
+                                                            reinterpret_cast<float4*>(m->m1 + firstFloat), reinterpret_cast<float4*>(m->m2 + firstFloat), n4,
+                                                            m->lr, m->wd, m->beta1, m->beta2, m->eps, c1, c2));
+        return NRC_OK;
+    }
     NRC_LAUNCH(m->ctx, st, K_MRHE_STEP,
                k_mrhe_step<<<blocks, 256, 0, st>>>(reinterpret_cast<float4*>(m->tables + firstFloat),
                                                    reinterpret_cast<float4*>(m->delta + firstFloat), n4, m->lr, m->wd));
+    if (firstFloat <= nrc_mrhe_grad_extent(m) && m->wd == 0.0f && !m->fixed && !m->adam) m->tailClean = true;
     return NRC_OK;
 }
 

@@ -16,13 +16,12 @@ import neuralradiancecaching_b200 as N  # noqa: E402
 from neuralradiancecaching_b200.dist import FusedExchange, GradientExchange  # noqa: E402
 
 
-def main():
-    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist.init_process_group("nccl", device_id=dev)
-    ctx = N.Context(local)
-    T = 16384
+def run_case(ctx, dev, rank, world, name, T, shard=None, adam=False, fixed=False, iters=5, timing=0):
+    """fused vs NCCL + step kernels from the same per-rank gradients, `iters` frames; returns a one-line report"""
+    if shard is None:
+        os.environ.pop("NRC_DP_SHARD", None)
+    else:
+        os.environ["NRC_DP_SHARD"] = shard
     params = Cm.S.mlp_init(1)
     tables = Cm.S.table_init(2, 16, T, 2)
     mom = Cm.S.init_params(5, 20995, 0.01)
@@ -32,20 +31,22 @@ def main():
         nrc.set_params(params)
         m = N.MRHE(ctx, 0.1, 0.01, 16, T, 2, 16, 512, Cm.RES_INTENDED, seed=0)
         m.set_tables(tables)
+        if fixed:
+            m.set_fixed_mode(True)
+        if adam:
+            nrc.set_adam(True); m.set_adam(True)
         return nrc, m
 
     a_nrc, a_m = replica()     # NCCL path
     b_nrc, b_m = replica()     # fused path
     nccl = GradientExchange(ctx, a_nrc, a_m, dev)
     fused = FusedExchange(b_nrc, b_m, rank, world, dev)
-    for it in range(5):        # several frames: the flag epochs advance, the arenas are cleared and refilled
+    extent = b_m.grad_ptr()[1]
+    for it in range(iters):    # several frames: the flag epochs advance, the arenas are cleared and refilled
         g = Cm.S.init_params(1000 * it + rank, 20995, 0.3)
         t = np.zeros_like(tables)
-        t[:2 * T] = Cm.S.init_params(7000 * it + rank, 2 * T, 0.2)
-        if it == 0:
-            mm = mom
-        else:
-            mm = None
+        t[:extent] = Cm.S.init_params(7000 * it + rank, extent, 0.2)
+        mm = mom if it == 0 else None
         for nrc, m in ((a_nrc, a_m), (b_nrc, b_m)):
             nrc.set_state(delta=g, momentum=mm)
             m.set_tables(None, t)
@@ -63,19 +64,68 @@ def main():
             np.testing.assert_array_equal(ap.view(np.uint32), bp.view(np.uint32))
             np.testing.assert_array_equal(am.view(np.uint32), bm.view(np.uint32))
             np.testing.assert_array_equal(at.view(np.uint32), bt.view(np.uint32))
+            if adam:
+                np.testing.assert_array_equal(a_nrc.get_adam_state()[0].view(np.uint32), b_nrc.get_adam_state()[0].view(np.uint32))
+                for x, y in zip(a_m.get_adam_state()[:2], b_m.get_adam_state()[:2]):
+                    np.testing.assert_array_equal(x.view(np.uint32), y.view(np.uint32))
         else:
             np.testing.assert_allclose(ap, bp, rtol=1e-5, atol=1e-6)
             np.testing.assert_allclose(at, bt, rtol=1e-5, atol=1e-6)
         # every replica of the fused path holds the same bits
-        mine = torch.from_numpy(np.concatenate([bp, bt]).view(np.int32).copy()).to(dev)
+        parts = [bp, bt] + (list(b_m.get_adam_state()[:2]) if adam else [])
+        mine = torch.from_numpy(np.concatenate(parts).view(np.int32).copy()).to(dev)
         lo, hi = mine.clone(), mine.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN)
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        assert bool((lo == hi).all()), "replicas diverged"
+        assert bool((lo == hi).all()), "replicas diverged (%s)" % name
+    report = "%s: T=%d head=%.1f MB ok" % (name, T, extent * 4 / 1e6)
+    if timing:                 # the exchange + steps alone, ranks aligned: device time of `timing` back-to-back frames
+        ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+        res = {}
+        for label, fn in (("fused", lambda: fused()), ("nccl+steps", lambda: (nccl(), N.optimizer_step(a_nrc, a_m)))):
+            for _ in range(3):
+                fn()
+            ctx.sync(); torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(ext):
+                e0.record()
+            for _ in range(timing):
+                fn()
+            with torch.cuda.stream(ext):
+                e1.record()
+            ctx.sync(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / timing], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res[label] = float(t[0])
+        nv = 2.0 * (world - 1) / world * extent * 4      # bytes this rank moves over NVLink per exchange in sharded form (in + out)
+        report += "; fused %.3f ms (%.0f GB/s NVLink per rank, in+out) vs nccl+steps %.3f ms" % (res["fused"], nv / res["fused"] / 1e6, res["nccl+steps"])
     assert not fused.timed_out()
     dist.barrier()
     fused.close()
+    for o in (a_nrc, a_m, b_nrc, b_m):
+        o.Destroy()
+    return report
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    ctx = N.Context(local)
+    big = os.environ.get("CHECK_DP_BIG")
+    reports = [
+        run_case(ctx, dev, rank, world, "replicated", 16384, shard="0"),
+        run_case(ctx, dev, rank, world, "sharded (forced)", 16384, shard="1"),
+        run_case(ctx, dev, rank, world, "adam + fixed preset, replicated", 4096, shard="0", adam=True, fixed=True, iters=3),
+        run_case(ctx, dev, rank, world, "adam + fixed preset, sharded", 4096, shard="1", adam=True, fixed=True, iters=3),
+        run_case(ctx, dev, rank, world, "large table (sharded by size)", (1 << 22) if big else (1 << 20), iters=2, timing=20),
+    ]
+    if big:                    # the fixed preset at config 5's table size: the whole 512 MiB table is exchanged
+        reports.append(run_case(ctx, dev, rank, world, "fixed preset at T=2^22 (sharded by size)", 1 << 22, fixed=True, iters=1, timing=5))
     if rank == 0:
+        for r in reports:
+            print("DP-CHECK", r)
         print("DP-CHECK OK world=%d" % world)
     dist.destroy_process_group()
 

@@ -30,9 +30,12 @@ def _sum_rank_order(parts):
     return acc
 
 
-@pytest.mark.parametrize("world,wd", [(1, 0.0), (3, 0.0), (4, 0.01)])
-def test_fused_reduce_step_matches_oracle_bit_exact(N, ctx, world, wd):
+@pytest.mark.parametrize("world,wd,shard", [(1, 0.0, "0"), (3, 0.0, "0"), (4, 0.01, "0"), (3, 0.0, "1"), (4, 0.01, "1")])
+def test_fused_reduce_step_matches_oracle_bit_exact(N, ctx, world, wd, shard, monkeypatch):
+    """shard = "1": the sharded form (reduce-scatter + sharded step + all-gather in one kernel; what tables beyond 2^20 head floats
+    use) forced on the small table: replica r steps slice r and writes it into every replica."""
     from neuralradiancecaching_b200.dist import FusedExchange
+    monkeypatch.setenv("NRC_DP_SHARD", shard)
     T = 16384
     params = Cm.S.mlp_init(1)
     params[20672:] = Cm.S.init_params(7, 323, 0.01)
@@ -98,10 +101,65 @@ def test_fused_rejects_unconnected_and_oversized(N, ctx):
     with pytest.raises(L.NrcError):
         d()                                                    # not connected
     d.close()
-    big = N.MRHE(ctx, 0.01, 0.0, 16, 1 << 20, 2, 16, 512, Cm.RES_INTENDED, seed=0)   # head = 2^21 floats: NCCL regime
-    with pytest.raises(L.NrcError):
-        FusedExchange(nrc, big, 0, 2, connect=False)
-    nrc.Destroy(); m.Destroy(); big.Destroy()
+    nrc.Destroy(); m.Destroy()
+
+
+@pytest.mark.parametrize("shard", ["0", "1"])
+def test_fused_exchange_with_adam_and_the_fixed_preset(N, ctx, shard, monkeypatch):
+    """The opt-in preset through the fused kernel (round 1 refused it): per-level gradient tables (the whole table is exchanged) and
+    Adam in both steps.  Three replicas against ONE replica that is handed the rank-ordered sum and stepped by nrc_optimizer_step:
+    parameters, tables and all moments bit for bit, over two steps (bias corrections advance)."""
+    from neuralradiancecaching_b200.dist import FusedExchange
+    monkeypatch.setenv("NRC_DP_SHARD", shard)
+    world, T = 3, 4096
+    params = Cm.S.mlp_init(1)
+    tables = Cm.S.table_init(2, 16, T, 2)
+
+    def replica():
+        nrc = N.NeuralRadianceCache(ctx, 0.01, 0.001, 0.9, seed=0)
+        nrc.set_params(params)
+        m = N.MRHE(ctx, 0.02, 0.001, 16, T, 2, 16, 512, Cm.RES_INTENDED, seed=0)
+        m.set_tables(tables)
+        m.set_fixed_mode(True)
+        nrc.set_adam(True); m.set_adam(True)
+        return nrc, m
+
+    reps = [replica() for _ in range(world)]
+    ref_nrc, ref_m = replica()
+    dps = [FusedExchange(nrc, m, r, world, connect=False) for r, (nrc, m) in enumerate(reps)]
+    for d in dps:
+        d.connect([x.handle for x in dps], same_process=True)
+    for it in range(2):
+        gm = [Cm.S.init_params(100 + 10 * it + r, 20995, 0.3) for r in range(world)]
+        gt = [Cm.S.init_params(200 + 10 * it + r, 16 * T * 2, 0.2) for r in range(world)]
+        for (nrc, m), g, t in zip(reps, gm, gt):
+            nrc.set_state(delta=g); m.set_tables(None, t)
+        ref_nrc.set_state(delta=_sum_rank_order(gm)); ref_m.set_tables(None, _sum_rank_order(gt))
+        N.optimizer_step(ref_nrc, ref_m)
+        for d in dps:
+            d.phase(0)
+        for d in dps:
+            d.phase(1)
+        ctx.sync()
+        rp, _, rm = ref_nrc.get_params()
+        rt, _ = ref_m.get_tables()
+        rs, _ = ref_nrc.get_adam_state()
+        rm1, rm2, _ = ref_m.get_adam_state()
+        for nrc, m in reps:
+            gp, gd, gmo = nrc.get_params()
+            np.testing.assert_array_equal(gp.view(np.uint32), rp.view(np.uint32))
+            np.testing.assert_array_equal(gmo.view(np.uint32), rm.view(np.uint32))
+            np.testing.assert_array_equal(nrc.get_adam_state()[0].view(np.uint32), rs.view(np.uint32))
+            tt, td = m.get_tables()
+            np.testing.assert_array_equal(tt.view(np.uint32), rt.view(np.uint32))
+            m1, m2, _ = m.get_adam_state()
+            np.testing.assert_array_equal(m1.view(np.uint32), rm1.view(np.uint32))
+            np.testing.assert_array_equal(m2.view(np.uint32), rm2.view(np.uint32))
+            assert not gd.any() and not td.any()
+    for d in dps:
+        d.close()
+    for nrc, m in reps + [(ref_nrc, ref_m)]:
+        nrc.Destroy(); m.Destroy()
 
 
 def test_fused_exchange_fails_closed_when_a_peer_never_arrives(N, ctx, monkeypatch):

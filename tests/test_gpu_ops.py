@@ -170,6 +170,46 @@ def test_step_scrubbing_rules(N, ctx):
     nrc.Destroy(); m.Destroy()
 
 
+def test_head_only_mrhe_step_is_the_full_step(N, ctx):
+    """mrhe-step.comp visits every entry every frame; the library visits the tail once and then only the head the gradients can reach
+    (weight decay 0: the tail is a fixed point of the step, csrc/steps.cu).  Against the oracle's full steps, bit for bit, with bad
+    values in the tail (scrubbed by the first step), a mid-run set_tables (full pass again) and a weight-decay change (full passes)."""
+    T = 16384
+    tables = Cm.S.table_init()
+    tables[[2 * T + 5, 9 * T, 31 * T + 7]] = [np.nan, 5000.0, -np.inf]
+    sc = Cm.oracle_scene(Cm.scene_cfg(), tables=tables, mrhe_lr=(0.1, 0.0))
+    m = N.MRHE(ctx, 0.1, 0.0, seed=0)
+    m.set_tables(tables)
+
+    import torch
+    from neuralradiancecaching_b200.dist import DevArray
+    ptr, extent = m.grad_ptr()
+    assert extent == 2 * T
+    head = torch.as_tensor(DevArray(ptr, extent), device=torch.device("cuda", 0))   # the delta head, written like the train kernel writes it
+
+    def step(k):
+        d = np.zeros_like(tables)
+        d[:2 * T] = Cm.S.init_params(300 + k, 2 * T, 0.2)
+        sc.set_mrhe_delta(d)
+        ctx.sync()
+        head.copy_(torch.from_numpy(d[:2 * T]))
+        torch.cuda.synchronize()
+        sc.mrhe_step(); N.optimizer_step(None, m)
+        gt, gd = m.get_tables()
+        np.testing.assert_array_equal(gt.view(np.uint32), sc.get_mrhe()[0].view(np.uint32), err_msg="step %d" % k)
+        assert not gd.any()
+
+    for k in range(3):
+        step(k)
+    t2 = m.get_tables()[0].copy()
+    t2[5 * T + 1] = 2000.0                        # a bad value appears in the tail: the next step must scrub it
+    sc.set_mrhe(t2, Cm.RES_INTENDED, 0.1, 0.0); m.set_tables(t2)
+    step(3); step(4)
+    sc.set_mrhe(m.get_tables()[0], Cm.RES_INTENDED, 0.1, 0.01); m.set_config(0.1, 0.01)      # weight decay: every entry moves every step
+    step(5); step(6)
+    m.Destroy()
+
+
 def test_hdr4f_to_cdf_bit_exact(N, ctx):
     from oracle import oracle as O
     env = Cm.envmap()
