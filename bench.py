@@ -147,8 +147,6 @@ class Workload:
         self.exchange = GradientExchange(ctx, self.nrc, self.mrhe, dev)
         self.ext = self.exchange.stream
         kind = exchange or args.exchange
-        if 2 * table_size > (1 << 20) and not os.environ.get("NRC_DP_BIG"):
-            kind = "nccl"                         # heads beyond 2^20 floats go through NCCL unless the sharded fused exchange is asked for
         self.exchange_kind = kind if world > 1 else "none"
         self.fused = FusedExchange(self.nrc, self.mrhe, rank, world, dev) if (world > 1 and kind == "fused") else None
 
@@ -764,7 +762,7 @@ def finish_b200(args, v):
                    "envmap": ("file " + os.path.basename(os.environ["NRC_ENVMAP"])) if os.environ.get("NRC_ENVMAP") else "synthetic sky 1024x512 (the shape of data/image/photostudio.hdr; set NRC_ENVMAP=<file.hdr> to load it)",
                    "frame": [W, H], "train_grid": [v["TW"], v["TH"]], "hash_table": [16, v["table_size"], 2], "mlp": "64x5->3 relu",
                    "parallelism": "rows interleaved over %d GPU(s), train samples sharded, %s" % (
-                       world, "gradients summed over NVLink peer memory inside the fused step kernel" if (world > 1 and args.exchange == "fused")
+                       world, "gradients summed over NVLink peer memory inside the fused step kernel (sharded form for heads above 2^20 floats)" if (world > 1 and args.exchange == "fused")
                        else "NCCL all-reduce of gradients"),
                    "vertex_pool": "%d vertices per path%s" % (v["pool_per_path"] or 4, " (worst case: cannot overflow)" if v["pool_per_path"] >= 32 else ""),
                    "l2": "fresh per-frame RNG seed: every frame traces new paths; per-frame buffers (%.0f MB) exceed nothing but are rewritten, "

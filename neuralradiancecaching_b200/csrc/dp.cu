@@ -16,7 +16,7 @@
 // SHARDED form -- reduce-scatter + sharded step + all-gather in one launch.  Rank r owns slice r of the head: it reads the W gradient
 // slices over NVLink, adds them in rank order, applies mrhe-step.comp (or the opt-in Adam) to its slice and WRITES the new table
 // values (and Adam moments) into every replica (st.relaxed.sys.v4).  Per rank 2 x (W-1)/W x head bytes cross NVLink instead of
-// (W-1) x head; the grid grows to 64 blocks.  The handshakes are the same two: "gradients complete" before, "I have read yours and
+// (W-1) x head; the grid grows to 592 blocks (4 per SM).  The handshakes are the same two: "gradients complete" before, "I have read yours and
 // written my slice of your table" after -- the second one is what makes the peers' table writes visible before the next kernel here.
 // The reference has no multi-GPU path at all; the step arithmetic is the one of steps.cu (nrc-step.comp:200-406,
 // mrhe-step.comp:27-74).
@@ -29,7 +29,7 @@
 
 #define NRC_DP_MAX_WORLD 16
 #define NRC_DP_SHARD_FLOATS (1u << 20)   // heads above this many floats are exchanged in sharded form (NRC_DP_SHARD=1 forces it)
-#define NRC_DP_MAX_BLOCKS 64
+#define NRC_DP_MAX_BLOCKS 592   // sharded form: 4 blocks per SM of a B200, so that enough NVLink loads and stores are in flight
 #define NRC_DP_FLAG_COUNT (NRC_DP_MAX_BLOCKS * NRC_DP_MAX_WORLD * 2)
 
 struct nrc_dp {
@@ -222,6 +222,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_cons
             lo = min(per * (unsigned)a.rank, n4);
             hi = min(lo + per, n4);
         }
+#pragma unroll 2
         for (unsigned i4 = lo + t; i4 < hi; i4 += stride) {
             float4 g = dp_sum4(a.peerDelta, a.world, i4);
             float4 w = reinterpret_cast<const float4*>(a.tables)[i4];
@@ -251,7 +252,14 @@ __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_cons
             }
             reinterpret_cast<float4*>(a.grad)[i4] = z;
         }
-        for (unsigned i4 = t; i4 < a.extent / 4; i4 += stride) reinterpret_cast<float4*>(a.delta)[i4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        // Block b may only clear what block b of the READER has read (the handshakes pair equal block indices): in the sharded form slice s
+        // of my gradients is read by rank s, whose block b walks lo_s + t, lo_s + t + stride, ... -- so the clear walks every slice the same way.
+        const unsigned n4 = a.extent / 4;
+        const unsigned per = a.sharded ? (n4 + (unsigned)a.world - 1u) / (unsigned)a.world : n4;
+        for (unsigned lo = 0; lo < n4; lo += per) {
+            const unsigned hi = min(lo + per, n4);
+            for (unsigned i4 = lo + t; i4 < hi; i4 += stride) reinterpret_cast<float4*>(a.delta)[i4] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
     }
 }
 
@@ -401,7 +409,7 @@ static nrc_status dp_launch(nrc_dp* d, int barriers, int clear, bool reduce)
         const long ms = e ? atol(e) : 30000;
         a.timeoutNs = (unsigned long long)(ms > 0 ? ms : 30000) * 1000000ull;
     }
-    // latency regime: 16 small blocks; bandwidth regime (sharded): 64, so that enough NVLink loads and stores are in flight
+    // latency regime: 16 small blocks; bandwidth regime (sharded): 4 per SM, so that enough NVLink loads and stores are in flight
     const unsigned blocks = d->sharded ? NRC_DP_MAX_BLOCKS : DP_BLOCKS;
     NRC_LAUNCH(ctx, ctx->stream, K_DP_REDUCE_STEP, k_dp_reduce_step<<<blocks, DP_THREADS, 0, ctx->stream>>>(a));
     // the sticky time-out word follows every launch to pinned host memory: the next call / nrc_sync / nrc_readback_wait sees it
