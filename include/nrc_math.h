@@ -101,6 +101,9 @@ NRC_HD float nrc_min(float a, float b) { return (b < a) ? b : a; }
 /* uint(x) for a float: saturating, NaN -> 0 (what cvt.rzi.u32.f32 does). */
 NRC_HD uint32_t nrc_f2u(float x)
 {
+#if defined(__CUDA_ARCH__)
+    return __float2uint_rz(x);   /* cvt.rzi.u32.f32 itself: negative and NaN -> 0, too large -> 0xffffffff */
+#endif
     if (!(x > 0.0f)) return 0u;
     if (x >= 4294967296.0f) return 0xffffffffu;
     return (uint32_t)x;

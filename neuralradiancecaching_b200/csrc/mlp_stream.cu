@@ -59,24 +59,6 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v)
 
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-
-// whole-tile 1-D bulk copy global -> shared, completion counted in bytes on the mbarrier
-__device__ __forceinline__ void bulk_load(void* dstSmem, const void* srcGlobal, uint32_t bytes, uint64_t* bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dstSmem)),
-                 "l"(srcGlobal), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-
 // relu(hi), relu(lo) rounded to nearest-even bf16, hi in the upper half
 __device__ __forceinline__ uint32_t pack_relu_bf16(float lo, float hi)
 {

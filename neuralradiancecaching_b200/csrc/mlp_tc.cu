@@ -373,7 +373,7 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 #define TT_LOSS (TT_DROP + 512)                    // [8] float
 #define TT_GATE0 (TT_LOSS + 64)                    // [128][4] ushort: sign bits of the 64 fp32 network inputs (layer-0 gate)
 #define TT_BAR (TT_GATE0 + 1024)
-#define TT_SMEM_BYTES (TT_BAR + 16)
+#define TT_SMEM_BYTES (TT_BAR + 32)
 #define TT_HIST TT_ACT                             // after the last tile: the hash-gradient histogram (up to 128 KiB = TT_ACT .. TT_ET)
 #define TT_DW_COL(l) (64u + 80u * (uint32_t)(l))
 static_assert(TT_SMEM_BYTES <= 227 * 1024, "k_train_tc shared memory");
@@ -386,14 +386,24 @@ __device__ __forceinline__ void tt_stage8k(unsigned char* dst, const __nv_bfloat
     for (int i = threadIdx.x; i < bytes / 16; i += TC_THREADS) d[i] = __ldg(s + i);
 }
 
+// Weight staging by ONE thread with bulk copies (cp.async.bulk, completion counted on an mbarrier): the other 255 threads go straight
+// to their epilogue instead of stalling on L2 loads (13 % of the kernel's stall samples in profiles/r02t were the staging loop).
 // the three parts of layer l's forward weights into the three stages
-__device__ __forceinline__ void tt_stage_fwd(unsigned char* smem, const __nv_bfloat16* __restrict__ wimg, int l)
+__device__ __forceinline__ void tt_bulk_fwd(unsigned char* smem, const __nv_bfloat16* __restrict__ wimg, int l, uint64_t* barW)
 {
-    const int bytes = (l < 5) ? 8192 : 2048;
+    const uint32_t bytes = (l < 5) ? 8192u : 2048u;
     const int off = (l < 5) ? l * 4096 : 5 * 4096;
-    tt_stage8k(smem + TT_WF, wimg + off, bytes);
-    tt_stage8k(smem + TT_WF + 8192, wimg + TC_IMG_MID + off, bytes);
-    tt_stage8k(smem + TT_WF + 16384, wimg + TC_IMG_LO + off, bytes);
+    mbar_expect_tx(barW, 3u * bytes);
+    bulk_load(smem + TT_WF, wimg + off, bytes, barW);
+    bulk_load(smem + TT_WF + 8192, wimg + TC_IMG_MID + off, bytes, barW);
+    bulk_load(smem + TT_WF + 16384, wimg + TC_IMG_LO + off, bytes, barW);
+}
+// layer l's transposed weights into the backward stage
+__device__ __forceinline__ void tt_bulk_bwd(unsigned char* smem, const __nv_bfloat16* __restrict__ wimg, int l, uint64_t* barW)
+{
+    const uint32_t bytes = (l < 5) ? 8192u : 2048u;
+    mbar_expect_tx(barW, bytes);
+    bulk_load(smem + TT_WB, wimg + TC_IMG_T + ((l < 5) ? l * 4096 : 5 * 4096), bytes, barW);
 }
 
 // element (feature m, sample k) of a K=sample operand
@@ -416,6 +426,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     float* lossS = reinterpret_cast<float*>(smem + TT_LOSS);
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + TT_BAR);
     uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(smem + TT_BAR + 8);
+    uint64_t* barW = reinterpret_cast<uint64_t*>(smem + TT_BAR + 16);   // weight stages filled (bulk copies of thread 0)
     unsigned short* gate0S = reinterpret_cast<unsigned short*>(smem + TT_GATE0);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -429,6 +440,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     for (int i = tid; i < 336; i += TC_THREADS) biasS[i] = (i < 323) ? __ldg(params + NRC_B_OFF(0) + i) : 0.0f;
     if (tid == 0) {
         mbar_init(bar, 1);
+        mbar_init(barW, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) tmem_alloc(tmemSlot, 512);
@@ -440,7 +452,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     tc_fence_after();
     const uint32_t tmemBase = *tmemSlot;
     const uint32_t sBase = smem_u32(smem);
-    uint32_t phase = 0;
+    uint32_t phase = 0, phaseW = 0;   // phaseW: thread 0 only
     float lossAcc = 0.0f;        // thread 0
     float dw5Acc = 0.0f;         // threads < 192: dW5[j][c]; threads 192..194: db5[j]
 
@@ -458,7 +470,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
         bool nanFlag;
         tc_encode_half<true>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, row, half, inRange, p, d, m, nanFlag, gate0S);
         if (half == 0) dropS[row] = (!inRange || nanFlag) ? 1 : 0;
-        tt_stage_fwd(smem, wimg, 0);
+        if (tid == 0) tt_bulk_fwd(smem, wimg, 0, barW);   // the forward stages are idle since the last tile's layer 5
         __syncthreads();
         const bool dropped = dropS[row] != 0;
         if (dropped) {   // a dropped sample contributes nothing: zero its inputs (its error rows are zeroed below)
@@ -475,6 +487,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
 #pragma unroll 1
         for (int l = 0; l < 6; l++) {
             if (tid == 0) {
+                mbar_wait(barW, phaseW);   // this layer's weights have landed
+                phaseW ^= 1u;
                 tc_fence_after();
                 const uint32_t nOut = (l < 5) ? 64u : 16u;
                 const uint32_t idesc = umma_idesc(TC_ROWS, nOut);
@@ -498,8 +512,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
             phase ^= 1u;
             tc_fence_after();
             // the forward stages are free again: fetch the next layer's weights (or the first backward stage) behind the epilogue
-            if (l < 5) tt_stage_fwd(smem, wimg, l + 1);
-            else tt_stage8k(smem + TT_WB, wimg + TC_IMG_T + 5 * 4096, 2048);     // W5^T: 64 rows x K 16
+            if (tid == 0) {
+                if (l < 5) tt_bulk_fwd(smem, wimg, l + 1, barW);
+                else tt_bulk_bwd(smem, wimg, 5, barW);     // W5^T: 64 rows x K 16
+            }
             if (l < 5) {
                 uint32_t v[32];
                 tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
@@ -578,6 +594,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
 #pragma unroll 1
         for (int L = 5; L >= 0; L--) {
             if (tid == 0) {
+                mbar_wait(barW, phaseW);   // W_L^T has landed
+                phaseW ^= 1u;
                 tc_fence_after();
                 if (L <= 4) {
                     const uint32_t idw = umma_idesc(128, 80);
@@ -600,7 +618,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
             tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
             tmem_ld_wait();
             if (L >= 1) {
-                tt_stage8k(smem + TT_WB, wimg + TC_IMG_T + (L - 1) * 4096, 8192);
+                if (tid == 0) tt_bulk_bwd(smem, wimg, L - 1, barW);
                 const uint4* aprev = reinterpret_cast<const uint4*>(smem + TT_ACT + (L - 1) * 16384);
                 uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
                 // gates: A_{L-1} > 0.  Hidden activations: the sign of the hi part; the network inputs (L == 1): the exact fp32 signs
