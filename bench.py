@@ -807,6 +807,8 @@ def finish_b200(args, v):
         side = []
         if world == 1:
             side.append(("config3", (1280, 720, 100, 100, 1, 16384, "none"), "BASELINE configs[2]: 1280x720, 1 spp, online training, env map, 1 GPU"))
+            side.append(("strong_4k", (3840, 2160, 100, 100, 1, 16384, "strong"),
+                         "BASELINE configs[3] on one GPU: the 3840x2160 frame + 10^4 samples whose split over 2/4/8 ranks is the strong-scaling series"))
             side.append(("config5_n1", (1920, 1080, 100, 100, 4, 1 << 22, "none"),
                          "BASELINE configs[4] on one GPU: refined 500x340x612 cloud, 2^22-entry hash tables, 1080p"))
         else:

@@ -427,6 +427,9 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     if (walkStreams == 0) {
         const size_t px = (size_t)part_count(r->y0, r->y1, r->ystride) * r->width;
         walkStreams = px >= 1500000 ? 1 : (px >= 600000 ? 2 : 3);
+        // a grid whose bricks do not fit L2 (config 5: 838 MB) doubles the walk's latency (every tap goes to HBM): 5.6 ms against a frame of
+        // ~6 ms of throughput work -- keep three walks in flight there
+        if ((size_t)(r->vol->nx + 1) * (r->vol->ny + 1) * (r->vol->nz + 1) * sizeof(uint2) > ((size_t)96 << 20)) walkStreams = NRC_TRAIN_WALK_STREAMS;
     }
     cudaStream_t tw = ahead ? ctx->streamWalk[r->trainSeq % (unsigned)walkStreams] : st;
     cudaStream_t tl = ahead ? ctx->stream4 : st;

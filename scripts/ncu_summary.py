@@ -66,5 +66,31 @@ def main(path):
               float(r[col["smsp__inst_executed.sum"]]) / 1e6))
 
 
+def to_json(path, out, source):
+    """profiles/ncu_frame.json for bench.py: DRAM bytes (read + write) and executed warp instructions per launch of every frame kernel,
+    keyed by the names the library's profiler uses (nrc_kernel_name)."""
+    import json
+    rows = list(csv.reader(open(path)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    col = {h: i for i, h in enumerate(hdr)}
+    scale = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}
+    kernels = {}
+    for r in data:
+        full = r[col["Kernel Name"]]
+        n = full.split("(")[0].replace("void ", "")
+        if n.startswith("k_light<"):
+            n = "k_light<render>" if n.startswith("k_light<1") or n.startswith("k_light<true") else "k_light<train>"
+        n = re.sub(r"<.*>$", "", n) if not n.startswith("k_light<") else n
+        dram = float(r[col["dram__bytes_read.sum"]].replace(",", "")) * scale[units[col["dram__bytes_read.sum"]]] + \
+            float(r[col["dram__bytes_write.sum"]].replace(",", "")) * scale[units[col["dram__bytes_write.sum"]]]
+        inst = float(r[col["smsp__inst_executed.sum"]].replace(",", ""))
+        if n not in kernels:      # the first captured launch of each kernel
+            kernels[n] = [dram, inst]
+    json.dump({"source": source, "kernels": kernels}, open(out, "w"), indent=1)
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--json":
+        to_json(sys.argv[1], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else sys.argv[1])
+    else:
+        main(sys.argv[1])
