@@ -88,5 +88,5 @@ def test_headless_main_reads_its_data_from_files(tmp_path):
     assert p.stdout.count("NRC MSE Loss") == 4
     data = open(out, "rb").read()
     assert len(set(data[14:])) > 8
-    p = subprocess.run([exe, "--frames=1", "--density=" + grid, "--grid=10,10,10000"], capture_output=True, text=True, timeout=300)
+    p = subprocess.run([exe, "--frames=1", "--density=" + grid, "--grid=200,200,200"], capture_output=True, text=True, timeout=300)
     assert p.returncode == 1 and "Failed to read" in p.stderr
