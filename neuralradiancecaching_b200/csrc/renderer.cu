@@ -416,7 +416,7 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     const bool ahead = !(noOverlap || noAhead);
     // Walks in flight: enough to hide the walk's latency (~2.5 ms beside the other kernels) behind the frame time, no more -- measured
     // (profiles/r02_walks_in_flight.md): a 1080p frame (2.9 ms) is fastest with one walk at a time (2.92 vs 3.26 ms with three), a 720p
-    // frame (1.8-1.9 ms) with two or three (1.82-1.9 vs 2.15 ms with one).  NRC_TRAIN_WALK=n overrides the choice.
+    // frame (1.8-1.9 ms) with three (1.82-1.9 vs 2.15 ms with one).  NRC_TRAIN_WALK=n overrides the choice.
     static int walkEnv = -1;
     if (walkEnv < 0) {
         const char* e = getenv("NRC_TRAIN_WALK");
@@ -426,7 +426,7 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     int walkStreams = walkEnv;
     if (walkStreams == 0) {
         const size_t px = (size_t)part_count(r->y0, r->y1, r->ystride) * r->width;
-        walkStreams = px >= 1500000 ? 1 : (px >= 600000 ? 2 : 3);
+        walkStreams = px >= 1500000 ? 1 : 3;
         // a grid whose bricks do not fit L2 (config 5: 838 MB) doubles the walk's latency (every tap goes to HBM): 5.6 ms against a frame of
         // ~6 ms of throughput work -- keep three walks in flight there
         if ((size_t)(r->vol->nx + 1) * (r->vol->ny + 1) * (r->vol->nz + 1) * sizeof(uint2) > ((size_t)96 << 20)) walkStreams = NRC_TRAIN_WALK_STREAMS;

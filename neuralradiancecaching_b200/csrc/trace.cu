@@ -219,11 +219,23 @@ __device__ __forceinline__ void render_path_store(const TraceParams& P, RenderPa
 template <int MB>
 __global__ void __launch_bounds__(128, MB) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
                                                      uint32_t spp, VertexPool pool, RenderPaths paths, float4* __restrict__ background,
-                                                     uint32_t* __restrict__ counters, int splitAt)
+                                                     uint32_t* __restrict__ counters, int splitAt, int tiled)
 {
+    // A warp = an 8 x 4 tile of this rank's pixels (rows of the partition), not 32 pixels of one row: neighbouring paths in BOTH directions
+    // take similar walks, so fewer lanes idle through the marches (NRC_RWALK_TILE=0: the row-major mapping, for comparison).  Which lane
+    // walks which pixel changes nothing a pixel computes.
     uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-    if (local >= rows * P.width) return;
-    uint32_t px = local % P.width, py = y0 + (local / P.width) * ystride;
+    uint32_t px, prow;
+    if (tiled) {
+        const uint32_t tilesX = (P.width + 7u) >> 3, tile = local >> 5, lane = local & 31u;
+        px = (tile % tilesX) * 8u + (lane & 7u);
+        prow = (tile / tilesX) * 4u + (lane >> 3);
+    } else {
+        px = local % P.width;
+        prow = local / P.width;
+    }
+    if (px >= P.width || prow >= rows) return;
+    uint32_t py = y0 + prow * ystride;
     size_t pix = (size_t)py * P.width + px;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
@@ -857,10 +869,13 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
     if (splitEnv < 0 || splitEnv >= NRC_RENDER_WALK_STEPS) splitEnv = 0;
     // the caller zeroes *paths.spillCount on this stream before the call (renderer.cu: render_pass)
     const int split = (spp == 1 && paths.spill != nullptr && paths.spillStride >= n) ? splitEnv : 0;
-    const unsigned blocks = (n + 127) / 128;
+    const unsigned blocks = (n + 127) / 128;   // the tail launch: one thread per spilled path
+    static int tiled = -1;
+    if (tiled < 0) { const char* e = getenv("NRC_RWALK_TILE"); tiled = e ? (atoi(e) != 0) : 1; }
+    const unsigned headBlocks = tiled ? (((P.width + 7u) / 8u) * ((rows + 3u) / 4u) * 32u + 127u) / 128u : blocks;
 #define RWALK_CASE(MBV)                                                                                                                    \
     NRC_LAUNCH(ctx, st, K_RENDER_WALK,                                                                                                     \
-               (k_render_walk<MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split))); \
+               (k_render_walk<MBV><<<headBlocks, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split, tiled))); \
     if (split > 0)                                                                                                                         \
         NRC_LAUNCH(ctx, st, K_RENDER_WALK_TAIL, (k_render_walk_tail<MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, paths, counters, split)));
     if (mb == 8) { RWALK_CASE(8) }

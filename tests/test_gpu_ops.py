@@ -24,8 +24,17 @@ def ctx(N):
 
 
 def _rel(a, b):
-    """max |a-b| relative to the largest magnitude of the reference array"""
+    """max |a-b| relative to the largest magnitude of the reference array (the max-norm bound: DESIGN.md section 2 states this norm)"""
     return float(np.max(np.abs(a.astype(np.float64) - b.astype(np.float64))) / max(float(np.max(np.abs(b))), 1e-30))
+
+
+def _elementwise_ok(a, b, rel=REL, floor=1e-4):
+    """north_star words the fp32 bar as "within 1e-3 relative": besides the max-norm bound every ELEMENT must agree to
+    rel * |reference| + floor * (largest reference magnitude) -- the floor keeps sums that cancel to nearly zero (whose relative error
+    is unbounded in any fp32 evaluation order) from failing the test, and is 10x tighter than the max-norm bound itself."""
+    a, b = a.astype(np.float64), b.astype(np.float64)
+    tol = rel * np.abs(b) + floor * max(float(np.max(np.abs(b))), 1e-30)
+    return bool(np.all(np.abs(a - b) <= tol))
 
 
 @pytest.mark.parametrize("res", [Cm.RES_INTENDED, Cm.RES_SHIPPED], ids=["intended", "as_shipped_std140"])
@@ -101,6 +110,7 @@ def test_infer_fp32_parity(N, ctx):
         got = N.infer(nrc, m, pos, d)
         want = sc.infer(pos, d)
         assert _rel(got, want) < REL, n
+        assert _elementwise_ok(got, want), n
     nrc.Destroy(); m.Destroy()
 
 
@@ -117,18 +127,20 @@ def test_train_accumulate_and_steps_parity(N, ctx):
     opred, dropped = sc.train_accumulate(pos, d, target)
     assert dropped[7] == 1 and dropped.sum() == 1
     gpred = N.train_accumulate(nrc, m, pos, d, target, scale, want_pred=True)
-    assert _rel(gpred, opred) < REL
+    assert _rel(gpred, opred) < REL and _elementwise_ok(gpred, opred)
     _, od, _ = sc.get_mlp()
     _, gd, _ = nrc.get_params()
     for l in range(6):
         a, b = (l * 4096, l * 4096 + (4096 if l < 5 else 192))
         assert _rel(gd[a:b], od[a:b]) < REL, "dW%d" % l
+        assert _elementwise_ok(gd[a:b], od[a:b]), "dW%d element-wise" % l
         a, b = (20672 + 64 * l, 20672 + 64 * l + (64 if l < 5 else 3))
         assert _rel(gd[a:b], od[a:b]) < REL, "db%d" % l
     _, otd = sc.get_mrhe()
     _, gtd = m.get_tables()
     assert np.count_nonzero(gtd[2 * 16384:]) == 0          # only level 0's slice is ever touched
     assert _rel(gtd[:2 * 16384], otd[:2 * 16384]) < REL
+    assert _elementwise_ok(gtd[:2 * 16384], otd[:2 * 16384])
     assert abs(nrc.GetStats().mseLoss - sc.mse_loss()) <= REL * abs(sc.mse_loss())
     # optimiser steps from IDENTICAL gradients are bit-exact (strict arithmetic on both sides)
     nrc.set_state(delta=od)

@@ -83,14 +83,23 @@ def test_frame_with_tc_inference(N, ctx):
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
 
 
-# Stated bounds for gradients computed from bf16 operands (per tensor, max abs error relative to the tensor's largest
-# magnitude).  Measured on B200 (scripts/tc_err.py): MLP tensors 0.2-7.6 %, worst for 128-sample batches.  The hash-table
-# gradient is ill-conditioned BY the reference's formula -- its corner weights are products of unbounded "lerp factors"
-# (world position minus grid floor, SURVEY A2/A11: magnitudes of 10^2..10^7 with alternating signs), so the per-entry sums
-# are small differences of huge terms and amplify the ~1-2 % bf16 noise of dL/dx0 to 3-30 %.  (mrhe-step.comp then clips
-# every |g| > 1000 to 100 anyway.)  The fp32 path keeps the 1e-3 bar for all of these.
-TC_GRAD_REL = 1e-1
-TC_TABLE_GRAD_REL = 4e-1
+# Stated bounds for the tensor-core TRAINING path (per tensor, max abs error relative to the tensor's largest magnitude).  Round 1 ran
+# the whole kernel in bf16 and measured 7.6 % on the MLP gradients and 30 % on the hash-table gradient: the ReLU gates of the backward
+# pass were read off bf16-rounded forward activations (sign flips of pre-activations inside the rounding noise; OneBlob bins that are
+# fp32 denormals round to +0 in bf16 and closed the layer-0 gate for ~20 % of all directions), and the reference's unbounded corner
+# weights let a few such samples dominate a table entry.  Now the forward pass runs in split precision (bf16x3, six
+# partial products per K step: fp32-accurate activations and gates), the layer-0 gate is taken from the exact fp32 inputs, and only the
+# backward GEMMs stay bf16: measured 0.2-0.5 % on the MLP gradients, 0.4-0.7 % on the table gradient (scripts/tc_err.py,
+# scripts/tc_split_emul.py).  The fp32 path keeps the 1e-3 bar for all of these.
+TC_GRAD_REL = 3e-2
+TC_TABLE_GRAD_REL = 2e-2
+TC_COSINE_MIN = 0.999          # direction-sensitive: per layer / per level, a wrong sign or scale of one block cannot hide in a max-norm
+
+
+def _cosine(a, b):
+    a, b = a.astype(np.float64).ravel(), b.astype(np.float64).ravel()
+    na, nb = np.linalg.norm(a), np.linalg.norm(b)
+    return 1.0 if na == 0 and nb == 0 else float(a @ b / max(na * nb, 1e-300))
 
 
 @pytest.mark.parametrize("n", [128, 3000, 1 << 15])
@@ -114,18 +123,32 @@ def test_train_tc_gradients_match_oracle(N, ctx, n):
     for l in range(6):
         a, b = (l * 4096, l * 4096 + (4096 if l < 5 else 192))
         assert _rel(gd[a:b], od[a:b]) < TC_GRAD_REL, ("dW%d" % l, _rel(gd[a:b], od[a:b]))
+        assert _cosine(gd[a:b], od[a:b]) >= TC_COSINE_MIN, ("dW%d cosine" % l, _cosine(gd[a:b], od[a:b]))
+        wa, wb = a, b
         a, b = (20672 + 64 * l, 20672 + 64 * l + (64 if l < 5 else 3))
         assert _rel(gd[a:b], od[a:b]) < TC_GRAD_REL, ("db%d" % l, _rel(gd[a:b], od[a:b]))
+        assert _cosine(gd[a:b], od[a:b]) >= TC_COSINE_MIN, ("db%d cosine" % l)
+        # db is the ones-column of the same GEMM that produces dW (M = 128, N = 80): both must come out of it consistently --
+        # the oracle's db / dW ratio pattern is reproduced row by row (rows with a non-negligible bias gradient)
+        if l < 5:
+            rows = np.abs(od[a:b]) > 1e-3 * np.abs(od[a:b]).max()
+            gw, ow = gd[wa:wb].reshape(64, 64)[rows], od[wa:wb].reshape(64, 64)[rows]
+            ratio_g = gw / gd[a:b][rows][:, None]
+            ratio_o = ow / od[a:b][rows][:, None]
+            assert _rel(ratio_g, ratio_o) < 2 * TC_GRAD_REL, "dW%d / db%d rows inconsistent" % (l, l)
     _, otd = sc.get_mrhe()
     _, gtd = m.get_tables()
     assert np.count_nonzero(gtd[2 * 16384:]) == 0
     assert _rel(gtd[:2 * 16384], otd[:2 * 16384]) < TC_TABLE_GRAD_REL
+    assert _cosine(gtd[:2 * 16384], otd[:2 * 16384]) >= TC_COSINE_MIN
+    # both features of an entry receive the same value (A9), as in the oracle
+    np.testing.assert_array_equal(gtd[0:2 * 16384:2], gtd[1:2 * 16384:2])
     assert abs(nrc.GetStats().mseLoss - sc.mse_loss()) <= TC_REL * abs(sc.mse_loss())
     nrc.Destroy(); m.Destroy()
 
 
 def test_tc_training_converges_like_fp32(N, ctx):
-    """20 optimiser steps on a fixed batch: the loss under the tensor-core path tracks the fp32 oracle's."""
+    """40 optimiser steps on a fixed batch: the loss under the tensor-core path tracks the fp32 oracle's step by step."""
     sc, nrc, m = _pair(N, ctx, 0.1)
     n = 4096
     pos, d = Cm.rand_queries(n, seed=77)
@@ -133,14 +156,14 @@ def test_tc_training_converges_like_fp32(N, ctx):
     sc.set_loss_scale(1.0 / n, 1.0)
     nrc.set_config(0.02, 0.0, 0.5); sc.set_mlp(None, 0.02, 0.0, 0.5)
     lo, lg = [], []
-    for it in range(20):
+    for it in range(40):
         sc.reset_stats(); nrc.ResetStats()
         sc.train_accumulate(pos, d, target)
         N.train_accumulate(nrc, m, pos, d, target, 1.0 / n)
         lo.append(sc.mse_loss()); lg.append(nrc.GetStats().mseLoss)
         sc.nrc_step(); sc.mrhe_step(); N.optimizer_step(nrc, m)
     assert lo[-1] < 0.7 * lo[0]                      # it trains
-    assert abs(lg[-1] - lo[-1]) <= 0.1 * lo[-1]      # and the bf16 path lands within 10 % of the fp32 loss
+    assert max(abs(a - b) / b for a, b in zip(lg, lo)) <= 0.03      # and the tensor-core path follows the fp32 loss curve within 3 % at every step
     nrc.Destroy(); m.Destroy()
 
 
