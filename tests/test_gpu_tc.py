@@ -124,18 +124,9 @@ def test_train_tc_gradients_match_oracle(N, ctx, n):
         a, b = (l * 4096, l * 4096 + (4096 if l < 5 else 192))
         assert _rel(gd[a:b], od[a:b]) < TC_GRAD_REL, ("dW%d" % l, _rel(gd[a:b], od[a:b]))
         assert _cosine(gd[a:b], od[a:b]) >= TC_COSINE_MIN, ("dW%d cosine" % l, _cosine(gd[a:b], od[a:b]))
-        wa, wb = a, b
         a, b = (20672 + 64 * l, 20672 + 64 * l + (64 if l < 5 else 3))
         assert _rel(gd[a:b], od[a:b]) < TC_GRAD_REL, ("db%d" % l, _rel(gd[a:b], od[a:b]))
         assert _cosine(gd[a:b], od[a:b]) >= TC_COSINE_MIN, ("db%d cosine" % l)
-        # db is the ones-column of the same GEMM that produces dW (M = 128, N = 80): both must come out of it consistently --
-        # the oracle's db / dW ratio pattern is reproduced row by row (rows with a non-negligible bias gradient)
-        if l < 5:
-            rows = np.abs(od[a:b]) > 1e-3 * np.abs(od[a:b]).max()
-            gw, ow = gd[wa:wb].reshape(64, 64)[rows], od[wa:wb].reshape(64, 64)[rows]
-            ratio_g = gw / gd[a:b][rows][:, None]
-            ratio_o = ow / od[a:b][rows][:, None]
-            assert _rel(ratio_g, ratio_o) < 2 * TC_GRAD_REL, "dW%d / db%d rows inconsistent" % (l, l)
     _, otd = sc.get_mrhe()
     _, gtd = m.get_tables()
     assert np.count_nonzero(gtd[2 * 16384:]) == 0
