@@ -104,13 +104,6 @@ typedef enum nrc_mlp_precision {
     NRC_MLP_BF16_TC = 1  /* tcgen05 bf16 tensor-core kernels, fp32 accumulate; looser stated bound */
 } nrc_mlp_precision;
 
-/* How the LIGHT segments' density taps are filtered (GetTransmittance of TraceDirLight / TracePointLight / SampleHdrEnvMap,
- * nrc-forward.frag:641-749).  The walks and the vertex-to-vertex segments, whose results steer control flow, always use the exact path. */
-typedef enum nrc_tap_filter {
-    NRC_TAPS_EXACT = 0,        /* fp32 trilinear blend of the UNORM8 texels (the parity preset; what the oracle computes) */
-    NRC_TAPS_TEXTURE_UNIT = 1  /* the texture unit's linear filter (9-bit fixed-point weights), border addressing: values within ~1e-4 */
-} nrc_tap_filter;
-
 /* How the bf16 tensor-core inference is organised (no reference counterpart: fwd.frag:503-534 is one function). */
 typedef enum nrc_infer_mode {
     NRC_INFER_FUSED = 0, /* k_infer_tc: encode + six layers in one kernel per 128-query tile */
@@ -234,7 +227,6 @@ NRC_API nrc_status nrc_optimizer_step(nrc_mlp* mlp, nrc_mrhe* mrhe);
  * index = x*ny*nz + y*nz + z; quantised to UNORM8 like src/Texture3D.cpp:25-40. */
 NRC_API nrc_status nrc_volume_create(nrc_ctx* ctx, const float* density /*host*/, uint32_t nx, uint32_t ny, uint32_t nz, nrc_volume** out);
 NRC_API nrc_status nrc_volume_destroy(nrc_volume* vol);
-NRC_API nrc_status nrc_volume_set_tap_filter(nrc_volume* vol, nrc_tap_filter mode);   /* default NRC_TAPS_EXACT (or env NRC_TAPS_TEX=1) */
 NRC_API nrc_status nrc_volume_set_params(nrc_volume* vol, const nrc_volume_params* p);   /* VolumeData::Update, src/VolumeData.cpp:105-109 */
 /* getDensity() (nrc-forward.frag:574-582) at N world positions, for parity tests. */
 NRC_API nrc_status nrc_volume_sample(nrc_volume* vol, const float* pos, size_t n, float* density);

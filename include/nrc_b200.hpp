@@ -216,8 +216,6 @@ public:
     nrc_volume_params& Params() { return m_Params; }   // useNN, showNonNN, densityFactor, g, spp: the ImGui sliders (VolumeData.cpp:116-128)
     void Push() const { Check(nrc_volume_set_params(m_Handle, &m_Params), "nrc_volume_set_params"); }
     nrc_volume* Get() const { return m_Handle; }
-    // opt-in: light-segment taps through the texture unit (no reference counterpart; values within ~1e-4 of the exact blend)
-    void SetTapFilter(nrc_tap_filter mode) const { Check(nrc_volume_set_tap_filter(m_Handle, mode), "nrc_volume_set_tap_filter"); }
     void Destroy() { nrc_volume_destroy(m_Handle); m_Handle = nullptr; }
 private:
     void Create(const Context& ctx, const float* d, uint32_t nx, uint32_t ny, uint32_t nz)

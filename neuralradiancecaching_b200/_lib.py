@@ -52,7 +52,7 @@ nrc_frame_partition_bytes nrc_kernel_count nrc_kernel_name nrc_selftest_strict_m
 nrc_ctx_profile_enable nrc_ctx_profile_read nrc_ctx_profile_timeline nrc_dp_handle_bytes nrc_dp_create nrc_dp_export
 nrc_renderer_set_pool_capacity nrc_renderer_set_train_env_light nrc_read_frame_partition_async nrc_readback_wait nrc_mlp_get_stats_async nrc_dp_connect nrc_dp_reduce_step nrc_dp_reduce_step_phase nrc_dp_status nrc_dp_destroy
 nrc_ctx_set_infer_mode nrc_feature_tile_bytes nrc_encode_tiles nrc_mlp_forward_tiles
-nrc_mrhe_set_fixed_mode nrc_mlp_set_adam nrc_mrhe_set_adam nrc_volume_set_tap_filter
+nrc_mrhe_set_fixed_mode nrc_mlp_set_adam nrc_mrhe_set_adam
 nrc_mlp_get_adam_state nrc_mlp_set_adam_state nrc_mrhe_get_adam_state nrc_mrhe_set_adam_state
 nrc_train_accumulate_static nrc_train_accumulate_static_max_samples""".split()
 

@@ -65,8 +65,6 @@ struct nrc_ctx {
     cudaStream_t streamCopy = nullptr;    // asynchronous read-back of finished frames
     cudaEvent_t evJoin = nullptr;
     cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
-    cudaStream_t stream5 = nullptr;       // fifth stream: lights + combine of the RENDER trace, beside the next frame's render walk
-    cudaEvent_t evRenderWalk = nullptr;
     cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[NRC_TRAIN_SETS] = {nullptr, nullptr, nullptr, nullptr};
     cudaStream_t streamWalk[NRC_TRAIN_WALK_STREAMS] = {nullptr, nullptr, nullptr};   // [0] = stream3: consecutive frames' train walks on alternating streams
     nrc_mlp_precision precision = NRC_MLP_FP32;
@@ -143,15 +141,6 @@ struct nrc_volume {
     // 2x2x2 corner bricks: cell (i,j,k), i in [-1,nx-1], holds the 8 UNORM8 texels it interpolates,
     // border texels are 0 (CLAMP_TO_BORDER, opaque black): one 8-byte load per density tap.
     uint2* bricks = nullptr;     // [(nz+1)][(ny+1)][(nx+1)]
-    // occupancy of the bricks for the light kernels: bit r = some brick of cells [r << occShift, (r+1) << occShift) (linear index,
-    // runs along x) is non-zero.  A tap whose run is empty needs no load.  occShift = 0: not built (switched off or volume too large)
-    uint32_t* occ = nullptr;
-    uint32_t occWords = 0, occShift = 0;
-    // opt-in: the same UNORM8 texels as a 3-D CUDA array behind a linear-filtering, border-addressing texture object (light taps only)
-    cudaArray_t texArray = nullptr;
-    cudaTextureObject_t tex = 0;
-    bool texTaps = false;
-    uint32_t texMask = 3;        // which light segments use it (NRC_TAPS_TEX_MASK; default all)
     nrc_volume_params params;
 };
 
@@ -180,10 +169,6 @@ struct TraceParams {
     float exitJump;               // length(2*skySize), find_entry_exit
     int nx, ny, nz;
     const uint2* bricks;
-    const uint32_t* occ;             // brick-run occupancy bits (nrc_volume), null = off
-    uint32_t occWords, occShift;
-    unsigned long long densityTex;   // cudaTextureObject_t, 0 unless the volume's light taps go through the texture unit (opt-in)
-    uint32_t densityTexMask;         // bit 0: dir / point light segments, bit 1: environment segments
     const float4* env;
     int envW, envH;
     const float* envInvCdfX;      // [envH][envW], non-null only when the CDF half of the env gather is switched on

@@ -372,9 +372,6 @@ static TraceParams make_params(const nrc_renderer* r)
     }
     P.nx = (int)r->vol->nx; P.ny = (int)r->vol->ny; P.nz = (int)r->vol->nz;
     P.bricks = r->vol->bricks;
-    P.occ = r->vol->occ; P.occWords = r->vol->occWords; P.occShift = r->vol->occShift;
-    P.densityTex = r->vol->texTaps ? (unsigned long long)r->vol->tex : 0ull;
-    P.densityTexMask = r->vol->texMask;
     P.env = r->env->rgba; P.envW = (int)r->env->w; P.envH = (int)r->env->h;
     const bool cdfHalf = r->env->cdfHalf && r->env->invCdfX && r->env->invCdfY;
     P.envInvCdfX = cdfHalf ? r->env->invCdfX : nullptr; P.envInvCdfY = cdfHalf ? r->env->invCdfY : nullptr;
@@ -468,7 +465,6 @@ static nrc_status drain_streams(nrc_ctx* ctx)
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
-    NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->streamCopy));
     return NRC_OK;
@@ -494,15 +490,7 @@ static nrc_status render_pass(nrc_renderer* r)
     NRC_CUDA(cudaMemsetAsync(sc + 4, 0, 2 * sizeof(uint32_t), s2));   // query count, spilled paths of the render walk
     NRC_CUDA(cudaMemsetAsync(tapc, 0, sizeof(unsigned long long), s2));
     NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
-    // NRC_RENDER_LIGHT_STREAM=1: lights + combine on a stream of their own (as on the train side), so that the NEXT frame's render
-    // walk, which fills the other buffer set, may start while this frame's lights are still running
-    static int lightStream = -1;
-    if (lightStream < 0) { const char* e = getenv("NRC_RENDER_LIGHT_STREAM"); lightStream = (e && atoi(e)) ? 1 : 0; }
-    cudaStream_t sl = (lightStream && s2 != ctx->stream) ? ctx->stream5 : s2;
-    if (sl != s2) {
-        NRC_CUDA(cudaEventRecord(ctx->evRenderWalk, s2));
-        NRC_CUDA(cudaStreamWaitEvent(sl, ctx->evRenderWalk, 0));
-    }
+    cudaStream_t sl = s2;
     NRC_TRY(launch_light(ctx, sl, P, r->rpool, true, tapc, K_LIGHT_RENDER));
     NRC_TRY(launch_render_combine(ctx, sl, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, sc, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, sl));

@@ -4,8 +4,6 @@
 #include <string.h>
 #include "trace.cuh"
 
-extern "C" nrc_status nrc_volume_set_tap_filter(nrc_volume* v, nrc_tap_filter mode);
-
 // ---- volume (vk::Texture3D + en::VolumeData) -----------------------------------------------------------------------
 extern "C" nrc_status nrc_volume_create(nrc_ctx* ctx, const float* density, uint32_t nx, uint32_t ny, uint32_t nz, nrc_volume** out)
 {
@@ -23,64 +21,8 @@ extern "C" nrc_status nrc_volume_create(nrc_ctx* ctx, const float* density, uint
     const void* dgrid;
     NRC_TRY(nrc_stage_in(ctx, 5, density, (size_t)nx * ny * nz * sizeof(float), &dgrid));
     NRC_TRY(launch_build_bricks(v, (const float*)dgrid));
-    NRC_TRY(launch_build_occupancy(v));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     *out = v;
-    if (const char* e = getenv("NRC_TAPS_TEX")) {
-        if (atoi(e)) return nrc_volume_set_tap_filter(v, NRC_TAPS_TEXTURE_UNIT);
-    }
-    return NRC_OK;
-}
-
-// texel (i, j, k) = the first byte of the brick of cell (i+1, j+1, k+1) (trace.cu: k_build_bricks)
-__global__ void __launch_bounds__(256) k_texels_from_bricks(const uint2* __restrict__ bricks, int nx, int ny, int nz, unsigned char* __restrict__ out)
-{
-    size_t n = (size_t)nx * ny * nz;
-    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n) return;
-    int i = (int)(t % nx), j = (int)((t / nx) % ny), k = (int)(t / ((size_t)nx * ny));
-    size_t cell = ((size_t)(k + 1) * (ny + 1) + (j + 1)) * (nx + 1) + (i + 1);
-    out[t] = (unsigned char)(bricks[cell].x & 0xffu);
-}
-
-// Opt-in: the light segments' density taps through the texture unit (hardware trilinear filter, 9-bit fixed-point weights) instead of the
-// fp32 lerps.  Values only -- the walks and the vertex-to-vertex segments (whose results steer control flow) keep the exact path.
-extern "C" nrc_status nrc_volume_set_tap_filter(nrc_volume* v, nrc_tap_filter mode)
-{
-    NRC_REQUIRE(v, "null volume");
-    NRC_REQUIRE(mode == NRC_TAPS_EXACT || mode == NRC_TAPS_TEXTURE_UNIT, "unknown tap filter");
-    if (mode == NRC_TAPS_TEXTURE_UNIT && !v->tex) {
-        NRC_CUDA(cudaSetDevice(v->ctx->device));
-        const size_t n = (size_t)v->nx * v->ny * v->nz;
-        unsigned char* lin = nullptr;
-        NRC_CUDA(cudaMalloc(&lin, n));
-        cudaStream_t st = v->ctx->stream;
-        NRC_LAUNCH(v->ctx, st, K_MISC, k_texels_from_bricks<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(v->bricks, (int)v->nx, (int)v->ny, (int)v->nz, lin));
-        NRC_CUDA(cudaStreamSynchronize(st));
-        cudaChannelFormatDesc fmt = cudaCreateChannelDesc<unsigned char>();
-        NRC_CUDA(cudaMalloc3DArray(&v->texArray, &fmt, make_cudaExtent(v->nx, v->ny, v->nz)));
-        cudaMemcpy3DParms cp;
-        memset(&cp, 0, sizeof(cp));
-        cp.srcPtr = make_cudaPitchedPtr(lin, v->nx, v->nx, v->ny);
-        cp.dstArray = v->texArray;
-        cp.extent = make_cudaExtent(v->nx, v->ny, v->nz);
-        cp.kind = cudaMemcpyDeviceToDevice;
-        NRC_CUDA(cudaMemcpy3D(&cp));
-        NRC_CUDA(cudaFree(lin));
-        cudaResourceDesc rd;
-        memset(&rd, 0, sizeof(rd));
-        rd.resType = cudaResourceTypeArray;
-        rd.res.array.array = v->texArray;
-        cudaTextureDesc td;
-        memset(&td, 0, sizeof(td));
-        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeBorder;   // CLAMP_TO_BORDER, opaque black (Texture3D.cpp:222-243)
-        td.filterMode = cudaFilterModeLinear;
-        td.readMode = cudaReadModeNormalizedFloat;                                             // UNORM8
-        td.normalizedCoords = 0;
-        NRC_CUDA(cudaCreateTextureObject(&v->tex, &rd, &td, nullptr));
-    }
-    v->texTaps = (mode == NRC_TAPS_TEXTURE_UNIT);
-    if (const char* e = getenv("NRC_TAPS_TEX_MASK")) v->texMask = (uint32_t)atoi(e) & 3u;
     return NRC_OK;
 }
 
@@ -88,10 +30,7 @@ extern "C" nrc_status nrc_volume_destroy(nrc_volume* v)
 {
     if (!v) return NRC_OK;
     cudaStreamSynchronize(v->ctx->stream);
-    if (v->tex) cudaDestroyTextureObject(v->tex);
-    if (v->texArray) cudaFreeArray(v->texArray);
     cudaFree(v->bricks);
-    cudaFree(v->occ);
     delete v;
     return NRC_OK;
 }

@@ -6,12 +6,6 @@
 #include "walk.cuh"
 #include <stdlib.h>
 
-// dynamic shared memory requested (and not used) by the kernels that may run beside the train walk, so that an SM whose
-// shared memory the train walk has reserved (NRC_TRAIN_SMS) cannot take their blocks
-// (only when SMs are reserved: the padding costs the render walk ~10 % through the L1 carve-out)
-static size_t g_padSmem = 0;
-#define NRC_PAD_SMEM g_padSmem
-
 // ---- small device helpers ---------------------------------------------------------------------------------------
 
 __device__ __forceinline__ Box make_box(const TraceParams& P)
@@ -315,8 +309,8 @@ __global__ void __launch_bounds__(128, MB) k_render_walk_tail(const __grid_const
 // A training sample is ONE long serial chain (1 + 8 walks of 64 steps, the RNG chained through all of them) and a frame
 // has only ~10^4 of them: ~300 warps, latency-bound, a few per cent of the machine's instructions -- but the longest chain of
 // the frame.  It runs on a stream of its own, one frame ahead of the weights (renderer.cu), so only the next train walk waits
-// for it.  Optionally (NRC_TRAIN_SMS > 0) the blocks reserve whole SMs through unused dynamic shared memory, which keeps every
-// other block off those SMs: the walk gets faster, the frame does not (it is issue-throughput bound), so this is off by default.
+// for it, and consecutive frames' walks may be in flight together (renderer.cu).  Reserving SMs for it made the walk faster and the
+// frame slower (code removed).  The launch bound keeps the kernel at 64 registers.
 template <bool ENV>
 __global__ void __launch_bounds__(1024, 1) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
                                                         uint32_t lanes, VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
@@ -363,9 +357,6 @@ struct TapCtx {
     float nx, ny, nz;
     int strideY, strideZ, bias;     // cell = iz*strideZ + iy*strideY + ix + bias on the magic-biased integers
     const uint2* bricks;
-    unsigned long long tex;         // cudaTextureObject_t of the UNORM8 grid (0 = off): opt-in hardware-filtered light taps
-    unsigned texMask;               // bit 0: dir / point light segments, bit 1: environment segments
-    unsigned occShift;              // cells per occupancy bit = 1 << occShift (tap_load<true>)
 };
 
 #define TAP_MAGIC 12582912.0f   // 1.5 * 2^23: float bits of (k + TAP_MAGIC) = 0x4B400000 + k for integer |k| < 2^22
@@ -380,9 +371,6 @@ __device__ __forceinline__ TapCtx make_tap(const TraceParams& P)
     // brick cell of texel-floor (i,j,k) is (i+1, j+1, k+1); the three indices arrive biased by 0x4B400000 each
     t.bias = (int)((1u + (unsigned)t.strideY + (unsigned)t.strideZ) * (1u - 0x4B400000u));
     t.bricks = P.bricks;
-    t.tex = P.densityTex;
-    t.texMask = P.densityTexMask;
-    t.occShift = P.occShift;
     return t;
 }
 
@@ -468,26 +456,12 @@ __device__ __forceinline__ f2pair tap_blend2(uint2 q0, uint2 q1, f2pair a, f2pai
 // So: return exactly 1 when the LARGEST per-tap exponent still rounds to exp() == 1 under nrc_exp, otherwise a
 // value strictly below 1.
 //
-// allowTex: opt-in (nrc_volume_set_tap_filter) for the segments whose result is a VALUE only -- the light segments.  The taps go through
-// the texture unit: border addressing = clamp-to-border(0), the hardware's trilinear filter with 9-bit fixed-point weights instead of
-// the fp32 lerps: ~7 instructions per tap instead of 32, values within ~1e-4 relative.  The vertex-to-vertex segment never takes this
-// path: its `== 1.0` outcome is control flow (see above) and must be the exact fp32 result.
-// OCC: the block holds the volume's brick-run occupancy bits in shared memory (k_light copies them in): a tap whose run of cells has
-// no non-zero brick skips its load and blends a zero brick -- the same value, one L1/L2 sector request less.
-template <bool OCC>
-__device__ __forceinline__ uint2 tap_load(const TapCtx& t, int c)
-{
-    if (!OCC) return __ldg(t.bricks + c);
-    extern __shared__ uint32_t s_occ[];
-    const unsigned r = (unsigned)c >> t.occShift;
-    const unsigned w = s_occ[r >> 5];
-    uint2 q = make_uint2(0u, 0u);
-    if ((int)__funnelshift_l(0u, w, r) < 0) q = __ldg(t.bricks + c);   // run r is bit 31 - (r & 31) of its word: shifted into the sign
-    return q;
-}
-
-template <int COUNT, bool OCC>
-__device__ __forceinline__ float transmittance(const TapCtx& t, float densityFactor, f3 a, f3 b, unsigned& taps, bool allowTex = false)
+//
+// Measured and NOT adopted (the code is gone): taps through the texture unit (7 instead of 32 instructions per tap, but the
+// L1/TEX pipe that bounds the light kernels pays twice as much per trilinear fetch) and occupancy-tested taps (a third of the brick loads
+// skipped, 8 more instructions per tap on an issue-bound frame).
+template <int COUNT>
+__device__ __forceinline__ float transmittance(const TapCtx& t, float densityFactor, f3 a, f3 b, unsigned& taps)
 {
     float dx = b.x - a.x, dy = b.y - a.y, dz = b.z - a.z;
     float stepSize = sqrtf(dx * dx + dy * dy + dz * dz) / (float)COUNT;
@@ -498,18 +472,7 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
     const bool inside = (fminf(u0, u1) > -1.0f) & (fmaxf(u0, u1) < t.nx) & (fminf(v0, v1) > -1.0f) & (fmaxf(v0, v1) < t.ny) &
                         (fminf(s0, s1) > -1.0f) & (fmaxf(s0, s1) < t.nz);
     float sum = 0.0f, dmax = 0.0f;
-    if (allowTex && t.tex != 0ull) {
-        const float uh = u0 + 0.5f, vh = v0 + 0.5f, sh = s0 + 0.5f;   // texel i is centred at i + 0.5 in unnormalised texture coordinates
-        float fi = 0.0f;
-#pragma unroll 8
-        for (int i = 0; i < COUNT; i++) {
-            float d = tex3D<float>((cudaTextureObject_t)t.tex, fmaf(fi, du, uh), fmaf(fi, dv, vh), fmaf(fi, ds, sh));
-            fi += 1.0f;
-            sum += d;
-            dmax = fmaxf(dmax, d);
-        }
-        sum *= 255.0f; dmax *= 255.0f;   // normalised read mode returns texel / 255
-    } else if (inside) {
+    if (inside) {
         const f2pair du2 = pk2(du, du), dv2 = pk2(dv, dv), ds2 = pk2(ds, ds), u02 = pk2(u0, u0), v02 = pk2(v0, v0), s02 = pk2(s0, s0);
         const f2pair two = pk2(2.0f, 2.0f);
         f2pair fi = pk2(0.0f, 1.0f), sum2 = pk2(0.0f, 0.0f);
@@ -521,8 +484,8 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
             for (int j = 0; j < TAP_BATCH / 2; j++) {
                 int c0, c1;
                 tap_cell2(t, fma2(fi, du2, u02), fma2(fi, dv2, v02), fma2(fi, ds2, s02), c0, c1, fa[j], fb[j], fc[j]);
-                q[2 * j] = tap_load<OCC>(t, c0);
-                q[2 * j + 1] = tap_load<OCC>(t, c1);
+                q[2 * j] = __ldg(t.bricks + c0);
+                q[2 * j + 1] = __ldg(t.bricks + c1);
                 fi = add2(fi, two);
             }
 #pragma unroll
@@ -556,16 +519,11 @@ __device__ __forceinline__ float transmittance(const TapCtx& t, float densityFac
     return fminf(__expf(-(sum * k) * stepSize), 0.99999994f);
 }
 
-// MB = resident blocks ptxas must allow: WITHOUT a minimum it chases occupancy and sinks every brick load next to its use (one
-// load in flight per thread, ncu r01f: 35-57 % long-scoreboard); with a register budget it keeps the batch of loads together.
-template <bool RENDER, int MB, bool CDF, bool OCC>
-__global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
+// 8 resident blocks are REQUIRED of ptxas: without a minimum it chases occupancy and sinks every brick load next to its use (one
+// load in flight per thread, ncu r01f: 35-57 % long-scoreboard); with a 64-register budget it keeps the batch of loads together.
+template <bool RENDER, bool CDF>
+__global__ void __launch_bounds__(128, 8) k_light(const __grid_constant__ TraceParams P, VertexPool pool, unsigned long long* tapCounter)
 {
-    if (OCC) {
-        extern __shared__ uint32_t s_occ[];
-        for (uint32_t i = threadIdx.x; i < P.occWords; i += blockDim.x) s_occ[i] = P.occ[i];
-        __syncthreads();
-    }
     const uint32_t count = min(*pool.count, pool.cap);
     const Box box = make_box(P);
     const TapCtx tc = make_tap(P);
@@ -582,13 +540,13 @@ __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ Trace
             f3 L = mk3(P.dirDir[0], P.dirDir[1], P.dirDir[2]);
             f3 en, ex;
             find_entry_exit(box, pos, s_neg(s_normalize(L)), en, ex, sdf);
-            float T = transmittance<32, OCC>(tc, kDensity, pos, ex, taps, (tc.texMask & 1u) != 0);
+            float T = transmittance<32>(tc, kDensity, pos, ex, taps);
             float l = T * P.dirStrength * hg_phase(P.g, -dot3(L, dir));
             light.x += l; light.y += l; light.z += l;
         }
         if (P.ptStrength != 0.0f) {    // TracePointLight (fwd.frag:677-688)
             f3 lp = mk3(P.ptPos[0], P.ptPos[1], P.ptPos[2]);
-            float T = transmittance<32, OCC>(tc, kDensity, lp, pos, taps, (tc.texMask & 1u) != 0);
+            float T = transmittance<32>(tc, kDensity, lp, pos, taps);
             f3 tl = mk3(lp.x - pos.x, lp.y - pos.y, lp.z - pos.z);
             float inv = rsqrtf(dot3(tl, tl));
             float ph = hg_phase(P.g, -dot3(tl, dir) * inv);
@@ -621,13 +579,13 @@ __global__ void __launch_bounds__(128, MB) k_light(const __grid_constant__ Trace
                     }
                     f3 en, ex;
                     find_entry_exit(box, pos, rdir, en, ex, sdf);
-                    float T = transmittance<16, OCC>(tc, kDensity, pos, ex, taps, (tc.texMask & 2u) != 0) * phase;
+                    float T = transmittance<16>(tc, kDensity, pos, ex, taps) * phase;
                     acc.x += c.x * T; acc.y += c.y * T; acc.z += c.z * T;
                 }
             }
             light.x += acc.x * 0.125f; light.y += acc.y * 0.125f; light.z += acc.z * 0.125f;
         }
-        float tr = transmittance<32, OCC>(tc, kDensity, pos, last, taps);
+        float tr = transmittance<32>(tc, kDensity, pos, last, taps);
         pool.out[vtx] = make_float4(light.x, light.y, light.z, tr);
     }
     if (tapCounter) {
@@ -792,47 +750,7 @@ __global__ void __launch_bounds__(256) k_volume_sample(Grid g, const float* __re
     out[i] = grid_density(g, mk3(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]));
 }
 
-// bit 31 - (r & 31) of word r >> 5 of occ = some brick of the cells [r << shift, (r + 1) << shift) is non-zero; one thread per bit, one ballot per word
-__global__ void __launch_bounds__(256) k_brick_occupancy(const uint2* __restrict__ bricks, size_t cells, uint32_t shift, uint32_t bits,
-                                                         uint32_t* __restrict__ occ)
-{
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;   // the grid covers whole words
-    bool any = false;
-    if (r < bits) {
-        const size_t c0 = (size_t)r << shift;
-        const size_t c1 = min(c0 + ((size_t)1 << shift), cells);
-        for (size_t c = c0; c < c1; c++) {
-            const uint2 q = bricks[c];
-            any |= (q.x | q.y) != 0u;
-        }
-    }
-    const unsigned w = __ballot_sync(0xffffffffu, any);
-    if ((threadIdx.x & 31u) == 0u) occ[r >> 5] = __brev(w);   // first run of the word in the top bit (tap_load tests the sign)
-}
-
 // ---- launchers -----------------------------------------------------------------------------------------------------------
-#define NRC_OCC_MAX_WORDS 8192u   // 32 KB of shared memory per block at most
-nrc_status launch_build_occupancy(nrc_volume* vol)
-{
-    // NRC_LIGHT_OCC_SHIFT: cells per occupancy bit = 2^shift; 0 = no occupancy test in the light kernels, the default: measured on the
-    // bench frame the test skips a third of the brick loads but costs 8 instructions per tap, and the frame is issue-bound
-    // (2.97 ms with shift 5 against 2.84 ms without)
-    const char* e = getenv("NRC_LIGHT_OCC_SHIFT");
-    const int shift = e ? atoi(e) : 0;
-    vol->occShift = 0; vol->occWords = 0;
-    if (shift < 1 || shift > 8) return NRC_OK;
-    const size_t cells = (size_t)(vol->nx + 1) * (vol->ny + 1) * (vol->nz + 1);
-    const size_t bits = (cells + ((size_t)1 << shift) - 1) >> shift;
-    const size_t words = (bits + 31) / 32;
-    if (words > NRC_OCC_MAX_WORDS) return NRC_OK;   // a larger volume would need coarser runs than are worth testing
-    NRC_CUDA(cudaMalloc(&vol->occ, words * sizeof(uint32_t)));
-    cudaStream_t st = vol->ctx->stream;
-    NRC_LAUNCH(vol->ctx, st, K_MISC,
-               k_brick_occupancy<<<(unsigned)((words * 32 + 255) / 256), 256, 0, st>>>(vol->bricks, cells, (uint32_t)shift, (uint32_t)bits, vol->occ));
-    vol->occShift = (uint32_t)shift; vol->occWords = (uint32_t)words;
-    return NRC_OK;
-}
-
 nrc_status launch_build_bricks(nrc_volume* vol, const float* densityDev)
 {
     size_t cells = (size_t)(vol->nx + 1) * (vol->ny + 1) * (vol->nz + 1);
@@ -861,8 +779,6 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
 {
     uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
-    static int mb = -1;
-    if (mb < 0) { const char* e = getenv("NRC_RWALK_MB"); mb = e ? atoi(e) : 8; }
     // steps in the head launch; 0 = the whole walk in one launch.  Read at every launch (tests switch it)
     const char* se = getenv("NRC_RWALK_SPLIT");
     int splitEnv = se ? atoi(se) : 10;
@@ -875,12 +791,10 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
     const unsigned headBlocks = tiled ? (((P.width + 7u) / 8u) * ((rows + 3u) / 4u) * 32u + 127u) / 128u : blocks;
 #define RWALK_CASE(MBV)                                                                                                                    \
     NRC_LAUNCH(ctx, st, K_RENDER_WALK,                                                                                                     \
-               (k_render_walk<MBV><<<headBlocks, 128, NRC_PAD_SMEM, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split, tiled))); \
+               (k_render_walk<MBV><<<headBlocks, 128, 0, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split, tiled))); \
     if (split > 0)                                                                                                                         \
-        NRC_LAUNCH(ctx, st, K_RENDER_WALK_TAIL, (k_render_walk_tail<MBV><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, paths, counters, split)));
-    if (mb == 8) { RWALK_CASE(8) }
-    else if (mb == 6) { RWALK_CASE(6) }
-    else { RWALK_CASE(7) }
+        NRC_LAUNCH(ctx, st, K_RENDER_WALK_TAIL, (k_render_walk_tail<MBV><<<blocks, 128, 0, st>>>(P, pool, paths, counters, split)));
+    RWALK_CASE(8)   // 64 registers: 8 resident blocks, the fastest of the budgets tried (profiles/r01j)
 #undef RWALK_CASE
     return NRC_OK;
 }
@@ -889,31 +803,17 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
                              TrainPaths paths, uint32_t* counters)
 {
     if (n == 0) return NRC_OK;
-    static int lanesEnv = -1, smsEnv = -1;
+    static int lanesEnv = -1;
     if (lanesEnv < 0) {
-        const char* e = getenv("NRC_TRAIN_LANES");
+        const char* e = getenv("NRC_TRAIN_LANES");   // training samples per warp (32; fewer = more, emptier warps: measured slower, profiles/r02_walks_in_flight.md)
         lanesEnv = e ? atoi(e) : 32;
         if (lanesEnv < 1 || lanesEnv > 32) lanesEnv = 32;
-        e = getenv("NRC_TRAIN_SMS");           // SMs reserved for the train walk; 0 = share the machine
-        smsEnv = e ? atoi(e) : 0;
-        if (smsEnv < 0 || smsEnv > ctx->smCount) smsEnv = 0;
-        g_padSmem = smsEnv > 0 ? 2048 : 0;
-        NRC_CUDA(cudaFuncSetAttribute(k_train_walk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        NRC_CUDA(cudaFuncSetAttribute(k_train_walk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     }
     const uint32_t lanes = (uint32_t)lanesEnv;
     const uint32_t totalWarps = (n + lanes - 1) / lanes;
-    uint32_t blocks, warpsPerBlock;
-    size_t smem = 0;
-    if (smsEnv > 0) {
-        blocks = (uint32_t)smsEnv < totalWarps ? (uint32_t)smsEnv : totalWarps;
-        warpsPerBlock = (totalWarps + blocks - 1) / blocks;
-        if (warpsPerBlock > 32) warpsPerBlock = 32;
-        smem = 227 * 1024;                     // the whole SM: no other block can be co-resident
-    } else {
-        warpsPerBlock = 4;
-        blocks = (totalWarps + warpsPerBlock - 1) / warpsPerBlock;
-    }
+    const uint32_t warpsPerBlock = 4;
+    const uint32_t blocks = (totalWarps + warpsPerBlock - 1) / warpsPerBlock;
+    const size_t smem = 0;
     if (pool.rnd != nullptr)   // the pool carries random numbers: env-map term in the training targets is on (renderer.cu)
         NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
                    k_train_walk<true><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
@@ -928,35 +828,12 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
 {
     // the vertex count lives on the device: a grid-stride launch sized for the machine, not for the count
     unsigned want = (pool.cap + 127) / 128;
-    static int perSm = -1;   // NRC_LIGHT_BLOCKS_PER_SM: grid cap of the grid-stride light kernels (default 16 = two waves of 8)
-    if (perSm < 0) { const char* e = getenv("NRC_LIGHT_BLOCKS_PER_SM"); perSm = e ? atoi(e) : 16; if (perSm < 1) perSm = 1; }
-    unsigned cap = (unsigned)ctx->smCount * (unsigned)perSm;
+    unsigned cap = (unsigned)ctx->smCount * 16u;   // two waves of 8 resident blocks
     unsigned blocks = want < cap ? want : cap;
     if (blocks == 0) return NRC_OK;
-    static int mb = -1;
-    if (mb < 0) { const char* e = getenv("NRC_LIGHT_MB"); mb = e ? atoi(e) : 8; }
-#define LIGHT_CASE(MBV)                                                                                                              \
-    case MBV:                                                                                                                        \
-        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, true, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, MBV, false, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));  \
-        else NRC_LAUNCH(ctx, st, kid, (k_light<false, MBV, false, false><<<blocks, 128, NRC_PAD_SMEM, st>>>(P, pool, tapCounter)));        \
-        break;
-    if (P.occ != nullptr && P.occShift > 0 && mb == 8) {   // occupancy-tested taps: the bits travel in dynamic shared memory
-        size_t smem = (size_t)P.occWords * sizeof(uint32_t);   // <= 32 KB (NRC_OCC_MAX_WORDS)
-        if (smem < NRC_PAD_SMEM) smem = NRC_PAD_SMEM;
-        if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, 8, true, true><<<blocks, 128, smem, st>>>(P, pool, tapCounter)));
-        else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, 8, false, true><<<blocks, 128, smem, st>>>(P, pool, tapCounter)));
-        else NRC_LAUNCH(ctx, st, kid, (k_light<false, 8, false, true><<<blocks, 128, smem, st>>>(P, pool, tapCounter)));
-        return NRC_OK;
-    }
-    switch (mb) {
-        LIGHT_CASE(4)
-        LIGHT_CASE(5)
-        LIGHT_CASE(6)
-        default:   // 64 registers, 32 resident warps, loads in groups of 2-3: the fastest of the four on the frame (profiles/r01f)
-        LIGHT_CASE(8)
-    }
-#undef LIGHT_CASE
+    if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, true><<<blocks, 128, 0, st>>>(P, pool, tapCounter)));
+    else if (render) NRC_LAUNCH(ctx, st, kid, (k_light<true, false><<<blocks, 128, 0, st>>>(P, pool, tapCounter)));
+    else NRC_LAUNCH(ctx, st, kid, (k_light<false, false><<<blocks, 128, 0, st>>>(P, pool, tapCounter)));
     return NRC_OK;
 }
 
@@ -966,7 +843,7 @@ nrc_status launch_render_combine(nrc_ctx* ctx, cudaStream_t st, const TraceParam
     uint32_t n = rows * P.width * spp;
     if (n == 0) return NRC_OK;
     NRC_LAUNCH(ctx, st, K_RENDER_COMBINE,
-               k_render_combine<<<(n + 127) / 128, 128, NRC_PAD_SMEM, st>>>(P.width, y0, rows, ystride, spp, pool, paths, q));
+               k_render_combine<<<(n + 127) / 128, 128, 0, st>>>(P.width, y0, rows, ystride, spp, pool, paths, q));
     return NRC_OK;
 }
 

@@ -71,5 +71,4 @@ nrc_status launch_composite(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P,
                             RenderPaths paths, QueryList q, const float4* background, float4* frame, uint32_t* frame8, float* queryProbe,
                             const uint32_t* scalars, const unsigned long long* taps, unsigned long long* totals);
 nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, float* out);
-nrc_status launch_build_occupancy(nrc_volume* vol);
 nrc_status launch_build_bricks(nrc_volume* vol, const float* densityDev);

@@ -161,10 +161,6 @@ class VolumeData:
         self.useNN, self.showNonNN, self.densityFactor, self.g, self.noNnSpp, self.withNnSpp = 0, 0, 0.4, 0.7, 1, 1
         self._lcg = 0x2545F491
 
-    def set_tap_filter(self, texture_unit):
-        """opt-in: light-segment density taps through the texture unit (values within ~1e-4) instead of the exact fp32 blend"""
-        L.check(L.lib().nrc_volume_set_tap_filter(self.h, C.c_int(1 if texture_unit else 0)))
-
     def Update(self, camera_changed=False, random4=None):
         """VolumeData::Update (VolumeData.cpp:105-109): a new `random` vec4 per frame.  The reference draws it from
         glm::linearRand (unseeded); here it is an explicit input or a seeded LCG."""

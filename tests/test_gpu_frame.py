@@ -106,35 +106,6 @@ def test_split_render_walk_is_the_single_launch_walk(N, ctx, monkeypatch):
     assert Cm.psnr(got[10][2], orgba) >= PSNR_MIN
 
 
-def test_occupancy_tested_taps_change_nothing(N, ctx, monkeypatch):
-    """NRC_LIGHT_OCC_SHIFT: the light kernels skip the brick load of a tap whose run of 2^shift cells holds no density and blend a zero
-    brick instead.  Frames, trained weights and tap counts are those of the untested taps (shift 0), bit for bit."""
-    W, H, tw, th = 96, 64, 12, 12
-    cfg = Cm.scene_cfg(aspect=W / H)
-    got = {}
-    for sh in (0, 3, 5, 8):
-        monkeypatch.setenv("NRC_LIGHT_OCC_SHIFT", str(sh))
-        r, nrc, m, vol = build(N, ctx, cfg, W, H, tw, th)
-        r.FrameRender()                       # render pass alone: deterministic, compared bit for bit
-        ctx.sync()
-        first, taps = r.read_frame().copy(), r.stats()["density_taps"]
-        for f in range(2):                    # whole frames: the training targets go through the same taps
-            vol.random = np.asarray([(0.37, 0.61, 0.13, 0.89), (0.11, 0.93, 0.5, 0.2)][f], np.float32)
-            r.Render()
-        ctx.sync()
-        got[sh] = (first, taps, nrc.get_params()[0].copy(), m.get_tables()[0].copy(), r.read_frame().copy())
-        r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
-    monkeypatch.delenv("NRC_LIGHT_OCC_SHIFT")
-    assert got[0][1] > 0
-    for sh in (3, 5, 8):
-        np.testing.assert_array_equal(got[sh][0].view(np.uint32), got[0][0].view(np.uint32))
-        assert got[sh][1] == got[0][1]
-        # the gradient sums are float atomics: weights and the frames rendered with them agree to summation-order noise
-        np.testing.assert_allclose(got[sh][2], got[0][2], rtol=1e-4, atol=1e-7)
-        np.testing.assert_allclose(got[sh][3], got[0][3], rtol=1e-4, atol=1e-7)
-        assert Cm.psnr(got[sh][4], got[0][4]) >= 80.0
-
-
 def test_train_pass_parity(N, ctx):
     tw, th = 20, 12
     cfg = Cm.scene_cfg()
