@@ -1,9 +1,12 @@
 """Checkpoint of the learnt state (the reference has none -- it retrains from random weights on every start,
 src/NeuralRadianceCache.cpp:629-659, src/MRHE.cpp:127-135).
 
-One little-endian file: magic "NRCB200\\0", version, five section sizes, then float32 sections in this order
-  MLP params (20 995: W0..W5, b0..b5 -- the C-ABI packing), MLP momentum (20 995), hash tables [L][T][F], table shape, hyper-parameters.
-Gradient accumulators are not state (zero between frames).  The C++ facade reads and writes the same layout
+One little-endian file: magic "NRCB200\\0", uint32 {version, nParams, nTables, L, T, F}, then float32 sections in this order
+  MLP params (20 995: W0..W5, b0..b5 -- the C-ABI packing), MLP momentum (20 995), hash tables [L][T][F].
+Gradient accumulators are not state (zero between frames).  NOT stored: learning rates / weight decay / beta, the resolution table
+and its mode (intended vs as_shipped_std140) and the fixed-preset switch -- they are constructor arguments of the objects the file is
+loaded INTO; a file trained under one resolution table or preset loads into objects built with another (the shapes match) and then
+decodes differently, so construct the objects as they were when the file was written.  The C++ facade reads and writes the same layout
 (include/nrc_b200.hpp: SaveCheckpoint / LoadCheckpoint).
 
 Version 2 = version 1 + a trailer with the Adam state of the opt-in fixed preset, written only when Adam is switched on:

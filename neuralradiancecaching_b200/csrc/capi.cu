@@ -372,15 +372,17 @@ extern "C" nrc_status nrc_mlp_get_params(nrc_mlp* m, float* params, float* delta
 extern "C" nrc_status nrc_mlp_reset_stats(nrc_mlp* m)
 {
     NRC_REQUIRE(m, "null mlp");
-    NRC_CUDA(cudaMemsetAsync(m->grad + NRC_MLP_PARAM_COUNT, 0, sizeof(float), m->ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(m->grad + NRC_MLP_PARAM_COUNT, 0, 2 * sizeof(float), m->ctx->stream));   // + the exchange's running total
     return NRC_OK;
 }
 
 extern "C" nrc_status nrc_mlp_get_stats(nrc_mlp* m, float* mseLoss)
 {
     NRC_REQUIRE(m && mseLoss, "null argument");
-    NRC_CUDA(cudaMemcpyAsync(mseLoss, m->grad + NRC_MLP_PARAM_COUNT, sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
+    float v[2] = {0.0f, 0.0f};   // [0] accumulated on this GPU since the last exchange, [1] global total published by the fused exchange (0 without one)
+    NRC_CUDA(cudaMemcpyAsync(v, m->grad + NRC_MLP_PARAM_COUNT, 2 * sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    *mseLoss = v[0] + v[1];
     return NRC_OK;
 }
 
@@ -389,7 +391,9 @@ extern "C" nrc_status nrc_mlp_get_stats(nrc_mlp* m, float* mseLoss)
 extern "C" nrc_status nrc_mlp_get_stats_async(nrc_mlp* m, float* mseLoss)
 {
     NRC_REQUIRE(m && mseLoss, "null argument");
-    NRC_CUDA(cudaMemcpyAsync(mseLoss, m->grad + NRC_MLP_PARAM_COUNT, sizeof(float), cudaMemcpyDeviceToHost, m->ctx->stream));
+    // with a fused exchange attached the frame's loss sits in the running-total slot (the exchanged slot has been cleared by then)
+    NRC_CUDA(cudaMemcpyAsync(mseLoss, m->grad + NRC_MLP_PARAM_COUNT + (m->lossTotalSlot ? 1 : 0), sizeof(float), cudaMemcpyDeviceToHost,
+                             m->ctx->stream));
     return NRC_OK;
 }
 

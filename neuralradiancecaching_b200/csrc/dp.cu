@@ -246,9 +246,14 @@ __global__ void __launch_bounds__(DP_THREADS) k_dp_reduce_step(const __grid_cons
     if (a.clear && !s_fail) {
         for (int i4 = t; i4 < DP_MLP_VEC; i4 += stride) {
             float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            if (i4 == DP_MLP_VEC - 1) {   // {b5[0..2] gradients, loss}: every rank reports the global loss
+            if (i4 == DP_MLP_VEC - 1) {   // {b5[0..2] gradients, loss accumulator}
+                // The exchanged slot [20995] holds what THIS rank accumulated since the last exchange; it restarts at zero.  The global
+                // sum goes to the running total in slot [20996], which is not exchanged -- GetStats() reports [20995] + [20996], and
+                // ResetStats() clears both.  (Round 1 wrote the global sum back into the exchanged slot: a host that did not reset the
+                // statistics every frame saw W * previous + new after the next exchange.)
                 float own = a.grad[NRC_MLP_PARAM_COUNT];
-                z.w = (a.clear == 1) ? lossSum : own;
+                if (a.clear == 1) a.grad[NRC_MLP_PARAM_COUNT + 1] += lossSum;
+                z.w = (a.clear == 1) ? 0.0f : own;
             }
             reinterpret_cast<float4*>(a.grad)[i4] = z;
         }
@@ -281,6 +286,7 @@ extern "C" nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int 
         if (world == 1) d->sharded = false;
     }
     d->mlpAdam = mlp->adam; d->mrheAdam = mrhe->adam;
+    mlp->lossTotalSlot = true;   // GetStats() must add the running total the exchange keeps in grad[20996]
     cudaError_t e = cudaMalloc(&d->flags, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));
     if (e == cudaSuccess) e = cudaMemset(d->flags, 0, sizeof(unsigned) * (NRC_DP_FLAG_COUNT + 1));
     if (e != cudaSuccess) {

@@ -107,6 +107,7 @@ struct nrc_mlp {
     uint32_t steps = 0;
     void* featTiles = nullptr;       // bf16 operand-image tiles of the split inference path (grown on demand)
     size_t featBytes = 0;
+    bool lossTotalSlot = false;  // a fused data-parallel exchange publishes the global loss in grad[20996] (dp.cu)
     bool dirtyT = true;          // paramsT needs a rebuild after params changed
     bool dirtyBf16 = true;       // paramsBf16 needs a rebuild
 };

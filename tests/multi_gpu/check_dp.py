@@ -107,6 +107,39 @@ def run_case(ctx, dev, rank, world, name, T, shard=None, adam=False, fixed=False
     return report
 
 
+def check_loss(ctx, dev, rank, world):
+    """GetStats() with the fused exchange attached: every rank reports the GLOBAL loss, accumulated linearly over frames until
+    ResetStats() (the old kernel wrote the global sum into the exchanged slot, so a host that did not reset every frame
+    saw W * previous + new)."""
+    os.environ.pop("NRC_DP_SHARD", None)
+    nrc = N.NeuralRadianceCache(ctx, 0.001, 0.0, 0.5, seed=0)
+    nrc.set_params(Cm.S.mlp_init(1))
+    m = N.MRHE(ctx, 0.01, 0.0, seed=0)
+    m.set_tables(Cm.S.table_init())
+    fused = FusedExchange(nrc, m, rank, world, dev)
+    pos, d = Cm.rand_queries(256, seed=50 + rank)
+    target = np.full((256, 3), 0.5 + rank, np.float32)
+    nrc.ResetStats()
+    local, total = [], 0.0
+    for it in range(3):
+        before = nrc.GetStats().mseLoss
+        N.train_accumulate(nrc, m, pos, d, target, 1.0 / 256)
+        mine = nrc.GetStats().mseLoss - before
+        t = torch.tensor([mine], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)
+        total += float(t[0])
+        fused()
+        ctx.sync()
+        got = nrc.GetStats().mseLoss
+        assert abs(got - total) <= 1e-4 * total, (it, got, total)
+    nrc.ResetStats()
+    assert nrc.GetStats().mseLoss == 0.0
+    dist.barrier()
+    fused.close()
+    nrc.Destroy(); m.Destroy()
+    return "loss statistics: global and linear over 3 exchanges without ResetStats"
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -123,6 +156,7 @@ def main():
     ]
     if big:                    # the fixed preset at config 5's table size: the whole 512 MiB table is exchanged
         reports.append(run_case(ctx, dev, rank, world, "fixed preset at T=2^22 (sharded by size)", 1 << 22, fixed=True, iters=1, timing=5))
+    reports.append(check_loss(ctx, dev, rank, world))
     if rank == 0:
         for r in reports:
             print("DP-CHECK", r)
