@@ -16,7 +16,7 @@
 // SHARDED form -- reduce-scatter + sharded step + all-gather in one launch.  Rank r owns slice r of the head: it reads the W gradient
 // slices over NVLink, adds them in rank order, applies mrhe-step.comp (or the opt-in Adam) to its slice and WRITES the new table
 // values (and Adam moments) into every replica (st.relaxed.sys.v4).  Per rank 2 x (W-1)/W x head bytes cross NVLink instead of
-// (W-1) x head; the grid grows to 592 blocks (4 per SM).  The handshakes are the same two: "gradients complete" before, "I have read yours and
+// (W-1) x head; the grid grows to one block per SM.  The handshakes are the same two: "gradients complete" before, "I have read yours and
 // written my slice of your table" after -- the second one is what makes the peers' table writes visible before the next kernel here.
 // The reference has no multi-GPU path at all; the step arithmetic is the one of steps.cu (nrc-step.comp:200-406,
 // mrhe-step.comp:27-74).
@@ -29,7 +29,7 @@
 
 #define NRC_DP_MAX_WORLD 16
 #define NRC_DP_SHARD_FLOATS (1u << 20)   // heads above this many floats are exchanged in sharded form (NRC_DP_SHARD=1 forces it)
-#define NRC_DP_MAX_BLOCKS 592   // sharded form: 4 blocks per SM of a B200, so that enough NVLink loads and stores are in flight
+#define NRC_DP_MAX_BLOCKS 592   // upper bound of the grid (flag slots); the sharded form uses one block per SM by default
 #define NRC_DP_FLAG_COUNT (NRC_DP_MAX_BLOCKS * NRC_DP_MAX_WORLD * 2)
 
 struct nrc_dp {
@@ -416,7 +416,15 @@ static nrc_status dp_launch(nrc_dp* d, int barriers, int clear, bool reduce)
         a.timeoutNs = (unsigned long long)(ms > 0 ? ms : 30000) * 1000000ull;
     }
     // latency regime: 16 small blocks; bandwidth regime (sharded): 4 per SM, so that enough NVLink loads and stores are in flight
-    const unsigned blocks = d->sharded ? NRC_DP_MAX_BLOCKS : DP_BLOCKS;
+    unsigned blocks = DP_BLOCKS;
+    if (d->sharded) {   // enough CTAs that a thread walks ~8 float4 of its rank's slice: 16 .. 592
+        const size_t per4 = (size_t)a.extent / 4 / (size_t)d->world;
+        size_t want = per4 / (DP_THREADS * 8) + 1;
+        if (const char* e = getenv("NRC_DP_BLOCKS")) want = (size_t)atol(e);
+        else if (want > (size_t)ctx->smCount) want = (size_t)ctx->smCount;   // one CTA per SM is the measured optimum (T = 2^22, 2 GPUs:
+                                                                              // 0.346 / 0.196 / 0.110 / 0.124 / 0.171 ms with 32 / 64 / 148 / 296 / 592)
+        blocks = (unsigned)(want < DP_BLOCKS ? DP_BLOCKS : (want > NRC_DP_MAX_BLOCKS ? NRC_DP_MAX_BLOCKS : want));
+    }
     NRC_LAUNCH(ctx, ctx->stream, K_DP_REDUCE_STEP, k_dp_reduce_step<<<blocks, DP_THREADS, 0, ctx->stream>>>(a));
     // the sticky time-out word follows every launch to pinned host memory: the next call / nrc_sync / nrc_readback_wait sees it
     if (barriers) NRC_CUDA(cudaMemcpyAsync(d->hostFail, d->flags + NRC_DP_FLAG_COUNT, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));

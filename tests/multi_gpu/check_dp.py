@@ -147,6 +147,12 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     ctx = N.Context(local)
     big = os.environ.get("CHECK_DP_BIG")
+    if os.environ.get("CHECK_DP_ONLY") == "large":      # timing sweeps: the large-table case alone
+        r = run_case(ctx, dev, rank, world, "large table", (1 << 22) if big else (1 << 20), iters=1, timing=30, wd=0.0)
+        if rank == 0:
+            print("DP-CHECK", r)
+        dist.destroy_process_group()
+        return
     reports = [
         run_case(ctx, dev, rank, world, "replicated", 16384, shard="0"),
         run_case(ctx, dev, rank, world, "sharded (forced)", 16384, shard="1"),
