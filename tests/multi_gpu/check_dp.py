@@ -68,6 +68,12 @@ def run_case(ctx, dev, rank, world, name, T, shard=None, adam=False, fixed=False
                 np.testing.assert_array_equal(a_nrc.get_adam_state()[0].view(np.uint32), b_nrc.get_adam_state()[0].view(np.uint32))
                 for x, y in zip(a_m.get_adam_state()[:2], b_m.get_adam_state()[:2]):
                     np.testing.assert_array_equal(x.view(np.uint32), y.view(np.uint32))
+        elif adam:
+            # NCCL's ring sums in another order than rank order; Adam divides by sqrt(v), which turns last-bit differences of
+            # near-zero gradients into visible fractions of a step (lr 0.05 / 0.1): a tenth of a step is the bound here.  The exact
+            # claims are below (replicas bit-identical) and in tests/test_gpu_dp.py (bit-identical to the rank-ordered reference).
+            np.testing.assert_allclose(ap, bp, rtol=0, atol=5e-3)
+            np.testing.assert_allclose(at, bt, rtol=0, atol=1e-2)
         else:
             np.testing.assert_allclose(ap, bp, rtol=1e-5, atol=1e-6)
             np.testing.assert_allclose(at, bt, rtol=1e-5, atol=1e-6)
