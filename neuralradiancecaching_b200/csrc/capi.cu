@@ -101,7 +101,7 @@ static const char* const g_kernelNames[K_COUNT] = {
     "k_encode_pos", "k_encode_dir", "k_infer_fp32", "k_train_fp32", "k_reduce_partials", "k_transpose_weights", "k_nrc_step",
     "k_mrhe_step", "k_init_normal", "k_render_walk", "k_train_walk", "k_light<render>", "k_light<train>", "k_render_combine",
     "k_train_combine", "k_composite", "k_build_bricks", "k_volume_sample", "k_pack_records", "k_cdf_rows", "k_cdf_y",
-    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc", "k_dp_reduce_step", "k_encode_tiles", "k_mlp_stream", "k_render_walk_tail"};
+    "k_infer_tc", "k_train_tc", "k_pack_bf16", "misc", "k_dp_reduce_step", "k_encode_tiles", "k_mlp_stream", "k_render_walk_tail", "k_reduce_step"};
 
 void nrc_prof_begin(nrc_ctx* ctx, cudaStream_t st, int kid)
 {

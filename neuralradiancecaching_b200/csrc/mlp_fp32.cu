@@ -504,7 +504,7 @@ nrc_status train_scratch(nrc_mlp* mlp, nrc_mrhe* m, size_t n, bool* useHist)
 }
 
 nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
-                             float* pred, cudaStream_t st)
+                             float* pred, cudaStream_t st, int* deferred)
 {
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
@@ -523,6 +523,7 @@ nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
     NRC_LAUNCH(mlp->ctx, st, K_TRAIN_FP32,
                k_train_fp32<<<blocks, NTHREADS, smem, st>>>(pos, dir, target, nullptr, n, lossScale, w, make_mrhe_dev(m), mlp->partial, pred,
                                                             mlp->gScratch, useHist ? mlp->histPartial : nullptr));
+    if (deferred) { deferred[0] = blocks; deferred[1] = useHist ? 1 : 0; return NRC_OK; }
     return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }
 

@@ -696,10 +696,10 @@ nrc_status launch_reduce_partials(nrc_mlp* mlp, nrc_mrhe* m, int blocks, bool hi
 nrc_status train_scratch(nrc_mlp* mlp, nrc_mrhe* m, size_t n, bool* useHist);                            // mlp_fp32.cu
 
 nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
-                           float* pred, cudaStream_t st)
+                           float* pred, cudaStream_t st, int* deferred)
 {
     // the opt-in fixed preset (per-feature errors, per-level gradient tables) trains on the fp32 CUDA-core kernel
-    if (m->fixed) return launch_train_fp32(mlp, m, pos, dir, target, n, lossScale, pred, st);
+    if (m->fixed) return launch_train_fp32(mlp, m, pos, dir, target, n, lossScale, pred, st, deferred);
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
     NRC_TRY(tc_prepare(mlp, st));
@@ -720,5 +720,6 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
                                                                      reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16), mlp->params,
                                                                      make_mrhe_dev(m), mlp->partial, pred, mlp->gScratch,
                                                                      useHist ? mlp->histPartial : nullptr));
+    if (deferred) { deferred[0] = blocks; deferred[1] = useHist ? 1 : 0; return NRC_OK; }
     return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }

@@ -43,7 +43,7 @@ enum NrcKernelId {
     K_ENCODE_POS = 0, K_ENCODE_DIR, K_INFER_FP32, K_TRAIN_FP32, K_REDUCE_PARTIALS, K_TRANSPOSE_WEIGHTS, K_NRC_STEP, K_MRHE_STEP,
     K_INIT_NORMAL, K_RENDER_WALK, K_TRAIN_WALK, K_LIGHT_RENDER, K_LIGHT_TRAIN, K_RENDER_COMBINE, K_TRAIN_COMBINE, K_COMPOSITE,
     K_BUILD_BRICKS, K_VOLUME_SAMPLE, K_PACK_RECORDS, K_CDF_ROWS, K_CDF_Y, K_INFER_TC, K_TRAIN_TC, K_PACK_BF16, K_MISC, K_DP_REDUCE_STEP,
-    K_ENCODE_TILES, K_MLP_STREAM, K_RENDER_WALK_TAIL,
+    K_ENCODE_TILES, K_MLP_STREAM, K_RENDER_WALK_TAIL, K_REDUCE_STEP,
     K_COUNT
 };
 
@@ -222,18 +222,23 @@ nrc_status launch_encode_dir(nrc_ctx* ctx, const float* dir, size_t n, float* fe
 nrc_status launch_mlp_prepare(nrc_mlp* mlp);   // rebuild transposed weights after a parameter change
 nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n,
                              float* rgb, cudaStream_t st);
+// deferred != nullptr: the per-CTA partials are NOT reduced; deferred[0] = CTAs, deferred[1] = 1 if the histogram scatter was used --
+// the caller finishes with launch_reduce_step (fused with the optimiser steps) or launch_reduce_partials
 nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n,
-                             float lossScale, float* pred, cudaStream_t st);
+                             float lossScale, float* pred, cudaStream_t st, int* deferred = nullptr);
 // per-launch scratch of both train kernels: partial arenas, the dL/dx0 rows, the per-CTA histograms (useHist: the shared-memory path applies)
 nrc_status train_scratch(nrc_mlp* mlp, nrc_mrhe* m, size_t n, bool* useHist);
 nrc_status launch_reduce_partials(nrc_mlp* mlp, nrc_mrhe* m, int blocks, bool hist, cudaStream_t st);
+// steps.cu: {k_reduce_partials, k_nrc_step, k_mrhe_step} as one launch, where that is exactly what the three would do
+bool reduce_step_fusable(const nrc_mlp* mlp, const nrc_mrhe* m, bool hist);
+nrc_status launch_reduce_step(nrc_mlp* mlp, nrc_mrhe* m, int blocks, cudaStream_t st);
 // steps.cu
 nrc_status launch_nrc_step(nrc_mlp* mlp, cudaStream_t st);
 nrc_status launch_mrhe_step(nrc_mrhe* m, cudaStream_t st);
 nrc_status launch_init_normal(nrc_ctx* ctx, float* dst, size_t n, float scale, uint64_t seed);
 // mlp_tc.cu (tcgen05 path)
 nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const float* target, size_t n, float lossScale,
-                           float* pred, cudaStream_t st);
+                           float* pred, cudaStream_t st, int* deferred = nullptr);
 nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n,
                            float* rgb, cudaStream_t st);
 // split inference: k_encode_tiles (mlp_tc.cu) -> bf16 operand-image tiles -> k_mlp_stream (mlp_stream.cu)

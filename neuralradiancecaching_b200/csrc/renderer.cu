@@ -392,7 +392,8 @@ static nrc_status infer_queries(nrc_renderer* r, cudaStream_t st)
 
 // nrc-train.comp over this rank's invocations: trace the records, then Backprop() them (gradients accumulate
 // into the MLP / MRHE delta arenas; the optimiser step is separate).
-extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
+// deferred: see launch_train_* -- nrc_render finishes the frame's training with one fused reduce + steps launch
+static nrc_status frame_train(nrc_renderer* r, int* deferred)
 {
     NRC_REQUIRE(r, "null renderer");
     nrc_ctx* ctx = r->ctx;
@@ -450,9 +451,9 @@ extern "C" nrc_status nrc_frame_train(nrc_renderer* r)
     }
     float lossScale = P.widthFactor * P.heightFactor;   // ONE_OVER_PIXEL_COUNT (nrc-train.comp:210)
     if (ctx->precision == NRC_MLP_BF16_TC)
-        NRC_TRY(launch_train_tc(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
+        NRC_TRY(launch_train_tc(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st, deferred));
     else
-        NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st));
+        NRC_TRY(launch_train_fp32(r->mlp, r->mrhe, r->tp.pos, r->tp.dir, r->tp.target, n, lossScale, nullptr, st, deferred));
     if (ahead) {
         NRC_CUDA(cudaEventRecord(ctx->evTrainFree[b], st));
         r->trainPending[b] = true;
@@ -560,12 +561,23 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
     return render_pass(r);
 }
 
-// Render(): train -> nrc-step -> mrhe-step -> render, like the recorded command buffer.
+extern "C" nrc_status nrc_frame_train(nrc_renderer* r) { return frame_train(r, nullptr); }
+
+// Render(): train -> nrc-step -> mrhe-step -> render, like the recorded command buffer.  The sum of the train kernel's per-CTA partial
+// gradients and both optimiser steps are ONE launch where that is exactly what the separate kernels would do (steps.cu).
 extern "C" nrc_status nrc_render(nrc_renderer* r)
 {
     NRC_REQUIRE(r, "null renderer");
-    NRC_TRY(nrc_frame_train(r));
-    NRC_TRY(nrc_optimizer_step(r->mlp, r->mrhe));
+    int deferred[2] = {-1, 0};
+    NRC_TRY(frame_train(r, deferred));
+    if (deferred[0] < 0) {                         // nothing to train on this rank
+        NRC_TRY(nrc_optimizer_step(r->mlp, r->mrhe));
+    } else if (reduce_step_fusable(r->mlp, r->mrhe, deferred[1] != 0)) {
+        NRC_TRY(launch_reduce_step(r->mlp, r->mrhe, deferred[0], r->ctx->stream));
+    } else {
+        NRC_TRY(launch_reduce_partials(r->mlp, r->mrhe, deferred[0], deferred[1] != 0, r->ctx->stream));
+        NRC_TRY(nrc_optimizer_step(r->mlp, r->mrhe));
+    }
     NRC_TRY(nrc_frame_render(r));
     return NRC_OK;
 }

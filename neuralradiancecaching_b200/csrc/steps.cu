@@ -118,6 +118,74 @@ __global__ void __launch_bounds__(256) k_mrhe_step(float4* __restrict__ tables, 
     }
 }
 
+// ---- one launch for {k_reduce_partials, k_nrc_step, k_mrhe_step} of a single-GPU frame ---------------------------------------------------
+// Thread i < 20 995: the fixed-order sum of the train kernel's per-CTA partial gradients, added to what the arena already holds, then
+// nrc-step.comp on it (the arithmetic of k_nrc_step, operation for operation).  Thread 20 995: the loss accumulator.  Threads from
+// NRC_HIST_FIRST on: entry h of the delta table's head = the fixed-order sum of the CTAs' histograms (both features, A9), then
+// mrhe-step.comp on it.  Only valid where the separate kernels would do exactly this: momentum-SGD steps (no Adam), the shared-memory
+// histogram scatter (so the head is covered entry for entry), and a table tail that is a fixed point of the step (nrc_mrhe::tailClean).
+#define NRC_HIST_FIRST 21248   // as in mlp_fp32.cu: first histogram thread, a multiple of the block size past the arena
+__global__ void __launch_bounds__(256) k_reduce_step(const float* __restrict__ partial, int nb, float* __restrict__ grad, float* __restrict__ params,
+                                                     float* __restrict__ momentum, float* __restrict__ paramsT, unsigned short* __restrict__ imgBf16,
+                                                     float lr, float wd, float beta1, const float* __restrict__ hist, uint32_t T,
+                                                     float2* __restrict__ delta, float2* __restrict__ tables, float mlr, float mwd)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= NRC_MLP_PARAM_COUNT) {
+        float s = 0.0f;
+        for (int b = 0; b < nb; b++) s += partial[(size_t)b * NRC_PARTIAL_STRIDE + i];
+        if (i == NRC_MLP_PARAM_COUNT) { grad[i] += s; return; }   // mseLoss
+        const float w = params[i];
+        float g = grad[i] + s;
+        if (bad_value(g)) g = __fmul_rn(1000.0f, sign_nan0(g));
+        g = __fadd_rn(g, __fmul_rn(-w, wd));
+        const float d = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, beta1), g), __fmul_rn(beta1, momentum[i]));
+        momentum[i] = d;
+        float nw = __fadd_rn(w, __fmul_rn(d, lr));
+        if (i < NRC_MLP_WEIGHT_COUNT && bad_value(nw)) nw = 0.0f;
+        params[i] = nw;
+        grad[i] = 0.0f;
+        if (i < 5 * 4096) {
+            int l = i >> 12, rem = i & 4095, o = rem >> 6, k = rem & 63;
+            paramsT[l * 4096 + k * 64 + o] = nw;
+        }
+        if (imgBf16 && i < NRC_MLP_WEIGHT_COUNT) tc_store_weight(imgBf16, i, nw);
+        return;
+    }
+    const uint32_t h = (uint32_t)i - NRC_HIST_FIRST;
+    if (i < NRC_HIST_FIRST || h >= T) return;
+    float s = 0.0f;
+    for (int b = 0; b < nb; b++) s += hist[(size_t)b * T + h];
+    float2 d = delta[h];
+    d.x += s; d.y += s;
+    float2 w = tables[h];
+    w.x = mrhe_update(w.x, d.x, mlr, mwd);
+    w.y = mrhe_update(w.y, d.y, mlr, mwd);
+    tables[h] = w;
+    delta[h] = make_float2(0.0f, 0.0f);
+}
+
+// true if the fused launch is exactly {reduce, nrc-step, mrhe-step} for the state the objects are in (see above)
+bool reduce_step_fusable(const nrc_mlp* mlp, const nrc_mrhe* m, bool hist)
+{
+    // Measured on the 1080p bench frame (alternating runs, same box): 2.938 / 2.933 ms fused against 2.906 / 2.875 ms with the three
+    // separate launches -- no gain (the frame is throughput-bound; two launch gaps on the main stream are not on its critical path).
+    // So it is opt-in: NRC_FUSED_STEP=1.
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("NRC_FUSED_STEP"); on = (e && atoi(e)) ? 1 : 0; }
+    return on && hist && !mlp->adam && !m->adam && !m->fixed && m->tailClean && m->wd == 0.0f && (size_t)2 * m->T < m->count;
+}
+
+nrc_status launch_reduce_step(nrc_mlp* mlp, nrc_mrhe* m, int blocks, cudaStream_t st)
+{
+    const unsigned threads = NRC_HIST_FIRST + m->T;
+    NRC_LAUNCH(mlp->ctx, st, K_REDUCE_STEP,
+               k_reduce_step<<<(threads + 255) / 256, 256, 0, st>>>(mlp->partial, blocks, mlp->grad, mlp->params, mlp->momentum, mlp->paramsT,
+                                                                    mlp->paramsBf16, mlp->lr, mlp->wd, mlp->beta1, mlp->histPartial, m->T,
+                                                                    reinterpret_cast<float2*>(m->delta), reinterpret_cast<float2*>(m->tables), m->lr, m->wd));
+    return NRC_OK;
+}
+
 // Counter-based N(0,1)*scale: splitmix64 per element + Box-Muller.  (The reference seeds from
 // std::random_device, src/NeuralRadianceCache.cpp:629 / src/MRHE.cpp:127: not reproducible; parity runs set
 // parameters explicitly.)
