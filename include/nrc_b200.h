@@ -181,7 +181,8 @@ NRC_API size_t nrc_mrhe_grad_extent(nrc_mrhe* mrhe);
  * nrc_*_set_adam: nrc-step.comp / mrhe-step.comp with a second moment and bias correction (the shipped "Adam" is first-moment momentum
  *   only, A16): g' as shipped (scrub, weight decay); m = b1 m + (1-b1) g'; v = b2 v + (1-b2) g'^2; w += lr * mhat / (sqrt(vhat) + eps).
  *   The MLP keeps the beta1 of nrc_mlp_create; the tables get their own.  Switching on (or off) resets moments and step count.
- *   The fused data-parallel exchange (nrc_dp_*) refuses Adam; use the all-reduce path. */
+ *   The fused data-parallel exchange (nrc_dp_*) applies the same Adam step inside its kernel (moments replicated, or sharded with the
+ *   table). */
 NRC_API nrc_status nrc_mrhe_set_fixed_mode(nrc_mrhe* mrhe, int on);
 NRC_API nrc_status nrc_mlp_set_adam(nrc_mlp* mlp, int on, float beta2, float eps);
 NRC_API nrc_status nrc_mrhe_set_adam(nrc_mrhe* mrhe, int on, float beta1, float beta2, float eps);
@@ -304,7 +305,8 @@ NRC_API nrc_status nrc_dp_create(nrc_mlp* mlp, nrc_mrhe* mrhe, int rank, int wor
 NRC_API nrc_status nrc_dp_export(nrc_dp* dp, void* handle /*host, nrc_dp_handle_bytes()*/);
 NRC_API nrc_status nrc_dp_connect(nrc_dp* dp, const void* allHandles /*host, world handles in rank order*/, int sameProcess);
 NRC_API nrc_status nrc_dp_reduce_step(nrc_dp* dp);
-/* replicas inside one process (single-GPU parity test): phase 0 on every replica, then phase 1 on every replica */
+/* replicas inside one process (single-GPU parity test): phase 0 on every replica, then phase 1 on every replica.  Phase 2 is a test
+ * hook: this rank posts its gradients and then waits for peers that never arrive, to exercise the time-out (fails closed). */
 NRC_API nrc_status nrc_dp_reduce_step_phase(nrc_dp* dp, int phase);
 /* 1 if a handshake gave up waiting for a peer (about 30 s; a crashed rank must not hang the other GPUs).  The exchange FAILS CLOSED:
  * the block that gave up skips its step and its clear, the mark is written into every rank's flag block, and from then on

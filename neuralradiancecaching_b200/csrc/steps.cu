@@ -171,8 +171,8 @@ bool reduce_step_fusable(const nrc_mlp* mlp, const nrc_mrhe* m, bool hist)
     // Measured on the 1080p bench frame (alternating runs, same box): 2.938 / 2.933 ms fused against 2.906 / 2.875 ms with the three
     // separate launches -- no gain (the frame is throughput-bound; two launch gaps on the main stream are not on its critical path).
     // So it is opt-in: NRC_FUSED_STEP=1.
-    static int on = -1;
-    if (on < 0) { const char* e = getenv("NRC_FUSED_STEP"); on = (e && atoi(e)) ? 1 : 0; }
+    const char* e = getenv("NRC_FUSED_STEP");   // read at every frame (tests switch it)
+    const bool on = e && atoi(e);
     return on && hist && !mlp->adam && !m->adam && !m->fixed && m->tailClean && m->wd == 0.0f && (size_t)2 * m->T < m->count;
 }
 

@@ -774,11 +774,32 @@ nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, flo
     return NRC_OK;
 }
 
+// Experiment knob NRC_CARVEOUT=pct: preferred shared-memory carve-out of every tracing kernel (they use no shared memory; an SM has to
+// drain before its L1 / shared split changes, so kernels with different splits cannot share an SM -- the MLP kernels want 100-224 KB)
+static void trace_carveout_once()
+{
+    static bool done = false;
+    if (done) return;
+    done = true;
+    const char* e = getenv("NRC_CARVEOUT");
+    if (!e) return;
+    const int pct = atoi(e);
+    const char* we = getenv("NRC_CARVEOUT_WHICH");   // bit 0: render walks, 1: train walk, 2: lights, 3: combine / composite
+    const int which = we ? atoi(we) : 15;
+#define CARVE(k) cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, pct)
+    if (which & 1) { CARVE(k_render_walk<8>); CARVE(k_render_walk_tail<8>); }
+    if (which & 2) { CARVE(k_train_walk<true>); CARVE(k_train_walk<false>); }
+    if (which & 4) { CARVE((k_light<true, true>)); CARVE((k_light<true, false>)); CARVE((k_light<false, false>)); }
+    if (which & 8) { CARVE(k_render_combine); CARVE(k_train_combine); CARVE(k_composite); }
+#undef CARVE
+}
+
 nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
                               VertexPool pool, RenderPaths paths, float4* background, uint32_t* counters)
 {
     uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
+    trace_carveout_once();
     // steps in the head launch; 0 = the whole walk in one launch.  Read at every launch (tests switch it)
     const char* se = getenv("NRC_RWALK_SPLIT");
     int splitEnv = se ? atoi(se) : 10;
@@ -803,6 +824,7 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
                              TrainPaths paths, uint32_t* counters)
 {
     if (n == 0) return NRC_OK;
+    trace_carveout_once();
     static int lanesEnv = -1;
     if (lanesEnv < 0) {
         const char* e = getenv("NRC_TRAIN_LANES");   // training samples per warp (32; fewer = more, emptier warps: measured slower, profiles/r02_walks_in_flight.md)

@@ -268,6 +268,36 @@ def test_queued_frames_equal_frames_read_one_by_one(N, ctx):
     assert abs(out[0][3] - out[1][3]) <= 1e-3 * abs(out[0][3])
 
 
+def test_fused_reduce_and_steps_launch_equals_the_three_launches(N, ctx, monkeypatch):
+    """NRC_FUSED_STEP=1: Render() sums the train kernel's partial gradients and applies nrc-step + mrhe-step in ONE launch (from the
+    second frame on, once the table tail is a fixed point).  Same weights, tables, momentum and frames as the three separate launches,
+    up to the summation order inside the train kernel's shared-memory histogram."""
+    W, H, tw, th = 64, 48, 16, 16
+    cfg = Cm.scene_cfg(aspect=W / H)
+    rnd = [(0.37, 0.61, 0.13, 0.89), (0.11, 0.93, 0.5, 0.2), (0.71, 0.29, 0.4, 0.6), (0.05, 0.45, 0.85, 0.25)]
+    out = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("NRC_FUSED_STEP", fused)
+        r, nrc, m, vol = build(N, ctx, cfg, W, H, tw, th)
+        n0 = ctx.launch_count()
+        for f in range(4):
+            vol.random = np.asarray(rnd[f], np.float32)
+            r.Render()
+        ctx.sync()
+        launches = ctx.launch_count() - n0
+        p, d, mo = nrc.get_params()
+        t, td = m.get_tables()
+        assert not d.any() and not td.any()
+        out.append((p.copy(), mo.copy(), t.copy(), r.read_frame().copy(), nrc.GetStats().mseLoss, launches))
+        r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+    monkeypatch.delenv("NRC_FUSED_STEP")
+    assert out[0][5] - out[1][5] == 2 * 3            # frames 2-4 save two launches each
+    for k in (0, 1, 2):
+        assert _relmax(out[1][k], out[0][k]) < 1e-5, k
+    assert Cm.psnr(out[1][3], out[0][3]) >= 80.0
+    assert abs(out[1][4] - out[0][4]) <= 1e-4 * abs(out[0][4])
+
+
 def test_async_readback_delivers_the_same_frames(N, ctx):
     """Render(k); async copy of frame k; Render(k+1) queued before frame k is awaited: each delivered frame and loss equals
     what the synchronous calls return for the same frame (the next composite must not overwrite a frame under its copy)."""
