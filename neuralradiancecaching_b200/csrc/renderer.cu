@@ -412,23 +412,16 @@ static nrc_status frame_train(nrc_renderer* r, int* deferred)
     if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
     if (noAhead < 0) { const char* e = getenv("NRC_NO_TRAIN_AHEAD"); noAhead = (e && atoi(e)) ? 1 : 0; }
     const bool ahead = !(noOverlap || noAhead);
-    // Walks in flight: enough to hide the walk's latency (~2.5 ms beside the other kernels) behind the frame time, no more -- measured
-    // (profiles/r02_walks_in_flight.md): a 1080p frame (2.9 ms) is fastest with one walk at a time (2.92 vs 3.26 ms with three), a 720p
-    // frame (1.8-1.9 ms) with three (1.82-1.9 vs 2.15 ms with one).  NRC_TRAIN_WALK=n overrides the choice.
+    // Walks in flight: three (all walk streams).  The walk is one dependent chain per sample (~1.2 ms alone, ~2.5 ms beside the other
+    // kernels); with the frames' walks overlapping it never bounds the frame: 720p 1.80 against 2.15 ms with one at a time, 1080p 2.77
+    // against 2.81 ms, 4K per rank the same either way (profiles/r02_walks_in_flight.md, r02_carveout.md).  NRC_TRAIN_WALK=n overrides.
     static int walkEnv = -1;
     if (walkEnv < 0) {
         const char* e = getenv("NRC_TRAIN_WALK");
         walkEnv = e ? atoi(e) : 0;
-        if (walkEnv < 0 || walkEnv > NRC_TRAIN_WALK_STREAMS) walkEnv = 0;
+        if (walkEnv < 1 || walkEnv > NRC_TRAIN_WALK_STREAMS) walkEnv = NRC_TRAIN_WALK_STREAMS;
     }
-    int walkStreams = walkEnv;
-    if (walkStreams == 0) {
-        const size_t px = (size_t)part_count(r->y0, r->y1, r->ystride) * r->width;
-        walkStreams = px >= 1500000 ? 1 : 3;
-        // a grid whose bricks do not fit L2 (config 5: 838 MB) doubles the walk's latency (every tap goes to HBM): 5.6 ms against a frame of
-        // ~6 ms of throughput work -- keep three walks in flight there
-        if ((size_t)(r->vol->nx + 1) * (r->vol->ny + 1) * (r->vol->nz + 1) * sizeof(uint2) > ((size_t)96 << 20)) walkStreams = NRC_TRAIN_WALK_STREAMS;
-    }
+    const int walkStreams = walkEnv;
     cudaStream_t tw = ahead ? ctx->streamWalk[r->trainSeq % (unsigned)walkStreams] : st;
     cudaStream_t tl = ahead ? ctx->stream4 : st;
     r->trainSeq++;

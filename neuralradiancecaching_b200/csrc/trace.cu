@@ -774,24 +774,27 @@ nrc_status launch_volume_sample(nrc_volume* vol, const float* pos, size_t n, flo
     return NRC_OK;
 }
 
-// Experiment knob NRC_CARVEOUT=pct: preferred shared-memory carve-out of every tracing kernel (they use no shared memory; an SM has to
-// drain before its L1 / shared split changes, so kernels with different splits cannot share an SM -- the MLP kernels want 100-224 KB)
-static void trace_carveout_once()
+// The tracing kernels use no shared memory, the MLP kernels 61-224 KB per CTA.  Left to the driver's default, an SM that has run an MLP
+// CTA keeps its large shared-memory split for the tracing CTAs that follow, which then gather through a fraction of the L1 (forcing the
+// largest split on them costs 40 %: 4.19 against 2.91 ms per 1080p frame).  An explicit preference hands them the L1 back: any value from
+// 5 to 28 % measures the same (1080p 2.91 -> 2.81 ms, 720p 1.97 -> 1.80 ms, profiles/r02_carveout.md); 25 % = 64 KB still takes one
+// CTA of the inference kernel beside them.  NRC_CARVEOUT=pct overrides, -1 leaves the driver's default.  Once per device.
+static void trace_carveout(nrc_ctx* ctx)
 {
-    static bool done = false;
-    if (done) return;
-    done = true;
+    static bool done[64] = {};
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64 || done[dev]) return;
+    done[dev] = true;
     const char* e = getenv("NRC_CARVEOUT");
-    if (!e) return;
-    const int pct = atoi(e);
-    const char* we = getenv("NRC_CARVEOUT_WHICH");   // bit 0: render walks, 1: train walk, 2: lights, 3: combine / composite
-    const int which = we ? atoi(we) : 15;
+    const int pct = e ? atoi(e) : 25;
+    if (pct < 0 || pct > 100) return;
 #define CARVE(k) cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, pct)
-    if (which & 1) { CARVE(k_render_walk<8>); CARVE(k_render_walk_tail<8>); }
-    if (which & 2) { CARVE(k_train_walk<true>); CARVE(k_train_walk<false>); }
-    if (which & 4) { CARVE((k_light<true, true>)); CARVE((k_light<true, false>)); CARVE((k_light<false, false>)); }
-    if (which & 8) { CARVE(k_render_combine); CARVE(k_train_combine); CARVE(k_composite); }
+    CARVE(k_render_walk<8>); CARVE(k_render_walk_tail<8>);
+    CARVE(k_train_walk<true>); CARVE(k_train_walk<false>);
+    CARVE((k_light<true, true>)); CARVE((k_light<true, false>)); CARVE((k_light<false, false>));
+    CARVE(k_render_combine); CARVE(k_train_combine); CARVE(k_composite);
 #undef CARVE
+    cudaGetLastError();   // a hint: nothing to report if the driver declines it
 }
 
 nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, uint32_t y0, uint32_t rows, uint32_t ystride, uint32_t spp,
@@ -799,7 +802,7 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
 {
     uint32_t n = rows * P.width;
     if (n == 0) return NRC_OK;
-    trace_carveout_once();
+    trace_carveout(ctx);
     // steps in the head launch; 0 = the whole walk in one launch.  Read at every launch (tests switch it)
     const char* se = getenv("NRC_RWALK_SPLIT");
     int splitEnv = se ? atoi(se) : 10;
@@ -824,7 +827,7 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
                              TrainPaths paths, uint32_t* counters)
 {
     if (n == 0) return NRC_OK;
-    trace_carveout_once();
+    trace_carveout(ctx);
     static int lanesEnv = -1;
     if (lanesEnv < 0) {
         const char* e = getenv("NRC_TRAIN_LANES");   // training samples per warp (32; fewer = more, emptier warps: measured slower, profiles/r02_walks_in_flight.md)
