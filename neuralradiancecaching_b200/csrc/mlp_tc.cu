@@ -64,12 +64,8 @@ __device__ __forceinline__ void tc_store_chunk(uint4* hi, uint4* mid, uint4* lo,
 
 template <bool SPLIT>
 __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int r, int half, bool live, f3 p, f3 d,
-                                               const MrheDev& m, bool& nanIn04, unsigned short* gate0 = nullptr)
+                                               const MrheDev& m, bool& nanIn04)
 {
-    // gate0 (training): gate0[4 r + f / 16] bit f % 16 = (network input f > 0) on the fp32 value -- the layer-0 ReLU gate of the reference
-    // (the error of layer 1 is gated by the raw input features).  It cannot be read off the bf16 operand: OneBlob bins a few
-    // sigma away from the angle are fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.
-    unsigned gm = 0u, gb = 0u;
     nanIn04 = false;
     uint4* chunk = reinterpret_cast<uint4*>(aTile);   // chunk(kc, row) = chunk[kc * 128 + row]
     uint4* chunkM = reinterpret_cast<uint4*>(aMid);
@@ -103,8 +99,6 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, unsigned ch
             o[2 * li + 1] = o1;
         }
         if (half == 0 && g == 0) nanIn04 = (o[0] != o[0]) | (o[1] != o[1]) | (o[2] != o[2]) | (o[3] != o[3]) | (o[4] != o[4]);   // train.comp:993-999
-#pragma unroll
-        for (int j = 0; j < 8; j++) gm |= (o[j] > 0.0f ? 1u : 0u) << (8 * g + j);
         tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (2 * half + g) * TC_ROWS + r, o);
     }
     float ang;
@@ -125,13 +119,7 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, unsigned ch
             float t2 = NRC_DIV(NRC_SUB(fi, ang), sigma);
             o[i] = live ? NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2))) : 0.0f;
         }
-#pragma unroll
-        for (int i = 0; i < 8; i++) gb |= (o[i] > 0.0f ? 1u : 0u) << (8 * g + i);
         tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (4 + 2 * half + g) * TC_ROWS + r, o);
-    }
-    if (gate0) {
-        gate0[4 * r + half] = (unsigned short)gm;
-        gate0[4 * r + 2 + half] = (unsigned short)gb;
     }
 }
 
@@ -375,16 +363,10 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 #define TT_BAR (TT_GATE0 + 1024)
 #define TT_SMEM_BYTES (TT_BAR + 32)
 #define TT_HIST TT_ACT                             // after the last tile: the hash-gradient histogram (up to 128 KiB = TT_ACT .. TT_ET)
+#define TT_ONES TT_AT                              // 128 samples x 16 features, MN-major: feature 0 = 1 (bf16), the rest 0 (4 KB)
 #define TT_DW_COL(l) (64u + 80u * (uint32_t)(l))
 static_assert(TT_SMEM_BYTES <= 227 * 1024, "k_train_tc shared memory");
 static_assert(TT_HIST + NRC_HIST_MAX_T * 4 <= TT_ET, "histogram overlaps live buffers");
-
-__device__ __forceinline__ void tt_stage8k(unsigned char* dst, const __nv_bfloat16* __restrict__ src, int bytes)
-{
-    const uint4* s = reinterpret_cast<const uint4*>(src);
-    uint4* d = reinterpret_cast<uint4*>(dst);
-    for (int i = threadIdx.x; i < bytes / 16; i += TC_THREADS) d[i] = __ldg(s + i);
-}
 
 // Weight staging by ONE thread with bulk copies (cp.async.bulk, completion counted on an mbarrier): the other 255 threads go straight
 // to their epilogue instead of stalling on L2 loads (13 % of the kernel's stall samples in profiles/r02t were the staging loop).
@@ -406,13 +388,95 @@ __device__ __forceinline__ void tt_bulk_bwd(unsigned char* smem, const __nv_bflo
     bulk_load(smem + TT_WB, wimg + TC_IMG_T + ((l < 5) ? l * 4096 : 5 * 4096), bytes, barW);
 }
 
+// The network inputs of row r, split into hi / mid / lo tiles, by PARTS threads per row: thread `part` encodes 16 / PARTS MRHE levels and
+// 32 / PARTS OneBlob bins (tc_encode_half is the PARTS = 2, unsplit form of the inference kernels; same strict arithmetic, same values).
+// gate0[8 r + c] bit j = (network input 8 c + j > 0) on the fp32 value -- the layer-0 ReLU gate of the reference (the error of
+// layer 1 is gated by the raw input features).  It cannot be read off the bf16 operand: OneBlob bins a few sigma away from the angle are
+// fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.
+template <int PARTS>
+__device__ __forceinline__ void tt_encode(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int r, int part, bool live, f3 p, f3 d,
+                                          const MrheDev& m, bool& nanIn04, unsigned char* gate0)
+{
+    constexpr int HC = 4 / PARTS;   // chunks of 4 levels (8 hash features) and chunks of 8 bins per thread
+    nanIn04 = false;
+    uint4* chunk = reinterpret_cast<uint4*>(aTile);   // chunk(kc, row) = chunk[kc * 128 + row]
+    uint4* chunkM = reinterpret_cast<uint4*>(aMid);
+    uint4* chunkL = reinterpret_cast<uint4*>(aLo);
+    f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
+    f3 np = mrhe_norm_pos(p, sky);
+#pragma unroll
+    for (int g = 0; g < HC; g++) {
+        const int hc = HC * part + g;
+        float o[8];
+#pragma unroll
+        for (int li = 0; li < 4; li++) {
+            uint32_t level = 4 * hc + li;
+            float o0 = 0.0f, o1 = 0.0f;
+            if (live && level < m.L) {
+                uint32_t idx[8];
+                f3 lerp;
+                mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp, m.fixed != 0);
+                lerp = mrhe_blend_factors(lerp, m.fixed != 0);
+                const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
+                float f0[8], f1[8];
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    float2 v = __ldg(tab + idx[c]);
+                    f0[c] = v.x;
+                    f1[c] = v.y;
+                }
+                o0 = mrhe_blend(f0, lerp);
+                o1 = mrhe_blend(f1, lerp);
+            }
+            o[2 * li] = o0;
+            o[2 * li + 1] = o1;
+        }
+        if (hc == 0) nanIn04 = (o[0] != o[0]) | (o[1] != o[1]) | (o[2] != o[2]) | (o[3] != o[3]) | (o[4] != o[4]);   // train.comp:993-999
+        unsigned gm = 0u;
+#pragma unroll
+        for (int j = 0; j < 8; j++) gm |= (o[j] > 0.0f ? 1u : 0u) << j;
+        gate0[8 * r + hc] = (unsigned char)gm;
+        tc_store_chunk<true>(chunk, chunkM, chunkL, hc * TC_ROWS + r, o);
+    }
+    float ang;
+    if (HC * part < 2) {
+        ang = NRC_ADD(NRC_DIV(nrc_atan2(d.z, d.x), NRC_PI), 0.5f);
+    } else {
+        float lenxz = NRC_SQRT(NRC_ADD(NRC_MUL(d.x, d.x), NRC_MUL(d.z, d.z)));
+        ang = NRC_ADD(NRC_DIV(nrc_atan2(lenxz, d.y), NRC_PI), 0.5f);
+    }
+    const float sigma = 0.25f;
+    const float term1 = NRC_DIV(1.0f, NRC_MUL(sigma, NRC_SQRT(NRC_MUL(2.0f, NRC_PI))));
+#pragma unroll
+    for (int g = 0; g < HC; g++) {
+        const int bc = HC * part + g;
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            float fi = (float)(8 * (bc & 1) + i);
+            float t2 = NRC_DIV(NRC_SUB(fi, ang), sigma);
+            o[i] = live ? NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2))) : 0.0f;
+        }
+        unsigned gb = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; i++) gb |= (o[i] > 0.0f ? 1u : 0u) << i;
+        gate0[8 * r + 4 + bc] = (unsigned char)gb;
+        tc_store_chunk<true>(chunk, chunkM, chunkL, (4 + bc) * TC_ROWS + r, o);
+    }
+}
+
 // element (feature m, sample k) of a K=sample operand
 __device__ __forceinline__ void tt_store_t(unsigned char* base, uint32_t lbo, int m, int k, unsigned short v)
 {
     *reinterpret_cast<unsigned short*>(base + (k >> 3) * lbo + m * 16 + (k & 7) * 2) = v;
 }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restrict__ pos, const float* __restrict__ dir,
+// PARTS threads per sample row (2: 256 threads, each 32 accumulator columns / 8 levels; 4: 512 threads, 16 columns / 4 levels).  The
+// kernel is bound by the latency of its per-thread phases (encode gathers, epilogues, the scatter's shared-memory atomics: 20 % issue
+// utilisation with 8 warps per SM, profiles/r02t), so twice the warps nearly halve them.  512 threads need a whole register file and
+// wait for an empty SM: for batches of many tiles per CTA; inside a frame (one tile per CTA, beside the tracing kernels) PARTS = 2.
+template <int PARTS>
+__global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __restrict__ pos, const float* __restrict__ dir,
                                                             const float* __restrict__ target, size_t n, float scale,
                                                             const __nv_bfloat16* __restrict__ wimg, const float* __restrict__ params, MrheDev m,
                                                             float* __restrict__ partialAll, float* __restrict__ predOut, float* gAll,
@@ -427,17 +491,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + TT_BAR);
     uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(smem + TT_BAR + 8);
     uint64_t* barW = reinterpret_cast<uint64_t*>(smem + TT_BAR + 16);   // weight stages filled (bulk copies of thread 0)
-    unsigned short* gate0S = reinterpret_cast<unsigned short*>(smem + TT_GATE0);
+    unsigned char* gate0S = smem + TT_GATE0;
+    constexpr int THREADS = 128 * PARTS;
+    constexpr int COLS = 64 / PARTS;       // accumulator columns per thread
+    constexpr int CH = COLS / 8;           // 16-byte chunks (8 features) per thread
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int quad = warp & 3, half = warp >> 2;
+    const int quad = warp & 3, part = warp >> 2;   // TMEM lanes 32 quad .. +31 are this warp's; part = which COLS columns of them
     const int row = quad * 32 + lane;
     float* partial = partialAll + (size_t)blockIdx.x * NRC_PARTIAL_STRIDE;
 
     // ---- one-time setup ----
-    for (int i = tid; i < NRC_PARTIAL_STRIDE; i += TC_THREADS) partial[i] = 0.0f;
-    for (int i = tid; i < (TT_BIAS - TT_ET) / 16; i += TC_THREADS) reinterpret_cast<uint4*>(smem + TT_ET)[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (int i = tid; i < 336; i += TC_THREADS) biasS[i] = (i < 323) ? __ldg(params + NRC_B_OFF(0) + i) : 0.0f;
+    for (int i = tid; i < NRC_PARTIAL_STRIDE; i += THREADS) partial[i] = 0.0f;
+    for (int i = tid; i < (TT_BIAS - TT_ET) / 16; i += THREADS) reinterpret_cast<uint4*>(smem + TT_ET)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 336; i += THREADS) biasS[i] = (i < 323) ? __ldg(params + NRC_B_OFF(0) + i) : 0.0f;
     if (tid == 0) {
         mbar_init(bar, 1);
         mbar_init(barW, 1);
@@ -445,7 +512,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
     }
     if (warp == 0) tmem_alloc(tmemSlot, 512);
     __syncthreads();
-    if (tid < 128) tt_store_t(smem + TT_AT, TT_AT_LBO, 64, tid, 0x3F80u);   // the ones row of [A | 1]^T (bf16 1.0)
+    if (tid < 128) reinterpret_cast<uint4*>(smem + TT_ONES)[tid] = make_uint4(0x3F80u, 0u, 0u, 0u);   // [1 0 .. 0] per sample: column 64 = db
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -468,13 +535,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
         }
         // ---- encode into A_0 = hi + mid + lo (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
         bool nanFlag;
-        tc_encode_half<true>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, row, half, inRange, p, d, m, nanFlag, gate0S);
-        if (half == 0) dropS[row] = (!inRange || nanFlag) ? 1 : 0;
+        tt_encode<PARTS>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, row, part, inRange, p, d, m, nanFlag, gate0S);
+        if (part == 0) dropS[row] = (!inRange || nanFlag) ? 1 : 0;
         if (tid == 0) tt_bulk_fwd(smem, wimg, 0, barW);   // the forward stages are idle since the last tile's layer 5
         __syncthreads();
         const bool dropped = dropS[row] != 0;
         if (dropped) {   // a dropped sample contributes nothing: zero its inputs (its error rows are zeroed below)
-            for (int c = 4 * half; c < 4 * half + 4; c++) {
+            for (int c = CH * part; c < CH * part + CH; c++) {
                 reinterpret_cast<uint4*>(smem + TT_ACT)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
                 reinterpret_cast<uint4*>(smem + TT_AM)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
                 reinterpret_cast<uint4*>(smem + TT_AL)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
@@ -517,21 +584,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                 else tt_bulk_bwd(smem, wimg, 5, barW);     // W5^T: 64 rows x K 16
             }
             if (l < 5) {
-                uint32_t v[32];
-                tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
+                uint32_t v[COLS];
+                tmem_ld_cols<COLS>(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(part * COLS), v);
                 tmem_ld_wait();
-                const float* b = biasS + l * 64 + half * 32;
+                const float* b = biasS + l * 64 + part * COLS;
                 uint4* cH = reinterpret_cast<uint4*>(smem + TT_ACT + (l + 1) * 16384);
                 uint4* cM = reinterpret_cast<uint4*>(smem + TT_AM);
                 uint4* cL = reinterpret_cast<uint4*>(smem + TT_AL);
 #pragma unroll
-                for (int c = 0; c < 4; c++) {
+                for (int c = 0; c < CH; c++) {
                     float x[8];
 #pragma unroll
                     for (int j = 0; j < 8; j++) x[j] = fmaxf(__uint_as_float(v[8 * c + j]) + b[8 * c + j], 0.0f);
-                    tc_store_chunk<true>(cH, cM, cL, (4 * half + c) * TC_ROWS + row, x);
+                    tc_store_chunk<true>(cH, cM, cL, (CH * part + c) * TC_ROWS + row, x);
                 }
-            } else if (half == 0) {
+            } else if (part == 0) {
                 // ---- output, loss, output error with the layer-5 gate (train.comp:1002-1012, 746-749) ----
                 uint32_t v[4];
                 tmem_ld4(tmemBase + ((uint32_t)(quad * 32) << 16), v);
@@ -598,11 +665,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                 phaseW ^= 1u;
                 tc_fence_after();
                 if (L <= 4) {
-                    const uint32_t idw = umma_idesc(128, 80);
+                    // K = sample: E_{L+1} and A_L are read where they lie, as MN-major operands (8 features of one sample per 16 bytes,
+                    // 8 samples per 128-byte core matrix: leading offset 128 B between groups of 8 samples, stride 2048 B between
+                    // groups of 8 features).  M = 128 reads 64 features past the E tile: those accumulator lanes are never read.
+                    const uint32_t idw = umma_idesc(128, 64) | UMMA_A_MN | UMMA_B_MN, idb = umma_idesc(128, 16) | UMMA_A_MN | UMMA_B_MN;
 #pragma unroll
-                    for (int ks = 0; ks < 8; ks++)
-                        umma_bf16(tmemBase + TT_DW_COL(L), umma_desc(sBase + TT_ET + ks * 2 * TT_ET_LBO, TT_ET_LBO, 128),
-                                  umma_desc(sBase + TT_AT + ks * 2 * TT_AT_LBO, TT_AT_LBO, 128), idw, (firstTile && ks == 0) ? 0u : 1u);
+                    for (int ks = 0; ks < 8; ks++) {
+                        const uint64_t eT = umma_desc(sBase + TT_E + ks * 256, 128, 2048);
+                        umma_bf16(tmemBase + TT_DW_COL(L), eT, umma_desc(sBase + TT_ACT + L * 16384 + ks * 256, 128, 2048), idw,
+                                  (firstTile && ks == 0) ? 0u : 1u);
+                        umma_bf16(tmemBase + TT_DW_COL(L) + 64u, eT, umma_desc(sBase + TT_ONES + ks * 256, 128, 2048), idb,
+                                  (firstTile && ks == 0) ? 0u : 1u);
+                    }
                 }
                 const uint32_t idx = umma_idesc(TC_ROWS, 64);
                 const int ksteps = (L == 5) ? 1 : 4;
@@ -614,18 +688,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
             mbar_wait(bar, phase);
             phase ^= 1u;
             tc_fence_after();
-            uint32_t v[32];
-            tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * 32), v);
+            uint32_t v[COLS];
+            tmem_ld_cols<COLS>(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(part * COLS), v);
             tmem_ld_wait();
             if (L >= 1) {
                 if (tid == 0) tt_bulk_bwd(smem, wimg, L - 1, barW);
                 const uint4* aprev = reinterpret_cast<const uint4*>(smem + TT_ACT + (L - 1) * 16384);
                 uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
                 // gates: A_{L-1} > 0.  Hidden activations: the sign of the hi part; the network inputs (L == 1): the exact fp32 signs
-                const uint32_t g0 = (uint32_t)gate0S[4 * row + 2 * half] | ((uint32_t)gate0S[4 * row + 2 * half + 1] << 16);
 #pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    uint4 a = aprev[(4 * half + c) * TC_ROWS + row];       // A_{L-1}[row][32h + 8c .. +7]
+                for (int c = 0; c < CH; c++) {
+                    const uint32_t g0 = gate0S[8 * row + CH * part + c];
+                    uint4 a = aprev[(CH * part + c) * TC_ROWS + row];       // A_{L-1}[row][COLS part + 8c .. +7]
                     uint32_t aw[4] = {a.x, a.y, a.z, a.w};
                     uint32_t ew[4];
 #pragma unroll
@@ -633,23 +707,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
                         unsigned short alo = (unsigned short)(aw[j2] & 0xffffu), ahi = (unsigned short)(aw[j2] >> 16);
                         float elo = __uint_as_float(v[8 * c + 2 * j2]), ehi = __uint_as_float(v[8 * c + 2 * j2 + 1]);
                         bool openLo = (alo & 0x7fffu) != 0u && (alo & 0x8000u) == 0u, openHi = (ahi & 0x7fffu) != 0u && (ahi & 0x8000u) == 0u;
-                        if (L == 1) { openLo = (g0 >> (8 * c + 2 * j2)) & 1u; openHi = (g0 >> (8 * c + 2 * j2 + 1)) & 1u; }
+                        if (L == 1) { openLo = (g0 >> (2 * j2)) & 1u; openHi = (g0 >> (2 * j2 + 1)) & 1u; }
                         if (!openLo) elo = 0.0f;
                         if (!openHi) ehi = 0.0f;
                         ew[j2] = pack_bf16(elo, ehi);
-                        const int f = 32 * half + 8 * c + 2 * j2;
-                        tt_store_t(smem + TT_ET, TT_ET_LBO, f, row, (unsigned short)(ew[j2] & 0xffffu));
-                        tt_store_t(smem + TT_ET, TT_ET_LBO, f + 1, row, (unsigned short)(ew[j2] >> 16));
-                        tt_store_t(smem + TT_AT, TT_AT_LBO, f, row, alo);
-                        tt_store_t(smem + TT_AT, TT_AT_LBO, f + 1, row, ahi);
                     }
-                    echunk[(4 * half + c) * TC_ROWS + row] = make_uint4(ew[0], ew[1], ew[2], ew[3]);
+                    echunk[(CH * part + c) * TC_ROWS + row] = make_uint4(ew[0], ew[1], ew[2], ew[3]);
                 }
-            } else if (half == 0 && inRange) {
+            } else if (part * COLS < 32 && inRange) {
                 // dX_0: the hash encoding's gradient lives in features 0..31 -> this sample's scratch row (mrhe_scatter.cuh, phase 1)
-                float4* go = reinterpret_cast<float4*>(gAll + q * 32);
+                float4* go = reinterpret_cast<float4*>(gAll + q * 32 + part * COLS);
 #pragma unroll
-                for (int j = 0; j < 8; j++)
+                for (int j = 0; j < (COLS < 32 ? COLS : 32) / 4; j++)
                     go[j] = dropped ? make_float4(0.0f, 0.0f, 0.0f, 0.0f)
                                     : make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
                                                   __uint_as_float(v[4 * j + 3]));
@@ -660,7 +729,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
         }
     }
     // ---- hash-table gradient (BackpropMrhe, train.comp:947-983): phase 2, over all tiles of this CTA ----
-    mrhe_scatter_tiles<TC_ROWS>(pos, gAll, n, m, scale, histAll ? reinterpret_cast<float*>(smem + TT_HIST) : nullptr,
+    mrhe_scatter_tiles<TC_ROWS, THREADS>(pos, gAll, n, m, scale, histAll ? reinterpret_cast<float*>(smem + TT_HIST) : nullptr,
                                 histAll ? histAll + (size_t)blockIdx.x * m.T : nullptr);
     // ---- gradients out: TMEM -> this CTA's partial arena (negative gradient times ONE_OVER_PIXEL_COUNT, A8) ----
     tc_fence_after();
@@ -668,15 +737,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_train_tc(const float* __restr
         const int o = quad * 32 + lane;   // output feature = TMEM lane
 #pragma unroll 1
         for (int l = 0; l < 5; l++) {
-            uint32_t v[32];
-            tmem_ld32(tmemBase + ((uint32_t)(quad * 32) << 16) + TT_DW_COL(l) + (uint32_t)(half * 32), v);
+            uint32_t v[COLS];
+            tmem_ld_cols<COLS>(tmemBase + ((uint32_t)(quad * 32) << 16) + TT_DW_COL(l) + (uint32_t)(part * COLS), v);
             tmem_ld_wait();
-            float4* dst = reinterpret_cast<float4*>(partial + NRC_W_OFF(l) + o * 64 + half * 32);
+            float4* dst = reinterpret_cast<float4*>(partial + NRC_W_OFF(l) + o * 64 + part * COLS);
 #pragma unroll
-            for (int j = 0; j < 8; j++)
+            for (int j = 0; j < COLS / 4; j++)
                 dst[j] = make_float4(-__uint_as_float(v[4 * j]) * scale, -__uint_as_float(v[4 * j + 1]) * scale,
                                      -__uint_as_float(v[4 * j + 2]) * scale, -__uint_as_float(v[4 * j + 3]) * scale);
-            if (half == 1) {
+            if (part == PARTS - 1) {
                 uint32_t b[4];
                 tmem_ld4(tmemBase + ((uint32_t)(quad * 32) << 16) + TT_DW_COL(l) + 64u, b);
                 tmem_ld_wait();
@@ -705,7 +774,8 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     NRC_TRY(tc_prepare(mlp, st));
     static bool attr = false;
     if (!attr) {
-        NRC_CUDA(cudaFuncSetAttribute(k_train_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
         attr = true;
     }
     bool useHist = false;
@@ -715,11 +785,21 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     static int capEnv = -1;   // NRC_TRAIN_TC_BLOCKS: cap on the CTAs of the train kernel (experiments)
     if (capEnv < 0) { const char* e = getenv("NRC_TRAIN_TC_BLOCKS"); capEnv = e ? atoi(e) : 0; }
     if (capEnv > 0 && blocks > capEnv) blocks = capEnv;
-    NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
-               k_train_tc<<<blocks, TC_THREADS, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale,
-                                                                     reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16), mlp->params,
-                                                                     make_mrhe_dev(m), mlp->partial, pred, mlp->gScratch,
-                                                                     useHist ? mlp->histPartial : nullptr));
+    // 512 threads (four per sample) when every CTA has several tiles to itself: a stand-alone batch.  A frame's batch (10^4 samples,
+    // one tile per CTA) runs beside the tracing kernels, where a CTA that needs the whole register file would wait for an empty SM.
+    // NRC_TRAIN_TC_THREADS=256/512 forces one form (read at every launch: tests switch it).
+    bool wide = tiles >= 4 * (size_t)mlp->ctx->smCount;
+    if (const char* e = getenv("NRC_TRAIN_TC_THREADS")) wide = atoi(e) == 512;
+    const __nv_bfloat16* wimg = reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16);
+    float* hist = useHist ? mlp->histPartial : nullptr;
+    if (wide)
+        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
+                   k_train_tc<4><<<blocks, 512, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, make_mrhe_dev(m), mlp->partial,
+                                                                    pred, mlp->gScratch, hist));
+    else
+        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
+                   k_train_tc<2><<<blocks, 256, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, make_mrhe_dev(m), mlp->partial,
+                                                                    pred, mlp->gScratch, hist));
     if (deferred) { deferred[0] = blocks; deferred[1] = useHist ? 1 : 0; return NRC_OK; }
     return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }

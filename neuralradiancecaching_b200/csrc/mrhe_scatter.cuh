@@ -36,21 +36,21 @@ __device__ __forceinline__ float peers_sum(unsigned peers, float v)
     return s;
 }
 
-// ROWS samples per tile (64: fp32 kernel, 128: tcgen05 kernel), 256 threads: thread (row, part) owns 16 / (256 / ROWS) levels of its row.
+// ROWS samples per tile (64: fp32 kernel, 128: tcgen05 kernel), THREADS threads: thread (row, part) owns 16 / (THREADS / ROWS) levels of its row.
 // gAll[q][32]: dL/dx0 of the 32 hash features of sample q (zeros for dropped samples).  hist: shared memory, T floats (or nullptr:
 // global path).  histOut: this CTA's partial row in global memory (T floats), written when hist != nullptr.
-template <int ROWS>
+template <int ROWS, int THREADS = 256>
 __device__ __forceinline__ void mrhe_scatter_tiles(const float* __restrict__ pos, const float* gAll, size_t n, const MrheDev& m,
                                                    float scale, float* hist, float* __restrict__ histOut)
 {
-    constexpr int PARTS = 256 / ROWS;
+    constexpr int PARTS = THREADS / ROWS;
     constexpr int LEVELS = 16 / PARTS;
     const int tid = threadIdx.x;
     const int row = tid % ROWS, part = tid / ROWS;
     const size_t tiles = (n + ROWS - 1) / ROWS;
     const f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
     if (hist) {
-        for (uint32_t i = tid; i < m.T / 4; i += 256) reinterpret_cast<float4*>(hist)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        for (uint32_t i = tid; i < m.T / 4; i += THREADS) reinterpret_cast<float4*>(hist)[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         __syncthreads();
     }
     for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
@@ -127,6 +127,6 @@ __device__ __forceinline__ void mrhe_scatter_tiles(const float* __restrict__ pos
     }
     if (hist) {
         __syncthreads();
-        for (uint32_t i = tid; i < m.T / 4; i += 256) reinterpret_cast<float4*>(histOut)[i] = reinterpret_cast<const float4*>(hist)[i];
+        for (uint32_t i = tid; i < m.T / 4; i += THREADS) reinterpret_cast<float4*>(histOut)[i] = reinterpret_cast<const float4*>(hist)[i];
     }
 }

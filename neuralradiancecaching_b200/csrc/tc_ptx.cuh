@@ -112,6 +112,10 @@ __device__ __forceinline__ constexpr uint32_t umma_idesc(uint32_t M, uint32_t N)
     return (1u << 4) | (1u << 7) | (1u << 10) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
+// operand majorness bits of the instruction descriptor: set = MN-major (the M / N index is the contiguous one), clear = K-major
+#define UMMA_A_MN (1u << 15)
+#define UMMA_B_MN (1u << 16)
+
 // 32 lanes x 32 consecutive fp32 columns: thread = its lane's row
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v)
 {
@@ -125,6 +129,23 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v)
           "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
         : "r"(taddr)
         : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v)
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+// COLS = 32 or 16 consecutive columns
+template <int COLS>
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, uint32_t* v)
+{
+    if (COLS == 32) tmem_ld32(taddr, v); else tmem_ld16(taddr, v);
 }
 
 __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t* v)
