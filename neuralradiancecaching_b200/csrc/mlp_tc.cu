@@ -42,9 +42,6 @@ __global__ void __launch_bounds__(256) k_pack_bf16(const float* __restrict__ par
 #define TC_SMEM_BAR (TC_SMEM_BIAS + 336 * 4)      // mbarrier (8 B) + TMEM base slot (4 B)
 #define TC_SMEM_BYTES (TC_SMEM_BAR + 16)
 
-// Encode half of row `r`'s network inputs into the A tile (SPLIT: into the hi / mid / lo tiles).  half 0: MRHE levels 0-7 + OneBlob theta; half 1: levels
-// 8-15 + OneBlob phi.  Index arithmetic and blends are the strict ones (bit-identical hash indices); only the final
-// rounding to bf16 differs from the fp32 path.
 // 8 consecutive network inputs of one row as one 16-byte chunk: bf16 (SPLIT = false) or the three bf16 parts hi / mid / lo of the fp32
 // values into three tiles of the same layout (the split-precision forward pass of the train kernel)
 template <bool SPLIT>
@@ -62,47 +59,100 @@ __device__ __forceinline__ void tc_store_chunk(uint4* hi, uint4* mid, uint4* lo,
     lo[index] = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-template <bool SPLIT>
-__device__ __forceinline__ void tc_encode_half(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int r, int half, bool live, f3 p, f3 d,
-                                               const MrheDev& m, bool& nanIn04)
+// The network inputs of one tile (EncodeRay: fwd.frag:483-501, train.comp:703-713) into the A-operand image, by PARTS threads per query row
+// (2: the 256-thread kernels; 4: the 512-thread train kernel).  Neighbouring lanes (2j, 2j+1) share a row: lane parity = the x SIDE of
+// the cell.  Each lane gathers the four corners of its side (both features) and multiplies them by its side's factor; one
+// shuffle per corner pair hands the partner the product it needs, and each lane finishes ONE feature (parity = feature) through the y
+// and z stages.  The products, the sums and their order are those of mrhe_blend() (the first stage is a sum of two products and a + b
+// = b + a), so the encoded values are bit-identical to the one-thread form -- with half the hashes and blends per thread, and, because
+// the two sides of a corner pair are neighbouring table entries (mrhe_level_indices_side), half the 128-byte lines per load instruction:
+// the encoders are bound by L1 lines per load (~2 cycles per line, 32 lines for 32 scattered lanes), not by instructions.
+// A second round of shuffles pairs the two features of a level for the bf16x2 words: lane 0 of a pair assembles the chunks of the first
+// half of the pair's levels, lane 1 those of the second half.  OneBlob: PARTS slices of the 32 bins.
+//   SPLIT: three bf16 parts hi / mid / lo into three tiles (the train kernel's split-precision forward pass)
+//   GATES (training): gate0[8 r + c] bit j = (network input 8 c + j > 0) on the fp32 value -- the layer-0 ReLU gate of the reference
+//   (the error of layer 1 is gated by the raw input features).  It cannot be read off the bf16 operand: OneBlob bins a few
+//   sigma away from the angle are fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.  dropS[r] = row r is past
+//   n or has a NaN among its first five inputs (train.comp:993-999).
+// Every thread of the CTA must call this (full-warp shuffles).
+template <int PARTS, bool SPLIT, bool GATES>
+__device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int tid, size_t tileBase, size_t n,
+                                               const float* __restrict__ pos, const float* __restrict__ dir, const MrheDev& m,
+                                               unsigned char* gate0, int* dropS)
 {
-    nanIn04 = false;
+    constexpr int LV = 32 / PARTS;   // levels per lane pair: 16 or 8
+    constexpr int H = LV / 2;        // levels whose chunks one lane assembles
+    constexpr int BC = 4 / PARTS;    // OneBlob chunks (8 bins each) per thread
+    const int side = tid & 1, r = (tid >> 1) & (TC_ROWS - 1), lh = tid >> 8;
+    const size_t q = tileBase + (size_t)r;
+    const bool live = q < n;
+    f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
+    if (live) {
+        p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
+        d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
+    }
     uint4* chunk = reinterpret_cast<uint4*>(aTile);   // chunk(kc, row) = chunk[kc * 128 + row]
     uint4* chunkM = reinterpret_cast<uint4*>(aMid);
     uint4* chunkL = reinterpret_cast<uint4*>(aLo);
-    f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
-    f3 np = mrhe_norm_pos(p, sky);
+    const f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
+    const f3 np = mrhe_norm_pos(p, sky);
+    float o[LV];   // feature `side` of levels LV * lh + i
 #pragma unroll
-    for (int g = 0; g < 2; g++) {
-        float o[8];
+    for (int i = 0; i < LV; i++) {
+        const uint32_t level = LV * lh + i;
+        float2 f[4];
+        f3 lerp = mk3(0.0f, 0.0f, 0.0f);
 #pragma unroll
-        for (int li = 0; li < 4; li++) {
-            uint32_t level = 8 * half + 4 * g + li;
-            float o0 = 0.0f, o1 = 0.0f;
-            if (live && level < m.L) {
-                uint32_t idx[8];
-                f3 lerp;
-                mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp, m.fixed != 0);
-                lerp = mrhe_blend_factors(lerp, m.fixed != 0);
-                const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
-                float f0[8], f1[8];
+        for (int k = 0; k < 4; k++) f[k] = make_float2(0.0f, 0.0f);
+        if (live && level < m.L) {
+            uint32_t idx[4];
+            mrhe_level_indices_side(p, np, m.res[level], m.T, side, idx, lerp, m.fixed != 0);
+            lerp = mrhe_blend_factors(lerp, m.fixed != 0);
+            const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    float2 v = __ldg(tab + idx[c]);
-                    f0[c] = v.x;
-                    f1[c] = v.y;
-                }
-                o0 = mrhe_blend(f0, lerp);
-                o1 = mrhe_blend(f1, lerp);
-            }
-            o[2 * li] = o0;
-            o[2 * li + 1] = o1;
+            for (int k = 0; k < 4; k++) f[k] = __ldg(tab + idx[k]);
         }
-        if (half == 0 && g == 0) nanIn04 = (o[0] != o[0]) | (o[1] != o[1]) | (o[2] != o[2]) | (o[3] != o[3]) | (o[4] != o[4]);   // train.comp:993-999
-        tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (2 * half + g) * TC_ROWS + r, o);
+        // mrhe_blend(): z_k = f[x0 corner k] * (1 - l.z) + f[x1 corner k] * l.z, then y, then x
+        const float w = side ? lerp.z : NRC_SUB(1.0f, lerp.z);
+        float z[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const float a0 = NRC_MUL(f[k].x, w), a1 = NRC_MUL(f[k].y, w);
+            const float got = __shfl_xor_sync(0xffffffffu, side ? a0 : a1, 1);   // the partner's product for MY feature
+            z[k] = side ? NRC_ADD(got, a1) : NRC_ADD(a0, got);
+        }
+        const float iy = NRC_SUB(1.0f, lerp.y), ix = NRC_SUB(1.0f, lerp.x);
+        const float y0 = NRC_ADD(NRC_MUL(z[0], iy), NRC_MUL(z[2], lerp.y));
+        const float y1 = NRC_ADD(NRC_MUL(z[1], iy), NRC_MUL(z[3], lerp.y));
+        o[i] = NRC_ADD(NRC_MUL(y0, ix), NRC_MUL(y1, lerp.x));
     }
+    // pair the features: lane 0 keeps levels [0, H), lane 1 levels [H, LV)
+    float f0[H], f1[H];
+#pragma unroll
+    for (int j = 0; j < H; j++) {
+        const float got = __shfl_xor_sync(0xffffffffu, side ? o[j] : o[H + j], 1);
+        f0[j] = side ? got : o[j];
+        f1[j] = side ? o[H + j] : got;
+    }
+#pragma unroll
+    for (int g = 0; g < H / 4; g++) {
+        const int ci = lh * (LV / 4) + side * (H / 4) + g;   // chunk = levels 4 ci .. 4 ci + 3
+        float v[8];
+#pragma unroll
+        for (int li = 0; li < 4; li++) { v[2 * li] = f0[4 * g + li]; v[2 * li + 1] = f1[4 * g + li]; }
+        if (GATES) {
+            if (ci == 0) dropS[r] = (!live || (v[0] != v[0]) | (v[1] != v[1]) | (v[2] != v[2]) | (v[3] != v[3]) | (v[4] != v[4])) ? 1 : 0;
+            unsigned gm = 0u;
+#pragma unroll
+            for (int j = 0; j < 8; j++) gm |= (v[j] > 0.0f ? 1u : 0u) << j;
+            gate0[8 * r + ci] = (unsigned char)gm;
+        }
+        tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, ci * TC_ROWS + r, v);
+    }
+    // OneBlob (train.comp:344-365): slice bq of the 32 bins
+    const int bq = side + 2 * lh;
     float ang;
-    if (half == 0) {
+    if (BC * bq < 2) {
         ang = NRC_ADD(NRC_DIV(nrc_atan2(d.z, d.x), NRC_PI), 0.5f);
     } else {
         float lenxz = NRC_SQRT(NRC_ADD(NRC_MUL(d.x, d.x), NRC_MUL(d.z, d.z)));
@@ -111,15 +161,22 @@ __device__ __forceinline__ void tc_encode_half(unsigned char* aTile, unsigned ch
     const float sigma = 0.25f;
     const float term1 = NRC_DIV(1.0f, NRC_MUL(sigma, NRC_SQRT(NRC_MUL(2.0f, NRC_PI))));
 #pragma unroll
-    for (int g = 0; g < 2; g++) {
-        float o[8];
+    for (int g = 0; g < BC; g++) {
+        const int bc = BC * bq + g;
+        float v[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
-            float fi = (float)(8 * g + i);
+            float fi = (float)(8 * (bc & 1) + i);
             float t2 = NRC_DIV(NRC_SUB(fi, ang), sigma);
-            o[i] = live ? NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2))) : 0.0f;
+            v[i] = live ? NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2))) : 0.0f;
         }
-        tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (4 + 2 * half + g) * TC_ROWS + r, o);
+        if (GATES) {
+            unsigned gb = 0u;
+#pragma unroll
+            for (int i = 0; i < 8; i++) gb |= (v[i] > 0.0f ? 1u : 0u) << i;
+            gate0[8 * r + 4 + bc] = (unsigned char)gb;
+        }
+        tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (4 + bc) * TC_ROWS + r, v);
     }
 }
 
@@ -162,15 +219,9 @@ __global__ void __launch_bounds__(TC_THREADS, 3) k_infer_tc(const float* __restr
     if (countDev) { size_t c = *countDev; n = c < nMax ? c : nMax; }
     const size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
-        const size_t q = tile * TC_ROWS + row;
+        const size_t q = tile * TC_ROWS + row;   // the row this thread reads out of the accumulator
         const bool live = q < n;
-        f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
-        if (live) {
-            p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
-            d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
-        }
-        bool nanFlag;
-        tc_encode_half<false>(aTile, nullptr, nullptr, row, half, live, p, d, m, nanFlag);
+        tc_encode_pair<2, false, false>(aTile, nullptr, nullptr, tid, tile * TC_ROWS, n, pos, dir, m, nullptr, nullptr);
         fence_async_smem();
         tc_fence_before();
         __syncthreads();
@@ -269,21 +320,11 @@ __global__ void __launch_bounds__(TC_THREADS) k_encode_tiles(const float* __rest
                                                              const uint32_t* __restrict__ countDev, size_t nMax, MrheDev m,
                                                              unsigned char* __restrict__ featTiles)
 {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int row = (warp & 3) * 32 + lane, half = warp >> 2;
     size_t n = nMax;
     if (countDev) { size_t c = *countDev; n = c < nMax ? c : nMax; }
     const size_t tile = blockIdx.x;
     if (tile * TC_ROWS >= n) return;
-    const size_t q = tile * TC_ROWS + row;
-    const bool live = q < n;
-    f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
-    if (live) {
-        p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
-        d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
-    }
-    bool nanFlag;
-    tc_encode_half<false>(featTiles + tile * 16384, nullptr, nullptr, row, half, live, p, d, m, nanFlag);
+    tc_encode_pair<2, false, false>(featTiles + tile * 16384, nullptr, nullptr, (int)threadIdx.x, tile * TC_ROWS, n, pos, dir, m, nullptr, nullptr);
 }
 
 nrc_status launch_encode_tiles(nrc_mrhe* m, const float* pos, const float* dir, const uint32_t* countDev, size_t n, void* featTiles,
@@ -388,83 +429,6 @@ __device__ __forceinline__ void tt_bulk_bwd(unsigned char* smem, const __nv_bflo
     bulk_load(smem + TT_WB, wimg + TC_IMG_T + ((l < 5) ? l * 4096 : 5 * 4096), bytes, barW);
 }
 
-// The network inputs of row r, split into hi / mid / lo tiles, by PARTS threads per row: thread `part` encodes 16 / PARTS MRHE levels and
-// 32 / PARTS OneBlob bins (tc_encode_half is the PARTS = 2, unsplit form of the inference kernels; same strict arithmetic, same values).
-// gate0[8 r + c] bit j = (network input 8 c + j > 0) on the fp32 value -- the layer-0 ReLU gate of the reference (the error of
-// layer 1 is gated by the raw input features).  It cannot be read off the bf16 operand: OneBlob bins a few sigma away from the angle are
-// fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.
-template <int PARTS>
-__device__ __forceinline__ void tt_encode(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int r, int part, bool live, f3 p, f3 d,
-                                          const MrheDev& m, bool& nanIn04, unsigned char* gate0)
-{
-    constexpr int HC = 4 / PARTS;   // chunks of 4 levels (8 hash features) and chunks of 8 bins per thread
-    nanIn04 = false;
-    uint4* chunk = reinterpret_cast<uint4*>(aTile);   // chunk(kc, row) = chunk[kc * 128 + row]
-    uint4* chunkM = reinterpret_cast<uint4*>(aMid);
-    uint4* chunkL = reinterpret_cast<uint4*>(aLo);
-    f3 sky = mk3(m.skySize[0], m.skySize[1], m.skySize[2]);
-    f3 np = mrhe_norm_pos(p, sky);
-#pragma unroll
-    for (int g = 0; g < HC; g++) {
-        const int hc = HC * part + g;
-        float o[8];
-#pragma unroll
-        for (int li = 0; li < 4; li++) {
-            uint32_t level = 4 * hc + li;
-            float o0 = 0.0f, o1 = 0.0f;
-            if (live && level < m.L) {
-                uint32_t idx[8];
-                f3 lerp;
-                mrhe_level_indices(p, np, m.res[level], m.T, idx, lerp, m.fixed != 0);
-                lerp = mrhe_blend_factors(lerp, m.fixed != 0);
-                const float2* tab = reinterpret_cast<const float2*>(m.tables) + (size_t)level * m.T;
-                float f0[8], f1[8];
-#pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    float2 v = __ldg(tab + idx[c]);
-                    f0[c] = v.x;
-                    f1[c] = v.y;
-                }
-                o0 = mrhe_blend(f0, lerp);
-                o1 = mrhe_blend(f1, lerp);
-            }
-            o[2 * li] = o0;
-            o[2 * li + 1] = o1;
-        }
-        if (hc == 0) nanIn04 = (o[0] != o[0]) | (o[1] != o[1]) | (o[2] != o[2]) | (o[3] != o[3]) | (o[4] != o[4]);   // train.comp:993-999
-        unsigned gm = 0u;
-#pragma unroll
-        for (int j = 0; j < 8; j++) gm |= (o[j] > 0.0f ? 1u : 0u) << j;
-        gate0[8 * r + hc] = (unsigned char)gm;
-        tc_store_chunk<true>(chunk, chunkM, chunkL, hc * TC_ROWS + r, o);
-    }
-    float ang;
-    if (HC * part < 2) {
-        ang = NRC_ADD(NRC_DIV(nrc_atan2(d.z, d.x), NRC_PI), 0.5f);
-    } else {
-        float lenxz = NRC_SQRT(NRC_ADD(NRC_MUL(d.x, d.x), NRC_MUL(d.z, d.z)));
-        ang = NRC_ADD(NRC_DIV(nrc_atan2(lenxz, d.y), NRC_PI), 0.5f);
-    }
-    const float sigma = 0.25f;
-    const float term1 = NRC_DIV(1.0f, NRC_MUL(sigma, NRC_SQRT(NRC_MUL(2.0f, NRC_PI))));
-#pragma unroll
-    for (int g = 0; g < HC; g++) {
-        const int bc = HC * part + g;
-        float o[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            float fi = (float)(8 * (bc & 1) + i);
-            float t2 = NRC_DIV(NRC_SUB(fi, ang), sigma);
-            o[i] = live ? NRC_MUL(term1, nrc_exp(NRC_MUL(NRC_MUL(-0.5f, t2), t2))) : 0.0f;
-        }
-        unsigned gb = 0u;
-#pragma unroll
-        for (int i = 0; i < 8; i++) gb |= (o[i] > 0.0f ? 1u : 0u) << i;
-        gate0[8 * r + 4 + bc] = (unsigned char)gb;
-        tc_store_chunk<true>(chunk, chunkM, chunkL, (4 + bc) * TC_ROWS + r, o);
-    }
-}
-
 // element (feature m, sample k) of a K=sample operand
 __device__ __forceinline__ void tt_store_t(unsigned char* base, uint32_t lbo, int m, int k, unsigned short v)
 {
@@ -526,17 +490,10 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
     const size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     bool firstTile = true;
     for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, firstTile = false) {
-        const size_t q = tile * TC_ROWS + row;
+        const size_t q = tile * TC_ROWS + row;   // the sample whose accumulator row this thread reads
         const bool inRange = q < n;
-        f3 p = mk3(0.0f, 0.0f, 0.0f), d = mk3(0.0f, 0.0f, 1.0f);
-        if (inRange) {
-            p = mk3(__ldg(pos + 3 * q), __ldg(pos + 3 * q + 1), __ldg(pos + 3 * q + 2));
-            d = mk3(__ldg(dir + 3 * q), __ldg(dir + 3 * q + 1), __ldg(dir + 3 * q + 2));
-        }
         // ---- encode into A_0 = hi + mid + lo (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
-        bool nanFlag;
-        tt_encode<PARTS>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, row, part, inRange, p, d, m, nanFlag, gate0S);
-        if (part == 0) dropS[row] = (!inRange || nanFlag) ? 1 : 0;
+        tc_encode_pair<PARTS, true, true>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, tid, tile * TC_ROWS, n, pos, dir, m, gate0S, dropS);
         if (tid == 0) tt_bulk_fwd(smem, wimg, 0, barW);   // the forward stages are idle since the last tile's layer 5
         __syncthreads();
         const bool dropped = dropS[row] != 0;
