@@ -448,11 +448,10 @@ nrc_status launch_infer_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
     NRC_TRY(launch_mlp_prepare(mlp));
-    static bool attr = false;
+    static bool attr[64] = {};   // per device: function attributes belong to the device's context
     size_t smem = 3 * 4096 * sizeof(float);
-    if (!attr) {
+    if (first_on_device(mlp->ctx, attr)) {
         NRC_CUDA(cudaFuncSetAttribute(k_infer_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
     }
     size_t tiles = (n + TILE - 1) / TILE;
     size_t cap = (size_t)mlp->ctx->smCount * 4 * 4;   // 4 CTAs/SM resident, a few waves, grid-stride beyond
@@ -509,11 +508,10 @@ nrc_status launch_train_fp32(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const 
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
     NRC_TRY(launch_mlp_prepare(mlp));
-    static bool attr = false;
+    static bool attr[64] = {};   // per device: function attributes belong to the device's context
     size_t smem = TRAIN_SMEM_FLOATS * sizeof(float);
-    if (!attr) {
+    if (first_on_device(mlp->ctx, attr)) {
         NRC_CUDA(cudaFuncSetAttribute(k_train_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
     }
     bool useHist = false;
     NRC_TRY(train_scratch(mlp, m, n, &useHist));
@@ -578,11 +576,10 @@ extern "C" nrc_status nrc_train_accumulate_static(nrc_mlp* mlp, nrc_mrhe* m, con
     const bool useHist = !m->fixed && m->T <= NRC_STATIC_MAX_T && (m->T % 4u) == 0u;   // larger tables / fixed preset: global atomics
     cudaStream_t st = ctx->stream;
     NRC_TRY(launch_mlp_prepare(mlp));
-    static bool attr = false;
+    static bool attr[64] = {};   // per device: function attributes belong to the device's context
     const size_t smem = TRAIN_SMEM_FLOATS * sizeof(float);
-    if (!attr) {
+    if (first_on_device(mlp->ctx, attr)) {
         NRC_CUDA(cudaFuncSetAttribute(k_train_fp32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
     }
     const size_t tiles = (n + TILE - 1) / TILE;
     const int blocks = (int)(tiles < NRC_STATIC_MAX_BLOCKS ? tiles : NRC_STATIC_MAX_BLOCKS);

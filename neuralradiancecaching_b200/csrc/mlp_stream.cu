@@ -288,10 +288,9 @@ static int ms_slots()   // NRC_MLP_SLOTS: tiles in flight per CTA (read at every
 template <int S, int NSTAGE, int DBG>
 static nrc_status ms_launch(nrc_mlp* mlp, const void* featTiles, const uint32_t* countDev, size_t n, float* rgb, cudaStream_t st)
 {
-    static bool attr = false;
-    if (!attr) {
+    static bool attr[64] = {};   // per device: function attributes belong to the device's context
+    if (first_on_device(mlp->ctx, attr)) {
         NRC_CUDA(cudaFuncSetAttribute(k_mlp_stream<S, NSTAGE, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, MS_SMEM_BYTES(NSTAGE)));
-        attr = true;
     }
     size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     size_t cap = (size_t)mlp->ctx->smCount;   // persistent: one CTA per SM owns all 512 TMEM columns

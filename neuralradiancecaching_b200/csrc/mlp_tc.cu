@@ -75,6 +75,9 @@ __device__ __forceinline__ void tc_store_chunk(uint4* hi, uint4* mid, uint4* lo,
 //   sigma away from the angle are fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.  dropS[r] = row r is past
 //   n or has a NaN among its first five inputs (train.comp:993-999).
 // Every thread of the CTA must call this (full-warp shuffles).
+// Against one thread per half row (round 1's form): 104 M instead of 90.9 M warp instructions per frame in k_infer_tc (both lanes of a pair
+// set up the level) and still the faster one in the frame (2.760 / 2.762 against 2.775 / 2.779 ms in alternating runs), 0.128 -> 0.109 ms
+// for 2^18 scattered queries, k_encode_tiles 0.169 -> 0.139 ms at 2^19 (profiles/r02y_ncu_summary.md, r02t_train_tc.md).
 template <int PARTS, bool SPLIT, bool GATES>
 __device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int tid, size_t tileBase, size_t n,
                                                const float* __restrict__ pos, const float* __restrict__ dir, const MrheDev& m,
@@ -298,10 +301,9 @@ nrc_status launch_infer_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
     NRC_TRY(tc_prepare(mlp, st));
-    static bool attr = false;
-    if (!attr) {
+    static bool attr[64] = {};   // per device: function attributes belong to the device's context
+    if (first_on_device(mlp->ctx, attr)) {
         NRC_CUDA(cudaFuncSetAttribute(k_infer_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        attr = true;
     }
     size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     size_t cap = (size_t)mlp->ctx->smCount * 3;   // persistent: 3 CTAs per SM, grid-stride over the tiles (1 / 2 / 4 per SM: 2.87 / 2.78 / 2.78 ms per frame against 2.77)
@@ -729,11 +731,10 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     if (n == 0) return NRC_OK;
     NRC_REQUIRE(m->F == 2 && m->L <= 16, "MLP kernels need featureCount == 2 and levelCount <= 16");
     NRC_TRY(tc_prepare(mlp, st));
-    static bool attr = false;
-    if (!attr) {
+    static bool attr[64] = {};   // per device: function attributes belong to the device's context
+    if (first_on_device(mlp->ctx, attr)) {
         NRC_CUDA(cudaFuncSetAttribute(k_train_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
         NRC_CUDA(cudaFuncSetAttribute(k_train_tc<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
-        attr = true;
     }
     bool useHist = false;
     NRC_TRY(train_scratch(mlp, m, n, &useHist));

@@ -188,6 +188,16 @@ struct MrheDev {
     uint32_t res[16];
     float skySize[3];
 };
+// true the first time it is called for ctx's device with this flag array (one-time per-device setup such as cudaFuncSetAttribute)
+inline bool first_on_device(const nrc_ctx* ctx, bool (&done)[64])
+{
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64) return true;
+    if (done[dev]) return false;
+    done[dev] = true;
+    return true;
+}
+
 MrheDev make_mrhe_dev(const nrc_mrhe* m);
 
 // ---- helpers implemented in capi.cu ---------------------------------------------------------------
