@@ -172,6 +172,46 @@ def test_whole_frames_parity_and_partition(N, ctx):
     r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
 
 
+def test_ragged_sizes_parity(N, ctx):
+    """A frame whose width and height are no multiple of the render walk's 8 x 4 warp tile, a train grid that is no multiple of a warp,
+    and a strided partition whose row count is no multiple of 4: counters, queries and training records bit-exact against the oracle
+    (the ragged edges of every launch: partial tiles, partial warps, partial 128-row MLP tiles)."""
+    W, H, tw, th = 61, 37, 7, 5
+    cfg = Cm.scene_cfg(use_nn=1, aspect=W / H)
+    sc = Cm.oracle_scene(cfg)
+    sc.set_train_size(tw, th)
+    orgba, ocnt, oqry = sc.render(W, H)
+    orec, otc = sc.train_trace(tw, th)
+    r, nrc, m, vol = build(N, ctx, cfg, W, H, tw, th)
+    r.FrameRender()
+    ctx.sync()
+    cnt, qry = r.read_render_probes()
+    np.testing.assert_array_equal(cnt[..., 0], ocnt[..., 0])
+    np.testing.assert_array_equal(cnt[..., 1], ocnt[..., 1])
+    np.testing.assert_array_equal(cnt[..., 2], ocnt[..., 3])
+    np.testing.assert_array_equal(cnt[..., 3], oqry[..., 7].astype(np.uint32))
+    np.testing.assert_array_equal(qry[..., :6].view(np.uint32), oqry[..., :6].view(np.uint32))
+    full = r.read_frame().copy()
+    assert Cm.psnr(full, orgba) >= PSNR_MIN
+    r.FrameTrain()
+    ctx.sync()
+    rec, tc = r.read_train_probes()
+    np.testing.assert_array_equal(tc[:, 0], otc[:, 0])
+    np.testing.assert_array_equal(tc[:, 1], otc[:, 1])
+    np.testing.assert_array_equal(tc[:, 2], otc[:, 3])
+    np.testing.assert_array_equal(rec[:, :6].view(np.uint32), orec[:, :6].view(np.uint32))
+    # rank 1 of 3: rows 1, 4, ... (12 of 37 rows) and samples 1, 4, ... (12 of 35)
+    union = np.zeros_like(full)
+    for k in range(3):
+        r.SetPartitionStrided(k, 3, k, 3); r.FrameRender(); ctx.sync()
+        nrows = len(range(k, H, 3))
+        part = np.zeros((nrows, W, 4), np.float32)
+        r.read_frame_partition(part, N._lib.FRAME_RGBA32F)
+        union[k::3] = part
+    np.testing.assert_array_equal(union.view(np.uint32), full.view(np.uint32))
+    r.Destroy(); nrc.Destroy(); m.Destroy(); vol.Destroy()
+
+
 def test_resize_and_spp(N, ctx):
     cfg = Cm.scene_cfg(use_nn=0)
     r, nrc, m, vol = build(N, ctx, cfg, 32, 24, 4, 4)
