@@ -137,12 +137,15 @@ class Workload:
         self.r = N.NrcHpmRenderer(W, H, TW, TH, inp["cam"], self.vol, self.dl, self.pl, self.env, self.nrc, self.mrhe)
         if world > 1:
             self.r.SetPartitionStrided(rank, world, rank, world)
-        # Render vertex pool, vertices per path (NRC_BENCH_POOL; 0 = the library default of 4, grown and re-traced on overflow).  32 cannot
-        # overflow, so no read has to wait on the host for the overflow flag of the frame it hands out: e2e 2.93 instead of 3.00 ms/frame;
-        # 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are for.  Larger per-rank frames keep the library default.
-        self.pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "32" if (W * H // world) <= 2304 * 1296 else "0"))
-        if self.pool_per_path > 0:
+        # Render vertex pool, vertices per path.  Left to the library unless NRC_BENCH_POOL=n is set: it takes the worst case (32 per path:
+        # cannot overflow, so no frame waits on the host for its overflow flag; 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are
+        # for) when that is at most an eighth of the GPU's memory, else 4 per path with the deferred check (csrc/renderer.cu).
+        self.pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "0"))
+        self.pool_from_env = "NRC_BENCH_POOL" in os.environ
+        if self.pool_from_env and self.pool_per_path > 0:
             self.r.SetPoolCapacity(-(-H // world) * W * self.pool_per_path)      # the rank with the most rows
+        elif self.pool_from_env:
+            self.r.SetPoolCapacity(-(-H // world) * W * 4)                      # NRC_BENCH_POOL=0: force the small pool
         dev = torch.device("cuda", local)
         self.exchange = GradientExchange(ctx, self.nrc, self.mrhe, dev)
         self.ext = self.exchange.stream
@@ -547,6 +550,15 @@ FLOP_TRAIN = 124032.0        # forward + dW + dX per sample
 # ncu --set full capture of the default N=1 workload: DRAM bytes (read + write) and executed warp instructions per launch of every
 # frame kernel, read from the committed summary profiles/ncu_frame.json (written by scripts/ncu_summary.py --json from the capture named
 # in its "source"); only quoted when the run IS that workload.
+def vertex_pool_note(v):
+    """What the render vertex pool of the timed frames could hold, per path of this rank, and who chose it."""
+    my_rows = len(range(v["rank"], v["H"], v["world"]))
+    per_path = v["r"].GetPoolCapacity() / max(my_rows * v["W"], 1)
+    who = "NRC_BENCH_POOL" if "NRC_BENCH_POOL" in os.environ else "the library's choice"
+    return "%.0f vertices per path (%s)%s" % (per_path, who, ": worst case, cannot overflow, no host wait per frame" if per_path >= 32 else
+                                             ": a frame's overflow flag is read on the host before the next one is traced")
+
+
 def load_ncu_frame():
     try:
         d = json.load(open(os.path.join(ROOT, "profiles", "ncu_frame.json")))
@@ -764,7 +776,7 @@ def finish_b200(args, v):
                    "parallelism": "rows interleaved over %d GPU(s), train samples sharded, %s" % (
                        world, "gradients summed over NVLink peer memory inside the fused step kernel (sharded form for heads above 2^20 floats)" if (world > 1 and args.exchange == "fused")
                        else "NCCL all-reduce of gradients"),
-                   "vertex_pool": "%d vertices per path%s" % (v["pool_per_path"] or 4, " (worst case: cannot overflow)" if v["pool_per_path"] >= 32 else ""),
+                   "vertex_pool": vertex_pool_note(v),
                    "l2": "fresh per-frame RNG seed: every frame traces new paths; per-frame buffers (%.0f MB) exceed nothing but are rewritten, "
                          "the density grid (%s) %s" % (W * H * 120 / 1e6, "13 MB of bricks" if v["grid_scale"] == 1 else "838 MB of bricks",
                                                       "is L2-resident by design" if v["grid_scale"] == 1 else "does not fit L2: taps gather from HBM")},

@@ -258,10 +258,14 @@ NRC_API nrc_status nrc_renderer_set_partition(nrc_renderer* r, uint32_t y0, uint
 /* Interleaved partition for load balance (cloud pixels cluster mid-frame): this rank renders rows yFirst, yFirst+yStride, ...
  * and traces train invocations iFirst, iFirst+iStride, ...  (rank, worldSize, rank, worldSize) for data-parallel hosts. */
 NRC_API nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32_t yFirst, uint32_t yStride, uint32_t iFirst, uint32_t iStride);
-/* Initial capacity of the render vertex pool while the cache is on (0 = default: 4 vertices per path; the reference's
- * bound is 32 lit vertices per path, nrc-forward.frag:772-806, and a pool of that size cannot overflow).  A frame that
- * overflows a smaller pool is traced again with the worst-case pool before any read-back or nrc_sync returns. */
+/* Capacity of the render vertex pool while the cache is on.  The reference's bound is 32 lit vertices per path
+ * (nrc-forward.frag:772-806); a pool of that size cannot overflow.  0 = the library chooses: the worst-case pool when
+ * its two sets are at most an eighth of the GPU's memory (17 GB for a 1920x1080 frame at 1 spp), else 4 vertices per
+ * path.  A frame that overflows a smaller pool is traced again with the worst-case pool before any read-back or
+ * nrc_sync returns; the price of a smaller pool is one host wait per frame for the overflow flag. */
 NRC_API nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t vertices);
+/* the capacity the last frame was traced with (after the library's choice or a growth) */
+NRC_API nrc_status nrc_renderer_get_pool_capacity(nrc_renderer* r, uint64_t* vertices);
 /* Opt-in estimator, not the shipped behaviour: the env-map term of TraceScene in the training targets, commented out at
  * nrc-train.comp:1118 (SampleHdrEnvMap(pos, dir, 8) as in nrc-forward.frag:751-755).  Changes the train walk's RNG
  * consumption (16 more draws per lit vertex, before the two of NewRayDir). */

@@ -382,6 +382,7 @@ public:
     // initial capacity of the render vertex pool (0 = default); an overflowing frame is traced again before it is handed out
     void SetTrainEnvLight(bool on) { Check(nrc_renderer_set_train_env_light(m_Handle, on ? 1 : 0), "nrc_renderer_set_train_env_light"); }   // opt-in, train.comp:1118
     void SetPoolCapacity(uint64_t vertices) { Check(nrc_renderer_set_pool_capacity(m_Handle, vertices), "nrc_renderer_set_pool_capacity"); }
+    uint64_t GetPoolCapacity() const { uint64_t v = 0; Check(nrc_renderer_get_pool_capacity(m_Handle, &v), "nrc_renderer_get_pool_capacity"); return v; }
     void Destroy() { nrc_renderer_destroy(m_Handle); m_Handle = nullptr; }
     nrc_renderer* Get() const { return m_Handle; }
 private:

@@ -50,7 +50,7 @@ nrc_render nrc_frame_train nrc_frame_render nrc_frame_bytes nrc_frame_ptr nrc_re
 nrc_read_train_probes nrc_frame_stats nrc_frame_totals nrc_renderer_set_partition_strided nrc_read_frame_partition
 nrc_frame_partition_bytes nrc_kernel_count nrc_kernel_name nrc_selftest_strict_math
 nrc_ctx_profile_enable nrc_ctx_profile_read nrc_ctx_profile_timeline nrc_dp_handle_bytes nrc_dp_create nrc_dp_export
-nrc_renderer_set_pool_capacity nrc_renderer_set_train_env_light nrc_read_frame_partition_async nrc_readback_wait nrc_mlp_get_stats_async nrc_dp_connect nrc_dp_reduce_step nrc_dp_reduce_step_phase nrc_dp_status nrc_dp_destroy
+nrc_renderer_set_pool_capacity nrc_renderer_get_pool_capacity nrc_renderer_set_train_env_light nrc_read_frame_partition_async nrc_readback_wait nrc_mlp_get_stats_async nrc_dp_connect nrc_dp_reduce_step nrc_dp_reduce_step_phase nrc_dp_status nrc_dp_destroy
 nrc_ctx_set_infer_mode nrc_feature_tile_bytes nrc_encode_tiles nrc_mlp_forward_tiles
 nrc_mrhe_set_fixed_mode nrc_mlp_set_adam nrc_mrhe_set_adam
 nrc_mlp_get_adam_state nrc_mlp_set_adam_state nrc_mrhe_get_adam_state nrc_mrhe_set_adam_state

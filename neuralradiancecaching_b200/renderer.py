@@ -55,6 +55,12 @@ class NrcHpmRenderer:
         """Opt-in: env-map term in the training targets (train.comp:1118 has it commented out)."""
         L.check(L.lib().nrc_renderer_set_train_env_light(self.h, C.c_int(1 if on else 0)))
 
+    def GetPoolCapacity(self):
+        """Vertices the render pool of the last frame could hold (the library's choice unless SetPoolCapacity was called)."""
+        v = C.c_uint64(0)
+        L.check(L.lib().nrc_renderer_get_pool_capacity(self.h, C.byref(v)))
+        return int(v.value)
+
     def SetPoolCapacity(self, vertices):
         """Initial render vertex pool capacity (0 = default); an overflowing frame is redone with the worst-case pool."""
         L.check(L.lib().nrc_renderer_set_pool_capacity(self.h, C.c_uint64(vertices)))
