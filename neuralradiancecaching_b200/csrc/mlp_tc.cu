@@ -373,12 +373,14 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 //                                                              The hi part of every A_l stays in shared memory for the backward pass
 //                                                              (gates, dW operands); mid / lo live only until the next layer has read them.
 //   back-data E_l     = gate(E_{l+1} W_l)                      M=128 N=64 K=64, bf16, B = the TRANSPOSED weight image
-//   dW_l, db_l        = E_{l+1}^T [A_l | 1]                    M=128 (64 out rows + 64 zero rows) N=80 K=128 (the samples):
-//                                                              both operands are written transposed (K = sample) by the
-//                                                              epilogues; the accumulators of all five hidden layers live in
-//                                                              TMEM (5 x 80 columns) across ALL tiles of the CTA and are read
-//                                                              once at the end -> per-CTA partials, summed in fixed order by
-//                                                              k_reduce_partials.  No atomics on the MLP parameters.
+//   dW_l, db_l        = E_{l+1}^T [A_l | 1]                    M=128 (64 out rows; the other 64 lanes are never read) N=64 (+16 for db: a
+//                                                              constant ones tile) K=128 (the samples).  E_{l+1} and A_l are read WHERE
+//                                                              THEY LIE as MN-major operands (the feature index is the contiguous one
+//                                                              in the K-major tiles the other GEMMs use): no transposed copies.  The
+//                                                              accumulators of all five hidden layers live in TMEM (5 x 80 columns)
+//                                                              across ALL tiles of the CTA and are read once at the end -> per-CTA
+//                                                              partials, summed in fixed order by k_reduce_partials.  No atomics on the
+//                                                              MLP parameters.
 //   layer 5 (64 -> 3): forward and back-data on the tensor cores (N = 16 / K = 16 padded), dW5/db5 on CUDA cores.
 //   gates, loss, clamp, NaN guard: the reference's.
 //   hash-table gradient: dL/dx0 of every sample goes to a global scratch row; after the last tile the CTA scatters its samples into a
@@ -390,26 +392,23 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 #define TT_WF 0                                    // forward weight stages hi | mid | lo, 8 KB each
 #define TT_WB 24576                                // transposed weight stage (8 KB)
 #define TT_ACT 32768                               // A_0..A_5 (hi parts), 16 KB each, K-major (K = feature)
-#define TT_AM (TT_ACT + 6 * 16384)                 // mid part of the current layer's input
-#define TT_E (TT_AM + 16384)                       // E tile, K-major (K = feature): A operand of the back-data GEMM.  During the forward
-#define TT_AL TT_E                                 //   pass the same 16 KB hold the lo part of the current layer's input
-#define TT_ET_LBO (128 * 16 + 16)                  // padded so that the transposing 2-byte stores spread over the banks
-#define TT_ET (TT_E + 16384)                       // E^T, K = sample: 16 chunks x (128 rows x 16 B + pad)
-#define TT_AT_LBO (80 * 16 + 16)
-#define TT_AT (TT_ET + 16 * TT_ET_LBO)             // [A_l | 1]^T, K = sample: 16 chunks x (80 rows x 16 B + pad)
-#define TT_BIAS (TT_AT + 16 * TT_AT_LBO)           // 336 floats
+#define TT_E (TT_ACT + 6 * 16384)                  // E tile, K-major (K = feature): A operand of the back-data GEMM and, read MN-major, of the
+#define TT_AL TT_E                                 //   dW GEMMs.  During the forward pass the same 16 KB hold the lo part of the layer's input
+#define TT_AM (TT_E + 16384)                       // mid part of the current layer's input.  The dW GEMMs' M = 128 reads 64 feature rows past
+                                                   //   the E tile (lanes nobody reads): they fall into this tile, inside the allocation
+#define TT_ONES (TT_AM + 16384)                    // 128 samples x 16 features, MN-major: feature 0 = 1 (bf16), the rest 0 (4 KB): db = E^T 1
+#define TT_BIAS (TT_ONES + 4096)                   // 336 floats
 #define TT_E6 (TT_BIAS + 336 * 4)                  // [128][4] fp32 output errors
 #define TT_PRED (TT_E6 + 2048)                     // [128][4] fp32 predictions
 #define TT_DROP (TT_PRED + 2048)                   // [128] int
 #define TT_LOSS (TT_DROP + 512)                    // [8] float
-#define TT_GATE0 (TT_LOSS + 64)                    // [128][4] ushort: sign bits of the 64 fp32 network inputs (layer-0 gate)
+#define TT_GATE0 (TT_LOSS + 64)                    // [128][8] bytes: (input > 0) bits of the 64 fp32 network inputs (layer-0 gate)
 #define TT_BAR (TT_GATE0 + 1024)
 #define TT_SMEM_BYTES (TT_BAR + 32)
-#define TT_HIST TT_ACT                             // after the last tile: the hash-gradient histogram (up to 128 KiB = TT_ACT .. TT_ET)
-#define TT_ONES TT_AT                              // 128 samples x 16 features, MN-major: feature 0 = 1 (bf16), the rest 0 (4 KB)
+#define TT_HIST TT_ACT                             // after the last tile: the hash-gradient histogram (up to 128 KiB = TT_ACT .. TT_ONES)
 #define TT_DW_COL(l) (64u + 80u * (uint32_t)(l))
 static_assert(TT_SMEM_BYTES <= 227 * 1024, "k_train_tc shared memory");
-static_assert(TT_HIST + NRC_HIST_MAX_T * 4 <= TT_ET, "histogram overlaps live buffers");
+static_assert(TT_HIST + NRC_HIST_MAX_T * 4 <= TT_ONES, "histogram overlaps live buffers");
 
 // Weight staging by ONE thread with bulk copies (cp.async.bulk, completion counted on an mbarrier): the other 255 threads go straight
 // to their epilogue instead of stalling on L2 loads (13 % of the kernel's stall samples in profiles/r02t were the staging loop).
@@ -429,12 +428,6 @@ __device__ __forceinline__ void tt_bulk_bwd(unsigned char* smem, const __nv_bflo
     const uint32_t bytes = (l < 5) ? 8192u : 2048u;
     mbar_expect_tx(barW, bytes);
     bulk_load(smem + TT_WB, wimg + TC_IMG_T + ((l < 5) ? l * 4096 : 5 * 4096), bytes, barW);
-}
-
-// element (feature m, sample k) of a K=sample operand
-__device__ __forceinline__ void tt_store_t(unsigned char* base, uint32_t lbo, int m, int k, unsigned short v)
-{
-    *reinterpret_cast<unsigned short*>(base + (k >> 3) * lbo + m * 16 + (k & 7) * 2) = v;
 }
 
 // PARTS threads per sample row (2: 256 threads, each 32 accumulator columns / 8 levels; 4: 512 threads, 16 columns / 4 levels).  The
@@ -469,7 +462,7 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
 
     // ---- one-time setup ----
     for (int i = tid; i < NRC_PARTIAL_STRIDE; i += THREADS) partial[i] = 0.0f;
-    for (int i = tid; i < (TT_BIAS - TT_ET) / 16; i += THREADS) reinterpret_cast<uint4*>(smem + TT_ET)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 4096 / 16; i += THREADS) reinterpret_cast<uint4*>(smem + TT_ONES)[i] = make_uint4(0u, 0u, 0u, 0u);
     for (int i = tid; i < 336; i += THREADS) biasS[i] = (i < 323) ? __ldg(params + NRC_B_OFF(0) + i) : 0.0f;
     if (tid == 0) {
         mbar_init(bar, 1);
