@@ -22,6 +22,7 @@
 // the 1e-3 parity path.
 #include <cuda_bf16.h>
 #include <stdlib.h>
+#include <string.h>
 #include "nrc_internal.cuh"
 #include "strict.cuh"
 
@@ -74,11 +75,13 @@ __device__ __forceinline__ void tc_store_chunk(uint4* hi, uint4* mid, uint4* lo,
 //   (the error of layer 1 is gated by the raw input features).  It cannot be read off the bf16 operand: OneBlob bins a few
 //   sigma away from the angle are fp32 denormals (> 0) that round to +0 in bf16, for ~20 % of all directions.  dropS[r] = row r is past
 //   n or has a NaN among its first five inputs (train.comp:993-999).
-// Every thread of the CTA must call this (full-warp shuffles).
+//   ZERO (training, PARTS = 2): a dropped row's inputs are stored as zeros right here (the drop decision travels to the pair's other
+//   lane by one more shuffle); without it the caller zeroes the rows after a barrier.
+// Every thread of the CTA (of the calling warps) must call this (full-warp shuffles).
 // Against one thread per half row (round 1's form): 104 M instead of 90.9 M warp instructions per frame in k_infer_tc (both lanes of a pair
 // set up the level) and still the faster one in the frame (2.760 / 2.762 against 2.775 / 2.779 ms in alternating runs), 0.128 -> 0.109 ms
 // for 2^18 scattered queries, k_encode_tiles 0.169 -> 0.139 ms at 2^19 (profiles/r02y_ncu_summary.md, r02t_train_tc.md).
-template <int PARTS, bool SPLIT, bool GATES>
+template <int PARTS, bool SPLIT, bool GATES, bool ZERO = false>
 __device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned char* aMid, unsigned char* aLo, int tid, size_t tileBase, size_t n,
                                                const float* __restrict__ pos, const float* __restrict__ dir, const MrheDev& m,
                                                unsigned char* gate0, int* dropS)
@@ -86,6 +89,7 @@ __device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned ch
     constexpr int LV = 32 / PARTS;   // levels per lane pair: 16 or 8
     constexpr int H = LV / 2;        // levels whose chunks one lane assembles
     constexpr int BC = 4 / PARTS;    // OneBlob chunks (8 bins each) per thread
+    static_assert(!ZERO || (PARTS == 2 && GATES), "ZERO: both lanes of a row's pair are in one warp");
     const int side = tid & 1, r = (tid >> 1) & (TC_ROWS - 1), lh = tid >> 8;
     const size_t q = tileBase + (size_t)r;
     const bool live = q < n;
@@ -137,6 +141,12 @@ __device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned ch
         f0[j] = side ? got : o[j];
         f1[j] = side ? o[H + j] : got;
     }
+    bool drop = false;   // ZERO: this row is past n or has a NaN among its first five inputs (lane 0 of the pair holds them)
+    if (ZERO) {
+        int d0 = (!live || (f0[0] != f0[0]) | (f1[0] != f1[0]) | (f0[1] != f0[1]) | (f1[1] != f1[1]) | (f0[2] != f0[2])) ? 1 : 0;
+        drop = __shfl_sync(0xffffffffu, d0, (tid & 31) & ~1) != 0;
+        if (side == 0) dropS[r] = drop ? 1 : 0;
+    }
 #pragma unroll
     for (int g = 0; g < H / 4; g++) {
         const int ci = lh * (LV / 4) + side * (H / 4) + g;   // chunk = levels 4 ci .. 4 ci + 3
@@ -144,11 +154,15 @@ __device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned ch
 #pragma unroll
         for (int li = 0; li < 4; li++) { v[2 * li] = f0[4 * g + li]; v[2 * li + 1] = f1[4 * g + li]; }
         if (GATES) {
-            if (ci == 0) dropS[r] = (!live || (v[0] != v[0]) | (v[1] != v[1]) | (v[2] != v[2]) | (v[3] != v[3]) | (v[4] != v[4])) ? 1 : 0;
+            if (!ZERO && ci == 0) dropS[r] = (!live || (v[0] != v[0]) | (v[1] != v[1]) | (v[2] != v[2]) | (v[3] != v[3]) | (v[4] != v[4])) ? 1 : 0;
             unsigned gm = 0u;
 #pragma unroll
             for (int j = 0; j < 8; j++) gm |= (v[j] > 0.0f ? 1u : 0u) << j;
             gate0[8 * r + ci] = (unsigned char)gm;
+        }
+        if (ZERO && drop) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = 0.0f;
         }
         tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, ci * TC_ROWS + r, v);
     }
@@ -178,6 +192,10 @@ __device__ __forceinline__ void tc_encode_pair(unsigned char* aTile, unsigned ch
 #pragma unroll
             for (int i = 0; i < 8; i++) gb |= (v[i] > 0.0f ? 1u : 0u) << i;
             gate0[8 * r + 4 + bc] = (unsigned char)gb;
+        }
+        if (ZERO && drop) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = 0.0f;
         }
         tc_store_chunk<SPLIT>(chunk, chunkM, chunkL, (4 + bc) * TC_ROWS + r, v);
     }
@@ -391,24 +409,37 @@ nrc_status launch_infer_split(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const
 
 #define TT_WF 0                                    // forward weight stages hi | mid | lo, 8 KB each
 #define TT_WB 24576                                // transposed weight stage (8 KB)
-#define TT_ACT 32768                               // A_0..A_5 (hi parts), 16 KB each, K-major (K = feature)
-#define TT_E (TT_ACT + 6 * 16384)                  // E tile, K-major (K = feature): A operand of the back-data GEMM and, read MN-major, of the
-#define TT_AL TT_E                                 //   dW GEMMs.  During the forward pass the same 16 KB hold the lo part of the layer's input
-#define TT_AM (TT_E + 16384)                       // mid part of the current layer's input.  The dW GEMMs' M = 128 reads 64 feature rows past
-                                                   //   the E tile (lanes nobody reads): they fall into this tile, inside the allocation
-#define TT_ONES (TT_AM + 16384)                    // 128 samples x 16 features, MN-major: feature 0 = 1 (bf16), the rest 0 (4 KB): db = E^T 1
-#define TT_BIAS (TT_ONES + 4096)                   // 336 floats
-#define TT_E6 (TT_BIAS + 336 * 4)                  // [128][4] fp32 output errors
-#define TT_PRED (TT_E6 + 2048)                     // [128][4] fp32 predictions
-#define TT_DROP (TT_PRED + 2048)                   // [128] int
-#define TT_LOSS (TT_DROP + 512)                    // [8] float
-#define TT_GATE0 (TT_LOSS + 64)                    // [128][8] bytes: (input > 0) bits of the 64 fp32 network inputs (layer-0 gate)
-#define TT_BAR (TT_GATE0 + 1024)
-#define TT_SMEM_BYTES (TT_BAR + 32)
-#define TT_HIST TT_ACT                             // after the last tile: the hash-gradient histogram (up to 128 KiB = TT_ACT .. TT_ONES)
+// WS = the warp-specialised form (below): a second network-input set that the encoder warps fill while the first is in use
+template <bool WS>
+struct TT {
+    static constexpr uint32_t ACT1 = 32768;                        // A_1..A_5 (hi parts), 16 KB each, K-major (K = feature)
+    static constexpr uint32_t SET0 = ACT1 + 5 * 16384;             // the network inputs A_0 of a tile: hi | lo | mid, 16 KB each.  hi stays for the
+                                                                   //   backward pass (gates, dW_0 operand); mid / lo then carry the parts of every
+                                                                   //   layer's input, and lo becomes the E tile (K-major A operand of the back-data
+                                                                   //   GEMMs; read MN-major by the dW GEMMs, whose M = 128 runs 64 feature rows past
+                                                                   //   it into mid: lanes nobody reads, inside the allocation)
+    static constexpr uint32_t SET1 = SET0 + 49152;                 // WS only
+    static constexpr uint32_t ONES = WS ? SET1 + 49152 : SET1;     // 128 samples x 16 features, MN-major: feature 0 = 1 (bf16), the rest 0 (4 KB): db = E^T 1
+    static constexpr uint32_t BIAS = ONES + 4096;                  // 336 floats
+    static constexpr uint32_t E6 = BIAS + 336 * 4;                 // [128][4] fp32 output errors
+    static constexpr uint32_t PRED = E6 + 2048;                    // [128][4] fp32 predictions
+    static constexpr uint32_t DROP = PRED + 2048;                  // [2][128] int (one per input set)
+    static constexpr uint32_t LOSS = DROP + 1024;                  // [8] float
+    static constexpr uint32_t GATE0 = LOSS + 64;                   // [2][128][8] bytes: (input > 0) bits of the 64 fp32 network inputs (layer-0 gate)
+    static constexpr uint32_t BAR = GATE0 + 2048;
+    static constexpr uint32_t BYTES = BAR + 32;
+    static constexpr uint32_t HIST = ACT1;                         // after the last tile: the hash-gradient histogram (up to 128 KiB = A_1..A_5 + set 0)
+    static_assert(BYTES <= 227 * 1024, "k_train_tc shared memory");
+    static_assert(HIST + NRC_HIST_MAX_T * 4 <= SET1, "histogram overlaps live buffers");
+};
 #define TT_DW_COL(l) (64u + 80u * (uint32_t)(l))
-static_assert(TT_SMEM_BYTES <= 227 * 1024, "k_train_tc shared memory");
-static_assert(TT_HIST + NRC_HIST_MAX_T * 4 <= TT_ONES, "histogram overlaps live buffers");
+
+// named barriers of the warp-specialised form (0 is __syncthreads)
+#define TT_BAR_COMPUTE 1
+#define TT_BAR_FULL 2      // + set: the encoder warps have filled input set `set`
+#define TT_BAR_EMPTY 4     // + set: the compute warps are done with input set `set`
+__device__ __forceinline__ void named_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void named_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
 
 // Weight staging by ONE thread with bulk copies (cp.async.bulk, completion counted on an mbarrier): the other 255 threads go straight
 // to their epilogue instead of stalling on L2 loads (13 % of the kernel's stall samples in profiles/r02t were the staging loop).
@@ -430,28 +461,33 @@ __device__ __forceinline__ void tt_bulk_bwd(unsigned char* smem, const __nv_bflo
     bulk_load(smem + TT_WB, wimg + TC_IMG_T + ((l < 5) ? l * 4096 : 5 * 4096), bytes, barW);
 }
 
-// PARTS threads per sample row (2: 256 threads, each 32 accumulator columns / 8 levels; 4: 512 threads, 16 columns / 4 levels).  The
-// kernel is bound by the latency of its per-thread phases (encode gathers, epilogues, the scatter's shared-memory atomics: 20 % issue
-// utilisation with 8 warps per SM, profiles/r02t), so twice the warps nearly halve them.  512 threads need a whole register file and
-// wait for an empty SM: for batches of many tiles per CTA; inside a frame (one tile per CTA, beside the tracing kernels) PARTS = 2.
-template <int PARTS>
-__global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __restrict__ pos, const float* __restrict__ dir,
+// PARTS threads per sample row (2: 256 threads, each 32 accumulator columns / 8 levels; 4: 512 threads, 16 columns / 4 levels): the
+// scatter's shared-memory atomics are latency-bound and halve with twice the warps.
+// WS (with PARTS = 2): warp-specialised, 512 threads.  Threads 0-255 run the tile (forward, backward, dW5) exactly as in the plain form;
+// threads 256-511 ENCODE THE NEXT TILE meanwhile into the other of two input sets (a tile's encode is a third of its time and is bound
+// by gathered sectors from L2, the rest by issue slots and shared memory: they overlap).  Hand-over by named barriers: FULL[set]
+// (encoders arrive, compute warps wait), EMPTY[set] (compute warps arrive after their last read of the set, encoders wait before they
+// overwrite it two tiles later).  512-thread CTAs want most of a register file and wait for a nearly empty SM: both 512-thread forms are
+// for batches of many tiles per CTA; inside a frame (one tile per CTA, beside the tracing kernels) the plain 256-thread form runs.
+template <int PARTS, bool WS>
+__global__ void __launch_bounds__(WS ? 512 : 128 * PARTS, 1) k_train_tc(const float* __restrict__ pos, const float* __restrict__ dir,
                                                             const float* __restrict__ target, size_t n, float scale,
                                                             const __nv_bfloat16* __restrict__ wimg, const float* __restrict__ params, MrheDev m,
                                                             float* __restrict__ partialAll, float* __restrict__ predOut, float* gAll,
                                                             float* __restrict__ histAll)
 {
     extern __shared__ __align__(128) unsigned char smem[];
-    float* biasS = reinterpret_cast<float*>(smem + TT_BIAS);
-    float* e6S = reinterpret_cast<float*>(smem + TT_E6);
-    float* predS = reinterpret_cast<float*>(smem + TT_PRED);
-    int* dropS = reinterpret_cast<int*>(smem + TT_DROP);
-    float* lossS = reinterpret_cast<float*>(smem + TT_LOSS);
-    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + TT_BAR);
-    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(smem + TT_BAR + 8);
-    uint64_t* barW = reinterpret_cast<uint64_t*>(smem + TT_BAR + 16);   // weight stages filled (bulk copies of thread 0)
-    unsigned char* gate0S = smem + TT_GATE0;
-    constexpr int THREADS = 128 * PARTS;
+    static_assert(!WS || PARTS == 2, "the warp-specialised form computes with two threads per row");
+    using M = TT<WS>;
+    float* biasS = reinterpret_cast<float*>(smem + M::BIAS);
+    float* e6S = reinterpret_cast<float*>(smem + M::E6);
+    float* predS = reinterpret_cast<float*>(smem + M::PRED);
+    float* lossS = reinterpret_cast<float*>(smem + M::LOSS);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + M::BAR);
+    uint32_t* tmemSlot = reinterpret_cast<uint32_t*>(smem + M::BAR + 8);
+    uint64_t* barW = reinterpret_cast<uint64_t*>(smem + M::BAR + 16);   // weight stages filled (bulk copies of thread 0)
+    constexpr int CT = 128 * PARTS;              // threads that run the tile
+    constexpr int THREADS = WS ? 2 * CT : CT;    // all threads of the CTA
     constexpr int COLS = 64 / PARTS;       // accumulator columns per thread
     constexpr int CH = COLS / 8;           // 16-byte chunks (8 features) per thread
 
@@ -462,7 +498,7 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
 
     // ---- one-time setup ----
     for (int i = tid; i < NRC_PARTIAL_STRIDE; i += THREADS) partial[i] = 0.0f;
-    for (int i = tid; i < 4096 / 16; i += THREADS) reinterpret_cast<uint4*>(smem + TT_ONES)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 4096 / 16; i += THREADS) reinterpret_cast<uint4*>(smem + M::ONES)[i] = make_uint4(0u, 0u, 0u, 0u);
     for (int i = tid; i < 336; i += THREADS) biasS[i] = (i < 323) ? __ldg(params + NRC_B_OFF(0) + i) : 0.0f;
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -471,7 +507,7 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
     }
     if (warp == 0) tmem_alloc(tmemSlot, 512);
     __syncthreads();
-    if (tid < 128) reinterpret_cast<uint4*>(smem + TT_ONES)[tid] = make_uint4(0x3F80u, 0u, 0u, 0u);   // [1 0 .. 0] per sample: column 64 = db
+    if (tid < 128) reinterpret_cast<uint4*>(smem + M::ONES)[tid] = make_uint4(0x3F80u, 0u, 0u, 0u);   // [1 0 .. 0] per sample: column 64 = db
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
@@ -484,24 +520,48 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
 
     const size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     bool firstTile = true;
-    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, firstTile = false) {
+    uint32_t kTile = 0;   // this CTA's k-th tile: input set k & 1 in the warp-specialised form
+    if (WS && tid >= CT) {
+        // ---- encoder warps: tile k into set k & 1, one tile ahead of the compute warps ----
+        for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, kTile++) {
+            const uint32_t set = kTile & 1u, so = M::SET0 + set * 49152u;
+            if (kTile >= 2u) named_sync(TT_BAR_EMPTY + (int)set, THREADS);   // the tile that used this set two tiles ago is done with it
+            tc_encode_pair<2, true, true, true>(smem + so, smem + so + 32768, smem + so + 16384, tid - CT, tile * TC_ROWS, n, pos, dir, m,
+                                                smem + M::GATE0 + set * 1024u, reinterpret_cast<int*>(smem + M::DROP + set * 512u));
+            fence_async_smem();
+            named_arrive(TT_BAR_FULL + (int)set, THREADS);
+        }
+    } else
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, firstTile = false, kTile++) {
         const size_t q = tile * TC_ROWS + row;   // the sample whose accumulator row this thread reads
         const bool inRange = q < n;
-        // ---- encode into A_0 = hi + mid + lo (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
-        tc_encode_pair<PARTS, true, true>(smem + TT_ACT, smem + TT_AM, smem + TT_AL, tid, tile * TC_ROWS, n, pos, dir, m, gate0S, dropS);
+        const uint32_t set = WS ? (kTile & 1u) : 0u;
+        const uint32_t hiOff = M::SET0 + set * 49152u, loOff = hiOff + 16384u, midOff = hiOff + 32768u;   // lo doubles as the E tile
+        const int* dropS = reinterpret_cast<const int*>(smem + M::DROP + set * 512u);
+        const unsigned char* gate0S = smem + M::GATE0 + set * 1024u;
+        auto actOff = [&](int l) -> uint32_t { return l == 0 ? hiOff : M::ACT1 + (uint32_t)(l - 1) * 16384u; };   // hi part of A_l
         if (tid == 0) tt_bulk_fwd(smem, wimg, 0, barW);   // the forward stages are idle since the last tile's layer 5
-        __syncthreads();
-        const bool dropped = dropS[row] != 0;
-        if (dropped) {   // a dropped sample contributes nothing: zero its inputs (its error rows are zeroed below)
-            for (int c = CH * part; c < CH * part + CH; c++) {
-                reinterpret_cast<uint4*>(smem + TT_ACT)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
-                reinterpret_cast<uint4*>(smem + TT_AM)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
-                reinterpret_cast<uint4*>(smem + TT_AL)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+        bool dropped;
+        if (WS) {
+            named_sync(TT_BAR_FULL + (int)set, THREADS);   // the encoder warps have filled this set (dropped rows already zero)
+            dropped = dropS[row] != 0;
+        } else {
+            // ---- encode into A_0 = hi + mid + lo (EncodeRay, train.comp:703-713) + NaN guard (train.comp:993-999) ----
+            tc_encode_pair<PARTS, true, true, false>(smem + hiOff, smem + midOff, smem + loOff, tid, tile * TC_ROWS, n, pos, dir, m,
+                                                     smem + M::GATE0, reinterpret_cast<int*>(smem + M::DROP));
+            __syncthreads();
+            dropped = dropS[row] != 0;
+            if (dropped) {   // a dropped sample contributes nothing: zero its inputs (its error rows are zeroed below)
+                for (int c = CH * part; c < CH * part + CH; c++) {
+                    reinterpret_cast<uint4*>(smem + hiOff)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+                    reinterpret_cast<uint4*>(smem + midOff)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+                    reinterpret_cast<uint4*>(smem + loOff)[c * TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
+                }
             }
+            fence_async_smem();
+            tc_fence_before();
+            __syncthreads();
         }
-        fence_async_smem();
-        tc_fence_before();
-        __syncthreads();
         // ---- forward (train.comp:715-741), split precision ----
 #pragma unroll 1
         for (int l = 0; l < 6; l++) {
@@ -512,7 +572,7 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
                 const uint32_t nOut = (l < 5) ? 64u : 16u;
                 const uint32_t idesc = umma_idesc(TC_ROWS, nOut);
                 const uint32_t wLbo = nOut * 16u;
-                const uint32_t aH = sBase + TT_ACT + (uint32_t)l * 16384u, aM = sBase + TT_AM, aL = sBase + TT_AL;
+                const uint32_t aH = sBase + actOff(l), aM = sBase + midOff, aL = sBase + loOff;
                 const uint32_t wH = sBase + TT_WF, wM = wH + 8192u, wL = wH + 16384u;
 #pragma unroll
                 for (int ks = 0; ks < 4; ks++) {
@@ -540,9 +600,9 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
                 tmem_ld_cols<COLS>(tmemBase + ((uint32_t)(quad * 32) << 16) + (uint32_t)(part * COLS), v);
                 tmem_ld_wait();
                 const float* b = biasS + l * 64 + part * COLS;
-                uint4* cH = reinterpret_cast<uint4*>(smem + TT_ACT + (l + 1) * 16384);
-                uint4* cM = reinterpret_cast<uint4*>(smem + TT_AM);
-                uint4* cL = reinterpret_cast<uint4*>(smem + TT_AL);
+                uint4* cH = reinterpret_cast<uint4*>(smem + M::ACT1 + l * 16384);
+                uint4* cM = reinterpret_cast<uint4*>(smem + midOff);
+                uint4* cL = reinterpret_cast<uint4*>(smem + loOff);
 #pragma unroll
                 for (int c = 0; c < CH; c++) {
                     float x[8];
@@ -555,7 +615,7 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
                 uint32_t v[4];
                 tmem_ld4(tmemBase + ((uint32_t)(quad * 32) << 16), v);
                 tmem_ld_wait();
-                const unsigned short* a5 = reinterpret_cast<const unsigned short*>(smem + TT_ACT + 5 * 16384 + row * 16);   // features 0..7 of this row
+                const unsigned short* a5 = reinterpret_cast<const unsigned short*>(smem + M::ACT1 + 4 * 16384 + row * 16);   // features 0..7 of this row
                 float lsum = 0.0f, e[3];
 #pragma unroll
                 for (int j = 0; j < 3; j++) {
@@ -578,7 +638,7 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
                     for (int j = 0; j < 3; j++) predOut[3 * q + j] = predS[row * 4 + j];
                 }
                 // E_6 as the A operand of the layer-5 back-data GEMM (K = 16: two chunks); the lo part that lived here is dead
-                uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
+                uint4* echunk = reinterpret_cast<uint4*>(smem + loOff);
                 echunk[row] = make_uint4(pack_bf16(e[0], e[1]), pack_bf16(e[2], 0.0f), 0u, 0u);
                 echunk[TC_ROWS + row] = make_uint4(0u, 0u, 0u, 0u);
                 lsum = (lsum / 3.0f) * scale;
@@ -588,13 +648,13 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
             }
             fence_async_smem();
             tc_fence_before();
-            __syncthreads();
+            if (WS) named_sync(TT_BAR_COMPUTE, CT); else __syncthreads();
         }
         if (tid == 0) lossAcc += (lossS[0] + lossS[1]) + (lossS[2] + lossS[3]);
         // ---- dW5, db5 on the CUDA cores (Backprop5, train.comp:751-774): 192 + 3 threads, accumulated over the CTA's tiles ----
         if (tid < 192) {
             int c = tid & 63, j = tid >> 6;
-            const unsigned char* a5 = smem + TT_ACT + 5 * 16384 + (c >> 3) * 2048 + (c & 7) * 2;
+            const unsigned char* a5 = smem + M::ACT1 + 4 * 16384 + (c >> 3) * 2048 + (c & 7) * 2;
             float s = 0.0f;
 #pragma unroll 8
             for (int r = 0; r < TC_ROWS; r++)
@@ -623,17 +683,17 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
                     const uint32_t idw = umma_idesc(128, 64) | UMMA_A_MN | UMMA_B_MN, idb = umma_idesc(128, 16) | UMMA_A_MN | UMMA_B_MN;
 #pragma unroll
                     for (int ks = 0; ks < 8; ks++) {
-                        const uint64_t eT = umma_desc(sBase + TT_E + ks * 256, 128, 2048);
-                        umma_bf16(tmemBase + TT_DW_COL(L), eT, umma_desc(sBase + TT_ACT + L * 16384 + ks * 256, 128, 2048), idw,
+                        const uint64_t eT = umma_desc(sBase + loOff + ks * 256, 128, 2048);
+                        umma_bf16(tmemBase + TT_DW_COL(L), eT, umma_desc(sBase + actOff(L) + ks * 256, 128, 2048), idw,
                                   (firstTile && ks == 0) ? 0u : 1u);
-                        umma_bf16(tmemBase + TT_DW_COL(L) + 64u, eT, umma_desc(sBase + TT_ONES + ks * 256, 128, 2048), idb,
+                        umma_bf16(tmemBase + TT_DW_COL(L) + 64u, eT, umma_desc(sBase + M::ONES + ks * 256, 128, 2048), idb,
                                   (firstTile && ks == 0) ? 0u : 1u);
                     }
                 }
                 const uint32_t idx = umma_idesc(TC_ROWS, 64);
                 const int ksteps = (L == 5) ? 1 : 4;
                 for (int ks = 0; ks < ksteps; ks++)
-                    umma_bf16(tmemBase, umma_desc(sBase + TT_E + ks * 4096, 2048, 128), umma_desc(sBase + TT_WB + ks * 2048, 1024, 128), idx,
+                    umma_bf16(tmemBase, umma_desc(sBase + loOff + ks * 4096, 2048, 128), umma_desc(sBase + TT_WB + ks * 2048, 1024, 128), idx,
                               ks > 0 ? 1u : 0u);
                 umma_commit(bar);
             }
@@ -645,8 +705,8 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
             tmem_ld_wait();
             if (L >= 1) {
                 if (tid == 0) tt_bulk_bwd(smem, wimg, L - 1, barW);
-                const uint4* aprev = reinterpret_cast<const uint4*>(smem + TT_ACT + (L - 1) * 16384);
-                uint4* echunk = reinterpret_cast<uint4*>(smem + TT_E);
+                const uint4* aprev = reinterpret_cast<const uint4*>(smem + actOff(L - 1));
+                uint4* echunk = reinterpret_cast<uint4*>(smem + loOff);
                 // gates: A_{L-1} > 0.  Hidden activations: the sign of the hi part; the network inputs (L == 1): the exact fp32 signs
 #pragma unroll
                 for (int c = 0; c < CH; c++) {
@@ -677,15 +737,17 @@ __global__ void __launch_bounds__(128 * PARTS, 1) k_train_tc(const float* __rest
             }
             fence_async_smem();
             tc_fence_before();
-            __syncthreads();
+            if (WS) named_sync(TT_BAR_COMPUTE, CT); else __syncthreads();
         }
+        if (WS) named_arrive(TT_BAR_EMPTY + (int)set, THREADS);   // nothing of this tile reads its input set any more
     }
+    if (WS) __syncthreads();   // encoder and compute warps meet again: the histogram below overwrites the activations
     // ---- hash-table gradient (BackpropMrhe, train.comp:947-983): phase 2, over all tiles of this CTA ----
-    mrhe_scatter_tiles<TC_ROWS, THREADS>(pos, gAll, n, m, scale, histAll ? reinterpret_cast<float*>(smem + TT_HIST) : nullptr,
+    mrhe_scatter_tiles<TC_ROWS, THREADS>(pos, gAll, n, m, scale, histAll ? reinterpret_cast<float*>(smem + M::HIST) : nullptr,
                                 histAll ? histAll + (size_t)blockIdx.x * m.T : nullptr);
     // ---- gradients out: TMEM -> this CTA's partial arena (negative gradient times ONE_OVER_PIXEL_COUNT, A8) ----
     tc_fence_after();
-    if (quad < 2) {
+    if (tid < CT && quad < 2) {
         const int o = quad * 32 + lane;   // output feature = TMEM lane
 #pragma unroll 1
         for (int l = 0; l < 5; l++) {
@@ -726,8 +788,9 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     NRC_TRY(tc_prepare(mlp, st));
     static bool attr[64] = {};   // per device: function attributes belong to the device's context
     if (first_on_device(mlp->ctx, attr)) {
-        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
-        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TT_SMEM_BYTES));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TT<false>::BYTES));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TT<false>::BYTES));
+        NRC_CUDA(cudaFuncSetAttribute(k_train_tc<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TT<true>::BYTES));
     }
     bool useHist = false;
     NRC_TRY(train_scratch(mlp, m, n, &useHist));
@@ -736,21 +799,23 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     static int capEnv = -1;   // NRC_TRAIN_TC_BLOCKS: cap on the CTAs of the train kernel (experiments)
     if (capEnv < 0) { const char* e = getenv("NRC_TRAIN_TC_BLOCKS"); capEnv = e ? atoi(e) : 0; }
     if (capEnv > 0 && blocks > capEnv) blocks = capEnv;
-    // 512 threads (four per sample) when every CTA has several tiles to itself: a stand-alone batch.  A frame's batch (10^4 samples,
-    // one tile per CTA) runs beside the tracing kernels, where a CTA that needs the whole register file would wait for an empty SM.
-    // NRC_TRAIN_TC_THREADS=256/512 forces one form (read at every launch: tests switch it).
-    bool wide = tiles >= 4 * (size_t)mlp->ctx->smCount;
-    if (const char* e = getenv("NRC_TRAIN_TC_THREADS")) wide = atoi(e) == 512;
+    // The form: a frame's batch (10^4 samples, one tile per CTA) runs beside the tracing kernels, where a 512-thread CTA would wait for a
+    // nearly empty SM: plain, 256 threads.  A stand-alone batch with several tiles per CTA: warp-specialised (encoders one tile ahead).
+    // NRC_TRAIN_TC_FORM=256 / 512 / ws forces one (read at every launch: tests switch it).
+    int form = tiles >= 4 * (size_t)mlp->ctx->smCount ? 2 : 0;
+    if (const char* e = getenv("NRC_TRAIN_TC_FORM")) form = !strcmp(e, "ws") ? 2 : (atoi(e) == 512 ? 1 : 0);
     const __nv_bfloat16* wimg = reinterpret_cast<const __nv_bfloat16*>(mlp->paramsBf16);
     float* hist = useHist ? mlp->histPartial : nullptr;
-    if (wide)
-        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
-                   k_train_tc<4><<<blocks, 512, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, make_mrhe_dev(m), mlp->partial,
-                                                                    pred, mlp->gScratch, hist));
+    const MrheDev md = make_mrhe_dev(m);
+    if (form == 2)
+        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC, (k_train_tc<2, true><<<blocks, 512, TT<true>::BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, md,
+                                                                                                       mlp->partial, pred, mlp->gScratch, hist)));
+    else if (form == 1)
+        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC, (k_train_tc<4, false><<<blocks, 512, TT<false>::BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, md,
+                                                                                                         mlp->partial, pred, mlp->gScratch, hist)));
     else
-        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC,
-                   k_train_tc<2><<<blocks, 256, TT_SMEM_BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, make_mrhe_dev(m), mlp->partial,
-                                                                    pred, mlp->gScratch, hist));
+        NRC_LAUNCH(mlp->ctx, st, K_TRAIN_TC, (k_train_tc<2, false><<<blocks, 256, TT<false>::BYTES, st>>>(pos, dir, target, n, lossScale, wimg, mlp->params, md,
+                                                                                                         mlp->partial, pred, mlp->gScratch, hist)));
     if (deferred) { deferred[0] = blocks; deferred[1] = useHist ? 1 : 0; return NRC_OK; }
     return launch_reduce_partials(mlp, m, blocks, useHist, st);
 }

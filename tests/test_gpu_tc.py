@@ -102,10 +102,12 @@ def _cosine(a, b):
     return 1.0 if na == 0 and nb == 0 else float(a @ b / max(na * nb, 1e-300))
 
 
-@pytest.mark.parametrize("threads", [256, 512])     # two / four threads per sample row (csrc/mlp_tc.cu: k_train_tc<PARTS>); the launcher picks by batch size
+# the forms of csrc/mlp_tc.cu::k_train_tc: two / four threads per sample row, and the warp-specialised one (encoder warps a tile ahead); the
+# launcher picks by batch size
+@pytest.mark.parametrize("form", ["256", "512", "ws"])
 @pytest.mark.parametrize("n", [128, 3000, 1 << 15])
-def test_train_tc_gradients_match_oracle(N, ctx, n, threads, monkeypatch):
-    monkeypatch.setenv("NRC_TRAIN_TC_THREADS", str(threads))
+def test_train_tc_gradients_match_oracle(N, ctx, n, form, monkeypatch):
+    monkeypatch.setenv("NRC_TRAIN_TC_FORM", form)
     sc, nrc, m = _pair(N, ctx, 0.1)
     pos, d = Cm.rand_queries(n, seed=21 + n)
     g = np.random.Generator(np.random.PCG64(4))
@@ -140,10 +142,10 @@ def test_train_tc_gradients_match_oracle(N, ctx, n, threads, monkeypatch):
     nrc.Destroy(); m.Destroy()
 
 
-@pytest.mark.parametrize("threads", [256, 512])
-def test_tc_training_converges_like_fp32(N, ctx, threads, monkeypatch):
+@pytest.mark.parametrize("form", ["256", "512", "ws"])
+def test_tc_training_converges_like_fp32(N, ctx, form, monkeypatch):
     """40 optimiser steps on a fixed batch: the loss under the tensor-core path tracks the fp32 oracle's step by step."""
-    monkeypatch.setenv("NRC_TRAIN_TC_THREADS", str(threads))
+    monkeypatch.setenv("NRC_TRAIN_TC_FORM", form)
     sc, nrc, m = _pair(N, ctx, 0.1)
     n = 4096
     pos, d = Cm.rand_queries(n, seed=77)
