@@ -796,9 +796,6 @@ nrc_status launch_train_tc(nrc_mlp* mlp, nrc_mrhe* m, const float* pos, const fl
     NRC_TRY(train_scratch(mlp, m, n, &useHist));
     size_t tiles = (n + TC_ROWS - 1) / TC_ROWS;
     int blocks = (int)(tiles < (size_t)mlp->ctx->smCount ? tiles : (size_t)mlp->ctx->smCount);
-    static int capEnv = -1;   // NRC_TRAIN_TC_BLOCKS: cap on the CTAs of the train kernel (experiments)
-    if (capEnv < 0) { const char* e = getenv("NRC_TRAIN_TC_BLOCKS"); capEnv = e ? atoi(e) : 0; }
-    if (capEnv > 0 && blocks > capEnv) blocks = capEnv;
     // The form: a frame's batch (10^4 samples, one tile per CTA) runs beside the tracing kernels, where a 512-thread CTA would wait for a
     // nearly empty SM: plain, 256 threads.  A stand-alone batch with several tiles per CTA: warp-specialised (encoders one tile ahead).
     // NRC_TRAIN_TC_FORM=256 / 512 / ws forces one (read at every launch: tests switch it).

@@ -213,21 +213,15 @@ __device__ __forceinline__ void render_path_store(const TraceParams& P, RenderPa
 template <int MB>
 __global__ void __launch_bounds__(128, MB) k_render_walk(const __grid_constant__ TraceParams P, uint32_t y0, uint32_t rows, uint32_t ystride,
                                                      uint32_t spp, VertexPool pool, RenderPaths paths, float4* __restrict__ background,
-                                                     uint32_t* __restrict__ counters, int splitAt, int tiled)
+                                                     uint32_t* __restrict__ counters, int splitAt)
 {
     // A warp = an 8 x 4 tile of this rank's pixels (rows of the partition), not 32 pixels of one row: neighbouring paths in BOTH directions
-    // take similar walks, so fewer lanes idle through the marches (NRC_RWALK_TILE=0: the row-major mapping, for comparison).  Which lane
-    // walks which pixel changes nothing a pixel computes.
-    uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t px, prow;
-    if (tiled) {
-        const uint32_t tilesX = (P.width + 7u) >> 3, tile = local >> 5, lane = local & 31u;
-        px = (tile % tilesX) * 8u + (lane & 7u);
-        prow = (tile / tilesX) * 4u + (lane >> 3);
-    } else {
-        px = local % P.width;
-        prow = local / P.width;
-    }
+    // take similar walks, so fewer lanes idle through the marches (-0.5 % on the frame against the row-major mapping).  Which lane walks
+    // which pixel changes nothing a pixel computes.
+    const uint32_t local = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t tilesX = (P.width + 7u) >> 3, tile = local >> 5, lane = local & 31u;
+    const uint32_t px = (tile % tilesX) * 8u + (lane & 7u);
+    const uint32_t prow = (tile / tilesX) * 4u + (lane >> 3);
     if (px >= P.width || prow >= rows) return;
     uint32_t py = y0 + prow * ystride;
     size_t pix = (size_t)py * P.width + px;
@@ -313,17 +307,18 @@ __global__ void __launch_bounds__(128, MB) k_render_walk_tail(const __grid_const
 // frame slower (code removed).  The launch bound keeps the kernel at 64 registers.
 template <bool ENV>
 __global__ void __launch_bounds__(1024, 1) k_train_walk(const __grid_constant__ TraceParams P, uint32_t i0, uint32_t n, uint32_t istride,
-                                                        uint32_t lanes, VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
+                                                        VertexPool pool, TrainPaths paths, uint32_t* __restrict__ counters)
 {
+    // 32 samples per warp: fewer (more, emptier warps) lose -- the walk's time is instruction latency per warp, not divergence, and the
+    // extra warps compete with the render walk (profiles/r02_walks_in_flight.md)
     const uint32_t lane = threadIdx.x & 31u;
-    if (lane >= lanes) return;
     const uint32_t warpsPerBlock = blockDim.x >> 5;
-    const uint32_t totalWarps = (n + lanes - 1) / lanes;
+    const uint32_t totalWarps = (n + 31u) / 32u;
     const Box box = make_box(P);
     const Grid grid = make_grid(P);
     const WalkParams W = make_walk(P);
     for (uint32_t w = blockIdx.x * warpsPerBlock + (threadIdx.x >> 5); w < totalWarps; w += gridDim.x * warpsPerBlock) {
-    const uint32_t local = w * lanes + lane;
+    const uint32_t local = w * 32u + lane;
     if (local >= n) continue;
     ChunkEmitter em;
     em.pool = pool;
@@ -810,12 +805,10 @@ nrc_status launch_render_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& 
     // the caller zeroes *paths.spillCount on this stream before the call (renderer.cu: render_pass)
     const int split = (spp == 1 && paths.spill != nullptr && paths.spillStride >= n) ? splitEnv : 0;
     const unsigned blocks = (n + 127) / 128;   // the tail launch: one thread per spilled path
-    static int tiled = -1;
-    if (tiled < 0) { const char* e = getenv("NRC_RWALK_TILE"); tiled = e ? (atoi(e) != 0) : 1; }
-    const unsigned headBlocks = tiled ? (((P.width + 7u) / 8u) * ((rows + 3u) / 4u) * 32u + 127u) / 128u : blocks;
+    const unsigned headBlocks = (((P.width + 7u) / 8u) * ((rows + 3u) / 4u) * 32u + 127u) / 128u;   // the head launch: 8 x 4 pixel tiles
 #define RWALK_CASE(MBV)                                                                                                                    \
     NRC_LAUNCH(ctx, st, K_RENDER_WALK,                                                                                                     \
-               (k_render_walk<MBV><<<headBlocks, 128, 0, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split, tiled))); \
+               (k_render_walk<MBV><<<headBlocks, 128, 0, st>>>(P, y0, rows, ystride, spp, pool, paths, background, counters, split))); \
     if (split > 0)                                                                                                                         \
         NRC_LAUNCH(ctx, st, K_RENDER_WALK_TAIL, (k_render_walk_tail<MBV><<<blocks, 128, 0, st>>>(P, pool, paths, counters, split)));
     RWALK_CASE(8)   // 64 registers: 8 resident blocks, the fastest of the budgets tried (profiles/r01j)
@@ -828,23 +821,16 @@ nrc_status launch_train_walk(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P
 {
     if (n == 0) return NRC_OK;
     trace_carveout(ctx);
-    static int lanesEnv = -1;
-    if (lanesEnv < 0) {
-        const char* e = getenv("NRC_TRAIN_LANES");   // training samples per warp (32; fewer = more, emptier warps: measured slower, profiles/r02_walks_in_flight.md)
-        lanesEnv = e ? atoi(e) : 32;
-        if (lanesEnv < 1 || lanesEnv > 32) lanesEnv = 32;
-    }
-    const uint32_t lanes = (uint32_t)lanesEnv;
-    const uint32_t totalWarps = (n + lanes - 1) / lanes;
+    const uint32_t totalWarps = (n + 31u) / 32u;
     const uint32_t warpsPerBlock = 4;
     const uint32_t blocks = (totalWarps + warpsPerBlock - 1) / warpsPerBlock;
     const size_t smem = 0;
     if (pool.rnd != nullptr)   // the pool carries random numbers: env-map term in the training targets is on (renderer.cu)
         NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
-                   k_train_walk<true><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
+                   k_train_walk<true><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, pool, paths, counters));
     else
         NRC_LAUNCH(ctx, st, K_TRAIN_WALK,
-                   k_train_walk<false><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, lanes, pool, paths, counters));
+                   k_train_walk<false><<<blocks, 32 * warpsPerBlock, smem, st>>>(P, i0, n, istride, pool, paths, counters));
     return NRC_OK;
 }
 
