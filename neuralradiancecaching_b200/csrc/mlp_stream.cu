@@ -59,14 +59,6 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v)
 
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// relu(hi), relu(lo) rounded to nearest-even bf16, hi in the upper half
-__device__ __forceinline__ uint32_t pack_relu_bf16(float lo, float hi)
-{
-    uint32_t d;
-    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-    return d;
-}
-
 // issuer-side wait without the hardware suspend window of try_wait (5 threads per CTA poll; the wake-up is on the chain)
 __device__ __forceinline__ void mbar_spin(uint64_t* bar, uint32_t parity)
 {
@@ -82,20 +74,6 @@ __device__ __forceinline__ void mbar_spin(uint64_t* bar, uint32_t parity)
             : "r"(smem_u32(bar)), "r"(parity)
             : "memory");
     } while (!done);
-}
-
-// packed fp32 pair add (Blackwell FADD2): {a.x + b.x, a.y + b.y}
-__device__ __forceinline__ void add2(float& x0, float& x1, uint32_t a0, uint32_t a1, float b0, float b1)
-{
-    asm("{\n\t"
-        ".reg .b64 ra, rb, rc;\n\t"
-        "mov.b64 ra, {%2, %3};\n\t"
-        "mov.b64 rb, {%4, %5};\n\t"
-        "add.rn.f32x2 rc, ra, rb;\n\t"
-        "mov.b64 {%0, %1}, rc;\n\t"
-        "}"
-        : "=f"(x0), "=f"(x1)
-        : "r"(a0), "r"(a1), "f"(b0), "f"(b1));
 }
 
 // ---- shared-memory map ----------------------------------------------------------------------------------------------------
@@ -239,8 +217,8 @@ __global__ void __launch_bounds__(160 * S + 32, 1)
                             if (DBG & 2) { w[2 * c] = v[4 * c]; w[2 * c + 1] = v[4 * c + 2]; continue; }
                             float4 bb = b[c];
                             float x0, x1, x2, x3;
-                            add2(x0, x1, v[4 * c], v[4 * c + 1], bb.x, bb.y);
-                            add2(x2, x3, v[4 * c + 2], v[4 * c + 3], bb.z, bb.w);
+                            add2_bits(x0, x1, v[4 * c], v[4 * c + 1], bb.x, bb.y);
+                            add2_bits(x2, x3, v[4 * c + 2], v[4 * c + 3], bb.z, bb.w);
                             w[2 * c] = pack_relu_bf16(x0, x1);
                             w[2 * c + 1] = pack_relu_bf16(x2, x3);
                         }

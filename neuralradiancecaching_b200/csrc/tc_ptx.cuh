@@ -158,6 +158,28 @@ __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t* v)
 
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// relu(hi), relu(lo) rounded to nearest-even bf16, hi in the upper half
+__device__ __forceinline__ uint32_t pack_relu_bf16(float lo, float hi)
+{
+    uint32_t d;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+
+// packed fp32 pair add (Blackwell FADD2): {a.x + b.x, a.y + b.y}
+__device__ __forceinline__ void add2_bits(float& x0, float& x1, uint32_t a0, uint32_t a1, float b0, float b1)
+{
+    asm("{\n\t"
+        ".reg .b64 ra, rb, rc;\n\t"
+        "mov.b64 ra, {%2, %3};\n\t"
+        "mov.b64 rb, {%4, %5};\n\t"
+        "add.rn.f32x2 rc, ra, rb;\n\t"
+        "mov.b64 {%0, %1}, rc;\n\t"
+        "}"
+        : "=f"(x0), "=f"(x1)
+        : "r"(a0), "r"(a1), "f"(b0), "f"(b1));
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
 {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
