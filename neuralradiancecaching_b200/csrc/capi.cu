@@ -223,6 +223,8 @@ extern "C" nrc_status nrc_ctx_create(int device, nrc_ctx** out)
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainTrace, cudaEventDisableTiming));
     NRC_CUDA(cudaStreamCreateWithPriority(&c->stream4, cudaStreamNonBlocking, (prHigh + 1 <= prLow) ? prHigh + 1 : prHigh));
     NRC_CUDA(cudaStreamCreateWithFlags(&c->streamCopy, cudaStreamNonBlocking));
+    NRC_CUDA(cudaStreamCreateWithPriority(&c->stream5, cudaStreamNonBlocking, prLow));
+    NRC_CUDA(cudaEventCreateWithFlags(&c->evRenderWalk, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainWalk, cudaEventDisableTiming));
     for (int i = 0; i < NRC_TRAIN_SETS; i++) NRC_CUDA(cudaEventCreateWithFlags(&c->evTrainFree[i], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming));
@@ -239,6 +241,7 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaStreamSynchronize(c->stream2);
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) cudaStreamSynchronize(c->streamWalk[i]);
     cudaStreamSynchronize(c->stream4);
+    cudaStreamSynchronize(c->stream5);
     cudaStreamSynchronize(c->streamCopy);
     for (int i = 0; i < 6; i++) if (c->scratch[i]) cudaFree(c->scratch[i]);
     if (c->pinned) cudaFreeHost(c->pinned);
@@ -252,6 +255,8 @@ extern "C" nrc_status nrc_ctx_destroy(nrc_ctx* c)
     cudaEventDestroy(c->evTrainWalk);
     for (int i = 0; i < NRC_TRAIN_SETS; i++) cudaEventDestroy(c->evTrainFree[i]);
     cudaStreamDestroy(c->stream4);
+    cudaStreamDestroy(c->stream5);
+    cudaEventDestroy(c->evRenderWalk);
     cudaStreamDestroy(c->streamCopy);
     delete c;
     return NRC_OK;

@@ -64,6 +64,8 @@ struct nrc_ctx {
     cudaStream_t stream3 = nullptr;       // third stream: the train TRACE of frame k+1 (needs no weights) runs ahead of frame k's MLP tail
     cudaStream_t streamCopy = nullptr;    // asynchronous read-back of finished frames
     cudaEvent_t evJoin = nullptr;
+    cudaStream_t stream5 = nullptr;       // fifth stream: lights + combine of the render trace, beside the next frame's render walk (stream2)
+    cudaEvent_t evRenderWalk = nullptr;
     cudaStream_t stream4 = nullptr;       // fourth stream: lights + combine of the train trace, beside the next frame's walk
     cudaEvent_t evTrainTrace = nullptr, evTrainWalk = nullptr, evTrainFree[NRC_TRAIN_SETS] = {nullptr, nullptr, nullptr, nullptr};
     cudaStream_t streamWalk[NRC_TRAIN_WALK_STREAMS] = {nullptr, nullptr, nullptr};   // [0] = stream3: consecutive frames' train walks on alternating streams

@@ -241,6 +241,7 @@ extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
     cudaStreamSynchronize(r->ctx->stream2);
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) cudaStreamSynchronize(r->ctx->streamWalk[i]);
     cudaStreamSynchronize(r->ctx->stream4);
+    cudaStreamSynchronize(r->ctx->stream5);
     cudaStreamSynchronize(r->ctx->streamCopy);
     free_frame(r);
     free_train(r);
@@ -305,6 +306,7 @@ extern "C" nrc_status nrc_resize(nrc_renderer* r, uint32_t width, uint32_t heigh
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(r->ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->streamCopy));
     r->width = width; r->height = height;
     r->y0 = r->ystride > 1 ? r->y0 : 0; r->y1 = height;
@@ -323,6 +325,7 @@ extern "C" nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t v
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(r->ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->streamCopy));
     r->poolCapHint = (size_t)vertices;
     uint32_t spp = r->sppAlloc ? r->sppAlloc : 1;
@@ -342,6 +345,7 @@ extern "C" nrc_status nrc_renderer_set_train_env_light(nrc_renderer* r, int on)
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream2));
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(r->ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(r->ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(r->ctx->stream5));
     r->trainEnvLight = on != 0;
     for (int b = 0; b < NRC_TRAIN_SETS; b++) r->trainPending[b] = false;
     return alloc_train(r);
@@ -458,8 +462,10 @@ static nrc_status frame_train(nrc_renderer* r, int* deferred)
 
 static nrc_status drain_streams(nrc_ctx* ctx)
 {
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->streamCopy));
@@ -486,7 +492,17 @@ static nrc_status render_pass(nrc_renderer* r)
     NRC_CUDA(cudaMemsetAsync(sc + 4, 0, 2 * sizeof(uint32_t), s2));   // query count, spilled paths of the render walk
     NRC_CUDA(cudaMemsetAsync(tapc, 0, sizeof(unsigned long long), s2));
     NRC_TRY(launch_render_walk(ctx, s2, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->background, r->counters));
-    cudaStream_t sl = s2;
+    // Lights + combine on a stream of their own: the NEXT frame's render walk (stream2, other buffer set) runs beside this frame's
+    // lights.  The walk is bound by instruction issue and the lights by L1 gathers, so side by side they finish sooner than one after
+    // the other: 2.75 -> 2.65 ms at 1080p, 1.80 -> 1.71 ms at 720p (profiles/r02_carveout.md; NRC_RENDER_LIGHT_STREAM=0: one stream).
+    // Round 1 measured no gain from the same split -- with the tracing kernels still inheriting the MLP kernels' shared-memory carve-out.
+    static int lightStream = -1;
+    if (lightStream < 0) { const char* e = getenv("NRC_RENDER_LIGHT_STREAM"); lightStream = e ? (atoi(e) != 0) : 1; }
+    cudaStream_t sl = (lightStream && s2 != ctx->stream) ? ctx->stream5 : s2;
+    if (sl != s2) {
+        NRC_CUDA(cudaEventRecord(ctx->evRenderWalk, s2));
+        NRC_CUDA(cudaStreamWaitEvent(sl, ctx->evRenderWalk, 0));
+    }
     NRC_TRY(launch_light(ctx, sl, P, r->rpool, true, tapc, K_LIGHT_RENDER));
     NRC_TRY(launch_render_combine(ctx, sl, P, r->y0, rows, r->ystride, spp, r->rpool, r->rp, r->ql));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, sc, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, sl));
@@ -743,6 +759,7 @@ extern "C" nrc_status nrc_frame_totals(nrc_renderer* r, uint64_t totals[6], int 
     nrc_ctx* ctx = r->ctx;
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     unsigned long long t[6];
@@ -759,6 +776,7 @@ extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, u
     NRC_TRY(resolve_overflow(r, true));
     for (int i = 0; i < NRC_TRAIN_WALK_STREAMS; i++) NRC_CUDA(cudaStreamSynchronize(ctx->streamWalk[i]));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream4));
+    NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars + 8 * r->renderBuf, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
