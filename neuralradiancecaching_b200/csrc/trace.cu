@@ -839,7 +839,12 @@ nrc_status launch_light(nrc_ctx* ctx, cudaStream_t st, const TraceParams& P, Ver
 {
     // the vertex count lives on the device: a grid-stride launch sized for the machine, not for the count
     unsigned want = (pool.cap + 127) / 128;
-    unsigned cap = (unsigned)ctx->smCount * 16u;   // two waves of 8 resident blocks
+    // 64 blocks per SM (8 are resident at a time): the lights run beside the walks of other frames, and many short-lived blocks share the
+    // SMs with them more evenly than two waves of long-lived ones (16 per SM: 2.656 ms per 1080p frame; 32: 2.62; 64: 2.604; 128: 2.607;
+    // 8 and below lose).  NRC_LIGHT_BLOCKS_PER_SM=n overrides.
+    static int perSm = 0;
+    if (perSm == 0) { const char* le = getenv("NRC_LIGHT_BLOCKS_PER_SM"); perSm = le ? atoi(le) : 64; if (perSm < 1) perSm = 64; }
+    unsigned cap = (unsigned)ctx->smCount * (unsigned)perSm;
     unsigned blocks = want < cap ? want : cap;
     if (blocks == 0) return NRC_OK;
     if (render && P.envInvCdfX) NRC_LAUNCH(ctx, st, kid, (k_light<true, true><<<blocks, 128, 0, st>>>(P, pool, tapCounter)));
