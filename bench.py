@@ -138,8 +138,8 @@ class Workload:
         if world > 1:
             self.r.SetPartitionStrided(rank, world, rank, world)
         # Render vertex pool, vertices per path.  Left to the library unless NRC_BENCH_POOL=n is set: it takes the worst case (32 per path:
-        # cannot overflow, so no frame waits on the host for its overflow flag; 2 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are
-        # for) when that is at most an eighth of the GPU's memory, else 4 per path with the deferred check (csrc/renderer.cu).
+        # cannot overflow, so no frame waits on the host for its overflow flag; 3 x 8.5 GB of HBM per 1080p rank, which is what 180 GB are
+        # for) when that is at most a sixth of the GPU's memory, else 4 per path with the deferred check (csrc/renderer.cu).
         self.pool_per_path = int(os.environ.get("NRC_BENCH_POOL", "0"))
         self.pool_from_env = "NRC_BENCH_POOL" in os.environ
         if self.pool_from_env and self.pool_per_path > 0:

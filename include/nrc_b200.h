@@ -260,7 +260,7 @@ NRC_API nrc_status nrc_renderer_set_partition(nrc_renderer* r, uint32_t y0, uint
 NRC_API nrc_status nrc_renderer_set_partition_strided(nrc_renderer* r, uint32_t yFirst, uint32_t yStride, uint32_t iFirst, uint32_t iStride);
 /* Capacity of the render vertex pool while the cache is on.  The reference's bound is 32 lit vertices per path
  * (nrc-forward.frag:772-806); a pool of that size cannot overflow.  0 = the library chooses: the worst-case pool when
- * its two sets are at most an eighth of the GPU's memory (17 GB for a 1920x1080 frame at 1 spp), else 4 vertices per
+ * its three sets are at most a sixth of the GPU's memory (25.5 GB for a 1920x1080 frame at 1 spp), else 4 vertices per
  * path.  A frame that overflows a smaller pool is traced again with the worst-case pool before any read-back or
  * nrc_sync returns; the price of a smaller pool is one host wait per frame for the overflow flag. */
 NRC_API nrc_status nrc_renderer_set_pool_capacity(nrc_renderer* r, uint64_t vertices);

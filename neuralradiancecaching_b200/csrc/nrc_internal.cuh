@@ -51,6 +51,7 @@ struct NrcProfRec { int kid; cudaEvent_t a, b; };
 // The train trace (walk -> light -> combine) reads no weights, so consecutive frames' traces are independent of each other: up to
 // NRC_TRAIN_WALK_STREAMS train walks are in flight at once (a walk is ~300 warps of pure dependent latency, so several of them take
 // barely longer than one), each filling its own buffer set; a set is reused once the train kernel that read it has finished.
+#define NRC_RENDER_SETS 3          // buffer sets of the render trace: walk(k+2) beside light(k+1) beside inference / composite(k)
 #define NRC_TRAIN_SETS 4
 #define NRC_TRAIN_WALK_STREAMS 3
 nrc_status nrc_renderer_resolve_pending(nrc_renderer* r);   // renderer.cu

@@ -35,10 +35,10 @@ struct nrc_renderer {
     RenderPaths rp;
     VertexPool rpool;
     QueryList ql;
-    struct RenderSet { RenderPaths rp; VertexPool rpool; QueryList ql; float4* background; } rs[2];
+    struct RenderSet { RenderPaths rp; VertexPool rpool; QueryList ql; float4* background; } rs[NRC_RENDER_SETS];
     int renderBuf = 1;
-    bool setPending[2] = {false, false};  // evSetFree[b]: the composite that last read set b has finished
-    cudaEvent_t evSetFree[2] = {nullptr, nullptr};
+    bool setPending[NRC_RENDER_SETS] = {};  // evSetFree[b]: the composite that last read set b has finished
+    cudaEvent_t evSetFree[NRC_RENDER_SETS] = {};
     cudaEvent_t evScalars = nullptr;      // the last frame's device scalars have reached hostScalars
     bool overflowPending = false;         // the last frame used a pool below the worst case and its overflow flag is unread
     TraceParams lastP;                    // what the last frame was traced with (a redo after an overflow repeats it)
@@ -61,9 +61,9 @@ struct nrc_renderer {
     uint32_t* trainCountersB[NRC_TRAIN_SETS] = {nullptr, nullptr, nullptr, nullptr};   // per set: walks of different frames run concurrently
     uint32_t trainAlloc = 0;
     // device scalars, render set b at base 8*b: [0] vertex count, [1] overflow, [4] query count, [5] render-walk paths handed to the tail launch;
-    // train set b: {16 + 2b, 17 + 2b} = vertex count, overflow
+    // train set b: {32 + 2b, 33 + 2b} = vertex count, overflow
     uint32_t* scalars = nullptr;
-    unsigned long long* taps = nullptr;   // [0], [3] render taps of the two sets; [4 + b] train taps of set b
+    unsigned long long* taps = nullptr;   // [3 b] render taps of set b; [12 + b] train taps of set b
     unsigned long long* totals = nullptr; // [6] running totals (nrc_frame_totals)
     uint32_t* hostScalars = nullptr;      // pinned mirror
     unsigned long long* hostTaps = nullptr;
@@ -89,7 +89,7 @@ static nrc_status alloc_pool(VertexPool& p, uint32_t cap, bool withRnd, uint32_t
 static void free_frame(nrc_renderer* r)
 {
     FREE(r->frame); FREE(r->frame8); FREE(r->counters); FREE(r->queryProbe);
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < NRC_RENDER_SETS; b++) {
         nrc_renderer::RenderSet& S = r->rs[b];
         FREE(S.background);
         FREE(S.rp.head); FREE(S.rp.qposPhase); FREE(S.rp.qdirValid); FREE(S.rp.result); FREE(S.rp.qweight); FREE(S.rp.qslot); FREE(S.rp.spill);
@@ -123,7 +123,7 @@ static nrc_status alloc_frame(nrc_renderer* r, uint32_t spp, uint32_t poolCap)
     NRC_CUDA(cudaMemsetAsync(r->frame8, 0, px * sizeof(uint32_t), r->ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->counters, 0, px * 4 * sizeof(uint32_t), r->ctx->stream));
     NRC_CUDA(cudaMemsetAsync(r->queryProbe, 0, px * 8 * sizeof(float), r->ctx->stream));
-    for (int b = 0; b < 2; b++) {
+    for (int b = 0; b < NRC_RENDER_SETS; b++) {
         nrc_renderer::RenderSet& S = r->rs[b];
         NRC_CUDA(cudaMalloc(&S.background, px * sizeof(float4)));
         NRC_CUDA(cudaMalloc(&S.rp.head, paths * sizeof(int)));
@@ -180,7 +180,7 @@ static nrc_status alloc_train(nrc_renderer* r)
         NRC_CUDA(cudaMemsetAsync(tp.pos, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
         NRC_CUDA(cudaMemsetAsync(tp.dir, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
         NRC_CUDA(cudaMemsetAsync(tp.target, 0, (size_t)n * 3 * sizeof(float), r->ctx->stream));
-        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, r->trainEnvLight, r->scalars + 16 + 2 * b, r->scalars + 17 + 2 * b));
+        NRC_TRY(alloc_pool(r->tpoolb[b], (uint32_t)cap, r->trainEnvLight, r->scalars + 32 + 2 * b, r->scalars + 33 + 2 * b));
     }
     for (int b = 0; b < NRC_TRAIN_SETS; b++) {
         NRC_CUDA(cudaMalloc(&r->trainCountersB[b], (size_t)n * 4 * sizeof(uint32_t)));
@@ -210,21 +210,21 @@ extern "C" nrc_status nrc_renderer_create(nrc_ctx* ctx, uint32_t width, uint32_t
     memset(&r->rp, 0, sizeof(r->rp)); memset(&r->rpool, 0, sizeof(r->rpool)); memset(&r->ql, 0, sizeof(r->ql));
     memset(&r->tp, 0, sizeof(r->tp)); memset(&r->tpool, 0, sizeof(r->tpool));
     memset(r->tpb, 0, sizeof(r->tpb)); memset(r->tpoolb, 0, sizeof(r->tpoolb));
-    NRC_CUDA(cudaMalloc(&r->scalars, 32 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMalloc(&r->taps, 8 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMalloc(&r->scalars, 64 * sizeof(uint32_t)));
+    NRC_CUDA(cudaMalloc(&r->taps, 16 * sizeof(unsigned long long)));
     NRC_CUDA(cudaMalloc(&r->totals, 6 * sizeof(unsigned long long)));
     NRC_CUDA(cudaMemsetAsync(r->totals, 0, 6 * sizeof(unsigned long long), ctx->stream));
-    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 32 * sizeof(uint32_t), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->scalars, 0, 64 * sizeof(uint32_t), ctx->stream));
     memset(r->rs, 0, sizeof(r->rs));
-    for (int b = 0; b < 2; b++) NRC_CUDA(cudaEventCreateWithFlags(&r->evSetFree[b], cudaEventDisableTiming));
+    for (int b = 0; b < NRC_RENDER_SETS; b++) NRC_CUDA(cudaEventCreateWithFlags(&r->evSetFree[b], cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&r->evScalars, cudaEventDisableTiming));
     NRC_CUDA(cudaEventCreateWithFlags(&r->evCopyReady, cudaEventDisableTiming));
     for (int k = 0; k < 4; k++) NRC_CUDA(cudaEventCreateWithFlags(&r->evCopyDone[k], cudaEventDisableTiming));
-    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    NRC_CUDA(cudaMemsetAsync(r->taps, 0, 16 * sizeof(unsigned long long), ctx->stream));
     NRC_CUDA(cudaMallocHost(&r->hostScalars, 8 * sizeof(uint32_t)));
-    NRC_CUDA(cudaMallocHost(&r->hostTaps, 8 * sizeof(unsigned long long)));
+    NRC_CUDA(cudaMallocHost(&r->hostTaps, 16 * sizeof(unsigned long long)));
     memset(r->hostScalars, 0, 8 * sizeof(uint32_t));
-    memset(r->hostTaps, 0, 8 * sizeof(unsigned long long));
+    memset(r->hostTaps, 0, 16 * sizeof(unsigned long long));
     NRC_TRY(alloc_frame(r, 1, (uint32_t)((size_t)width * height * 4)));
     NRC_TRY(alloc_train(r));
     ctx->renderers.push_back(r);
@@ -246,7 +246,7 @@ extern "C" nrc_status nrc_renderer_destroy(nrc_renderer* r)
     free_frame(r);
     free_train(r);
     FREE(r->scalars); FREE(r->taps); FREE(r->totals);
-    for (int b = 0; b < 2; b++) if (r->evSetFree[b]) cudaEventDestroy(r->evSetFree[b]);
+    for (int b = 0; b < NRC_RENDER_SETS; b++) if (r->evSetFree[b]) cudaEventDestroy(r->evSetFree[b]);
     if (r->evScalars) cudaEventDestroy(r->evScalars);
     if (r->evCopyReady) cudaEventDestroy(r->evCopyReady);
     for (int k = 0; k < 4; k++) if (r->evCopyDone[k]) cudaEventDestroy(r->evCopyDone[k]);
@@ -436,14 +436,14 @@ static nrc_status frame_train(nrc_renderer* r, int* deferred)
     r->tp = r->tpb[b]; r->tpool = r->tpoolb[b]; r->trainCounters = r->trainCountersB[b];
     if (ahead && r->trainPending[b]) NRC_CUDA(cudaStreamWaitEvent(tw, ctx->evTrainFree[b], 0));
     NRC_CUDA(cudaMemsetAsync(r->tpool.count, 0, 2 * sizeof(uint32_t), tw));          // count + overflow of this set
-    NRC_CUDA(cudaMemsetAsync(r->taps + 4 + b, 0, sizeof(unsigned long long), tw));
+    NRC_CUDA(cudaMemsetAsync(r->taps + 12 + b, 0, sizeof(unsigned long long), tw));
     NRC_TRY(launch_train_walk(ctx, tw, P, r->i0, n, r->istride, r->tpool, r->tp, r->trainCounters));
     if (ahead) {
         NRC_CUDA(cudaEventRecord(ctx->evTrainWalk, tw));
         NRC_CUDA(cudaStreamWaitEvent(tl, ctx->evTrainWalk, 0));
     }
-    NRC_TRY(launch_light(ctx, tl, P, r->tpool, r->trainEnvLight, r->taps + 4 + b, K_LIGHT_TRAIN));
-    NRC_TRY(launch_train_combine(ctx, tl, n, r->tpool, r->tp, r->taps + 4 + b, r->totals));
+    NRC_TRY(launch_light(ctx, tl, P, r->tpool, r->trainEnvLight, r->taps + 12 + b, K_LIGHT_TRAIN));
+    NRC_TRY(launch_train_combine(ctx, tl, n, r->tpool, r->tp, r->taps + 12 + b, r->totals));
     if (ahead) {
         NRC_CUDA(cudaEventRecord(ctx->evTrainTrace, tl));
         NRC_CUDA(cudaStreamWaitEvent(st, ctx->evTrainTrace, 0));
@@ -482,7 +482,7 @@ static nrc_status render_pass(nrc_renderer* r)
     static int noOverlap = -1;
     if (noOverlap < 0) { const char* e = getenv("NRC_NO_OVERLAP"); noOverlap = (e && atoi(e)) ? 1 : 0; }
     cudaStream_t s2 = noOverlap ? ctx->stream : ctx->stream2;
-    const int b = noOverlap ? r->renderBuf : (r->renderBuf ^ 1);
+    const int b = noOverlap ? r->renderBuf : ((r->renderBuf + 1) % NRC_RENDER_SETS);
     use_render_set(r, b);
     uint32_t* sc = r->scalars + 8 * b;
     unsigned long long* tapc = r->taps + 3 * b;
@@ -569,15 +569,15 @@ extern "C" nrc_status nrc_frame_render(nrc_renderer* r)
     size_t wantCap = px * spp * (useNN ? 4 : 32);
     if (useNN && r->poolCapHint) wantCap = r->poolCapHint < px * spp * 32 ? r->poolCapHint : px * spp * 32;
     if (useNN && !r->poolCapHint) {
-        // No capacity set by the caller: the worst-case pool (32 lit vertices per path, 128 B each, two sets: 17 GB at 1080p) when that is a
+        // No capacity set by the caller: the worst-case pool (32 lit vertices per path, 128 B each, three sets: 25.5 GB at 1080p) when that is a
         // small part of this GPU's memory -- it cannot overflow, so no frame ever waits on the host for its overflow flag (e2e 2.75
         // instead of 2.83 ms at 1080p, 1.77 instead of 2.02 ms at 720p) -- else 4 vertices per path with the deferred check.
         if (r->autoPaths != px * spp) {
             size_t freeB = 0, totalB = 0;
             NRC_CUDA(cudaMemGetInfo(&freeB, &totalB));
-            const size_t need = px * spp * 32 * 128 * 2;
-            const size_t have = (size_t)r->rpool.cap * 128 * 2;   // what the current pools give back when they are replaced
-            r->autoWorst = need <= totalB / 8 && need <= (freeB + have) / 2;
+            const size_t need = px * spp * 32 * 128 * NRC_RENDER_SETS;
+            const size_t have = (size_t)r->rpool.cap * 128 * NRC_RENDER_SETS;   // what the current pools give back when they are replaced
+            r->autoWorst = need <= totalB / 6 && need <= (freeB + have) / 2;
             r->autoPaths = px * spp;
         }
         if (r->autoWorst) wantCap = px * spp * 32;
@@ -779,11 +779,11 @@ extern "C" nrc_status nrc_frame_stats(nrc_renderer* r, uint64_t* inferQueries, u
     NRC_CUDA(cudaStreamSynchronize(ctx->stream5));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream2));
     NRC_CUDA(cudaMemcpyAsync(r->hostScalars, r->scalars + 8 * r->renderBuf, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    NRC_CUDA(cudaMemcpyAsync(r->hostTaps, r->taps, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     NRC_CUDA(cudaStreamSynchronize(ctx->stream));
     if (inferQueries) *inferQueries = r->hostScalars[4];
     if (trainSamples) *trainSamples = part_count(r->i0, r->i1, r->istride);
     // + one tap per walk step is not counted here: densityTaps are the light kernels' taps (the bulk)
-    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[3 * r->renderBuf] + (uint64_t)r->hostTaps[4 + r->trainBuf];
+    if (densityTaps) *densityTaps = (uint64_t)r->hostTaps[3 * r->renderBuf] + (uint64_t)r->hostTaps[12 + r->trainBuf];
     return NRC_OK;
 }
