@@ -29,7 +29,7 @@ struct nrc_renderer {
     float4* background = nullptr;
     uint32_t* counters = nullptr;     // [h*w][4]
     float* queryProbe = nullptr;      // [h*w][8]
-    // render paths / pool / queries: two sets, so that the trace of frame k+1 never waits for frame k's inference + composite.
+    // render paths / pool / queries: NRC_RENDER_SETS sets, so that the trace of frame k+1 (and the walk of k+2) never waits for frame k's inference + composite.
     // rp / rpool / ql / background alias the set of the last nrc_frame_render (what the probes read).
     uint32_t sppAlloc = 0;
     RenderPaths rp;
